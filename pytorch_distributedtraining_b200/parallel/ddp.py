@@ -1,0 +1,289 @@
+"""Replicated data parallel with bucketed, backward-overlapped gradient all-reduce.
+
+Parity target: the engine Stoke selects for ``distributed=DistributedOptions.ddp.value``
+without gradient sharding (Stoke-DDP.py:248) — torch ``DistributedDataParallel``
+semantics: rank-0 broadcast at construction, size-capped buckets in
+reverse parameter order with a small first bucket, reduction launched as each bucket
+fills, ``no_sync()``, per-forward buffer broadcast, compression comm hooks.
+
+B200-first differences
+  * Gradients *are* bucket views (always ``gradient_as_bucket_view``): a bucket is one
+    contiguous allocation, so the all-reduce needs no pack/unpack copies.
+  * There is no C++ reducer object: readiness is counted by post-accumulate hooks
+    (host side, no sync) and the reduction is launched on a dedicated comm stream
+    ordered after the producing kernels by an event.
+  * When a symmetric-memory arena is attached (``attach_peer_allreduce``) the bucket
+    lives in peer-mapped memory and the reduction is the fused
+    all-reduce + unscale + inf-check (+cast) kernel of ``ops.collectives`` (W1);
+    otherwise it is ``dist.all_reduce`` (the baseline).
+"""
+from __future__ import annotations
+
+import contextlib
+from typing import Any, Callable, Dict, Generator, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+from torch.autograd import Variable
+
+from . import comm
+
+__all__ = ["DistributedDataParallel", "fp16_compress_hook", "bf16_compress_hook", "GradBucket"]
+
+
+class GradBucket:
+    """One contiguous gradient buffer and the parameters whose ``.grad`` alias it."""
+
+    def __init__(self, index: int, params: List[torch.Tensor], buffer: torch.Tensor):
+        self.index = index
+        self.params = params
+        self.buffer = buffer
+        self.offsets: List[int] = []
+        off = 0
+        for p in params:
+            self.offsets.append(off)
+            off += p.numel()
+        self.numel = off
+        self.offset_of = {p: o for p, o in zip(params, self.offsets)}
+        self.pending = len(params)
+        self.launched = False
+        self.work: Any = None
+        self.ready_event: Optional[torch.cuda.Event] = None
+
+    def views(self) -> List[torch.Tensor]:
+        return [self.buffer[o: o + p.numel()].view_as(p) for p, o in zip(self.params, self.offsets)]
+
+    def reset(self) -> None:
+        self.pending = len(self.params)
+        self.launched = False
+        self.work = None
+
+
+def _compress_hook(dtype: torch.dtype) -> Callable[[Any, GradBucket], Any]:
+    def hook(ddp: "DistributedDataParallel", bucket: GradBucket):
+        wire = bucket.buffer[: bucket.numel].to(dtype).div_(ddp.world_size)
+        work = dist.all_reduce(wire, group=ddp.process_group, async_op=True)
+
+        def finish() -> None:
+            work.wait()
+            bucket.buffer[: bucket.numel].copy_(wire)
+
+        return finish
+
+    return hook
+
+
+fp16_compress_hook = _compress_hook(torch.float16)
+bf16_compress_hook = _compress_hook(torch.bfloat16)
+
+
+def compute_bucket_assignment(params: List[torch.Tensor], bucket_cap_bytes: int,
+                              first_bucket_bytes: int = 1 << 20) -> List[List[int]]:
+    """Indices of ``params`` grouped into buckets, in *reverse* registration order
+    (gradients become ready roughly back-to-front), split by (device, dtype), with a
+    small first bucket so communication starts early."""
+    buckets: List[List[int]] = []
+    cur: List[int] = []
+    cur_bytes = 0
+    cur_key = None
+    cap = min(first_bucket_bytes, bucket_cap_bytes)
+    for i in reversed(range(len(params))):
+        p = params[i]
+        key = (p.device, p.dtype)
+        nbytes = p.numel() * p.element_size()
+        if cur and (key != cur_key or cur_bytes + nbytes > cap):
+            buckets.append(cur)
+            cur, cur_bytes = [], 0
+            cap = bucket_cap_bytes
+        cur.append(i)
+        cur_bytes += nbytes
+        cur_key = key
+    if cur:
+        buckets.append(cur)
+    return buckets
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(
+        self,
+        module: nn.Module,
+        process_group: Optional[Any] = None,
+        broadcast_buffers: bool = True,
+        bucket_cap_mb: float = 25,
+        find_unused_parameters: bool = False,
+        gradient_as_bucket_view: bool = True,
+        sync_models_at_startup: bool = True,
+        grad_dtype: Optional[torch.dtype] = None,
+    ):
+        super().__init__()
+        self.module = module
+        self.process_group = process_group if process_group is not None else (
+            dist.group.WORLD if comm.is_initialized() else None)
+        self.world_size = comm.get_world_size(self.process_group)
+        self.rank = comm.get_rank(self.process_group)
+        self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = find_unused_parameters
+        self.bucket_cap_bytes = int(bucket_cap_mb * 1024 * 1024)
+        self.require_backward_grad_sync = True
+        self._comm_hook: Optional[Callable[[Any, GradBucket], Any]] = None
+        self._peer_allreduce: Any = None
+        self._post_reduce: Optional[Callable[[GradBucket], None]] = None
+        self._finishers: List[Callable[[], None]] = []
+        self._callback_queued = False
+        self._hook_handles: List[Any] = []
+        self._comm_stream: Optional[torch.cuda.Stream] = None
+
+        self._params = [p for p in module.parameters() if p.requires_grad]
+        if sync_models_at_startup:
+            self.sync_params_and_buffers()
+        self._build_buckets(grad_dtype)
+        self._register_hooks()
+
+    # ------------------------------------------------------------------ set-up
+    @torch.no_grad()
+    def sync_params_and_buffers(self) -> None:
+        tensors = [p.data for p in self.module.parameters()] + [b.data for b in self.module.buffers()]
+        comm.broadcast_coalesced(tensors, src=0, group=self.process_group)
+
+    def _alloc(self, numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+        return torch.zeros(numel, dtype=dtype, device=device)
+
+    def _build_buckets(self, grad_dtype: Optional[torch.dtype] = None,
+                       allocator: Optional[Callable[[int, torch.dtype, torch.device], torch.Tensor]] = None) -> None:
+        alloc = allocator or self._alloc
+        assignment = compute_bucket_assignment(self._params, self.bucket_cap_bytes)
+        self.buckets: List[GradBucket] = []
+        self._param_bucket: Dict[torch.Tensor, GradBucket] = {}
+        for bi, idxs in enumerate(assignment):
+            ps = [self._params[i] for i in idxs]
+            n = sum(p.numel() for p in ps)
+            n_pad = (n + 127) // 128 * 128  # 16-byte vector loads + whole CTA tiles in the fused kernel
+            buf = alloc(n_pad, grad_dtype or ps[0].dtype, ps[0].device)
+            b = GradBucket(bi, ps, buf)
+            for p, v in zip(ps, b.views()):
+                if p.grad is not None:
+                    v.copy_(p.grad)
+                p.grad = v
+                self._param_bucket[p] = b
+            self.buckets.append(b)
+
+    def rebuild_buckets(self, allocator: Callable[[int, torch.dtype, torch.device], torch.Tensor],
+                        grad_dtype: Optional[torch.dtype] = None) -> None:
+        """Re-home the gradient buckets (e.g. into peer-mapped symmetric memory)."""
+        self._build_buckets(grad_dtype, allocator)
+
+    def _register_hooks(self) -> None:
+        for h in self._hook_handles:
+            h.remove()
+        self._hook_handles = [p.register_post_accumulate_grad_hook(self._on_grad_ready) for p in self._params]
+
+    def register_comm_hook(self, state: Any, hook: Callable[[Any, GradBucket], Any]) -> None:
+        """``hook(ddp, bucket)`` launches the reduction and returns a ``finish()``
+        callable (or ``None``) that the end-of-backward callback invokes."""
+        self._comm_hook = hook
+
+    def attach_peer_allreduce(self, engine: Any) -> None:
+        """Use the fused peer-memory all-reduce for buckets (engine owns the arena)."""
+        self._peer_allreduce = engine
+
+    def set_post_reduce(self, fn: Optional[Callable[[GradBucket], None]]) -> None:
+        self._post_reduce = fn
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, *inputs: Any, **kwargs: Any) -> Any:
+        if self.broadcast_buffers and self.world_size > 1 and self.training:
+            bufs = [b.data for b in self.module.buffers()]
+            if bufs:
+                comm.broadcast_coalesced(bufs, src=0, group=self.process_group)
+        if torch.is_grad_enabled() and self.require_backward_grad_sync:
+            for b in self.buckets:
+                b.reset()
+        self._callback_queued = False
+        return self.module(*inputs, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self) -> Generator:
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def zero_grad(self, set_to_none: bool = False) -> None:
+        """Gradients alias the buckets, so zeroing is one memset per bucket and the
+        ``.grad`` views stay attached."""
+        for b in self.buckets:
+            b.buffer.zero_()
+        for b in self.buckets:
+            for p, v in zip(b.params, b.views()):
+                if p.grad is None or p.grad.data_ptr() != v.data_ptr():
+                    p.grad = v
+
+    # ------------------------------------------------------------------ backward
+    def _on_grad_ready(self, param: torch.Tensor) -> None:
+        b = self._param_bucket[param]
+        # keep .grad aliased to the bucket even if something replaced it (zero_grad(set_to_none=True))
+        g = param.grad
+        if g is not None:
+            off = b.offset_of[param]
+            if g.data_ptr() != b.buffer.data_ptr() + off * b.buffer.element_size() or g.dtype != b.buffer.dtype:
+                v = b.buffer[off: off + param.numel()].view_as(param)
+                v.copy_(g)
+                param.grad = v
+        if not self.require_backward_grad_sync or self.world_size == 1:
+            return
+        if not self._callback_queued:
+            self._callback_queued = True
+            Variable._execution_engine.queue_callback(self._finalize_backward)
+        b.pending -= 1
+        if b.pending == 0 and not b.launched:
+            self._launch(b)
+
+    def _launch(self, b: GradBucket) -> None:
+        b.launched = True
+        if self._comm_hook is not None:
+            fin = self._comm_hook(self, b)
+            if fin is not None:
+                self._finishers.append(fin)
+            return
+        if self._peer_allreduce is not None:
+            fin = self._peer_allreduce.launch(b)
+            if fin is not None:
+                self._finishers.append(fin)
+            return
+        b.buffer.div_(self.world_size)
+        work = dist.all_reduce(b.buffer, group=self.process_group, async_op=True)
+        self._finishers.append(work.wait)
+
+    def _finalize_backward(self) -> None:
+        self._callback_queued = False
+        if self.require_backward_grad_sync and self.world_size > 1:
+            for b in self.buckets:
+                if not b.launched:
+                    if b.pending != len(b.params) and not self.find_unused_parameters and b.pending != 0:
+                        raise RuntimeError(
+                            "Some parameters did not receive a gradient in this backward pass; "
+                            "construct with find_unused_parameters=True to reduce them as zeros.")
+                    if b.pending != len(b.params) or self.find_unused_parameters:
+                        self._launch(b)
+        for fin in self._finishers:
+            fin()
+        self._finishers.clear()
+        if self._post_reduce is not None:
+            for b in self.buckets:
+                self._post_reduce(b)
+
+    # convenience -------------------------------------------------------------
+    def state_dict(self, *args: Any, **kwargs: Any):  # type: ignore[override]
+        return self.module.state_dict(*args, **kwargs)
+
+    def load_state_dict(self, *args: Any, **kwargs: Any):  # type: ignore[override]
+        return self.module.load_state_dict(*args, **kwargs)
+
+    def __getattr__(self, name: str) -> Any:
+        try:
+            return super().__getattr__(name)
+        except AttributeError:
+            return getattr(self.module, name)
