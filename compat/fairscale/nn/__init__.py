@@ -1,0 +1,2 @@
+from pytorch_distributedtraining_b200.parallel import (FullyShardedDataParallel, ShardedDataParallel,  # noqa: F401
+                                                        auto_wrap)

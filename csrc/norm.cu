@@ -1,0 +1,494 @@
+// Normalisation kernels (W8, W6 local part, LayerNorm for ViT / SwinIR).
+//
+// BatchNorm works on channels-last activations viewed as x[rows, C].  A thread owns one
+// group of 8 consecutive channels (one 16-byte access) for the whole kernel, so the
+// per-channel constants live in registers and the row loop is a pure stream.  The two
+// reductions write one partial per CTA to caller-provided scratch and the last CTA of a
+// channel column adds them in a fixed order (deterministic, no float atomics).
+#include "common.cuh"
+
+namespace b200dp {
+
+constexpr int kBNThreads = 256;
+constexpr int kBNMaxCols = 64;  // counters available per call (channel columns of 256 channels)
+
+struct BNGeom {
+    int tpr;   // 8-channel groups per row
+    int cgb;   // channel groups per CTA (<= 32)
+    int rpb;   // rows per CTA iteration
+    int gx;    // channel columns
+    int gy;    // row slices
+};
+
+static inline BNGeom bn_geom(int64_t rows, int C) {
+    BNGeom g;
+    g.tpr = C / 8;
+    g.cgb = g.tpr < 32 ? g.tpr : 32;
+    g.rpb = kBNThreads / g.cgb;
+    g.gx = (g.tpr + g.cgb - 1) / g.cgb;
+    int64_t want = (B200DP_SMS * 4 + g.gx - 1) / g.gx;        // ~4 CTAs per SM in total
+    int64_t maxy = (rows + (int64_t)g.rpb * 4 - 1) / ((int64_t)g.rpb * 4);  // >= 4 rows per thread
+    if (maxy < 1) maxy = 1;
+    g.gy = (int)(want < maxy ? want : maxy);
+    if (g.gy < 1) g.gy = 1;
+    return g;
+}
+
+// Shared tail of the two reductions: in-CTA reduce across the rpb row lanes, partial to
+// scratch, last CTA of the column sums the partials.
+__device__ __forceinline__ void bn_reduce_tail(float (&a)[8], float (&b)[8], int C, int cgb, int rpb, int rl,
+                                               int cgl, int cg, bool active, float* __restrict__ scratch,
+                                               unsigned int* __restrict__ counters, float* __restrict__ out) {
+    __shared__ float sm[2][kBNThreads * 8];
+    __shared__ bool is_last;
+    const int nch = cgb * 8;  // channels handled by this CTA
+    if (active) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            sm[0][rl * nch + cgl * 8 + k] = a[k];
+            sm[1][rl * nch + cgl * 8 + k] = b[k];
+        }
+    }
+    __syncthreads();
+    const int c0 = blockIdx.x * nch;
+    if ((int)threadIdx.x < nch && c0 + (int)threadIdx.x < C) {
+        float s0 = 0.f, s1 = 0.f;
+        for (int r = 0; r < rpb; ++r) {
+            s0 += sm[0][r * nch + threadIdx.x];
+            s1 += sm[1][r * nch + threadIdx.x];
+        }
+        float* part = scratch + (int64_t)blockIdx.y * 2 * C;
+        part[c0 + threadIdx.x] = s0;
+        part[C + c0 + threadIdx.x] = s1;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(counters + blockIdx.x, 1u) == gridDim.y - 1u);
+    __syncthreads();
+    if (is_last) {
+        __threadfence();
+        if ((int)threadIdx.x < nch && c0 + (int)threadIdx.x < C) {
+            float s0 = 0.f, s1 = 0.f;
+            for (int y = 0; y < (int)gridDim.y; ++y) {
+                const float* part = scratch + (int64_t)y * 2 * C;
+                s0 += __ldcg(part + c0 + threadIdx.x);
+                s1 += __ldcg(part + C + c0 + threadIdx.x);
+            }
+            out[c0 + threadIdx.x] = s0;
+            out[C + c0 + threadIdx.x] = s1;
+        }
+        if (threadIdx.x == 0) counters[blockIdx.x] = 0u;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBNThreads) bn_reduce_kernel(const T* __restrict__ x, int64_t rows, int C,
+                                                               int tpr, int cgb, int rpb,
+                                                               float* __restrict__ scratch,
+                                                               unsigned int* __restrict__ counters,
+                                                               float* __restrict__ sums) {
+    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
+    const int cg = blockIdx.x * cgb + cgl;
+    const bool active = rl < rpb && cg < tpr;
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (active) {
+        const int64_t rstep = (int64_t)gridDim.y * rpb;
+        const T* xp = x + (int64_t)cg * 8;
+        int64_t r = (int64_t)blockIdx.y * rpb + rl;
+        for (; r + 3 * rstep < rows; r += 4 * rstep) {
+            float v0[8], v1[8], v2[8], v3[8];
+            load8<T>(xp + r * C, v0);
+            load8<T>(xp + (r + rstep) * C, v1);
+            load8<T>(xp + (r + 2 * rstep) * C, v2);
+            load8<T>(xp + (r + 3 * rstep) * C, v3);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                s[k] += (v0[k] + v1[k]) + (v2[k] + v3[k]);
+                q[k] += (v0[k] * v0[k] + v1[k] * v1[k]) + (v2[k] * v2[k] + v3[k] * v3[k]);
+            }
+        }
+        for (; r < rows; r += rstep) {
+            float v[8];
+            load8<T>(xp + r * C, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] += v[k] * v[k]; }
+        }
+    }
+    bn_reduce_tail(s, q, C, cgb, rpb, rl, cgl, cg, active, scratch, counters, sums);
+}
+
+template <typename T, bool kTrain>
+__global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
+    const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t rows, int C, int tpr, int cgb,
+    int rpb, const float* __restrict__ sums, float count, const float* __restrict__ gamma,
+    const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
+    float* __restrict__ running_var, float* __restrict__ mean_out, float* __restrict__ invstd_out, int relu) {
+    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
+    const int cg = blockIdx.x * cgb + cgl;
+    if (!(rl < rpb && cg < tpr)) return;
+    float sc[8], sh[8];
+    const int c0 = cg * 8;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        float mean, invstd;
+        if (kTrain) {
+            mean = sums[c0 + k] / count;
+            const float var = fmaxf(sums[C + c0 + k] / count - mean * mean, 0.f);
+            invstd = rsqrtf(var + eps);
+            if (blockIdx.y == 0 && rl == 0) {
+                mean_out[c0 + k] = mean;
+                invstd_out[c0 + k] = invstd;
+                if (running_mean != nullptr) {
+                    const float unbiased = var * (count / fmaxf(count - 1.f, 1.f));
+                    running_mean[c0 + k] = (1.f - momentum) * running_mean[c0 + k] + momentum * mean;
+                    running_var[c0 + k] = (1.f - momentum) * running_var[c0 + k] + momentum * unbiased;
+                }
+            }
+        } else {
+            mean = running_mean[c0 + k];
+            invstd = rsqrtf(running_var[c0 + k] + eps);
+        }
+        sc[k] = gamma[c0 + k] * invstd;
+        sh[k] = beta[c0 + k] - mean * sc[k];
+    }
+    const int64_t rstep = (int64_t)gridDim.y * rpb;
+    for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
+        float v[8];
+        load8<T>(x + r * C + c0, v);
+        if (res != nullptr) {
+            float rv[8];
+            load8<T>(res + r * C + c0, rv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = v[k] * sc[k] + sh[k] + rv[k];
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = v[k] * sc[k] + sh[k];
+        }
+        if (relu) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+        }
+        store8<T>(y + r * C + c0, v);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBNThreads) bn_bwd_reduce_kernel(
+    const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, int64_t rows, int C, int tpr,
+    int cgb, int rpb, const float* __restrict__ mean, const float* __restrict__ invstd, int relu,
+    float* __restrict__ scratch, unsigned int* __restrict__ counters, float* __restrict__ dsums) {
+    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
+    const int cg = blockIdx.x * cgb + cgl;
+    const bool active = rl < rpb && cg < tpr;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (active) {
+        const int c0 = cg * 8;
+        float mu[8], is[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { mu[k] = mean[c0 + k]; is[k] = invstd[c0 + k]; }
+        const int64_t rstep = (int64_t)gridDim.y * rpb;
+        for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
+            float d[8], xv[8];
+            load8<T>(dy + r * C + c0, d);
+            load8<T>(x + r * C + c0, xv);
+            if (relu) {
+                float yv[8];
+                load8<T>(y + r * C + c0, yv);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] = yv[k] > 0.f ? d[k] : 0.f;
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                a[k] += d[k];
+                b[k] += d[k] * (xv[k] - mu[k]) * is[k];
+            }
+        }
+    }
+    bn_reduce_tail(a, b, C, cgb, rpb, rl, cgl, cg, active, scratch, counters, dsums);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kBNThreads) bn_bwd_apply_kernel(
+    const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ dx,
+    T* __restrict__ dres, int64_t rows, int C, int tpr, int cgb, int rpb, const float* __restrict__ mean,
+    const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ dsums,
+    float count, int relu) {
+    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
+    const int cg = blockIdx.x * cgb + cgl;
+    if (!(rl < rpb && cg < tpr)) return;
+    const int c0 = cg * 8;
+    float mu[8], is[8], ga[8], m1[8], m2[8];
+    const float inv_n = 1.f / count;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        mu[k] = mean[c0 + k];
+        is[k] = invstd[c0 + k];
+        ga[k] = gamma[c0 + k] * is[k];
+        m1[k] = dsums[c0 + k] * inv_n;
+        m2[k] = dsums[C + c0 + k] * inv_n;
+    }
+    const int64_t rstep = (int64_t)gridDim.y * rpb;
+    for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
+        float d[8], xv[8];
+        load8<T>(dy + r * C + c0, d);
+        load8<T>(x + r * C + c0, xv);
+        if (relu) {
+            float yv[8];
+            load8<T>(y + r * C + c0, yv);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) d[k] = yv[k] > 0.f ? d[k] : 0.f;
+        }
+        if (dres != nullptr) store8<T>(dres + r * C + c0, d);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float xhat = (xv[k] - mu[k]) * is[k];
+            d[k] = ga[k] * (d[k] - m1[k] - xhat * m2[k]);
+        }
+        store8<T>(dx + r * C + c0, d);
+    }
+}
+
+// ---------------------------------------------------------------- LayerNorm
+constexpr int kLNWarps = 4;
+constexpr int kLNMaxChunks = 8;  // D <= 2048
+
+template <typename T>
+__global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwd_kernel(
+    const T* __restrict__ x, T* __restrict__ y, int64_t rows, int D, const float* __restrict__ gamma,
+    const float* __restrict__ beta, float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * kLNWarps + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nchunk = D / 8;
+    float v[kLNMaxChunks][8];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < kLNMaxChunks; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+            load8<T>(x + row * D + ch * 8, v[j]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s += v[j][k];
+        }
+    }
+    const float mu = warp_sum(s) / D;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < kLNMaxChunks; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const float d = v[j][k] - mu; q += d * d; }
+        }
+    }
+    const float rs = rsqrtf(warp_sum(q) / D + eps);
+    if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+#pragma unroll
+    for (int j = 0; j < kLNMaxChunks; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+            float g[8], b[8], o[8];
+            load8<float>(gamma + ch * 8, g);
+            load8<float>(beta + ch * 8, b);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = (v[j][k] - mu) * rs * g[k] + b[k];
+            store8<T>(y + row * D + ch * 8, o);
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kLNWarps * 32) layernorm_bwd_dx_kernel(
+    const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t rows, int D,
+    const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * kLNWarps + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nchunk = D / 8;
+    const float mu = mean[row], rs = rstd[row];
+    float g[kLNMaxChunks][8], xh[kLNMaxChunks][8];
+    float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < kLNMaxChunks; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+            float d[8], xv[8], ga[8];
+            load8<T>(dy + row * D + ch * 8, d);
+            load8<T>(x + row * D + ch * 8, xv);
+            load8<float>(gamma + ch * 8, ga);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                xh[j][k] = (xv[k] - mu) * rs;
+                g[j][k] = d[k] * ga[k];
+                c1 += g[j][k] * xh[j][k];
+                c2 += g[j][k];
+            }
+        }
+    }
+    c1 = warp_sum(c1) / D;
+    c2 = warp_sum(c2) / D;
+#pragma unroll
+    for (int j = 0; j < kLNMaxChunks; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = rs * (g[j][k] - c2 - xh[j][k] * c1);
+            store8<T>(dx + row * D + ch * 8, o);
+        }
+    }
+}
+
+// dgamma = sum_rows dy * xhat, dbeta = sum_rows dy: same column-reduction shape as BatchNorm.
+template <typename T>
+__global__ void __launch_bounds__(kBNThreads) layernorm_bwd_dparams_kernel(
+    const T* __restrict__ dy, const T* __restrict__ x, int64_t rows, int D, int tpr, int cgb, int rpb,
+    const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ scratch,
+    unsigned int* __restrict__ counters, float* __restrict__ out /* [dbeta(D) | dgamma(D)] */) {
+    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
+    const int cg = blockIdx.x * cgb + cgl;
+    const bool active = rl < rpb && cg < tpr;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (active) {
+        const int c0 = cg * 8;
+        const int64_t rstep = (int64_t)gridDim.y * rpb;
+        for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
+            float d[8], xv[8];
+            load8<T>(dy + r * D + c0, d);
+            load8<T>(x + r * D + c0, xv);
+            const float mu = mean[r], rs = rstd[r];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { a[k] += d[k]; b[k] += d[k] * (xv[k] - mu) * rs; }
+        }
+    }
+    bn_reduce_tail(a, b, D, cgb, rpb, rl, cgl, cg, active, scratch, counters, out);
+}
+
+}  // namespace b200dp
+
+using namespace b200dp;
+
+#define BN_COMMON_CHECKS(name)                                                                       \
+    B200DP_REQUIRE(rows > 0 && C > 0 && C % 8 == 0, name ": C must be a positive multiple of 8");    \
+    const BNGeom g = bn_geom(rows, C);                                                               \
+    B200DP_REQUIRE(g.gx <= kBNMaxCols, name ": C too large (max %d)", kBNMaxCols * 256);             \
+    const dim3 grid(g.gx, g.gy);                                                                     \
+    cudaStream_t s = (cudaStream_t)stream;
+
+extern "C" {
+
+int64_t b200dp_bn_scratch_floats(int64_t rows, int C) {
+    if (rows <= 0 || C <= 0 || C % 8) return 0;
+    const BNGeom g = bn_geom(rows, C);
+    return (int64_t)g.gy * 2 * C;
+}
+
+int b200dp_bn_reduce(const void* x, int64_t rows, int C, b200dp_dtype dtype, float* scratch,
+                     unsigned int* counter, float* sums, void* stream) {
+    B200DP_REQUIRE(x && scratch && counter && sums, "bn_reduce: null argument");
+    BN_COMMON_CHECKS("bn_reduce")
+    B200DP_DISPATCH_HALF(dtype, T, {
+        bn_reduce_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)x, rows, C, g.tpr, g.cgb, g.rpb, scratch,
+                                                         counter, sums);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                    const float* sums, float count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, float* mean_out,
+                    float* invstd_out, int relu, void* stream) {
+    B200DP_REQUIRE(x && y && sums && gamma && beta && mean_out && invstd_out, "bn_apply: null argument");
+    BN_COMMON_CHECKS("bn_apply")
+    B200DP_DISPATCH_HALF(dtype, T, {
+        bn_apply_kernel<T, true><<<grid, kBNThreads, 0, s>>>((const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr,
+                                                             g.cgb, g.rpb, sums, count, gamma, beta, eps, momentum,
+                                                             running_mean, running_var, mean_out, invstd_out, relu);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                    const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                    float eps, int relu, void* stream) {
+    B200DP_REQUIRE(x && y && gamma && beta && running_mean && running_var, "bn_infer: null argument");
+    BN_COMMON_CHECKS("bn_infer")
+    B200DP_DISPATCH_HALF(dtype, T, {
+        bn_apply_kernel<T, false><<<grid, kBNThreads, 0, s>>>(
+            (const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr, g.cgb, g.rpb, nullptr, 1.f, gamma, beta, eps,
+            0.f, const_cast<float*>(running_mean), const_cast<float*>(running_var), nullptr, nullptr, relu);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+int b200dp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t rows, int C, b200dp_dtype dtype,
+                         const float* mean, const float* invstd, int relu, float* scratch,
+                         unsigned int* counter, float* dsums, void* stream) {
+    B200DP_REQUIRE(dy && x && mean && invstd && scratch && counter && dsums, "bn_bwd_reduce: null argument");
+    B200DP_REQUIRE(!relu || y, "bn_bwd_reduce: relu needs the forward output y");
+    BN_COMMON_CHECKS("bn_bwd_reduce")
+    B200DP_DISPATCH_HALF(dtype, T, {
+        bn_bwd_reduce_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, g.tpr,
+                                                            g.cgb, g.rpb, mean, invstd, relu, scratch, counter,
+                                                            dsums);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+int b200dp_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int64_t rows, int C,
+                        b200dp_dtype dtype, const float* mean, const float* invstd, const float* gamma,
+                        const float* dsums, float count, int relu, void* stream) {
+    B200DP_REQUIRE(dy && x && dx && mean && invstd && gamma && dsums, "bn_bwd_apply: null argument");
+    B200DP_REQUIRE(!relu || y, "bn_bwd_apply: relu needs the forward output y");
+    BN_COMMON_CHECKS("bn_bwd_apply")
+    B200DP_DISPATCH_HALF(dtype, T, {
+        bn_bwd_apply_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)y, (const T*)x, (T*)dx, (T*)dres,
+                                                           rows, C, g.tpr, g.cgb, g.rpb, mean, invstd, gamma, dsums,
+                                                           count, relu);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+int64_t b200dp_ln_scratch_floats(int64_t rows, int D) { return b200dp_bn_scratch_floats(rows, D); }
+
+int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dtype dtype, const float* gamma,
+                         const float* beta, float eps, float* mean, float* rstd, void* stream) {
+    B200DP_REQUIRE(x && y && gamma && beta && mean && rstd, "layernorm_fwd: null argument");
+    B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_fwd: D must be a multiple of 8, <= %d",
+                   kLNMaxChunks * 256);
+    const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
+    B200DP_DISPATCH_DTYPE(dtype, T, {
+        layernorm_fwd_kernel<T><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, rows, D, gamma,
+                                                                                    beta, eps, mean, rstd);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
+                         const float* gamma, const float* mean, const float* rstd, float* scratch,
+                         unsigned int* counter, float* dgamma, float* dbeta, void* stream) {
+    B200DP_REQUIRE(dy && x && dx && gamma && mean && rstd && scratch && counter && dgamma && dbeta,
+                   "layernorm_bwd: null argument");
+    B200DP_REQUIRE(dgamma == dbeta + D, "layernorm_bwd: dbeta and dgamma must be one buffer [dbeta(D) | dgamma(D)]");
+    B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_bwd: D must be a multiple of 8, <= %d",
+                   kLNMaxChunks * 256);
+    const int C = D;
+    BN_COMMON_CHECKS("layernorm_bwd")
+    const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
+    B200DP_DISPATCH_DTYPE(dtype, T, {
+        layernorm_bwd_dx_kernel<T><<<blocks, kLNWarps * 32, 0, s>>>((const T*)dy, (const T*)x, (T*)dx, rows, D, gamma,
+                                                                    mean, rstd);
+        layernorm_bwd_dparams_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)x, rows, D, g.tpr, g.cgb,
+                                                                    g.rpb, mean, rstd, scratch, counter, dbeta);
+    });
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,178 @@
+/*
+ * b200dp — hand-written sm_100a kernels for sharded data-parallel training.
+ *
+ * Plain C ABI: every entry point takes raw device pointers and the CUDA stream to
+ * launch on (as void*), returns 0 on success (otherwise a cudaError_t value or a
+ * negative B200DP_ERR_* code; b200dp_last_error() has the text) and never
+ * synchronises the host.  Unless an entry point says otherwise it allocates nothing:
+ * scratch memory is passed in by the caller.
+ *
+ * "Reference" citations name the call site in the reference scripts whose library
+ * call the kernel replaces (the reference itself ships no native code).
+ */
+#ifndef B200DP_H
+#define B200DP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200DP_ERR_INVALID (-1)
+#define B200DP_ERR_UNSUPPORTED (-2)
+#define B200DP_ERR_TIMEOUT (-3)
+
+typedef enum { B200DP_F32 = 0, B200DP_F16 = 1, B200DP_BF16 = 2 } b200dp_dtype;
+
+const char* b200dp_last_error(void);
+int b200dp_version(void);
+
+/* ------------------------------------------------------------------ multi-tensor ops
+ * A "tensor list" is described on the device by an array of b200dp_tensor_desc and a
+ * chunk table: chunk c covers elements [chunks[c].y * B200DP_CHUNK, +B200DP_CHUNK) of
+ * tensor chunks[c].x.  One CTA per chunk.  The caller builds both tables once and
+ * reuses them while the pointers stay the same. */
+#define B200DP_CHUNK 8192
+
+typedef struct {
+    void* p;      /* fp32 parameter (master copy)            */
+    void* g;      /* gradient, dtype given per call          */
+    void* m;      /* fp32 first moment / momentum buffer     */
+    void* v;      /* fp32 second moment (AdamW only)         */
+    void* p_lp;   /* optional 16-bit copy of the parameter   */
+    int64_t n;    /* elements                                */
+} b200dp_tensor_desc;
+
+typedef struct { int32_t x, y; } b200dp_chunk;
+
+typedef struct {
+    float lr, beta1, beta2, eps, weight_decay;
+    int adamw;            /* 1: decoupled weight decay (AdamW); 0: L2 (Adam)   */
+    int maximize;
+} b200dp_adam_hparams;
+
+typedef struct {
+    float lr, momentum, dampening, weight_decay;
+    int nesterov;
+    int maximize;
+} b200dp_sgd_hparams;
+
+/* Fused AdamW over a tensor list (reference: AdamW built at Stoke-DDP.py:226-235 /
+ * Fairscale-DDP.py:78-86, stepped at Stoke-DDP.py:82 / Fairscale-DDP.py:101).
+ *   step       device float: number of steps INCLUDING this one (see b200dp_step_advance)
+ *   grad_mult  device float or NULL: every gradient is multiplied by it first
+ *              (1/loss_scale x clip coefficient — AMP unscale and clipping fused in)
+ *   found_inf  device float or NULL: if non-zero the kernel returns without touching
+ *              anything (the GradScaler "skip this step" decision, made on the device)
+ *   lp_dtype   dtype of desc.p_lp copies (ignored where p_lp is NULL)               */
+int b200dp_multi_adam(const b200dp_tensor_desc* descs, const b200dp_chunk* chunks, int n_chunks,
+                      b200dp_dtype grad_dtype, b200dp_dtype lp_dtype, b200dp_adam_hparams hp,
+                      const float* step, const float* grad_mult, const float* found_inf, void* stream);
+
+/* Fused SGD (momentum / nesterov / weight decay).  `first_step` non-zero initialises the
+ * momentum buffer with the gradient (torch semantics). */
+int b200dp_multi_sgd(const b200dp_tensor_desc* descs, const b200dp_chunk* chunks, int n_chunks,
+                     b200dp_dtype grad_dtype, b200dp_dtype lp_dtype, b200dp_sgd_hparams hp, int first_step,
+                     const float* grad_mult, const float* found_inf, void* stream);
+
+/* step += (found_inf == 0) ? 1 : 0   (one thread; keeps the step count on the device) */
+int b200dp_step_advance(float* step, const float* found_inf, void* stream);
+
+/* In-place g *= inv_scale over a tensor list, found_inf = 1 if any element is non-finite
+ * (reference: GradScaler configured at Stoke-DDP.py:182-184; replaces
+ * _amp_foreach_non_finite_check_and_unscale_). */
+int b200dp_multi_unscale_check(const b200dp_tensor_desc* descs, const b200dp_chunk* chunks, int n_chunks,
+                               b200dp_dtype grad_dtype, const float* inv_scale, float* found_inf, void* stream);
+
+/* Sum of squares of every gradient in a tensor list plus a non-finite check, in one
+ * read of the gradients (reference: ClipGradNormConfig at Stoke-DDP.py:253).
+ *   scratch   n_chunks floats of caller-provided scratch (per-CTA partial sums)
+ *   counter   one uint32 of caller-provided scratch, must be zero on entry; the kernel
+ *             leaves it zero again
+ *   out[0]    sum of squares (deterministic: fixed-order final reduction by the last CTA)
+ *   out[1]    1.0 if any element is non-finite, else left unchanged                  */
+int b200dp_multi_sumsq_check(const b200dp_tensor_desc* descs, const b200dp_chunk* chunks, int n_chunks,
+                             b200dp_dtype grad_dtype, float* scratch, unsigned int* counter, float* out,
+                             void* stream);
+
+/* grad_mult = inv_scale * min(1, max_norm / (sqrt(sumsq) * inv_scale + 1e-6));
+ * total_norm = sqrt(sumsq) * inv_scale.  inv_scale may be NULL (= 1).  One thread. */
+int b200dp_clip_coef(const float* sumsq, const float* inv_scale, float max_norm, float* grad_mult,
+                     float* total_norm, void* stream);
+
+/* Dynamic loss-scale update (replaces _amp_update_scale_); also clears found_inf. */
+int b200dp_scaler_update(float* scale, int* growth_tracker, float* found_inf, float growth_factor,
+                         float backoff_factor, int growth_interval, void* stream);
+
+/* Flat sum of squares of n floats (two-stage, deterministic).
+ *   scratch: at least b200dp_sumsq_scratch_floats(n) floats; counter: one zeroed uint32. */
+int64_t b200dp_sumsq_scratch_floats(int64_t n);
+int b200dp_sumsq_f32(const float* x, int64_t n, float* scratch, unsigned int* counter, float* out, void* stream);
+
+/* ------------------------------------------------------------------ losses
+ * Softmax cross-entropy with mean reduction, forward and backward in one pass over the
+ * logits (reference: classification loss implied by BASELINE configs; nn.MSELoss at
+ * Fairscale-DDP.py:76 is b200dp_mse below).
+ *   logits [rows, classes] (dtype), labels int64 [rows]
+ *   loss_rows  float [rows]   per-row loss
+ *   dlogits    [rows, classes] (dtype) = (softmax - onehot) / rows   (may be NULL)
+ *   loss_mean  device float, overwritten (uses loss_rows as its partials: no other scratch) */
+int b200dp_cross_entropy(const void* logits, const int64_t* labels, int rows, int classes, b200dp_dtype dtype,
+                         float* loss_rows, void* dlogits, float* loss_mean, float label_smoothing, void* stream);
+/* x *= *scale in place (backward of the above: dlogits *= upstream gradient) */
+int b200dp_scale_inplace(void* x, int64_t n, b200dp_dtype dtype, const float* scale, void* stream);
+
+/* Mean squared error: out = mean((a-b)^2); optionally grad = 2 (a-b) / n.
+ *   scratch: b200dp_sumsq_scratch_floats(n) floats; counter: one zeroed uint32. */
+int b200dp_mse(const void* a, const void* b, int64_t n, b200dp_dtype dtype, void* grad, float* scratch,
+               unsigned int* counter, float* out, void* stream);
+
+/* ------------------------------------------------------------------ normalisation (NHWC)
+ * BatchNorm over channels-last activations x[rows, C] (rows = N*H*W), 16-bit storage,
+ * fp32 statistics (reference: BatchNorm inside the CNN of Fairscale-DDP.py:74 and the
+ * SyncBatchNorm conversion at Stoke-DDP.py:192).
+ *
+ * forward, training:
+ *   1. b200dp_bn_reduce        sums[0:C] = sum x, sums[C:2C] = sum x^2      (one read of x)
+ *      (multi-GPU: all-reduce `sums` and the row count between 1 and 2)
+ *   2. b200dp_bn_apply         y = act(gamma*(x-mean)*invstd + beta + residual), also writes
+ *                              mean/invstd and updates the running statistics
+ * backward:
+ *   3. b200dp_bn_bwd_reduce    dsums[0:C] = sum dz, dsums[C:2C] = sum dz*xhat, dz = dy*(y>0)
+ *      (multi-GPU: all-reduce `dsums`)
+ *   4. b200dp_bn_bwd_apply     dx = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)); dres = dz
+ *
+ * scratch for the two reductions: b200dp_bn_scratch_floats(rows, C) floats + one zeroed uint32. */
+int64_t b200dp_bn_scratch_floats(int64_t rows, int C);
+int b200dp_bn_reduce(const void* x, int64_t rows, int C, b200dp_dtype dtype, float* scratch,
+                     unsigned int* counter, float* sums, void* stream);
+int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                    const float* sums, float count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, float* mean_out,
+                    float* invstd_out, int relu, void* stream);
+/* inference: y = act(gamma*(x-running_mean)*rsqrt(running_var+eps) + beta + residual) */
+int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                    const float* gamma, const float* beta, const float* running_mean,
+                    const float* running_var, float eps, int relu, void* stream);
+int b200dp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t rows, int C,
+                         b200dp_dtype dtype, const float* mean, const float* invstd, int relu,
+                         float* scratch, unsigned int* counter, float* dsums, void* stream);
+int b200dp_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int64_t rows,
+                        int C, b200dp_dtype dtype, const float* mean, const float* invstd,
+                        const float* gamma, const float* dsums, float count, int relu, void* stream);
+
+/* LayerNorm over the last dimension, x[rows, D] (reference: SwinIR / ViT blocks,
+ * Stoke-DDP.py:206-208).  mean/rstd are float[rows].  dgamma/dbeta are accumulated via
+ * scratch of b200dp_ln_scratch_floats(rows, D) floats + one zeroed uint32. */
+int64_t b200dp_ln_scratch_floats(int64_t rows, int D);
+int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dtype dtype, const float* gamma,
+                         const float* beta, float eps, float* mean, float* rstd, void* stream);
+int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
+                         const float* gamma, const float* mean, const float* rstd, float* scratch,
+                         unsigned int* counter, float* dgamma, float* dbeta, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DP_H */

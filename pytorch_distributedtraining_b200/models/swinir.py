@@ -1,0 +1,337 @@
+"""SwinIR image-restoration transformer.
+
+Parity target: ``SwinIR(upscale=2, in_chans=3, img_size=64, window_size=8, img_range=1.,
+depths=[6,6,6,6], embed_dim=60, num_heads=[6,6,6,6], mlp_ratio=2,
+upsampler='pixelshuffledirect', resi_connection='1conv')`` (Stoke-DDP.py:206-208).  The
+``models.network_swinir`` module is absent from the reference; this is an independent
+implementation of the published architecture (shallow conv → residual Swin transformer
+blocks with shifted 8×8 window attention and relative position bias → conv → upsampler)
+with the same constructor surface and the conventional parameter names so the public
+``params`` checkpoints (Stoke-DDP.py:209-213) load with ``strict=True``.
+
+Supported upsamplers: ``pixelshuffledirect`` (the reference's), ``pixelshuffle``,
+``nearest+conv`` and ``''`` (denoising: no upsampling).
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+__all__ = ["SwinIR"]
+
+
+def window_partition(x: torch.Tensor, ws: int) -> torch.Tensor:
+    """[B, H, W, C] -> [B * nW, ws, ws, C]"""
+    B, H, W, C = x.shape
+    x = x.view(B, H // ws, ws, W // ws, ws, C)
+    return x.permute(0, 1, 3, 2, 4, 5).reshape(-1, ws, ws, C)
+
+
+def window_reverse(windows: torch.Tensor, ws: int, H: int, W: int) -> torch.Tensor:
+    B = windows.shape[0] // ((H // ws) * (W // ws))
+    x = windows.view(B, H // ws, W // ws, ws, ws, -1)
+    return x.permute(0, 1, 3, 2, 4, 5).reshape(B, H, W, -1)
+
+
+class Mlp(nn.Module):
+    def __init__(self, dim: int, hidden: int, drop: float = 0.0):
+        super().__init__()
+        self.fc1 = nn.Linear(dim, hidden)
+        self.act = nn.GELU()
+        self.fc2 = nn.Linear(hidden, dim)
+        self.drop = nn.Dropout(drop)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+
+
+class WindowAttention(nn.Module):
+    def __init__(self, dim: int, window_size: Tuple[int, int], num_heads: int, qkv_bias: bool = True,
+                 qk_scale: Optional[float] = None, attn_drop: float = 0.0, proj_drop: float = 0.0):
+        super().__init__()
+        self.dim, self.window_size, self.num_heads = dim, window_size, num_heads
+        self.scale = qk_scale or (dim // num_heads) ** -0.5
+        wh, ww = window_size
+        self.relative_position_bias_table = nn.Parameter(torch.zeros((2 * wh - 1) * (2 * ww - 1), num_heads))
+        coords = torch.stack(torch.meshgrid(torch.arange(wh), torch.arange(ww), indexing="ij")).flatten(1)
+        rel = (coords[:, :, None] - coords[:, None, :]).permute(1, 2, 0).contiguous()
+        rel[:, :, 0] += wh - 1
+        rel[:, :, 1] += ww - 1
+        rel[:, :, 0] *= 2 * ww - 1
+        self.register_buffer("relative_position_index", rel.sum(-1))
+        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+        self.attn_drop = nn.Dropout(attn_drop)
+        self.proj = nn.Linear(dim, dim)
+        self.proj_drop = nn.Dropout(proj_drop)
+        nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
+
+    def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        B_, N, C = x.shape
+        qkv = self.qkv(x).reshape(B_, N, 3, self.num_heads, C // self.num_heads).permute(2, 0, 3, 1, 4)
+        q, k, v = qkv[0], qkv[1], qkv[2]
+        bias = self.relative_position_bias_table[self.relative_position_index.view(-1)].view(N, N, -1)
+        bias = bias.permute(2, 0, 1).unsqueeze(0).to(q.dtype)            # [1, heads, N, N]
+        if mask is not None:
+            nW = mask.shape[0]
+            m = mask.to(q.dtype).view(1, nW, 1, N, N).expand(B_ // nW, -1, -1, -1, -1).reshape(B_, 1, N, N)
+            bias = bias + m                                               # [B_, heads, N, N]
+        else:
+            bias = bias.expand(B_, -1, -1, -1)
+        # one fused attention call: softmax(q k^T * scale + bias) v
+        o = F.scaled_dot_product_attention(q, k, v, attn_mask=bias,
+                                           dropout_p=self.attn_drop.p if self.training else 0.0, scale=self.scale)
+        return self.proj_drop(self.proj(o.transpose(1, 2).reshape(B_, N, C)))
+
+
+class SwinTransformerBlock(nn.Module):
+    def __init__(self, dim: int, input_resolution: Tuple[int, int], num_heads: int, window_size: int = 7,
+                 shift_size: int = 0, mlp_ratio: float = 4.0, qkv_bias: bool = True, qk_scale=None, drop: float = 0.0,
+                 attn_drop: float = 0.0, drop_path: float = 0.0, norm_layer=nn.LayerNorm):
+        super().__init__()
+        self.dim, self.input_resolution, self.num_heads = dim, input_resolution, num_heads
+        self.window_size, self.shift_size = window_size, shift_size
+        if min(input_resolution) <= window_size:
+            self.shift_size, self.window_size = 0, min(input_resolution)
+        self.norm1 = norm_layer(dim)
+        self.attn = WindowAttention(dim, (self.window_size, self.window_size), num_heads, qkv_bias, qk_scale,
+                                    attn_drop, drop)
+        self.drop_path_p = drop_path
+        self.norm2 = norm_layer(dim)
+        self.mlp = Mlp(dim, int(dim * mlp_ratio), drop)
+        self.register_buffer("attn_mask", self.calculate_mask(input_resolution) if self.shift_size > 0 else None)
+
+    def calculate_mask(self, x_size: Tuple[int, int]) -> torch.Tensor:
+        H, W = x_size
+        img = torch.zeros((1, H, W, 1))
+        cnt = 0
+        sl = (slice(0, -self.window_size), slice(-self.window_size, -self.shift_size), slice(-self.shift_size, None))
+        for h in sl:
+            for w in sl:
+                img[:, h, w, :] = cnt
+                cnt += 1
+        mw = window_partition(img, self.window_size).view(-1, self.window_size * self.window_size)
+        m = mw.unsqueeze(1) - mw.unsqueeze(2)
+        return m.masked_fill(m != 0, -100.0).masked_fill(m == 0, 0.0)
+
+    def _drop_path(self, x: torch.Tensor) -> torch.Tensor:
+        if self.drop_path_p == 0.0 or not self.training:
+            return x
+        keep = 1 - self.drop_path_p
+        mask = x.new_empty((x.shape[0],) + (1,) * (x.dim() - 1)).bernoulli_(keep)
+        return x * mask / keep
+
+    def forward(self, x: torch.Tensor, x_size: Tuple[int, int]) -> torch.Tensor:
+        H, W = x_size
+        B, L, C = x.shape
+        shortcut = x
+        x = self.norm1(x).view(B, H, W, C)
+        if self.shift_size > 0:
+            x = torch.roll(x, shifts=(-self.shift_size, -self.shift_size), dims=(1, 2))
+        xw = window_partition(x, self.window_size).view(-1, self.window_size * self.window_size, C)
+        if self.shift_size > 0:
+            mask = (self.attn_mask if tuple(self.input_resolution) == tuple(x_size)
+                    else self.calculate_mask(x_size).to(x.device))
+        else:
+            mask = None
+        aw = self.attn(xw, mask=mask).view(-1, self.window_size, self.window_size, C)
+        x = window_reverse(aw, self.window_size, H, W)
+        if self.shift_size > 0:
+            x = torch.roll(x, shifts=(self.shift_size, self.shift_size), dims=(1, 2))
+        x = shortcut + self._drop_path(x.view(B, H * W, C))
+        return x + self._drop_path(self.mlp(self.norm2(x)))
+
+
+class BasicLayer(nn.Module):
+    def __init__(self, dim, input_resolution, depth, num_heads, window_size, mlp_ratio=4.0, qkv_bias=True, qk_scale=None,
+                 drop=0.0, attn_drop=0.0, drop_path=0.0, norm_layer=nn.LayerNorm, use_checkpoint=False):
+        super().__init__()
+        self.use_checkpoint = use_checkpoint
+        self.blocks = nn.ModuleList([
+            SwinTransformerBlock(dim, input_resolution, num_heads, window_size, 0 if i % 2 == 0 else window_size // 2,
+                                 mlp_ratio, qkv_bias, qk_scale, drop, attn_drop,
+                                 drop_path[i] if isinstance(drop_path, (list, tuple)) else drop_path, norm_layer)
+            for i in range(depth)])
+
+    def forward(self, x: torch.Tensor, x_size: Tuple[int, int]) -> torch.Tensor:
+        for blk in self.blocks:
+            if self.use_checkpoint and self.training:
+                import torch.utils.checkpoint as cp
+                x = cp.checkpoint(blk, x, x_size, use_reentrant=False)
+            else:
+                x = blk(x, x_size)
+        return x
+
+
+class PatchEmbed(nn.Module):
+    def __init__(self, embed_dim: int, norm_layer=None):
+        super().__init__()
+        self.norm = norm_layer(embed_dim) if norm_layer is not None else None
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = x.flatten(2).transpose(1, 2)
+        return self.norm(x) if self.norm is not None else x
+
+
+class PatchUnEmbed(nn.Module):
+    def __init__(self, embed_dim: int):
+        super().__init__()
+        self.embed_dim = embed_dim
+
+    def forward(self, x: torch.Tensor, x_size: Tuple[int, int]) -> torch.Tensor:
+        B = x.shape[0]
+        return x.transpose(1, 2).reshape(B, self.embed_dim, x_size[0], x_size[1])
+
+
+class RSTB(nn.Module):
+    """Residual Swin Transformer Block: Swin layers + conv, with a skip connection."""
+
+    def __init__(self, dim, input_resolution, depth, num_heads, window_size, mlp_ratio=4.0, qkv_bias=True, qk_scale=None,
+                 drop=0.0, attn_drop=0.0, drop_path=0.0, norm_layer=nn.LayerNorm, use_checkpoint=False,
+                 resi_connection="1conv"):
+        super().__init__()
+        self.residual_group = BasicLayer(dim, input_resolution, depth, num_heads, window_size, mlp_ratio, qkv_bias,
+                                         qk_scale, drop, attn_drop, drop_path, norm_layer, use_checkpoint)
+        if resi_connection == "1conv":
+            self.conv: nn.Module = nn.Conv2d(dim, dim, 3, 1, 1)
+        elif resi_connection == "3conv":
+            self.conv = nn.Sequential(nn.Conv2d(dim, dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, True),
+                                      nn.Conv2d(dim // 4, dim // 4, 1, 1, 0), nn.LeakyReLU(0.2, True),
+                                      nn.Conv2d(dim // 4, dim, 3, 1, 1))
+        else:
+            raise ValueError(resi_connection)
+        self.patch_embed = PatchEmbed(dim)
+        self.patch_unembed = PatchUnEmbed(dim)
+
+    def forward(self, x: torch.Tensor, x_size: Tuple[int, int]) -> torch.Tensor:
+        return self.patch_embed(self.conv(self.patch_unembed(self.residual_group(x, x_size), x_size))) + x
+
+
+class Upsample(nn.Sequential):
+    def __init__(self, scale: int, num_feat: int):
+        m: List[nn.Module] = []
+        if (scale & (scale - 1)) == 0:
+            for _ in range(int(math.log2(scale))):
+                m += [nn.Conv2d(num_feat, 4 * num_feat, 3, 1, 1), nn.PixelShuffle(2)]
+        elif scale == 3:
+            m += [nn.Conv2d(num_feat, 9 * num_feat, 3, 1, 1), nn.PixelShuffle(3)]
+        else:
+            raise ValueError(f"scale {scale} is not supported (2^n and 3 are)")
+        super().__init__(*m)
+
+
+class UpsampleOneStep(nn.Sequential):
+    """conv + pixel-shuffle in one step (``pixelshuffledirect``, the lightweight variant)."""
+
+    def __init__(self, scale: int, num_feat: int, num_out_ch: int):
+        super().__init__(nn.Conv2d(num_feat, (scale ** 2) * num_out_ch, 3, 1, 1), nn.PixelShuffle(scale))
+
+
+class SwinIR(nn.Module):
+    fsdp_wrap_classes = (RSTB,)
+
+    def __init__(self, img_size: int = 64, patch_size: int = 1, in_chans: int = 3, embed_dim: int = 96,
+                 depths: Sequence[int] = (6, 6, 6, 6), num_heads: Sequence[int] = (6, 6, 6, 6), window_size: int = 7,
+                 mlp_ratio: float = 4.0, qkv_bias: bool = True, qk_scale=None, drop_rate: float = 0.0,
+                 attn_drop_rate: float = 0.0, drop_path_rate: float = 0.1, norm_layer=nn.LayerNorm, ape: bool = False,
+                 patch_norm: bool = True, use_checkpoint: bool = False, upscale: int = 2, img_range: float = 1.0,
+                 upsampler: str = "", resi_connection: str = "1conv", **_kw):
+        super().__init__()
+        num_feat = 64
+        self.img_range, self.upscale, self.upsampler, self.window_size = img_range, upscale, upsampler, window_size
+        mean = torch.tensor((0.4488, 0.4371, 0.4040)).view(1, 3, 1, 1) if in_chans == 3 else torch.zeros(1, 1, 1, 1)
+        self.register_buffer("mean", mean, persistent=False)
+        self.conv_first = nn.Conv2d(in_chans, embed_dim, 3, 1, 1)
+        self.num_layers, self.embed_dim, self.ape, self.patch_norm = len(depths), embed_dim, ape, patch_norm
+        self.patch_embed = PatchEmbed(embed_dim, norm_layer if patch_norm else None)
+        self.patch_unembed = PatchUnEmbed(embed_dim)
+        res = (img_size // patch_size, img_size // patch_size)
+        if ape:
+            self.absolute_pos_embed = nn.Parameter(torch.zeros(1, res[0] * res[1], embed_dim))
+            nn.init.trunc_normal_(self.absolute_pos_embed, std=0.02)
+        self.pos_drop = nn.Dropout(drop_rate)
+        dpr = torch.linspace(0, drop_path_rate, sum(depths)).tolist()
+        self.layers = nn.ModuleList([
+            RSTB(embed_dim, res, depths[i], num_heads[i], window_size, mlp_ratio, qkv_bias, qk_scale, drop_rate,
+                 attn_drop_rate, dpr[sum(depths[:i]): sum(depths[: i + 1])], norm_layer, use_checkpoint, resi_connection)
+            for i in range(self.num_layers)])
+        self.norm = norm_layer(embed_dim)
+        if resi_connection == "1conv":
+            self.conv_after_body: nn.Module = nn.Conv2d(embed_dim, embed_dim, 3, 1, 1)
+        else:
+            self.conv_after_body = nn.Sequential(nn.Conv2d(embed_dim, embed_dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, True),
+                                                 nn.Conv2d(embed_dim // 4, embed_dim // 4, 1, 1, 0),
+                                                 nn.LeakyReLU(0.2, True), nn.Conv2d(embed_dim // 4, embed_dim, 3, 1, 1))
+        if upsampler == "pixelshuffle":
+            self.conv_before_upsample = nn.Sequential(nn.Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
+            self.upsample: nn.Module = Upsample(upscale, num_feat)
+            self.conv_last = nn.Conv2d(num_feat, in_chans, 3, 1, 1)
+        elif upsampler == "pixelshuffledirect":
+            self.upsample = UpsampleOneStep(upscale, embed_dim, in_chans)
+        elif upsampler == "nearest+conv":
+            self.conv_before_upsample = nn.Sequential(nn.Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
+            self.conv_up1 = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            if upscale == 4:
+                self.conv_up2 = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_hr = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_last = nn.Conv2d(num_feat, in_chans, 3, 1, 1)
+            self.lrelu = nn.LeakyReLU(0.2, inplace=True)
+        else:
+            self.conv_last = nn.Conv2d(embed_dim, in_chans, 3, 1, 1)
+        self.apply(self._init_weights)
+
+    @staticmethod
+    def _init_weights(m: nn.Module) -> None:
+        if isinstance(m, nn.Linear):
+            nn.init.trunc_normal_(m.weight, std=0.02)
+            if m.bias is not None:
+                nn.init.zeros_(m.bias)
+        elif isinstance(m, nn.LayerNorm):
+            nn.init.ones_(m.weight)
+            nn.init.zeros_(m.bias)
+
+    def check_image_size(self, x: torch.Tensor) -> torch.Tensor:
+        _, _, h, w = x.shape
+        ph = (self.window_size - h % self.window_size) % self.window_size
+        pw = (self.window_size - w % self.window_size) % self.window_size
+        return F.pad(x, (0, pw, 0, ph), "reflect") if (ph or pw) else x
+
+    def forward_features(self, x: torch.Tensor) -> torch.Tensor:
+        x_size = (x.shape[2], x.shape[3])
+        x = self.patch_embed(x)
+        if self.ape:
+            x = x + self.absolute_pos_embed
+        x = self.pos_drop(x)
+        for layer in self.layers:
+            x = layer(x, x_size)
+        return self.patch_unembed(self.norm(x), x_size)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        H, W = x.shape[2:]
+        x = self.check_image_size(x)
+        mean = self.mean.to(x.dtype)
+        x = (x - mean) * self.img_range
+        if self.upsampler == "pixelshuffle":
+            x = self.conv_first(x)
+            x = self.conv_after_body(self.forward_features(x)) + x
+            x = self.conv_last(self.upsample(self.conv_before_upsample(x)))
+        elif self.upsampler == "pixelshuffledirect":
+            x = self.conv_first(x)
+            x = self.conv_after_body(self.forward_features(x)) + x
+            x = self.upsample(x)
+        elif self.upsampler == "nearest+conv":
+            x = self.conv_first(x)
+            x = self.conv_after_body(self.forward_features(x)) + x
+            x = self.conv_before_upsample(x)
+            x = self.lrelu(self.conv_up1(F.interpolate(x, scale_factor=2, mode="nearest")))
+            if self.upscale == 4:
+                x = self.lrelu(self.conv_up2(F.interpolate(x, scale_factor=2, mode="nearest")))
+            x = self.conv_last(self.lrelu(self.conv_hr(x)))
+        else:
+            first = self.conv_first(x)
+            x = x + self.conv_last(self.conv_after_body(self.forward_features(first)) + first)
+        x = x / self.img_range + mean
+        return x[:, :, : H * self.upscale, : W * self.upscale]

@@ -1,0 +1,100 @@
+"""ViT-B/16 (and friends) for BASELINE.json config 4 (FSDP bf16).
+
+Shapes and parameter count match torchvision's ``vit_b_16`` (86,567,656 parameters,
+152 tensors).  Every transformer block is an FSDP wrap unit
+(``fsdp_wrap_classes``): ≈7.1 M parameters → 14 MB in bf16, 1.8 MB per rank at 8 GPUs.
+
+B200-first: linears go through ``ops.layers.Linear`` (tcgen05 GEMM with fused bias /
+GELU epilogue on CUDA), LayerNorm through the fused kernel, attention through
+``F.scaled_dot_product_attention`` (library flash kernel: attention over 197 tokens is
+<4 % of the block's FLOPs and is not on the work list).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ..ops.layers import LayerNorm, Linear
+
+__all__ = ["VisionTransformer", "vit_b_16", "vit_s_16", "vit_tiny"]
+
+
+class Attention(nn.Module):
+    def __init__(self, dim: int, heads: int):
+        super().__init__()
+        self.heads = heads
+        self.in_proj = Linear(dim, 3 * dim)
+        self.out_proj = Linear(dim, dim)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        B, S, D = x.shape
+        qkv = self.in_proj(x).view(B, S, 3, self.heads, D // self.heads).permute(2, 0, 3, 1, 4)
+        o = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2])
+        return self.out_proj(o.transpose(1, 2).reshape(B, S, D))
+
+
+class MLP(nn.Module):
+    def __init__(self, dim: int, hidden: int):
+        super().__init__()
+        self.fc1 = Linear(dim, hidden, act="gelu")
+        self.fc2 = Linear(hidden, dim)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.fc2(self.fc1(x))
+
+
+class EncoderBlock(nn.Module):
+    def __init__(self, dim: int, heads: int, mlp_dim: int):
+        super().__init__()
+        self.ln_1 = LayerNorm(dim, eps=1e-6)
+        self.self_attention = Attention(dim, heads)
+        self.ln_2 = LayerNorm(dim, eps=1e-6)
+        self.mlp = MLP(dim, mlp_dim)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = x + self.self_attention(self.ln_1(x))
+        return x + self.mlp(self.ln_2(x))
+
+
+class VisionTransformer(nn.Module):
+    fsdp_wrap_classes = (EncoderBlock,)
+
+    def __init__(self, image_size: int = 224, patch_size: int = 16, layers: int = 12, heads: int = 12,
+                 hidden_dim: int = 768, mlp_dim: int = 3072, num_classes: int = 1000):
+        super().__init__()
+        self.patch_size, self.hidden_dim = patch_size, hidden_dim
+        self.conv_proj = nn.Conv2d(3, hidden_dim, kernel_size=patch_size, stride=patch_size)
+        seq = (image_size // patch_size) ** 2 + 1
+        self.class_token = nn.Parameter(torch.zeros(1, 1, hidden_dim))
+        self.pos_embedding = nn.Parameter(torch.empty(1, seq, hidden_dim).normal_(std=0.02))
+        self.layers = nn.ModuleList([EncoderBlock(hidden_dim, heads, mlp_dim) for _ in range(layers)])
+        self.ln = LayerNorm(hidden_dim, eps=1e-6)
+        self.head = Linear(hidden_dim, num_classes)
+        for m in self.modules():
+            if isinstance(m, nn.Linear):
+                nn.init.trunc_normal_(m.weight, std=0.02)
+                if m.bias is not None:
+                    nn.init.zeros_(m.bias)
+        nn.init.zeros_(self.head.weight)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        B = x.shape[0]
+        x = self.conv_proj(x).flatten(2).transpose(1, 2)          # [B, S-1, D]
+        x = torch.cat([self.class_token.expand(B, -1, -1).to(x.dtype), x], dim=1) + self.pos_embedding.to(x.dtype)
+        for blk in self.layers:
+            x = blk(x)
+        return self.head(self.ln(x)[:, 0])
+
+
+def vit_b_16(num_classes: int = 1000, image_size: int = 224) -> VisionTransformer:
+    return VisionTransformer(image_size, 16, 12, 12, 768, 3072, num_classes)
+
+
+def vit_s_16(num_classes: int = 1000, image_size: int = 224) -> VisionTransformer:
+    return VisionTransformer(image_size, 16, 12, 6, 384, 1536, num_classes)
+
+
+def vit_tiny(num_classes: int = 10, image_size: int = 32) -> VisionTransformer:
+    """Test-sized model (CPU/gloo plumbing)."""
+    return VisionTransformer(image_size, 8, 2, 2, 64, 128, num_classes)

@@ -1,0 +1,87 @@
+"""Which implementation serves a call: the sm_100a kernel or the stock torch op.
+
+Policy: on a CUDA tensor the custom kernel is used whenever the (dtype, layout,
+shape) is inside the kernel's envelope and the feature flag is on; the envelope is
+stated here, in one place, so it can be read and tested.  Flags can be flipped with
+``B200DP_DISABLE=conv,gemm,...`` for A/B measurements.
+"""
+from __future__ import annotations
+
+import os
+from typing import Any
+
+import torch
+
+_DISABLED = {s.strip() for s in os.environ.get("B200DP_DISABLE", "").split(",") if s.strip()}
+_HALF = (torch.float16, torch.bfloat16)
+
+
+def enabled(feature: str) -> bool:
+    return feature not in _DISABLED
+
+
+def disable(feature: str) -> None:
+    _DISABLED.add(feature)
+
+
+def enable(feature: str) -> None:
+    _DISABLED.discard(feature)
+
+
+def _lib_ok() -> bool:
+    from . import library_available
+    return library_available()
+
+
+def _autocast_dtype(x: torch.Tensor):
+    if torch.is_autocast_enabled():
+        return torch.get_autocast_dtype("cuda")
+    return x.dtype
+
+
+def bn_supported(mod: Any, x: torch.Tensor) -> bool:
+    """NHWC (channels-last) fp16/bf16/fp32 activations, C % 8 == 0, affine, training or eval."""
+    if not (enabled("bn") and _lib_ok()):
+        return False
+    if x.dim() != 4 or not mod.affine or not mod.track_running_stats:
+        return False
+    if x.dtype not in _HALF:
+        return False
+    if x.shape[1] % 8 != 0:
+        return False
+    return x.is_contiguous(memory_format=torch.channels_last)
+
+
+def ln_supported(mod: Any, x: torch.Tensor) -> bool:
+    if not (enabled("ln") and _lib_ok()):
+        return False
+    if len(mod.normalized_shape) != 1 or mod.weight is None or mod.bias is None:
+        return False
+    d = mod.normalized_shape[0]
+    return x.dtype in _HALF + (torch.float32,) and d % 8 == 0 and d <= 8192 and x.is_contiguous()
+
+
+def linear_supported(mod: Any, x: torch.Tensor) -> bool:
+    """tcgen05 GEMM envelope: fp16/bf16 compute (directly or under autocast), K % 64 == 0, N % 16 == 0."""
+    if not (enabled("gemm") and _lib_ok()):
+        return False
+    from . import gemm
+    if not gemm.available():
+        return False
+    dt = _autocast_dtype(x)
+    if dt not in _HALF:
+        return False
+    return mod.in_features % 64 == 0 and mod.out_features % 16 == 0
+
+
+def conv_supported(mod: Any, x: torch.Tensor) -> bool:
+    """Implicit-GEMM envelope: NHWC fp16/bf16, groups == 1, dilation == 1, Cin % 64 == 0, Cout % 16 == 0."""
+    if not (enabled("conv") and _lib_ok()):
+        return False
+    from . import conv
+    if not conv.available():
+        return False
+    dt = _autocast_dtype(x)
+    if dt not in _HALF or mod.groups != 1 or mod.dilation != (1, 1) or mod.padding_mode != "zeros":
+        return False
+    return conv.shape_supported(mod, x)

@@ -1,0 +1,180 @@
+"""ctypes bindings for the multi-tensor / AMP / norm kernels of ``csrc/optim.cu``.
+
+Everything here launches on the current torch CUDA stream and never synchronises.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from ._lib import check, require_library
+
+CHUNK = 8192
+DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+_DESC = np.dtype([("p", "<u8"), ("g", "<u8"), ("m", "<u8"), ("v", "<u8"), ("lp", "<u8"), ("n", "<i8")])
+
+
+class AdamHParams(ctypes.Structure):
+    _fields_ = [("lr", ctypes.c_float), ("beta1", ctypes.c_float), ("beta2", ctypes.c_float),
+                ("eps", ctypes.c_float), ("weight_decay", ctypes.c_float), ("adamw", ctypes.c_int),
+                ("maximize", ctypes.c_int)]
+
+
+class SGDHParams(ctypes.Structure):
+    _fields_ = [("lr", ctypes.c_float), ("momentum", ctypes.c_float), ("dampening", ctypes.c_float),
+                ("weight_decay", ctypes.c_float), ("nesterov", ctypes.c_int), ("maximize", ctypes.c_int)]
+
+
+def ptr(t: Optional[torch.Tensor]) -> ctypes.c_void_p:
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream_ptr(device: Optional[torch.device] = None) -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+# --------------------------------------------------------------------------- workspace
+class Workspace:
+    """Per-(device, stream) scratch: a growable float buffer plus 64 zeroed completion
+    counters.  Kernels leave the counters zero, so they are allocated and cleared once."""
+
+    _cache: Dict[Tuple[int, int], "Workspace"] = {}
+
+    def __init__(self, device: torch.device):
+        self.device = device
+        self.counters = torch.zeros(64, dtype=torch.int32, device=device)
+        self._scratch = torch.empty(1 << 16, dtype=torch.float32, device=device)
+
+    @classmethod
+    def get(cls, device: torch.device) -> "Workspace":
+        key = (device.index if device.index is not None else torch.cuda.current_device(),
+               torch.cuda.current_stream(device).cuda_stream)
+        ws = cls._cache.get(key)
+        if ws is None:
+            ws = cls._cache[key] = Workspace(device)
+        return ws
+
+    def scratch(self, floats: int) -> torch.Tensor:
+        if self._scratch.numel() < floats:
+            self._scratch = torch.empty(int(floats * 1.5), dtype=torch.float32, device=self.device)
+        return self._scratch
+
+
+# --------------------------------------------------------------------------- tensor lists
+class TensorList:
+    """Device-side descriptor + chunk tables for a list of (param, grad, m, v, lp) tensors."""
+
+    def __init__(self, p: Sequence[Optional[torch.Tensor]], g: Sequence[Optional[torch.Tensor]],
+                 m: Optional[Sequence[Optional[torch.Tensor]]] = None,
+                 v: Optional[Sequence[Optional[torch.Tensor]]] = None,
+                 lp: Optional[Sequence[Optional[torch.Tensor]]] = None):
+        n = len(g)
+        ref = next(t for t in list(g) + list(p) if t is not None)
+        self.device = ref.device
+        desc = np.zeros(n, dtype=_DESC)
+        chunks: List[Tuple[int, int]] = []
+        for i in range(n):
+            t = g[i] if g[i] is not None else p[i]
+            numel = t.numel()
+            for name, seq in (("p", p), ("g", g), ("m", m), ("v", v), ("lp", lp)):
+                x = seq[i] if seq is not None and i < len(seq) else None
+                if x is not None:
+                    if not x.is_contiguous():
+                        raise ValueError("fused kernels need contiguous tensors")
+                    desc[name][i] = x.data_ptr()
+            desc["n"][i] = numel
+            chunks.extend((i, c) for c in range((numel + CHUNK - 1) // CHUNK))
+        self.n_chunks = len(chunks)
+        self.key = tuple(int(x) for x in desc["g"]) + tuple(int(x) for x in desc["p"])
+        self.desc = torch.from_numpy(desc.view(np.uint8).copy()).to(self.device)
+        self.chunks = torch.tensor(chunks if chunks else [(0, 0)], dtype=torch.int32).to(self.device)
+        self.keepalive = (p, g, m, v, lp)
+
+
+def unscale_check_(grads: List[torch.Tensor], inv_scale: torch.Tensor, found_inf: torch.Tensor) -> None:
+    """In-place ``g *= inv_scale`` over ``grads`` with a non-finite check (K13)."""
+    lib = require_library()
+    by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
+    for g in grads:
+        by_dtype.setdefault(g.dtype, []).append(g)
+    for dtype, gs in by_dtype.items():
+        tl = TensorList([None] * len(gs), gs)
+        check(lib.b200dp_multi_unscale_check(ptr(tl.desc), ptr(tl.chunks), ctypes.c_int(tl.n_chunks),
+                                             ctypes.c_int(DT[dtype]), ptr(inv_scale), ptr(found_inf),
+                                             stream_ptr(tl.device)), "multi_unscale_check")
+        _keep(tl)
+
+
+_KEEP: List[object] = []
+
+
+def _keep(obj: object, limit: int = 64) -> None:
+    """Keep short-lived device tables alive until the stream has certainly consumed them
+    (the caching allocator would otherwise be free to hand the memory out again)."""
+    _KEEP.append(obj)
+    if len(_KEEP) > limit:
+        del _KEEP[: limit // 2]
+
+
+def scaler_update_(scale: torch.Tensor, growth_tracker: torch.Tensor, found_inf: torch.Tensor, growth_factor: float,
+                   backoff_factor: float, growth_interval: int) -> None:
+    lib = require_library()
+    check(lib.b200dp_scaler_update(ptr(scale), ptr(growth_tracker), ptr(found_inf), ctypes.c_float(growth_factor),
+                                   ctypes.c_float(backoff_factor), ctypes.c_int(growth_interval),
+                                   stream_ptr(scale.device)), "scaler_update")
+
+
+def sumsq_check(tl: TensorList, grad_dtype: torch.dtype, out: torch.Tensor) -> None:
+    """``out[0] = sum g^2`` over the list, ``out[1] = 1`` if anything is non-finite (K8)."""
+    lib = require_library()
+    ws = Workspace.get(tl.device)
+    scratch = ws.scratch(max(tl.n_chunks, 1))
+    check(lib.b200dp_multi_sumsq_check(ptr(tl.desc), ptr(tl.chunks), ctypes.c_int(tl.n_chunks),
+                                       ctypes.c_int(DT[grad_dtype]), ptr(scratch), ptr(ws.counters), ptr(out),
+                                       stream_ptr(tl.device)), "multi_sumsq_check")
+
+
+def clip_coef(sumsq: torch.Tensor, inv_scale: Optional[torch.Tensor], max_norm: float, grad_mult: torch.Tensor,
+              total_norm: Optional[torch.Tensor]) -> None:
+    lib = require_library()
+    check(lib.b200dp_clip_coef(ptr(sumsq), ptr(inv_scale), ctypes.c_float(max_norm), ptr(grad_mult),
+                               ptr(total_norm), stream_ptr(sumsq.device)), "clip_coef")
+
+
+def step_advance(step: torch.Tensor, found_inf: Optional[torch.Tensor]) -> None:
+    lib = require_library()
+    check(lib.b200dp_step_advance(ptr(step), ptr(found_inf), stream_ptr(step.device)), "step_advance")
+
+
+def sumsq_f32(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Deterministic two-stage sum of squares of a flat fp32 tensor."""
+    lib = require_library()
+    lib.b200dp_sumsq_scratch_floats.restype = ctypes.c_int64
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    ws = Workspace.get(x.device)
+    n = x.numel()
+    scratch = ws.scratch(int(lib.b200dp_sumsq_scratch_floats(ctypes.c_int64(n))))
+    if out is None:
+        out = torch.empty((), dtype=torch.float32, device=x.device)
+    check(lib.b200dp_sumsq_f32(ptr(x), ctypes.c_int64(n), ptr(scratch), ptr(ws.counters), ptr(out),
+                               stream_ptr(x.device)), "sumsq_f32")
+    return out
+
+
+def multi_adam(tl: TensorList, grad_dtype: torch.dtype, lp_dtype: torch.dtype, hp: AdamHParams, step: torch.Tensor,
+               grad_mult: Optional[torch.Tensor], found_inf: Optional[torch.Tensor]) -> None:
+    lib = require_library()
+    check(lib.b200dp_multi_adam(ptr(tl.desc), ptr(tl.chunks), ctypes.c_int(tl.n_chunks), ctypes.c_int(DT[grad_dtype]),
+                                ctypes.c_int(DT.get(lp_dtype, 1)), hp, ptr(step), ptr(grad_mult), ptr(found_inf),
+                                stream_ptr(tl.device)), "multi_adam")
+
+
+def multi_sgd(tl: TensorList, grad_dtype: torch.dtype, lp_dtype: torch.dtype, hp: SGDHParams, first_step: bool,
+              grad_mult: Optional[torch.Tensor], found_inf: Optional[torch.Tensor]) -> None:
+    lib = require_library()
+    check(lib.b200dp_multi_sgd(ptr(tl.desc), ptr(tl.chunks), ctypes.c_int(tl.n_chunks), ctypes.c_int(DT[grad_dtype]),
+                               ctypes.c_int(DT.get(lp_dtype, 1)), hp, ctypes.c_int(int(first_step)), ptr(grad_mult),
+                               ptr(found_inf), stream_ptr(tl.device)), "multi_sgd")

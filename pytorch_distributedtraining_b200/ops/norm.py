@@ -1,0 +1,164 @@
+"""BatchNorm(+residual+ReLU) and LayerNorm autograd functions over ``csrc/norm.cu``
+(W8; the local half of W6 — cross-rank statistics are exchanged between the reduce
+and the apply kernel).
+
+Parity targets: the BatchNorm layers of the CNN (Fairscale-DDP.py:74), the
+``convert_to_sync_batch_norm=True`` flag (Stoke-DDP.py:192) and the LayerNorms of the
+transformer models (Stoke-DDP.py:206-208).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Any, Optional
+
+import torch
+import torch.distributed as dist
+
+from ._lib import check, require_library
+from .fused import DT, Workspace, ptr, stream_ptr
+
+
+def _rows_view(x: torch.Tensor):
+    """NCHW-shaped channels-last tensor -> (rows, C)."""
+    n, c, h, w = x.shape
+    return n * h * w, c
+
+
+def _allreduce_stats(buf: torch.Tensor, group: Any) -> None:
+    """Cross-rank sum of the moment vector (K6/K7): peer-memory one-shot all-reduce when
+    attached, NCCL otherwise."""
+    from ..parallel import peer
+    if not peer.small_allreduce(buf, group):
+        dist.all_reduce(buf, group=group)
+
+
+class _BatchNormActFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, group, world):  # type: ignore[override]
+        lib = require_library()
+        rows, C = _rows_view(x)
+        dt = ctypes.c_int(DT[x.dtype])
+        dev = x.device
+        ws = Workspace.get(dev)
+        scratch = ws.scratch(int(lib.b200dp_bn_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
+        sums = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
+        st = stream_ptr(dev)
+        check(lib.b200dp_bn_reduce(ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(scratch), ptr(ws.counters),
+                                   ptr(sums), st), "bn_reduce")
+        count = float(rows)
+        if world > 1:
+            sums[2 * C] = count
+            _allreduce_stats(sums, group)
+            count = float(rows) * world  # equal per-rank batch (DistributedSampler pads); avoids a host sync
+        y = torch.empty_like(x)
+        mean = torch.empty(C, dtype=torch.float32, device=dev)
+        invstd = torch.empty(C, dtype=torch.float32, device=dev)
+        check(lib.b200dp_bn_apply(ptr(x), ptr(residual), ptr(y), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(sums),
+                                  ctypes.c_float(count), ptr(weight), ptr(bias), ctypes.c_float(eps),
+                                  ctypes.c_float(momentum), ptr(running_mean), ptr(running_var), ptr(mean),
+                                  ptr(invstd), ctypes.c_int(int(relu)), st), "bn_apply")
+        ctx.save_for_backward(x, y if relu else None, weight, mean, invstd)
+        ctx.relu, ctx.group, ctx.world, ctx.count = relu, group, world, count
+        ctx.has_res = residual is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):  # type: ignore[override]
+        lib = require_library()
+        x, y, weight, mean, invstd = ctx.saved_tensors
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        rows, C = _rows_view(x)
+        dt = ctypes.c_int(DT[x.dtype])
+        dev = x.device
+        ws = Workspace.get(dev)
+        scratch = ws.scratch(int(lib.b200dp_bn_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
+        dsums = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        st = stream_ptr(dev)
+        relu = ctypes.c_int(int(ctx.relu))
+        check(lib.b200dp_bn_bwd_reduce(ptr(dy), ptr(y), ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(mean),
+                                       ptr(invstd), relu, ptr(scratch), ptr(ws.counters), ptr(dsums), st),
+              "bn_bwd_reduce")
+        # parameter gradients are the LOCAL sums (the data-parallel engine averages them)
+        dbias = dsums[:C].clone()
+        dweight = dsums[C:].clone()
+        if ctx.world > 1:
+            _allreduce_stats(dsums, ctx.group)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if ctx.has_res else None
+        check(lib.b200dp_bn_bwd_apply(ptr(dy), ptr(y), ptr(x), ptr(dx), ptr(dres), ctypes.c_int64(rows), ctypes.c_int(C),
+                                      dt, ptr(mean), ptr(invstd), ptr(weight), ptr(dsums), ctypes.c_float(ctx.count),
+                                      relu, st), "bn_bwd_apply")
+        return dx, dres, dweight.to(weight.dtype), dbias.to(weight.dtype), None, None, None, None, None, None, None
+
+
+def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) -> torch.Tensor:
+    """``act(bn(x) + residual)`` for a ``BatchNormAct2d`` module on NHWC 16-bit input."""
+    lib = require_library()
+    relu = mod.act == "relu"
+    if residual is not None and not residual.is_contiguous(memory_format=torch.channels_last):
+        residual = residual.contiguous(memory_format=torch.channels_last)
+    if residual is not None and residual.dtype != x.dtype:
+        residual = residual.to(x.dtype)
+    if not mod.training:
+        rows, C = _rows_view(x)
+        y = torch.empty_like(x)
+        check(lib.b200dp_bn_infer(ptr(x), ptr(residual), ptr(y), ctypes.c_int64(rows), ctypes.c_int(C),
+                                  ctypes.c_int(DT[x.dtype]), ptr(mod.weight), ptr(mod.bias), ptr(mod.running_mean),
+                                  ptr(mod.running_var), ctypes.c_float(mod.eps), ctypes.c_int(int(relu)),
+                                  stream_ptr(x.device)), "bn_infer")
+        return y
+    momentum = 0.1 if mod.momentum is None else mod.momentum
+    if mod.num_batches_tracked is not None:
+        mod.num_batches_tracked.add_(1)
+    world, group = 1, None
+    if mod.sync and dist.is_available() and dist.is_initialized():
+        group = mod.process_group if mod.process_group is not None else dist.group.WORLD
+        world = dist.get_world_size(group)
+    return _BatchNormActFn.apply(x, residual, mod.weight, mod.bias, mod.running_mean, mod.running_var, mod.eps,
+                                 momentum, relu, group, world)
+
+
+class _LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):  # type: ignore[override]
+        lib = require_library()
+        shape = x.shape
+        D = shape[-1]
+        x2 = x.reshape(-1, D)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        check(lib.b200dp_layernorm_fwd(ptr(x2), ptr(y), ctypes.c_int64(rows), ctypes.c_int(D), ctypes.c_int(DT[x.dtype]),
+                                       ptr(weight), ptr(bias), ctypes.c_float(eps), ptr(mean), ptr(rstd),
+                                       stream_ptr(x.device)), "layernorm_fwd")
+        ctx.save_for_backward(x2, weight, mean, rstd)
+        ctx.shape = shape
+        return y.view(shape)
+
+    @staticmethod
+    def backward(ctx, dy):  # type: ignore[override]
+        lib = require_library()
+        x2, weight, mean, rstd = ctx.saved_tensors
+        rows, D = x2.shape
+        dy2 = dy.reshape(rows, D)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        if dy2.dtype != x2.dtype:
+            dy2 = dy2.to(x2.dtype)
+        dx = torch.empty_like(x2)
+        ws = Workspace.get(x2.device)
+        scratch = ws.scratch(int(lib.b200dp_ln_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(D))))
+        dparams = torch.empty(2 * D, dtype=torch.float32, device=x2.device)  # [dbeta | dgamma]
+        check(lib.b200dp_layernorm_bwd(ptr(dy2), ptr(x2), ptr(dx), ctypes.c_int64(rows), ctypes.c_int(D),
+                                       ctypes.c_int(DT[x2.dtype]), ptr(weight), ptr(mean), ptr(rstd), ptr(scratch),
+                                       ptr(ws.counters), ptr(dparams[D:]), ptr(dparams[:D]), stream_ptr(x2.device)),
+              "layernorm_bwd")
+        return dx.view(ctx.shape), dparams[D:].to(weight.dtype), dparams[:D].to(weight.dtype), None
+
+
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float) -> torch.Tensor:
+    return _LayerNormFn.apply(x, weight.float(), bias.float(), eps)

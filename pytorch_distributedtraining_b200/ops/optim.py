@@ -1,0 +1,255 @@
+"""Fused sm_100a optimizers with stock ``torch.optim`` state_dict layouts (W10 / K14).
+
+Parity target: ``AdamW(lr=1e-3, betas=(0.9, 0.99), eps=1e-8, weight_decay=...)``
+(Fairscale-DDP.py:78-84, Stoke-DDP.py:226-235); ``SGD`` is imported by the reference
+(Stoke-DDP.py:27) and is the default of OSS.
+
+One kernel launch updates every parameter of a param group (multi-tensor chunk table,
+``csrc/optim.cu``).  Fused in: the AMP unscale, the clipping coefficient (both arrive
+as one device scalar ``grad_mult``) and the GradScaler's skip-on-inf decision (a device
+flag, so ``step`` never reads anything back to the host).  State tensors are views into
+flat per-group buffers; ``state_dict()`` is exactly torch's
+(``step`` / ``exp_avg`` / ``exp_avg_sq`` / ``momentum_buffer``).
+"""
+from __future__ import annotations
+
+from typing import Any, Callable, Dict, List, Optional, Tuple, Type
+
+import torch
+from torch.optim import Optimizer
+
+from . import fused
+
+__all__ = ["FusedAdamW", "FusedAdam", "FusedSGD", "fused_equivalent"]
+
+
+def _flat_like(params: List[torch.Tensor]) -> Tuple[torch.Tensor, List[torch.Tensor]]:
+    """One zeroed fp32 buffer with a 16-byte aligned view per parameter."""
+    offs, total = [], 0
+    for p in params:
+        offs.append(total)
+        total += (p.numel() + 3) // 4 * 4
+    flat = torch.zeros(max(total, 4), dtype=torch.float32, device=params[0].device)
+    return flat, [flat[o: o + p.numel()].view_as(p) for o, p in zip(offs, params)]
+
+
+class _FusedBase(Optimizer):
+    supports_device_skip = True
+
+    def __init__(self, params, defaults):
+        super().__init__(params, defaults)
+        self._tables: Dict[int, fused.TensorList] = {}
+        self._grad_mult: Optional[torch.Tensor] = None   # set by fused_unscale_clip, consumed by step
+        self._norm_buf: Optional[torch.Tensor] = None
+        self._total_norm: Optional[torch.Tensor] = None
+        self._norm_table: Optional[fused.TensorList] = None
+
+    # -- helpers ---------------------------------------------------------------
+    def _params_with_grad(self, group) -> List[torch.Tensor]:
+        out = []
+        for p in group["params"]:
+            if p.grad is not None:
+                if p.grad.is_sparse:
+                    raise RuntimeError("fused optimizers do not support sparse gradients")
+                if p.dtype != torch.float32:
+                    raise RuntimeError("fused optimizers expect fp32 master parameters")
+                out.append(p)
+        return out
+
+    def _all_grads(self) -> List[torch.Tensor]:
+        return [p.grad for g in self.param_groups for p in g["params"] if p.grad is not None]
+
+    def _device(self) -> torch.device:
+        return self.param_groups[0]["params"][0].device
+
+    @torch.no_grad()
+    def fused_unscale_clip(self, inv_scale: Optional[torch.Tensor], max_norm: Optional[float],
+                           found_inf: Optional[torch.Tensor], extra_sumsq_reduce: Optional[Callable] = None
+                           ) -> Optional[torch.Tensor]:
+        """ONE read of all gradients: sum of squares + non-finite flag; then a one-thread
+        kernel turns (sumsq, 1/scale, max_norm) into the multiplier the update kernel
+        applies.  Nothing is written back to the gradients.
+
+        ``extra_sumsq_reduce(buf)``: hook for sharded optimizers to all-reduce the partial
+        sum of squares (and flag) across ranks before the coefficient is computed.
+        Returns the total gradient norm (device scalar) when clipping, else ``None``.
+        """
+        grads = self._all_grads()
+        if not grads:
+            return None
+        dev = grads[0].device
+        if self._norm_buf is None:
+            self._norm_buf = torch.zeros(2, dtype=torch.float32, device=dev)
+            self._grad_mult = torch.ones((), dtype=torch.float32, device=dev)
+            self._total_norm = torch.zeros((), dtype=torch.float32, device=dev)
+        key = tuple(g.data_ptr() for g in grads)
+        if self._norm_table is None or self._norm_table.key[: len(key)] != key:
+            self._norm_table = fused.TensorList([None] * len(grads), grads)
+        self._norm_buf.zero_()
+        fused.sumsq_check(self._norm_table, grads[0].dtype, self._norm_buf)
+        if extra_sumsq_reduce is not None:
+            extra_sumsq_reduce(self._norm_buf)
+        if found_inf is not None:
+            torch.maximum(found_inf, self._norm_buf[1], out=found_inf)
+        fused.clip_coef(self._norm_buf[0:1], inv_scale, float(max_norm) if max_norm is not None else 3.0e38,
+                        self._grad_mult, self._total_norm)
+        self._use_grad_mult = True
+        return self._total_norm if max_norm is not None else None
+
+    def clip_grad_norm(self, max_norm: float, norm_type: float = 2.0) -> torch.Tensor:
+        if float(norm_type) != 2.0:
+            total = torch.nn.utils.clip_grad_norm_(
+                [p for g in self.param_groups for p in g["params"] if p.grad is not None], max_norm, norm_type)
+            return total
+        return self.fused_unscale_clip(None, max_norm, None)
+
+    def _consume_grad_mult(self) -> Optional[torch.Tensor]:
+        if getattr(self, "_use_grad_mult", False):
+            self._use_grad_mult = False
+            return self._grad_mult
+        return None
+
+
+class FusedAdamW(_FusedBase):
+    _adamw = 1
+
+    def __init__(self, params, lr: float = 1e-3, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2, amsgrad: bool = False, maximize: bool = False, **_ignored: Any):
+        if amsgrad:
+            raise NotImplementedError("amsgrad is not implemented in the fused kernel")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, maximize=maximize))
+
+    def _step_tensor(self, gi: int, params: List[torch.Tensor]) -> torch.Tensor:
+        """One device-resident step counter per param group, shared by its parameters."""
+        steps = self.__dict__.setdefault("_step_tensors", {})
+        t = steps.get(gi)
+        if t is None:
+            seasoned = [p for p in params if len(self.state[p]) > 0]
+            if seasoned:  # state came from a checkpoint
+                t = torch.as_tensor(self.state[seasoned[0]]["step"], dtype=torch.float32).to(
+                    params[0].device).reshape(()).clone()
+                for p in seasoned:
+                    self.state[p]["step"] = t
+            else:
+                t = torch.zeros((), dtype=torch.float32, device=params[0].device)
+            steps[gi] = t
+        return t
+
+    def _init_group_state(self, gi: int, params: List[torch.Tensor]) -> None:
+        step = self._step_tensor(gi, params)
+        new = [p for p in params if len(self.state[p]) == 0]
+        if not new:
+            return
+        _, ms = _flat_like(new)
+        _, vs = _flat_like(new)
+        for p, m, v in zip(new, ms, vs):
+            self.state[p] = {"step": step, "exp_avg": m, "exp_avg_sq": v}
+
+    @torch.no_grad()
+    def step(self, closure: Optional[Callable] = None, found_inf: Optional[torch.Tensor] = None,
+             grad_mult: Optional[torch.Tensor] = None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        if grad_mult is None:
+            grad_mult = self._consume_grad_mult()
+        for gi, group in enumerate(self.param_groups):
+            params = self._params_with_grad(group)
+            if not params:
+                continue
+            self._init_group_state(gi, params)
+            step_t = self._step_tensor(gi, params)
+            grads = [p.grad for p in params]
+            key = tuple(g.data_ptr() for g in grads) + tuple(p.data_ptr() for p in params)
+            tl = self._tables.get(gi)
+            if tl is None or tl.key != key:
+                tl = self._tables[gi] = fused.TensorList(
+                    params, grads, [self.state[p]["exp_avg"] for p in params],
+                    [self.state[p]["exp_avg_sq"] for p in params])
+            b1, b2 = group["betas"]
+            hp = fused.AdamHParams(float(group["lr"]), float(b1), float(b2), float(group["eps"]),
+                                   float(group["weight_decay"]), self._adamw, int(bool(group.get("maximize", False))))
+            fused.step_advance(step_t, found_inf)
+            fused.multi_adam(tl, grads[0].dtype, torch.float16, hp, step_t, grad_mult, found_inf)
+        return loss
+
+    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
+        super().load_state_dict(state_dict)
+        self._tables.clear()
+        self.__dict__["_step_tensors"] = {}
+        for st in self.state.values():
+            if "exp_avg" in st:
+                st["exp_avg"] = st["exp_avg"].float().contiguous()
+                st["exp_avg_sq"] = st["exp_avg_sq"].float().contiguous()
+
+
+class FusedAdam(FusedAdamW):
+    """Adam with L2 regularisation (weight decay added to the gradient)."""
+    _adamw = 0
+
+    def __init__(self, params, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0,
+                 **kw: Any):
+        super().__init__(params, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, **kw)
+
+
+class FusedSGD(_FusedBase):
+    def __init__(self, params, lr: float = 1e-3, momentum: float = 0.0, dampening: float = 0.0,
+                 weight_decay: float = 0.0, nesterov: bool = False, maximize: bool = False, **_ignored: Any):
+        if nesterov and (momentum <= 0 or dampening != 0):
+            raise ValueError("Nesterov momentum requires a momentum and zero dampening")
+        super().__init__(params, dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay,
+                                      nesterov=nesterov, maximize=maximize))
+
+    @torch.no_grad()
+    def step(self, closure: Optional[Callable] = None, found_inf: Optional[torch.Tensor] = None,
+             grad_mult: Optional[torch.Tensor] = None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        if grad_mult is None:
+            grad_mult = self._consume_grad_mult()
+        for gi, group in enumerate(self.param_groups):
+            params = self._params_with_grad(group)
+            if not params:
+                continue
+            mom = float(group["momentum"])
+            # first-step semantics are per launch: split new / seasoned parameters
+            for first, ps in ((True, [p for p in params if mom != 0 and "momentum_buffer" not in self.state[p]]),
+                              (False, [p for p in params if mom == 0 or "momentum_buffer" in self.state[p]])):
+                if not ps:
+                    continue
+                if first:
+                    _, bufs = _flat_like(ps)
+                    for p, b in zip(ps, bufs):
+                        self.state[p]["momentum_buffer"] = b
+                grads = [p.grad for p in ps]
+                key = tuple(g.data_ptr() for g in grads) + tuple(p.data_ptr() for p in ps)
+                tkey = gi * 2 + int(first)
+                tl = self._tables.get(tkey)
+                if tl is None or tl.key != key:
+                    tl = self._tables[tkey] = fused.TensorList(
+                        ps, grads, [self.state[p].get("momentum_buffer") for p in ps] if mom != 0 else None)
+                hp = fused.SGDHParams(float(group["lr"]), mom, float(group["dampening"]), float(group["weight_decay"]),
+                                      int(bool(group["nesterov"])), int(bool(group.get("maximize", False))))
+                fused.multi_sgd(tl, grads[0].dtype, torch.float16, hp, first, grad_mult, found_inf)
+        return loss
+
+    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
+        super().load_state_dict(state_dict)
+        self._tables.clear()
+        for st in self.state.values():
+            if st.get("momentum_buffer") is not None:
+                st["momentum_buffer"] = st["momentum_buffer"].float().contiguous()
+
+
+def fused_equivalent(cls: Type[Optimizer]) -> Type[Optimizer]:
+    """Map a stock optimizer class to its fused sm_100a implementation (identity if none)."""
+    if cls is torch.optim.AdamW:
+        return FusedAdamW
+    if cls is torch.optim.Adam:
+        return FusedAdam
+    if cls is torch.optim.SGD:
+        return FusedSGD
+    return cls

@@ -87,7 +87,7 @@ class _SyncBNFunction(torch.autograd.Function):
         dx = k * (dyf - (g_sum_dy / n).view(sh) - xmu * (invstd * invstd * g_sum_dy_xmu / n).view(sh))
         return (dx.to(x.dtype),
                 grad_weight.to(weight.dtype) if grad_weight is not None else None,
-                grad_bias.to(weight.dtype) if grad_bias is not None else None,
+                grad_bias.to(dy.dtype if weight is None else weight.dtype) if grad_bias is not None else None,
                 None, None, None, None, None, None)
 
 
@@ -117,23 +117,39 @@ class SyncBatchNorm(_BatchNorm):
         group = self.process_group if self.process_group is not None else (
             dist.group.WORLD if comm.is_initialized() else None)
         world = comm.get_world_size(group)
-        if x.is_cuda:
-            from ..ops import norm as _norm
-            if _norm.supports(x):
-                return _norm.sync_batch_norm(x, self.weight, self.bias,
-                                             self.running_mean if self.track_running_stats else None,
-                                             self.running_var if self.track_running_stats else None,
-                                             self.eps, momentum, group, world, relu=False)
         return _SyncBNFunction.apply(x, self.weight, self.bias,
                                      self.running_mean if self.track_running_stats else None,
                                      self.running_var if self.track_running_stats else None,
                                      self.eps, momentum, group, world)
 
 
+def sync_batch_norm_reference(bn: _BatchNorm, x: torch.Tensor) -> torch.Tensor:
+    """Training-mode cross-rank batch norm for any ``_BatchNorm``-shaped module (portable path)."""
+    momentum = 0.0 if bn.momentum is None else bn.momentum
+    if bn.track_running_stats and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+        if bn.momentum is None:
+            momentum = 1.0 / float(bn.num_batches_tracked)
+    group = getattr(bn, "process_group", None)
+    if group is None and comm.is_initialized():
+        group = dist.group.WORLD
+    world = comm.get_world_size(group)
+    return _SyncBNFunction.apply(x, bn.weight, bn.bias,
+                                 bn.running_mean if bn.track_running_stats else None,
+                                 bn.running_var if bn.track_running_stats else None,
+                                 bn.eps, momentum, group, world)
+
+
 def convert_sync_batchnorm(module: nn.Module, process_group: Optional[Any] = None) -> nn.Module:
     """Recursively replace every ``_BatchNorm`` by :class:`SyncBatchNorm`, keeping
     parameters, buffers and their ``state_dict`` names."""
     out = module
+    from ..ops.layers import BatchNormAct2d
+    if isinstance(module, BatchNormAct2d):
+        # fused norm+add+activation module: flip it to cross-rank statistics in place
+        module.sync = True
+        module.process_group = process_group
+        return module
     if isinstance(module, _BatchNorm) and not isinstance(module, SyncBatchNorm):
         out = SyncBatchNorm(module.num_features, module.eps, module.momentum, module.affine,
                             module.track_running_stats, process_group)
