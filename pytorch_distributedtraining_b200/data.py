@@ -26,7 +26,7 @@ import torch
 from torch.utils.data import DataLoader, Dataset, Sampler
 from torch.utils.data.distributed import DistributedSampler as _TorchDistributedSampler
 
-__all__ = ["StokeDataLoader", "DistributedSampler", "BucketedDistributedSampler", "SyntheticImageDataset",
+__all__ = ["StokeDataLoader", "DevicePrefetcher", "DistributedSampler", "BucketedDistributedSampler", "SyntheticImageDataset",
            "SyntheticPairedDataset", "PairedImageDataset", "CustomDataset", "to_device"]
 
 
@@ -168,25 +168,40 @@ class StokeDataLoader(DataLoader):
             for b in host_iter:
                 yield to_device(b, self._device, True, self._channels_last)
             return
-        copy_stream = torch.cuda.Stream(device=self._device)
-        nxt = None
+        yield from DevicePrefetcher(host_iter, self._device, self._channels_last)
 
-        def fetch() -> Any:
-            try:
-                host = next(host_iter)
-            except StopIteration:
-                return None
-            with torch.cuda.stream(copy_stream):
-                dev = to_device(host, self._device, True, self._channels_last)
-            return dev
 
-        nxt = fetch()
-        while nxt is not None:
-            cur = nxt
-            torch.cuda.current_stream(self._device).wait_stream(copy_stream)
-            _record_stream(cur, torch.cuda.current_stream(self._device))
-            nxt = fetch()
-            yield cur
+class DevicePrefetcher:
+    """Wrap an iterator of (ideally pinned) host batches: batch *i+1* is copied on a side
+    stream while batch *i* is being consumed, so the H2D transfer hides behind compute."""
+
+    def __init__(self, host_iter: Any, device: torch.device, channels_last: bool = False):
+        self._it = iter(host_iter)
+        self._device = device
+        self._channels_last = channels_last
+        self._stream = torch.cuda.Stream(device=device)
+        self._nxt = self._fetch()
+
+    def _fetch(self) -> Any:
+        try:
+            host = next(self._it)
+        except StopIteration:
+            return None
+        with torch.cuda.stream(self._stream):
+            return to_device(host, self._device, True, self._channels_last)
+
+    def __iter__(self) -> "DevicePrefetcher":
+        return self
+
+    def __next__(self) -> Any:
+        if self._nxt is None:
+            raise StopIteration
+        cur = self._nxt
+        main = torch.cuda.current_stream(self._device)
+        main.wait_stream(self._stream)
+        _record_stream(cur, main)
+        self._nxt = self._fetch()
+        return cur
 
 
 # --------------------------------------------------------------------------- datasets

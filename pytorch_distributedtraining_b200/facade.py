@@ -308,10 +308,17 @@ class Stoke:
         (unscale) → clip → step (skipped on inf) → scaler update → zero grads."""
         if not self._at_boundary():
             return
+        gc = self._grad_clip
+        fused = (hasattr(self._optimizer, "fused_unscale_clip") and not isinstance(gc, ClipGradConfig)
+                 and (gc is None or float(gc.norm_type) == 2.0))
         if self._scaler is not None:
-            if self._grad_clip is not None:
-                self._scaler.unscale_(self._optimizer)
-            self._clip()
+            if fused:
+                # one read of the gradients (inf flag + norm); unscale and clip ride inside the update kernel
+                self._scaler.unscale_and_clip_fused(self._optimizer, None if gc is None else gc.max_norm)
+            else:
+                if gc is not None:
+                    self._scaler.unscale_(self._optimizer)
+                self._clip()
             self._scaler.step(self._optimizer)
             self._scaler.update()
         else:

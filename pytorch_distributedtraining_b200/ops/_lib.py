@@ -130,7 +130,12 @@ def require_library() -> ctypes.CDLL:
     return lib
 
 
-def check(rc: int, what: str = "") -> None:
+LAUNCHES = 0  # kernels launched through this library in this process (bench.py reports it)
+
+
+def check(rc: int, what: str = "", launches: int = 1) -> None:
+    global LAUNCHES
+    LAUNCHES += launches
     if rc != 0:
         lib = require_library()
         msg = lib.b200dp_last_error().decode(errors="replace")

@@ -64,6 +64,35 @@ class Workspace:
 
 
 # --------------------------------------------------------------------------- tensor lists
+def is_dense(t: torch.Tensor) -> bool:
+    """Covers its storage span exactly once: plain contiguous or channels-last contiguous."""
+    if t.is_contiguous():
+        return True
+    if t.dim() == 4:
+        return t.is_contiguous(memory_format=torch.channels_last)
+    if t.dim() == 5:
+        return t.is_contiguous(memory_format=torch.channels_last_3d)
+    return False
+
+
+def same_layout(a: torch.Tensor, b: torch.Tensor) -> bool:
+    """Same logical->physical element order (the kernels walk raw memory linearly)."""
+    if a.shape != b.shape:
+        return False
+    if a.stride() == b.stride() or (a.is_contiguous() and b.is_contiguous()):
+        return True
+    if a.dim() == 4:
+        return a.is_contiguous(memory_format=torch.channels_last) and b.is_contiguous(memory_format=torch.channels_last)
+    return False
+
+
+def dense_view_like(flat: torch.Tensor, p: torch.Tensor) -> torch.Tensor:
+    """View of ``flat`` (``p.numel()`` elements) with ``p``'s shape AND memory layout."""
+    if p.is_contiguous() or not is_dense(p):
+        return flat.view(p.shape)
+    return flat.as_strided(p.shape, p.stride())
+
+
 class TensorList:
     """Device-side descriptor + chunk tables for a list of (param, grad, m, v, lp) tensors."""
 
@@ -82,8 +111,11 @@ class TensorList:
             for name, seq in (("p", p), ("g", g), ("m", m), ("v", v), ("lp", lp)):
                 x = seq[i] if seq is not None and i < len(seq) else None
                 if x is not None:
-                    if not x.is_contiguous():
-                        raise ValueError("fused kernels need contiguous tensors")
+                    if not is_dense(x):
+                        raise ValueError("fused kernels need dense (contiguous or channels-last) tensors")
+                    if not same_layout(x, t):
+                        raise ValueError(f"fused kernels walk raw memory: '{name}' of tensor {i} has strides "
+                                         f"{x.stride()} but its gradient has {t.stride()} (shape {tuple(t.shape)})")
                     desc[name][i] = x.data_ptr()
             desc["n"][i] = numel
             chunks.extend((i, c) for c in range((numel + CHUNK - 1) // CHUNK))

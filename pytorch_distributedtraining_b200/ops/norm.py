@@ -156,7 +156,7 @@ class _LayerNormFn(torch.autograd.Function):
         check(lib.b200dp_layernorm_bwd(ptr(dy2), ptr(x2), ptr(dx), ctypes.c_int64(rows), ctypes.c_int(D),
                                        ctypes.c_int(DT[x2.dtype]), ptr(weight), ptr(mean), ptr(rstd), ptr(scratch),
                                        ptr(ws.counters), ptr(dparams[D:]), ptr(dparams[:D]), stream_ptr(x2.device)),
-              "layernorm_bwd")
+              "layernorm_bwd", launches=2)
         return dx.view(ctx.shape), dparams[D:].to(weight.dtype), dparams[:D].to(weight.dtype), None
 
 

@@ -30,7 +30,7 @@ def _flat_like(params: List[torch.Tensor]) -> Tuple[torch.Tensor, List[torch.Ten
         offs.append(total)
         total += (p.numel() + 3) // 4 * 4
     flat = torch.zeros(max(total, 4), dtype=torch.float32, device=params[0].device)
-    return flat, [flat[o: o + p.numel()].view_as(p) for o, p in zip(offs, params)]
+    return flat, [fused.dense_view_like(flat[o: o + p.numel()], p) for o, p in zip(offs, params)]
 
 
 class _FusedBase(Optimizer):
@@ -180,8 +180,15 @@ class FusedAdamW(_FusedBase):
         self.__dict__["_step_tensors"] = {}
         for st in self.state.values():
             if "exp_avg" in st:
-                st["exp_avg"] = st["exp_avg"].float().contiguous()
-                st["exp_avg_sq"] = st["exp_avg_sq"].float().contiguous()
+                st["exp_avg"] = st["exp_avg"].float()
+                st["exp_avg_sq"] = st["exp_avg_sq"].float()
+        for g in self.param_groups:
+            for p in g["params"]:
+                st = self.state.get(p)
+                if st and "exp_avg" in st:  # state must share the parameter's memory layout
+                    for k in ("exp_avg", "exp_avg_sq"):
+                        if not fused.same_layout(st[k], p) or not fused.is_dense(st[k]):
+                            st[k] = torch.empty_like(p, dtype=torch.float32).copy_(st[k])
 
 
 class FusedAdam(FusedAdamW):
@@ -239,9 +246,14 @@ class FusedSGD(_FusedBase):
     def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
         super().load_state_dict(state_dict)
         self._tables.clear()
-        for st in self.state.values():
-            if st.get("momentum_buffer") is not None:
-                st["momentum_buffer"] = st["momentum_buffer"].float().contiguous()
+        for g in self.param_groups:
+            for p in g["params"]:
+                st = self.state.get(p)
+                if st and st.get("momentum_buffer") is not None:
+                    b = st["momentum_buffer"].float()
+                    if not fused.same_layout(b, p) or not fused.is_dense(b):
+                        b = torch.empty_like(p, dtype=torch.float32).copy_(b)
+                    st["momentum_buffer"] = b
 
 
 def fused_equivalent(cls: Type[Optimizer]) -> Type[Optimizer]:

@@ -51,8 +51,16 @@ class GradBucket:
         self.work: Any = None
         self.ready_event: Optional[torch.cuda.Event] = None
 
+    def view_of(self, p: torch.Tensor) -> torch.Tensor:
+        """The slice of the bucket that is ``p``'s gradient, with ``p``'s memory layout
+        (channels-last parameters get channels-last gradients, as autograd would make)."""
+        o = self.offset_of[p]
+        flat = self.buffer[o: o + p.numel()]
+        dense_cl = (p.dim() == 4 and not p.is_contiguous() and p.is_contiguous(memory_format=torch.channels_last))
+        return flat.as_strided(p.shape, p.stride()) if dense_cl else flat.view(p.shape)
+
     def views(self) -> List[torch.Tensor]:
-        return [self.buffer[o: o + p.numel()].view_as(p) for p, o in zip(self.params, self.offsets)]
+        return [self.view_of(p) for p in self.params]
 
     def reset(self) -> None:
         self.pending = len(self.params)
@@ -229,7 +237,7 @@ class DistributedDataParallel(nn.Module):
         if g is not None:
             off = b.offset_of[param]
             if g.data_ptr() != b.buffer.data_ptr() + off * b.buffer.element_size() or g.dtype != b.buffer.dtype:
-                v = b.buffer[off: off + param.numel()].view_as(param)
+                v = b.view_of(param)
                 v.copy_(g)
                 param.grad = v
         if not self.require_backward_grad_sync or self.world_size == 1:

@@ -129,6 +129,23 @@ class GradScaler:
     def _sync_found_inf(self) -> None:
         """Hook for the sharded subclass."""
 
+    def unscale_and_clip_fused(self, optimizer: Any, max_norm: Optional[float]) -> Optional[torch.Tensor]:
+        """Fused path for optimizers exposing ``fused_unscale_clip``: one read of the
+        gradients yields the inf flag and the squared norm; the unscale and the clip
+        coefficient are applied inside the update kernel, so gradients are never
+        rewritten.  Returns the (unscaled) total norm when clipping."""
+        st = self._per_optimizer[id(optimizer)]
+        if st["stage"] is not _OptState.READY:
+            raise RuntimeError("unscale has already happened for this optimizer since the last update().")
+        grads = self._grads_of(optimizer)
+        if self._scale is None:
+            self._lazy_init(grads[0].device if grads else torch.device("cpu"))
+        inv = self._scale.reciprocal()
+        total = optimizer.fused_unscale_clip(inv, max_norm, self._found_inf)
+        self._sync_found_inf()
+        st["stage"] = _OptState.UNSCALED
+        return total
+
     def step(self, optimizer: torch.optim.Optimizer, *args: Any, **kwargs: Any) -> Optional[float]:
         if not self._enabled:
             return optimizer.step(*args, **kwargs)

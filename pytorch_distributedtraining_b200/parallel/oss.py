@@ -432,6 +432,11 @@ class OSS(Optimizer):
                 self.optim.add_param_group(new_local)
 
     @property
+    def supports_device_skip(self) -> bool:
+        """True when the inner optimizer takes the GradScaler's inf flag as a device predicate."""
+        return bool(getattr(self.optim, "supports_device_skip", False))
+
+    @property
     def inner_state(self):
         return self.optim.state
 

@@ -1,0 +1,267 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op
+(SURVEY §4 kernel tier).  Needs a B200: ``pytest -m gpu``."""
+import copy
+import math
+
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+cuda = torch.device("cuda")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _lib():
+    from pytorch_distributedtraining_b200.ops import require_library
+    require_library()  # fail loudly: a GPU box without the kernel library is a broken build
+
+
+def _params(shapes, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    out = []
+    for s in shapes:
+        t = torch.randn(s, generator=g).to(cuda)
+        if len(s) == 4:  # conv weights live in channels-last, like the models on the GPU path
+            t = t.contiguous(memory_format=torch.channels_last)
+        out.append(t.requires_grad_(True))
+    return out
+
+
+SHAPES = [(64, 3, 7, 7), (1000,), (513,), (256, 64, 1, 1), (7,), (2048, 512), (3, 5)]
+
+
+@pytest.mark.parametrize("wd,maximize", [(1e-4, False), (0.0, False), (1e-2, True)])
+def test_fused_adamw_matches_torch(wd, maximize):
+    from pytorch_distributedtraining_b200.ops.optim import FusedAdamW
+    ps, ref = _params(SHAPES), _params(SHAPES)
+    kw = dict(lr=1e-3, betas=(0.9, 0.99), eps=1e-8, weight_decay=wd, maximize=maximize)
+    a, b = FusedAdamW(ps, **kw), torch.optim.AdamW(ref, **kw)
+    for it in range(5):
+        for p, r in zip(ps, ref):
+            g = torch.randn_like(p) * (it + 1)  # randn_like preserves the channels-last layout
+            p.grad, r.grad = g.clone(), g.clone()
+        a.step(); b.step()
+    for p, r in zip(ps, ref):
+        torch.testing.assert_close(p, r, rtol=2e-5, atol=2e-6)
+    sa, sb = a.state_dict(), b.state_dict()
+    assert sa["state"].keys() == sb["state"].keys()
+    for k in sb["state"]:
+        torch.testing.assert_close(sa["state"][k]["exp_avg_sq"], sb["state"][k]["exp_avg_sq"], rtol=1e-5, atol=1e-8)
+        assert float(sa["state"][k]["step"]) == float(sb["state"][k]["step"]) == 5.0
+    # state dict round trip into the stock optimizer and back
+    c = torch.optim.AdamW(_params(SHAPES), **kw); c.load_state_dict(copy.deepcopy(sa))
+    d = FusedAdamW(_params(SHAPES), **kw); d.load_state_dict(copy.deepcopy(sb))  # load_state_dict aliases tensors
+    for p, r in zip(d.param_groups[0]["params"], ref):
+        p.data.copy_(r.data)
+    for p, r in zip(d.param_groups[0]["params"], ref):
+        g = torch.randn_like(p); p.grad, r.grad = g.clone(), g.clone()
+    d.step(); b.step()
+    for p, r in zip(d.param_groups[0]["params"], ref):
+        torch.testing.assert_close(p, r, rtol=2e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("momentum,nesterov,wd", [(0.0, False, 0.0), (0.9, False, 1e-4), (0.9, True, 1e-4)])
+def test_fused_sgd_matches_torch(momentum, nesterov, wd):
+    from pytorch_distributedtraining_b200.ops.optim import FusedSGD
+    ps, ref = _params(SHAPES), _params(SHAPES)
+    kw = dict(lr=0.1, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    a, b = FusedSGD(ps, **kw), torch.optim.SGD(ref, **kw)
+    for it in range(4):
+        for p, r in zip(ps, ref):
+            g = torch.randn_like(p); p.grad, r.grad = g.clone(), g.clone()
+        a.step(); b.step()
+    for p, r in zip(ps, ref):
+        torch.testing.assert_close(p, r, rtol=1e-5, atol=1e-6)
+
+
+def test_fused_unscale_clip_and_device_skip():
+    from pytorch_distributedtraining_b200.ops.optim import FusedAdamW
+    from pytorch_distributedtraining_b200.parallel import GradScaler
+    ps, ref = _params(SHAPES), _params(SHAPES)
+    kw = dict(lr=1e-3, betas=(0.9, 0.99), eps=1e-8, weight_decay=1e-4)
+    a, b = FusedAdamW(ps, **kw), torch.optim.AdamW(ref, **kw)
+    scaler = GradScaler(init_scale=1024.0, growth_interval=3)
+    scaler._lazy_init(cuda)
+    for it in range(4):
+        for p, r in zip(ps, ref):
+            g = torch.randn_like(p)
+            p.grad, r.grad = g * scaler.get_scale(), g.clone()
+        total = scaler.unscale_and_clip_fused(a, 0.5)
+        ref_total = torch.nn.utils.clip_grad_norm_(ref, 0.5)
+        torch.testing.assert_close(total, ref_total, rtol=1e-4, atol=1e-5)
+        scaler.step(a); scaler.update(); b.step()
+    for p, r in zip(ps, ref):
+        torch.testing.assert_close(p, r, rtol=3e-5, atol=3e-6)
+    assert scaler.get_scale() == 2048.0
+    # an inf anywhere: the step is skipped on the device, step count does not advance, scale backs off
+    before = [p.detach().clone() for p in ps]
+    for p in ps:
+        p.grad = torch.randn_like(p)
+    ps[3].grad.view(-1)[5] = float("inf")
+    scaler.unscale_and_clip_fused(a, None)
+    scaler.step(a); scaler.update()
+    for p, q in zip(ps, before):
+        assert torch.equal(p, q)
+    assert float(a.state[ps[0]]["step"]) == 4.0 and scaler.get_scale() == 1024.0
+    # plain unscale_ kernel
+    gs = [torch.randn(1001, device=cuda), torch.randn(64, 64, device=cuda)]
+    want = [g / 8 for g in gs]
+    from pytorch_distributedtraining_b200.ops import fused
+    flag = torch.zeros((), device=cuda)
+    fused.unscale_check_(gs, torch.tensor(0.125, device=cuda), flag)
+    for g, w in zip(gs, want):
+        torch.testing.assert_close(g, w)
+    assert flag.item() == 0.0
+    gs[1][3, 3] = float("nan")
+    fused.unscale_check_(gs, torch.tensor(1.0, device=cuda), flag)
+    assert flag.item() == 1.0
+
+
+@pytest.mark.parametrize("n", [1, 1000, 16384, 1 << 20, (1 << 22) + 13])
+def test_sumsq_matches_torch(n):
+    from pytorch_distributedtraining_b200.ops import fused
+    x = torch.randn(n, device=cuda)
+    for _ in range(2):  # second call checks the completion counter was left at zero
+        got = fused.sumsq_f32(x)
+        torch.testing.assert_close(got, (x.double() ** 2).sum().float(), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("rows,classes,smooth", [(256, 1000, 0.0), (7, 10, 0.1), (32, 5000, 0.0)])
+def test_cross_entropy_matches_torch(dtype, rows, classes, smooth):
+    from pytorch_distributedtraining_b200.ops.loss import cross_entropy
+    x = (torch.randn(rows, classes, device=cuda) * 3).to(dtype).requires_grad_(True)
+    y = torch.randint(0, classes, (rows,), device=cuda)
+    xr = x.detach().float().requires_grad_(True)
+    loss = cross_entropy(x, y, smooth)
+    ref = F.cross_entropy(xr, y, label_smoothing=smooth)
+    torch.testing.assert_close(loss, ref, rtol=1e-4, atol=1e-5)
+    (loss * 3.0).backward(); (ref * 3.0).backward()
+    tol = 1e-6 if dtype == torch.float32 else 2e-3
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=1e-2 if dtype != torch.float32 else 1e-4, atol=tol)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+def test_mse_matches_torch(dtype):
+    from pytorch_distributedtraining_b200.ops.loss import mse_loss
+    a = torch.randn(4, 3, 33, 17, device=cuda).to(dtype).requires_grad_(True)
+    b = torch.randn(4, 3, 33, 17, device=cuda).to(dtype)
+    ar = a.detach().float().requires_grad_(True)
+    l, r = mse_loss(a, b), F.mse_loss(ar, b.float())
+    torch.testing.assert_close(l, r, rtol=1e-4, atol=1e-6)
+    l.backward(); r.backward()
+    torch.testing.assert_close(a.grad.float(), ar.grad, rtol=1e-2, atol=1e-5)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape,res,act", [((8, 64, 14, 14), False, "relu"), ((4, 256, 7, 7), True, "relu"),
+                                            ((3, 2048, 5, 5), True, "relu"), ((16, 24, 9, 9), False, None),
+                                            ((2, 512, 28, 28), True, "relu")])
+def test_batchnorm_act_matches_torch(dtype, shape, res, act):
+    from pytorch_distributedtraining_b200.ops.layers import BatchNormAct2d
+    torch.manual_seed(1)
+    C = shape[1]
+    bn = BatchNormAct2d(C, act=act).to(cuda)
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5); bn.bias.uniform_(-0.5, 0.5)
+    ref = copy.deepcopy(bn).float()
+    x = torch.randn(shape, device=cuda).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    r = torch.randn(shape, device=cuda).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True) if res else None
+    xr = x.detach().float().requires_grad_(True)
+    rr = r.detach().float().requires_grad_(True) if res else None
+    y = bn(x, r)
+    yr = F.batch_norm(xr, ref.running_mean, ref.running_var, ref.weight, ref.bias, True, 0.1, ref.eps)
+    if res:
+        yr = yr + rr
+    if act == "relu":
+        yr = F.relu(yr)
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=5e-3, atol=5e-3)
+    torch.testing.assert_close(y.float(), yr, **tol)
+    torch.testing.assert_close(bn.running_mean, ref.running_mean, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-3, atol=1e-4)
+    g = torch.randn(shape, device=cuda).to(dtype).contiguous(memory_format=torch.channels_last)
+    # compare backward through the same mask: use the reference's own forward for the reference
+    y.backward(g); yr.backward(g.float())
+    gtol = dict(rtol=5e-2, atol=5e-2) if dtype == torch.bfloat16 else dict(rtol=1e-2, atol=1e-2)
+    # elements whose pre-activation is within rounding of zero may flip the ReLU mask between
+    # the 16-bit kernel and the fp32 reference; allow a tiny fraction of mismatches
+    def close_frac(a, b, rtol, atol):
+        return ((a - b).abs() <= atol + rtol * b.abs()).float().mean().item()
+    assert close_frac(x.grad.float(), xr.grad, **gtol) > 0.995
+    if res:
+        assert close_frac(r.grad.float(), rr.grad, **gtol) > 0.995
+    n = shape[0] * shape[2] * shape[3]
+    torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=3e-2, atol=3e-2 * math.sqrt(n))
+    torch.testing.assert_close(bn.bias.grad, ref.bias.grad, rtol=3e-2, atol=3e-2 * math.sqrt(n))
+    # eval mode
+    bn.eval()
+    ye = bn(x.detach(), r.detach() if res else None)
+    yer = F.batch_norm(xr.detach(), ref.running_mean, ref.running_var, ref.weight, ref.bias, False, 0.0, ref.eps)
+    if res:
+        yer = yer + rr.detach()
+    if act == "relu":
+        yer = F.relu(yer)
+    torch.testing.assert_close(ye.float(), yer, **tol)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("rows,D", [(197 * 4, 768), (33, 64), (5, 2048), (1000, 384)])
+def test_layernorm_matches_torch(dtype, rows, D):
+    from pytorch_distributedtraining_b200.ops.layers import LayerNorm
+    torch.manual_seed(2)
+    ln = LayerNorm(D, eps=1e-6).to(cuda)
+    with torch.no_grad():
+        ln.weight.uniform_(0.5, 1.5); ln.bias.uniform_(-0.5, 0.5)
+    ref = copy.deepcopy(ln)
+    x = torch.randn(rows, D, device=cuda).to(dtype).requires_grad_(True)
+    xr = x.detach().float().requires_grad_(True)
+    y = ln(x)
+    yr = F.layer_norm(xr, (D,), ref.weight, ref.bias, 1e-6)
+    tol = {torch.float32: 1e-5, torch.float16: 5e-3, torch.bfloat16: 3e-2}[dtype]
+    torch.testing.assert_close(y.float(), yr, rtol=tol, atol=tol)
+    g = torch.randn(rows, D, device=cuda).to(dtype)
+    y.backward(g); yr.backward(g.float())
+    torch.testing.assert_close(x.grad.float(), xr.grad, rtol=tol * 4, atol=tol * 4)
+    torch.testing.assert_close(ln.weight.grad, ref.weight.grad, rtol=tol * 10, atol=tol * 4 * math.sqrt(rows))
+    torch.testing.assert_close(ln.bias.grad, ref.bias.grad, rtol=tol * 10, atol=tol * 4 * math.sqrt(rows))
+
+
+def test_resnet18_fused_path_matches_stock_ops():
+    """Whole-model check: the fused BN/ReLU/CE path must be as close to an fp32 reference as
+    the same model on stock torch fp16 ops is (both carry fp16 rounding; neither is exact)."""
+    from pytorch_distributedtraining_b200.models import resnet18
+    from pytorch_distributedtraining_b200.ops import dispatch
+    from pytorch_distributedtraining_b200.ops.loss import cross_entropy
+    torch.manual_seed(0)
+    m = resnet18(num_classes=10, small_input=True).to(cuda).to(memory_format=torch.channels_last)
+    stock, exact = copy.deepcopy(m), copy.deepcopy(m)
+    x = torch.randn(16, 3, 32, 32, device=cuda).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 10, (16,), device=cuda)
+    with torch.autocast("cuda", dtype=torch.float16):
+        l1 = cross_entropy(m(x), y)
+    l1.backward()
+    feats = ("bn", "ce", "gemm", "conv", "ln")
+    for f in feats:
+        dispatch.disable(f)
+    try:
+        with torch.autocast("cuda", dtype=torch.float16):
+            l2 = F.cross_entropy(stock(x).float(), y)
+        l2.backward()
+        l3 = F.cross_entropy(exact(x), y)   # fp32 everywhere
+        l3.backward()
+    finally:
+        for f in feats:
+            dispatch.enable(f)
+
+    def rel(model):
+        num = sum(((a.grad - b.grad) ** 2).sum() for a, b in zip(model.parameters(), exact.parameters()))
+        den = sum((b.grad ** 2).sum() for b in exact.parameters())
+        return (num / den).sqrt().item()
+
+    e_fused, e_stock = rel(m), rel(stock)
+    print(f"grad rel err vs fp32: fused {e_fused:.4f}, stock fp16 {e_stock:.4f}")
+    torch.testing.assert_close(l1, l3, rtol=2e-2, atol=2e-2)
+    assert e_fused < max(1.5 * e_stock, 2e-2), (e_fused, e_stock)
