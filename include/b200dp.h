@@ -110,6 +110,23 @@ int b200dp_scaler_update(float* scale, int* growth_tracker, float* found_inf, fl
 int64_t b200dp_sumsq_scratch_floats(int64_t n);
 int b200dp_sumsq_f32(const float* x, int64_t n, float* scratch, unsigned int* counter, float* out, void* stream);
 
+/* Sum of squares for callers that cannot allocate device memory (host callbacks and
+ * serving loops where a cudaMalloc would stall the GPU, processes whose memory is fully
+ * pre-partitioned, C hosts with no allocator to borrow a workspace from).  Same result as
+ * b200dp_sumsq_f32, but the partial sums and the ticket live in a fixed device array
+ * inside the library (65,792 bytes held on every GPU that loads it, until exit), so the
+ * caller passes only input and output.  No counterpart in the reference: the reference
+ * has no native code and no such constraint.
+ *   - n may be at most B200DP_NOALLOC_MAX_ELEMS; a larger n returns B200DP_ERR_INVALID
+ *     and launches nothing.
+ *   - All calls on a GPU share the one array: calls that can overlap on the GPU (different
+ *     streams) race; keep them on one stream.  The ticket word is cleared per call.
+ *   - The first call on each GPU resolves the array's device address
+ *     (cudaGetSymbolAddress, that GPU current); make it before any stream capture.
+ *   - Calls no cudaMalloc / cudaFree / allocating routine. */
+#define B200DP_NOALLOC_MAX_ELEMS (1ll << 28)
+int b200dp_sumsq_f32_noalloc(const float* x, int64_t n, float* out, void* stream);
+
 /* ------------------------------------------------------------------ losses
  * Softmax cross-entropy with mean reduction, forward and backward in one pass over the
  * logits (reference: classification loss implied by BASELINE configs; nn.MSELoss at
