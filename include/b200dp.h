@@ -189,6 +189,77 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
                          const float* gamma, const float* mean, const float* rstd, float* scratch,
                          unsigned int* counter, float* dgamma, float* dbeta, void* stream);
 
+/* ------------------------------------------------------------------ peer-memory collectives
+ * One kernel per rank; ranks meet at flag barriers in peer-mapped memory (csrc/collectives.cu
+ * explains the protocol).  Every buffer argument is a table of B200DP_MAX_RANKS pointers:
+ * entry p is rank p's buffer as mapped into THIS process (entry `rank` is the local one).
+ * Tables of rank-local objects (scalars, optimizer state) only need entry `rank`.
+ * `mc` arguments are the NVLS multicast address of the same buffer, or NULL to use plain
+ * peer loads/stores.  With ctx.emulate = 1 all ranks run on one GPU (tests).
+ *
+ * Reference: these replace the NCCL collectives the reference's libraries issue —
+ * DDP bucket all-reduce (Stoke-DDP.py:248), ShardedDDP reduce-to-owner (Fairscale-DDP.py:89,
+ * Stoke-DDP.py:250), OSS post-step broadcast (Fairscale-DDP.py:101, Stoke-DDP.py:197-199),
+ * FSDP all-gather / reduce-scatter (Stoke fairscale_fsdp flag), SyncBN / loss / norm scalar
+ * all-reduces (Stoke-DDP.py:192,86,253). */
+#define B200DP_MAX_RANKS 8
+
+typedef struct {
+    int rank;            /* this process's rank within the group (ignored when emulating)        */
+    int world;           /* number of ranks, <= B200DP_MAX_RANKS                                  */
+    int emulate;         /* 1: single-GPU emulation, grid.y = world, cooperative launch           */
+    int max_blocks;      /* rows in each flag array                                               */
+    uint32_t* flags[B200DP_MAX_RANKS];   /* [max_blocks][B200DP_MAX_RANKS] words per rank, zeroed once    */
+    uint32_t* epochs[B200DP_MAX_RANKS];  /* [max_blocks] per-CTA barrier counters (local entry used)      */
+    uint32_t* status[B200DP_MAX_RANKS];  /* one word per rank: non-zero after a barrier timed out         */
+    uint64_t timeout_ns; /* spin limit per barrier; 0 = wait forever                              */
+} b200dp_peer_ctx;
+
+/* `rounds` barriers back to back (protocol self-test / latency probe). */
+int b200dp_peer_barrier(const b200dp_peer_ctx* ctx, int blocks, int rounds, void* stream);
+
+/* In-place all-reduce of n elements: buf = pre_mult * (*mult_dev) * sum over ranks, and
+ * found_inf = 1 if any result is non-finite (W1: all-reduce + AMP unscale + inf check).
+ * algo 0 = one-shot (small), 1 = two-shot; with mc != NULL the NVLS two-shot is used.
+ * n must be a multiple of 16 bytes worth of elements. */
+int b200dp_peer_allreduce(const b200dp_peer_ctx* ctx, void* const* bufs, void* mc, int64_t n, b200dp_dtype dtype,
+                          float pre_mult, const void* const* mult_dev, void* const* found_inf, int algo, int blocks,
+                          void* stream);
+
+/* outs[rank][i] (= or +=) pre_mult * (*mult_dev) * sum_p in[p][rank*n_per_rank + i], fp32 out
+ * (W5: reduce-scatter + scale + cast to the fp32 shard gradient). */
+int b200dp_peer_reduce_scatter(const b200dp_peer_ctx* ctx, void* const* in_bufs, void* mc, int64_t n_per_rank,
+                               b200dp_dtype dtype, void* const* outs, float pre_mult, const void* const* mult_dev,
+                               void* const* found_inf, int accumulate, int blocks, void* stream);
+
+/* Every rank pushes cast(shard) into slot `rank` of every rank's output buffer (all-gather
+ * fused with the fp32 -> compute-dtype cast; one multicast store per 16 bytes with NVLS). */
+int b200dp_peer_all_gather(const b200dp_peer_ctx* ctx, void* const* outs, void* mc, const void* const* shards,
+                           int64_t n_per_rank, b200dp_dtype shard_dtype, b200dp_dtype out_dtype, int blocks,
+                           void* stream);
+
+/* ZeRO step on owner-ordered flat buffers (W2 + W3): rank r owns elements [seg[r], seg[r+1])
+ * (multiples of 8).  Reduce the owned gradient segment across ranks (or read it pre-reduced
+ * from local_grad), apply AdamW to the rank-local fp32 master/m/v, and publish the new
+ * parameter values into every rank's parameter buffer (fp32 or 16-bit wire). */
+int b200dp_peer_zero_adam(const b200dp_peer_ctx* ctx, void* const* grad_bufs, void* grad_mc, void* const* param_bufs,
+                          void* param_mc, const int64_t* seg, b200dp_dtype wire_dtype, void* const* master,
+                          void* const* m, void* const* v, b200dp_adam_hparams hp, const void* const* step,
+                          float pre_mult, const void* const* mult_dev, const void* const* found_inf, int prereduced,
+                          const void* const* local_grad, int blocks, void* stream);
+
+/* Reduce-to-owner only: local_out[rank] = scaled sum of the owned segment; norm_out[rank] =
+ * {sum of squares of it, non-finite flag}.  partials: `blocks` floats; counters: zeroed uint32. */
+int b200dp_peer_reduce_to_owner(const b200dp_peer_ctx* ctx, void* const* grad_bufs, const int64_t* seg,
+                                void* const* local_out, float pre_mult, const void* const* mult_dev,
+                                void* const* norm_out, void* const* partials, void* const* counters, int blocks,
+                                void* stream);
+
+/* In-place sum across ranks of n <= slot_floats fp32 values (SyncBN moments, loss, norm, inf
+ * flag: W6 / W11).  staging[p]: 2*slot_floats floats of peer memory; call_counter: local uint32. */
+int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
+                                int slot_floats, void* const* call_counter, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

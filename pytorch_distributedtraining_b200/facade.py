@@ -294,9 +294,16 @@ class Stoke:
         self._backward_steps += 1
         self._grad_accum_counter += 1
         total = sum(loss) if isinstance(loss, (list, tuple)) else loss
+        sync_now = self._at_boundary()
         if self._scaler is not None:
             total = self._scaler.scale(total)
-        sync_now = self._at_boundary()
+            ddp_eng = self._peer.get("ddp") if getattr(self, "_peer", None) else None
+            if ddp_eng is not None and sync_now:
+                # the fused bucket all-reduce applies 1/scale and raises the inf flag itself (W1)
+                if ddp_eng.inv_scale is None:
+                    ddp_eng.inv_scale = torch.empty((), dtype=torch.float32, device=self._device)
+                torch.reciprocal(self._scaler.scale_tensor, out=ddp_eng.inv_scale)
+                ddp_eng.found_inf = self._scaler.found_inf_tensor
         ctx = contextlib.nullcontext()
         if not sync_now and self._ddp_cfg.no_sync and hasattr(self._model, "no_sync"):
             ctx = self._model.no_sync()
@@ -309,21 +316,45 @@ class Stoke:
         if not self._at_boundary():
             return
         gc = self._grad_clip
-        fused = (hasattr(self._optimizer, "fused_unscale_clip") and not isinstance(gc, ClipGradConfig)
-                 and (gc is None or float(gc.norm_type) == 2.0))
-        if self._scaler is not None:
-            if fused:
-                # one read of the gradients (inf flag + norm); unscale and clip ride inside the update kernel
-                self._scaler.unscale_and_clip_fused(self._optimizer, None if gc is None else gc.max_norm)
+        opt = self._optimizer
+        norm_clip = isinstance(gc, ClipGradNormConfig) and float(gc.norm_type) == 2.0
+        fused = hasattr(opt, "fused_unscale_clip") and not isinstance(gc, ClipGradConfig) and (gc is None or norm_clip)
+        zero_eng = getattr(opt, "_flat_engine", None) if isinstance(opt, OSS) else None
+        ddp_eng = self._peer.get("ddp") if getattr(self, "_peer", None) else None
+        if zero_eng is not None and (gc is None or norm_clip):
+            # fused ZeRO-2 step: reduce-to-owner (+norm, +inf) -> tiny all-reduce -> AdamW + publish
+            if self._scaler is not None:
+                self._scaler._lazy_init(self._device)
+                inv = self._scaler.scale_tensor.reciprocal()
+                zero_eng.clip_grad_norm(gc.max_norm if gc is not None else 3.0e38, 2.0, inv_scale=inv,
+                                        found_inf=self._scaler.found_inf_tensor)
+                self._scaler.unscale_(opt, already_unscaled=True, flag_is_global=True)
+                self._scaler.step(opt)
+                self._scaler.update()
             else:
                 if gc is not None:
-                    self._scaler.unscale_(self._optimizer)
+                    zero_eng.clip_grad_norm(gc.max_norm, 2.0)
+                opt.step()
+        elif self._scaler is not None:
+            if ddp_eng is not None and ddp_eng.amp_fused:
+                # gradients arrive from the fused all-reduce already unscaled, flag already raised
+                self._scaler.unscale_(opt, already_unscaled=True, flag_is_global=True)
+                if fused and gc is not None:
+                    opt.fused_unscale_clip(None, gc.max_norm, self._scaler.found_inf_tensor)
+                else:
+                    self._clip()
+            elif fused:
+                # one read of the gradients (inf flag + norm); unscale and clip ride inside the update kernel
+                self._scaler.unscale_and_clip_fused(opt, None if gc is None else gc.max_norm)
+            else:
+                if gc is not None:
+                    self._scaler.unscale_(opt)
                 self._clip()
-            self._scaler.step(self._optimizer)
+            self._scaler.step(opt)
             self._scaler.update()
         else:
             self._clip()
-            self._optimizer.step()
+            opt.step()
         self.zero_grads()
         self._grad_accum_counter = 0
         self._agg_loss = None

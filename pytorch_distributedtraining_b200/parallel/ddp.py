@@ -141,6 +141,7 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         self._hook_handles: List[Any] = []
         self._comm_stream: Optional[torch.cuda.Stream] = None
+        self._next_bucket = 0
 
         self._params = [p for p in module.parameters() if p.requires_grad]
         if sync_models_at_startup:
@@ -207,6 +208,7 @@ class DistributedDataParallel(nn.Module):
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             for b in self.buckets:
                 b.reset()
+            self._next_bucket = 0
         self._callback_queued = False
         return self.module(*inputs, **kwargs)
 
@@ -246,8 +248,14 @@ class DistributedDataParallel(nn.Module):
             self._callback_queued = True
             Variable._execution_engine.queue_callback(self._finalize_backward)
         b.pending -= 1
-        if b.pending == 0 and not b.launched:
-            self._launch(b)
+        # launch strictly in bucket order: every rank must issue its collectives in the same
+        # sequence (flag barriers and NCCL alike), whatever order autograd finished them in
+        while self._next_bucket < len(self.buckets):
+            nb = self.buckets[self._next_bucket]
+            if nb.pending != 0 or nb.launched:
+                break
+            self._launch(nb)
+            self._next_bucket += 1
 
     def _launch(self, b: GradBucket) -> None:
         b.launched = True
@@ -268,7 +276,7 @@ class DistributedDataParallel(nn.Module):
     def _finalize_backward(self) -> None:
         self._callback_queued = False
         if self.require_backward_grad_sync and self.world_size > 1:
-            for b in self.buckets:
+            for b in self.buckets[self._next_bucket:]:
                 if not b.launched:
                     if b.pending != len(b.params) and not self.find_unused_parameters and b.pending != 0:
                         raise RuntimeError(

@@ -227,18 +227,19 @@ class FullyShardedDataParallel(nn.Module):
         if self._full_valid:
             return full
         shard = self.flat_param.detach()
-        if shard.dtype != self.compute_dtype:
-            shard = shard.to(self.compute_dtype)
         with torch.autograd._unsafe_preserve_version_counter(full):
             if self._peer_engine is not None:
+                # peer kernel: reads the fp32 shard, casts to the compute dtype on the fly (W4 producer half)
                 self._peer_engine.all_gather(full, shard)
             else:
+                if shard.dtype != self.compute_dtype:
+                    shard = shard.to(self.compute_dtype)
                 _all_gather_into(full, shard, self.process_group, self.world_size)
         self._full_valid = True
         return full
 
     def _free_full(self) -> None:
-        if self._full is not None:
+        if self._full is not None and not getattr(self, "_full_persistent", False):
             self._full.untyped_storage().resize_(0)
         self._full_valid = False
 
@@ -268,10 +269,12 @@ class FullyShardedDataParallel(nn.Module):
             self._grad_accum_full = None
         if self.fp32_reduce_scatter and grad_full.dtype != torch.float32:
             grad_full = grad_full.float()
-        out = torch.empty(self._shard_numel, dtype=grad_full.dtype, device=grad_full.device)
         if self._peer_engine is not None:
+            # peer kernel: sum across ranks, scale by 1/world and write the fp32 shard gradient (W5)
+            out = torch.empty(self._shard_numel, dtype=torch.float32, device=grad_full.device)
             self._peer_engine.reduce_scatter(out, grad_full, 1.0 / self.world_size)
             return out.to(self.flat_param.dtype)
+        out = torch.empty(self._shard_numel, dtype=grad_full.dtype, device=grad_full.device)
         if self.gradient_predivide_factor > 1:
             grad_full = grad_full / self.gradient_predivide_factor
         elif not grad_full.is_contiguous():

@@ -104,11 +104,12 @@ class GradScaler:
             torch._amp_foreach_non_finite_check_and_unscale_(gs, found_inf.to(dev), inv_scale.to(dev))
 
     def unscale_(self, optimizer: torch.optim.Optimizer, grads: Optional[List[torch.Tensor]] = None,
-                 already_unscaled: bool = False) -> None:
+                 already_unscaled: bool = False, flag_is_global: bool = False) -> None:
         """Divide gradients by the scale and record non-finite values.
 
         ``already_unscaled``: a fused collective did the arithmetic and wrote the flag
-        into ``found_inf_tensor`` itself; only bookkeeping remains.
+        into ``found_inf_tensor`` itself; only bookkeeping remains.  ``flag_is_global``: that
+        flag has already been combined across ranks (skip the sharded scaler's all-reduce).
         """
         if not self._enabled:
             return
@@ -123,7 +124,8 @@ class GradScaler:
         if not already_unscaled:
             inv = self._scale.double().reciprocal().float()
             self._unscale_grads(grads, inv, self._found_inf)
-        self._sync_found_inf()
+        if not flag_is_global:
+            self._sync_found_inf()
         st["stage"] = _OptState.UNSCALED
 
     def _sync_found_inf(self) -> None:

@@ -1,8 +1,456 @@
-"""Symmetric-memory arena and engine attachment (placeholder until ops.collectives lands)."""
+"""Symmetric-memory arena and the engines that put the peer-memory kernels on the hot path.
+
+``PeerArena`` allocates one block of torch symmetric memory per process group
+(``torch.distributed._symmetric_memory``: CUDA IPC / fabric handles under the hood, plus an
+NVLS multicast mapping when the NVSwitch supports it), exchanges the mappings once, and
+hands out sub-buffers together with their per-rank pointer tables.  Flag regions for the
+in-kernel barriers live in the same block.  Separate *contexts* (flag sets) exist for
+collectives issued on different streams, because two kernels that can overlap must not share
+barrier rows.
+
+Engines (attached by ``attach()`` from the facade):
+  * ``DDPPeerEngine``   gradient buckets live in the arena; each bucket is reduced by the
+    fused all-reduce (+1/world, +AMP unscale, +inf check) on a comm stream as soon as
+    backward has produced it (W1; replaces the NCCL all-reduce of Stoke-DDP.py:248).
+  * ``FSDPPeerEngine``  parameter all-gather with the fp32→compute-dtype cast fused in,
+    gradient reduce-scatter with the scale and fp32 cast fused in (W5 and the producer half
+    of W4).  Gathered parameters stay resident (180 GB HBM): no re-gather in backward.
+  * ``ZeroPeerEngine``  OSS + ShardedDDP as ONE kernel per step: reduce-to-owner, sharded
+    AdamW on the owner's fp32 master, publish to every rank (W2 + W3; replaces the
+    per-parameter ``dist.reduce`` of Fairscale-DDP.py:89 and the per-owner ``dist.broadcast``
+    after Fairscale-DDP.py:101).
+  * small one-shot all-reduce for SyncBN moments, loss, norm and inf flags (W6 / W11).
+"""
 from __future__ import annotations
 
-from typing import Any, Optional
+import math
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from ..ops import collectives as C
+from ..ops import fused
+from . import comm, peer
+
+_ALIGN = 4096
 
 
-def attach(engine: Any, optim: Any, status: Any, **cfg: Any) -> Optional[Any]:
-    return None
+class SymmBuffer:
+    """A typed view of arena memory plus where the same bytes live on every rank."""
+
+    def __init__(self, tensor: torch.Tensor, ptrs: List[int], mc: int):
+        self.tensor, self.ptrs, self.mc = tensor, ptrs, mc
+        self.table = C.table(ptrs)
+
+
+class PeerArena:
+    def __init__(self, group: Any, device: torch.device, nbytes: int, max_blocks: int = 64, timeout_s: float = 30.0):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group, self.device = group, device
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > C.MAX_RANKS:
+            raise RuntimeError(f"peer collectives support up to {C.MAX_RANKS} ranks per node, got {self.world}")
+        self.max_blocks, self.timeout_s = max_blocks, timeout_s
+        nbytes = (int(nbytes) + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.hdl = symm_mem.rendezvous(self.buf, group)
+        self.base = [int(p) for p in self.hdl.buffer_ptrs]
+        self.mc_base = int(getattr(self.hdl, "multicast_ptr", 0) or 0)   # 0: no NVLS multicast on this fabric
+        self.nbytes, self._off = nbytes, 0
+        self._contexts: Dict[str, C.PeerContext] = {}
+        self._keep: List[Any] = []
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        comm.barrier(group)
+
+    def alloc(self, numel: int, dtype: torch.dtype) -> SymmBuffer:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        off = self._off
+        end = off + (nbytes + _ALIGN - 1) // _ALIGN * _ALIGN
+        if end > self.nbytes:
+            raise MemoryError(f"peer arena exhausted: need {end} bytes of {self.nbytes}")
+        self._off = end
+        t = self.buf[off: off + nbytes].view(dtype)
+        return SymmBuffer(t, [b + off for b in self.base], (self.mc_base + off) if self.mc_base else 0)
+
+    def remaining(self) -> int:
+        return self.nbytes - self._off
+
+    def context(self, name: str) -> C.PeerContext:
+        """Flag set for one stream's worth of collectives."""
+        ctx = self._contexts.get(name)
+        if ctx is None:
+            flags = self.alloc(self.max_blocks * C.MAX_RANKS, torch.int32)
+            epochs = torch.zeros(self.max_blocks, dtype=torch.int32, device=self.device)
+            status = torch.zeros(1, dtype=torch.int32, device=self.device)
+            ctx = self._contexts[name] = C.PeerContext(self.rank, self.world, flags.ptrs, epochs, status,
+                                                       self.max_blocks, timeout_s=self.timeout_s)
+            self._keep.append(flags)
+        return ctx
+
+    def timed_out(self) -> bool:
+        return any(c.timed_out() for c in self._contexts.values())
+
+
+# --------------------------------------------------------------------------- small all-reduce
+class SmallAllReduce:
+    SLOT = 16384  # floats per staging slot (64 KB)
+
+    def __init__(self, arena: PeerArena):
+        self.arena = arena
+        self.ctx = arena.context("main")
+        self.staging = arena.alloc(2 * self.SLOT, torch.float32)
+        self.calls = torch.zeros(1, dtype=torch.int32, device=arena.device)
+        self.calls_table = C.local_table(arena.rank, self.calls)
+
+    def __call__(self, buf: torch.Tensor, group: Any) -> bool:
+        if buf.dtype != torch.float32 or not buf.is_contiguous() or buf.numel() > self.SLOT or not buf.is_cuda:
+            return False
+        if group is not None and group is not self.arena.group and group is not dist.group.WORLD:
+            return False
+        self.ctx.small_allreduce(self.staging.table, C.local_table(self.arena.rank, buf), buf.numel(), self.SLOT,
+                                 self.calls_table)
+        return True
+
+    small_allreduce = __call__
+
+
+# --------------------------------------------------------------------------- DDP
+class DDPPeerEngine:
+    """Bucket all-reduce on a comm stream, fused with 1/world, the AMP unscale and the inf check."""
+
+    ONE_SHOT_BYTES = 512 * 1024
+
+    def __init__(self, arena: PeerArena, ddp: Any, blocks: int = 32):
+        self.arena, self.ddp, self.blocks = arena, ddp, blocks
+        self.ctx = arena.context("comm")
+        self.stream = torch.cuda.Stream(device=arena.device)
+        self._bufs: Dict[int, SymmBuffer] = {}
+        self.inv_scale: Optional[torch.Tensor] = None     # set per step by the scaler glue
+        self.found_inf: Optional[torch.Tensor] = None
+        self._next = 0
+
+        def allocator(numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+            sb = arena.alloc(numel, dtype)
+            sb.tensor.zero_()
+            self._bufs[sb.tensor.data_ptr()] = sb
+            return sb.tensor
+
+        ddp.rebuild_buckets(allocator)
+        ddp.attach_peer_allreduce(self)
+        torch.cuda.synchronize(arena.device)
+        comm.barrier(arena.group)
+
+    @property
+    def amp_fused(self) -> bool:
+        return self.inv_scale is not None
+
+    def launch(self, bucket: Any) -> Callable[[], None]:
+        sb = self._bufs[bucket.buffer.data_ptr()]
+        n = bucket.buffer.numel()
+        main = torch.cuda.current_stream(self.arena.device)
+        self.stream.wait_stream(main)          # the bucket's gradients are produced on the main stream
+        nbytes = n * bucket.buffer.element_size()
+        algo = 0 if nbytes <= self.ONE_SHOT_BYTES else 1
+        mc = sb.mc if algo == 1 else 0
+        rank = self.arena.rank
+        self.ctx.allreduce(sb.table, mc, n, bucket.buffer.dtype, pre_mult=1.0 / self.arena.world,
+                           mult_dev=C.local_table(rank, self.inv_scale), found_inf=C.local_table(rank, self.found_inf),
+                           algo=algo, blocks=min(self.blocks, max(1, n // 4096)), stream=self.stream)
+
+        def finish() -> None:
+            torch.cuda.current_stream(self.arena.device).wait_stream(self.stream)
+
+        return finish
+
+
+# --------------------------------------------------------------------------- FSDP
+class FSDPPeerEngine:
+    def __init__(self, arena: PeerArena, root: Any, blocks: int = 32):
+        from .fsdp import FullyShardedDataParallel
+        self.arena, self.blocks = arena, blocks
+        self.ctx = arena.context("main")
+        units = [u for u in root.modules() if isinstance(u, FullyShardedDataParallel) and u.flat_param is not None]
+        biggest = max(u._padded for u in units)
+        self.grad_stage: Dict[torch.dtype, SymmBuffer] = {}
+        self._full: Dict[int, SymmBuffer] = {}
+        self._biggest = biggest
+        for u in units:
+            sb = arena.alloc(u._padded, u.compute_dtype)
+            u._full = sb.tensor
+            u._full_valid = False
+            u._full_persistent = True           # arena memory is never resized away
+            u.reshard_after_forward = False     # gathered params stay resident: no re-gather in backward
+            self._full[id(u)] = sb
+            u.attach_peer_engine(_FSDPUnitOps(self, u, sb))
+
+    def stage(self, dtype: torch.dtype) -> SymmBuffer:
+        sb = self.grad_stage.get(dtype)
+        if sb is None:
+            sb = self.grad_stage[dtype] = self.arena.alloc(self._biggest, dtype)
+        return sb
+
+
+class _FSDPUnitOps:
+    def __init__(self, eng: FSDPPeerEngine, unit: Any, full: SymmBuffer):
+        self.eng, self.unit, self.full = eng, unit, full
+
+    def all_gather(self, full: torch.Tensor, shard_compute: torch.Tensor) -> None:
+        # gather straight from the fp32 shard: the cast to the compute dtype happens in the kernel
+        u, a = self.unit, self.eng.arena
+        src = u.flat_param.detach()
+        self.eng.ctx.all_gather(self.full.table, self.full.mc, C.local_table(a.rank, src), u._shard_numel, src.dtype,
+                                u.compute_dtype, blocks=min(self.eng.blocks, max(1, u._shard_numel // 4096)))
+
+    def reduce_scatter(self, out: torch.Tensor, grad_full: torch.Tensor, scale: float) -> None:
+        u, a = self.unit, self.eng.arena
+        st = self.eng.stage(grad_full.dtype)
+        st.tensor[: grad_full.numel()].copy_(grad_full.reshape(-1))
+        out32 = out if out.dtype == torch.float32 else torch.empty_like(out, dtype=torch.float32)
+        self.eng.ctx.reduce_scatter(st.table, st.mc, u._shard_numel, grad_full.dtype, C.local_table(a.rank, out32),
+                                    pre_mult=scale, blocks=min(self.eng.blocks, max(1, u._shard_numel // 4096)))
+        if out32 is not out:
+            out.copy_(out32)
+
+
+# --------------------------------------------------------------------------- ZeRO-2 fused step
+class ZeroPeerEngine:
+    """OSS + ShardedDDP on owner-ordered flat buffers; see the module docstring."""
+
+    def __init__(self, arena: PeerArena, oss: Any, sddp: Any, wire_dtype: Optional[torch.dtype] = None, blocks: int = 48):
+        self.arena, self.oss, self.sddp, self.blocks = arena, oss, sddp, blocks
+        self.ctx = arena.context("main")
+        self.rank, self.world = arena.rank, arena.world
+        self.wire_dtype = wire_dtype or torch.float32
+        self.small = SmallAllReduce(arena) if peer._STATE.get("small") is None else peer._STATE["small"]
+        dev = arena.device
+        # ---- layout: for each param group, ranks in order, each rank's params in order, 8-aligned segments
+        self.groups: List[Dict[str, Any]] = []
+        total = 0
+        part = oss.partition_parameters()
+        for gi, group in enumerate(oss.param_groups):
+            seg = [total]
+            entries: List[Tuple[torch.Tensor, int, int]] = []  # (param, offset, owner)
+            for r in range(self.world):
+                off = seg[-1]
+                for p in part[r][gi]["params"]:
+                    if p.dtype != torch.float32:
+                        raise RuntimeError("fused ZeRO engine expects fp32 parameters")
+                    entries.append((p, off, r))
+                    off += p.numel()
+                seg.append((off + 7) // 8 * 8)
+            total = seg[-1]
+            self.groups.append({"seg": seg, "entries": entries})
+        self.total = max(total, 8)
+        self.G = arena.alloc(self.total, torch.float32)
+        self.P = arena.alloc(self.total, torch.float32)
+        self.P16 = arena.alloc(self.total, self.wire_dtype) if self.wire_dtype != torch.float32 else None
+        self.G.tensor.zero_()
+        self.P.tensor.zero_()
+        with torch.no_grad():
+            for g in self.groups:
+                for p, off, _r in g["entries"]:
+                    view = self.P.tensor[off: off + p.numel()].view(p.shape)
+                    view.copy_(p.detach())
+                    p.data = view
+                    gview = self.G.tensor[off: off + p.numel()].view(p.shape)
+                    if p.grad is not None:
+                        gview.copy_(p.grad)
+                    p.grad = gview
+        # ---- owner-local state per group
+        for g in self.groups:
+            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
+            n = max(s1 - s0, 8)
+            g["master"] = torch.zeros(n, dtype=torch.float32, device=dev)
+            g["master"][: s1 - s0].copy_(self.P.tensor[s0:s1])
+            g["m"] = torch.zeros(n, dtype=torch.float32, device=dev)
+            g["v"] = torch.zeros(n, dtype=torch.float32, device=dev)
+            g["step"] = torch.zeros((), dtype=torch.float32, device=dev)
+            g["reduced"] = None
+        self.norm_buf = torch.zeros(2, dtype=torch.float32, device=dev)
+        self.partials = torch.zeros(arena.max_blocks, dtype=torch.float32, device=dev)
+        self.counter = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.grad_mult = torch.ones((), dtype=torch.float32, device=dev)
+        self.total_norm = torch.zeros((), dtype=torch.float32, device=dev)
+        self._clip_pending = False
+        torch.cuda.synchronize(dev)
+        comm.barrier(arena.group)
+        oss.attach_flat_engine(self)
+        sddp.attach_fused_engine(self)
+
+    # hooks called by ShardedDataParallel ------------------------------------------
+    def pre_forward(self) -> None:
+        return
+
+    def zero_grad(self) -> None:
+        self.G.tensor.zero_()
+        for g in self.groups:
+            for p, off, _r in g["entries"]:
+                if p.grad is None or p.grad.data_ptr() != self.G.tensor.data_ptr() + off * 4:
+                    p.grad = self.G.tensor[off: off + p.numel()].view(p.shape)
+
+    def _reattach_grads(self) -> None:
+        """A foreign ``zero_grad(set_to_none=True)`` detaches the views; copy and re-alias."""
+        for g in self.groups:
+            for p, off, _r in g["entries"]:
+                want = self.G.tensor.data_ptr() + off * 4
+                if p.grad is not None and p.grad.data_ptr() != want:
+                    v = self.G.tensor[off: off + p.numel()].view(p.shape)
+                    v.copy_(p.grad)
+                    p.grad = v
+
+    # OSS surface --------------------------------------------------------------------
+    @torch.no_grad()
+    def clip_grad_norm(self, max_norm: float, norm_type: float = 2.0, inv_scale: Optional[torch.Tensor] = None,
+                       found_inf: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if float(norm_type) != 2.0:
+            raise NotImplementedError("the fused ZeRO engine clips by the 2-norm only")
+        self._reattach_grads()
+        self.norm_buf.zero_()
+        tmp = torch.zeros(2, dtype=torch.float32, device=self.arena.device)
+        for g in self.groups:
+            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
+            if g["reduced"] is None:
+                g["reduced"] = torch.empty(max(s1 - s0, 8), dtype=torch.float32, device=self.arena.device)
+            tmp.zero_()
+            self.ctx.reduce_to_owner(self.G.table, g["seg"], C.local_table(self.rank, g["reduced"]), 1.0 / self.world,
+                                     None, C.local_table(self.rank, tmp), C.local_table(self.rank, self.partials),
+                                     C.local_table(self.rank, self.counter), blocks=self._blocks(s1 - s0))
+            self.norm_buf += tmp
+        if not self.small(self.norm_buf, self.arena.group):
+            dist.all_reduce(self.norm_buf, group=self.arena.group)
+        if found_inf is not None:
+            torch.maximum(found_inf, (self.norm_buf[1] > 0).float(), out=found_inf)
+        fused.clip_coef(self.norm_buf[0:1], inv_scale, float(max_norm), self.grad_mult, self.total_norm)
+        self._clip_pending = True
+        return self.total_norm
+
+    def _blocks(self, n: int) -> int:
+        return int(min(self.blocks, self.arena.max_blocks, max(1, n // 8192)))
+
+    @torch.no_grad()
+    def step(self, closure: Optional[Callable] = None, found_inf: Optional[torch.Tensor] = None,
+             grad_mult: Optional[torch.Tensor] = None, **_kw: Any) -> Optional[float]:
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        self._reattach_grads()
+        oss = self.oss
+        prereduced = self._clip_pending
+        mult = grad_mult if grad_mult is not None else (self.grad_mult if prereduced else None)
+        for gi, (g, pg) in enumerate(zip(self.groups, oss.param_groups)):
+            b1, b2 = pg.get("betas", (0.9, 0.999))
+            hp = fused.AdamHParams(float(pg["lr"]), float(b1), float(b2), float(pg.get("eps", 1e-8)),
+                                   float(pg.get("weight_decay", 0.0)), 1 if self._is_adamw() else 0, 0)
+            fused.step_advance(g["step"], found_inf)
+            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
+            pbuf = self.P16 if self.P16 is not None else self.P
+            self.ctx.zero_adam(None if prereduced else self.G.table, 0 if prereduced else self.G.mc, pbuf.table,
+                               pbuf.mc if self.P16 is None else 0, g["seg"], self.wire_dtype,
+                               C.local_table(self.rank, g["master"]), C.local_table(self.rank, g["m"]),
+                               C.local_table(self.rank, g["v"]), hp, C.local_table(self.rank, g["step"]),
+                               pre_mult=1.0 if prereduced else 1.0 / self.world,
+                               mult_dev=C.local_table(self.rank, mult), found_inf=C.local_table(self.rank, found_inf),
+                               prereduced=prereduced, local_grad=C.local_table(self.rank, g["reduced"]) if prereduced else None,
+                               blocks=self._blocks(max(g["seg"][r + 1] - g["seg"][r] for r in range(self.world))))
+        if self.P16 is not None:
+            self.P.tensor.copy_(self.P16.tensor)     # local widen of the 16-bit wire copy
+        self._clip_pending = False
+        return loss
+
+    def _is_adamw(self) -> bool:
+        name = self.oss._optim_cls.__name__.lower()
+        return "adamw" in name
+
+    # state dict plumbing (torch layout, per original parameter) ---------------------
+    def local_state_dict(self) -> Dict[str, Any]:
+        state, gmap = {}, []
+        k = 0
+        for g in self.groups:
+            s0 = g["seg"][self.rank]
+            if float(g["step"].item()) == 0.0:
+                for p, off, r in g["entries"]:
+                    if r == self.rank:
+                        gmap.append(self.oss.param_to_index[id(p)])
+                        k += 1
+                continue
+            for p, off, r in g["entries"]:
+                if r != self.rank:
+                    continue
+                lo = off - s0
+                state[k] = {"step": g["step"].detach().clone(),
+                            "exp_avg": g["m"][lo: lo + p.numel()].view(p.shape).clone(),
+                            "exp_avg_sq": g["v"][lo: lo + p.numel()].view(p.shape).clone()}
+                gmap.append(self.oss.param_to_index[id(p)])
+                k += 1
+        return {"state": state, "param_groups": [], "global_index": gmap}
+
+    @torch.no_grad()
+    def load_full_state(self, full_state: Dict[Any, Any]) -> None:
+        for g in self.groups:
+            s0 = g["seg"][self.rank]
+            for p, off, r in g["entries"]:
+                if r != self.rank:
+                    continue
+                gi = self.oss.param_to_index[id(p)]
+                st = full_state.get(gi, full_state.get(str(gi)))
+                lo = off - s0
+                if st is not None:
+                    g["m"][lo: lo + p.numel()].copy_(st["exp_avg"].reshape(-1))
+                    g["v"][lo: lo + p.numel()].copy_(st["exp_avg_sq"].reshape(-1))
+                    g["step"].fill_(float(st["step"]))
+            n = g["seg"][self.rank + 1] - s0
+            g["master"][:n].copy_(self.P.tensor[s0: s0 + n])
+
+    @torch.no_grad()
+    def refresh_master(self) -> None:
+        """Parameters were overwritten from outside (checkpoint load): re-seed the masters."""
+        for g in self.groups:
+            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
+            g["master"][: s1 - s0].copy_(self.P.tensor[s0:s1])
+
+
+# --------------------------------------------------------------------------- attachment
+def _arena_bytes(engine: Any, optim: Any, status: Any) -> int:
+    n_params = sum(p.numel() for p in engine.parameters())
+    if status.fully_sharded:
+        from .fsdp import FullyShardedDataParallel
+        units = [u for u in engine.modules() if isinstance(u, FullyShardedDataParallel) and u.flat_param is not None]
+        total = sum(u._padded for u in units) * 2 + max(u._padded for u in units) * 4 * 2
+        return total + (8 << 20)
+    if status.sharded:
+        return n_params * 4 * 3 + (16 << 20)
+    return n_params * 4 + len(list(engine.parameters())) * 64 + (16 << 20)
+
+
+def attach(engine: Any, optim: Any, status: Any, timeout_s: float = 30.0, **cfg: Any) -> Optional[Any]:
+    """Create the arena for the default group and attach the engine that matches the run."""
+    from .ddp import DistributedDataParallel
+    from .fsdp import FullyShardedDataParallel
+    from .oss import OSS
+    from .sharded_ddp import ShardedDataParallel
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_backend() != "nccl":
+        return None
+    group = dist.group.WORLD
+    world = dist.get_world_size(group)
+    if world < 2 or world > C.MAX_RANKS:
+        return None
+    device = next(engine.parameters()).device
+    arena = PeerArena(group, device, _arena_bytes(engine, optim, status) + (4 << 20), timeout_s=timeout_s)
+    small = SmallAllReduce(arena)
+    peer._STATE["small"] = small
+    peer.set_engine(small)
+    out: Dict[str, Any] = {"arena": arena, "small": small}
+    if isinstance(engine, FullyShardedDataParallel):
+        out["fsdp"] = FSDPPeerEngine(arena, engine)
+    elif isinstance(engine, ShardedDataParallel) and isinstance(optim, OSS):
+        if "adam" not in optim._optim_cls.__name__.lower():
+            return out  # the fused ZeRO step implements Adam/AdamW; other optimizers keep the NCCL path
+        oss_cfg = cfg.get("oss_cfg")
+        wire = torch.float16 if (oss_cfg is not None and oss_cfg.broadcast_fp16) else None
+        out["zero"] = ZeroPeerEngine(arena, optim, engine, wire_dtype=wire)
+    elif isinstance(engine, DistributedDataParallel):
+        out["ddp"] = DDPPeerEngine(arena, engine)
+    return out
