@@ -71,7 +71,12 @@ class PeerArena:
         if end > self.nbytes:
             raise MemoryError(f"peer arena exhausted: need {end} bytes of {self.nbytes}")
         self._off = end
-        t = self.buf[off: off + nbytes].view(dtype)
+        # NOT a view of self.buf: an independent tensor over the same storage, so autograd version
+        # counters of unrelated sub-buffers are not shared (an in-place op on one bucket must not
+        # invalidate views that another engine saved for backward)
+        itemsize = nbytes // max(numel, 1) if numel else 1
+        t = torch.empty(0, dtype=dtype, device=self.device).set_(
+            self.buf.untyped_storage(), (self.buf.storage_offset() + off) // itemsize, (numel,), (1,))
         return SymmBuffer(t, [b + off for b in self.base], (self.mc_base + off) if self.mc_base else 0)
 
     def remaining(self) -> int:
