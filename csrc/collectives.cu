@@ -154,31 +154,47 @@ __device__ __forceinline__ void cta_barrier_all_ranks(const b200dp_peer_ctx& c, 
     __syncthreads();
 }
 
-// Sum over all ranks of 16 bytes at element offset `off` (in elements of T), as floats.
-template <typename T, bool kMC>
-__device__ __forceinline__ void reduce16(const b200dp_peer_ctx& c, const Rank& me, void* const* bufs, const void* mc,
-                                         int64_t off, float* acc) {
+// Sum over all ranks of U x 16 bytes (element offsets off[u], valid where ok[u]) as floats.
+// All loads are issued before the first add so that U x world (P2P) or U (NVLS) 16-byte
+// requests per thread are in flight: NVLink latency is ~2 us, and ~2 MB must be outstanding
+// per GPU to fill the link.  WMAX bounds the peer loop at compile time (registers).
+template <typename T, bool kMC, int WMAX, int U>
+__device__ __forceinline__ void reduce16_batch(const Rank& me, void* const* bufs, const void* mc,
+                                               const int64_t (&off)[U], const bool (&ok)[U],
+                                               float (&acc)[U][Pack<T>::N]) {
     if (kMC) {
-        Pack<T>::unpack(multimem_ld_reduce<T>((const T*)mc + off), acc);
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (ok[u]) v[u] = multimem_ld_reduce<T>((const T*)mc + off[u]);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (ok[u]) Pack<T>::unpack(v[u], acc[u]);
     } else {
+        uint4 v[U][WMAX];
 #pragma unroll
-        for (int k = 0; k < Pack<T>::N; ++k) acc[k] = 0.f;
-        // start with our own copy, then walk the peers in rank order (same order on every
-        // rank for a given element => bitwise identical results across ranks)
-        uint4 v[B200DP_MAX_RANKS];
+        for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int p = 0; p < B200DP_MAX_RANKS; ++p)
-            if (p < me.world) v[p] = ld_peer16((const T*)bufs[p] + off);
+            for (int p = 0; p < WMAX; ++p)
+                if (ok[u] && p < me.world) v[u][p] = ld_peer16((const T*)bufs[p] + off[u]);
+        // peers are added in rank order on every rank => bitwise identical results everywhere
 #pragma unroll
-        for (int p = 0; p < B200DP_MAX_RANKS; ++p)
-            if (p < me.world) {
-                float f[Pack<T>::N];
-                Pack<T>::unpack(v[p], f);
+        for (int u = 0; u < U; ++u) {
 #pragma unroll
-                for (int k = 0; k < Pack<T>::N; ++k) acc[k] += f[k];
-            }
+            for (int k = 0; k < Pack<T>::N; ++k) acc[u][k] = 0.f;
+#pragma unroll
+            for (int p = 0; p < WMAX; ++p)
+                if (ok[u] && p < me.world) {
+                    float f[Pack<T>::N];
+                    Pack<T>::unpack(v[u][p], f);
+#pragma unroll
+                    for (int k = 0; k < Pack<T>::N; ++k) acc[u][k] += f[k];
+                }
+        }
     }
 }
+
+template <bool kMC, int WMAX> struct Unroll { static constexpr int U = kMC ? 8 : (8 / WMAX); };
 
 struct PtrTable { void* p[B200DP_MAX_RANKS]; };
 struct CPtrTable { const void* p[B200DP_MAX_RANKS]; };
@@ -199,39 +215,42 @@ __global__ void __launch_bounds__(kCommThreads) peer_barrier_kernel(b200dp_peer_
 // algo 0: one-shot   every rank reads everything and writes its own copy (small buckets)
 // algo 1: two-shot   rank r reduces slice r, then every rank gathers all slices
 // kMC: NVLS — slice r is reduced in the switch and multicast-stored to every rank
-template <typename T, bool kMC>
+template <typename T, bool kMC, int WMAX>
 __global__ void __launch_bounds__(kCommThreads) peer_allreduce_kernel(
     b200dp_peer_ctx c, PtrTable bufs, void* mc, int64_t n, float pre_mult, CPtrTable mult_dev, PtrTable found_inf,
     int algo) {
     const Rank me(c);
     constexpr int V = Pack<T>::N;
+    constexpr int U = Unroll<kMC, WMAX>::U;
     const int64_t n_vec = n / V;  // n is a multiple of V (buckets are padded)
     const float* md = (const float*)mult_dev.p[me.rank];
     const float mult = pre_mult * (md ? *md : 1.f);
     bool bad = false;
+    T* mine = (T*)bufs.p[me.rank];
     cta_barrier_all_ranks(c, me);  // every rank's bucket is complete and visible
     if (algo == 0 && !kMC) {
         int64_t b, e;
         slice_range(n_vec, gridDim.x, blockIdx.x, b, e);
-        T* out = (T*)bufs.p[me.rank];
         // results go to registers first: nobody may overwrite a bucket while peers still read it
-        for (int64_t i0 = b; i0 < e; i0 += kCommThreads * 4) {
-            float acc[4][V];
+        for (int64_t i0 = b; i0 < e; i0 += (int64_t)kCommThreads * U) {
+            float acc[U][V];
+            int64_t off[U];
+            bool ok[U];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int64_t i = i0 + u * kCommThreads + threadIdx.x;
-                if (i < e) reduce16<T, false>(c, me, bufs.p, nullptr, i * V, acc[u]);
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+                ok[u] = i < e;
+                off[u] = i * V;
             }
+            reduce16_batch<T, false, WMAX, U>(me, bufs.p, nullptr, off, ok, acc);
             cta_barrier_all_ranks(c, me);  // all peers have read this chunk group
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int64_t i = i0 + u * kCommThreads + threadIdx.x;
-                if (i < e) {
+            for (int u = 0; u < U; ++u)
+                if (ok[u]) {
 #pragma unroll
                     for (int k = 0; k < V; ++k) { acc[u][k] *= mult; bad |= !isfinite(acc[u][k]); }
-                    *reinterpret_cast<uint4*>(out + i * V) = Pack<T>::pack(acc[u]);
+                    *reinterpret_cast<uint4*>(mine + off[u]) = Pack<T>::pack(acc[u]);
                 }
-            }
         }
     } else {
         // phase 1: reduce my slice; CTA b owns sub-range b of every slice on every rank
@@ -239,32 +258,54 @@ __global__ void __launch_bounds__(kCommThreads) peer_allreduce_kernel(
         slice_range(n_vec, me.world, me.rank, sb, se);
         slice_range(se - sb, gridDim.x, blockIdx.x, b, e);
         b += sb; e += sb;
-        T* mine = (T*)bufs.p[me.rank];
-        for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
-            float acc[V];
-            reduce16<T, kMC>(c, me, bufs.p, mc, i * V, acc);
+        for (int64_t i0 = b; i0 < e; i0 += (int64_t)kCommThreads * U) {
+            float acc[U][V];
+            int64_t off[U];
+            bool ok[U];
 #pragma unroll
-            for (int k = 0; k < V; ++k) { acc[k] *= mult; bad |= !isfinite(acc[k]); }
-            const uint4 r = Pack<T>::pack(acc);
-            if (kMC) multimem_st((T*)mc + i * V, r);              // lands in every rank's bucket
-            else *reinterpret_cast<uint4*>(mine + i * V) = r;     // slice r of my own bucket
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+                ok[u] = i < e;
+                off[u] = i * V;
+            }
+            reduce16_batch<T, kMC, WMAX, U>(me, bufs.p, mc, off, ok, acc);
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (ok[u]) {
+#pragma unroll
+                    for (int k = 0; k < V; ++k) { acc[u][k] *= mult; bad |= !isfinite(acc[u][k]); }
+                    const uint4 r = Pack<T>::pack(acc[u]);
+                    if (kMC) multimem_st((T*)mc + off[u], r);               // lands in every rank's bucket
+                    else *reinterpret_cast<uint4*>(mine + off[u]) = r;      // slice r of my own bucket
+                }
         }
         cta_barrier_all_ranks(c, me);  // every slice is reduced (and, with NVLS, already delivered)
         if (!kMC) {
-            // phase 2: gather the other slices from their owners
+            // phase 2: gather the other slices from their owners, 4 loads in flight per thread
             for (int p = 1; p < me.world; ++p) {
                 const int src = (me.rank + p) % me.world;
                 slice_range(n_vec, me.world, src, sb, se);
                 slice_range(se - sb, gridDim.x, blockIdx.x, b, e);
                 b += sb; e += sb;
                 const T* from = (const T*)bufs.p[src];
-                for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
-                    const uint4 r = ld_peer16(from + i * V);
-                    float f[V];
-                    Pack<T>::unpack(r, f);
+                for (int64_t i0 = b; i0 < e; i0 += (int64_t)kCommThreads * 4) {
+                    uint4 r[4];
 #pragma unroll
-                    for (int k = 0; k < V; ++k) bad |= !isfinite(f[k]);
-                    *reinterpret_cast<uint4*>(mine + i * V) = r;
+                    for (int u = 0; u < 4; ++u) {
+                        const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+                        if (i < e) r[u] = ld_peer16(from + i * V);
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+                        if (i < e) {
+                            float f[V];
+                            Pack<T>::unpack(r[u], f);
+#pragma unroll
+                            for (int k = 0; k < V; ++k) bad |= !isfinite(f[k]);
+                            *reinterpret_cast<uint4*>(mine + i * V) = r[u];
+                        }
+                    }
                 }
             }
             cta_barrier_all_ranks(c, me);  // nobody still reads a slice its owner may now overwrite
@@ -276,12 +317,13 @@ __global__ void __launch_bounds__(kCommThreads) peer_allreduce_kernel(
 
 // ---------------------------------------------------------------- reduce-scatter (+scale, fp32 shard out)
 // out[rank][i] (=|+=) mult * sum_p in[p][rank*n_per + i]
-template <typename T, bool kMC>
+template <typename T, bool kMC, int WMAX>
 __global__ void __launch_bounds__(kCommThreads) peer_reduce_scatter_kernel(
     b200dp_peer_ctx c, PtrTable in_bufs, void* mc, int64_t n_per, PtrTable outs, float pre_mult, CPtrTable mult_dev,
     PtrTable found_inf, int accumulate) {
     const Rank me(c);
     constexpr int V = Pack<T>::N;
+    constexpr int U = Unroll<kMC, WMAX>::U;
     const int64_t n_vec = n_per / V;
     const float* md = (const float*)mult_dev.p[me.rank];
     const float mult = pre_mult * (md ? *md : 1.f);
@@ -291,24 +333,33 @@ __global__ void __launch_bounds__(kCommThreads) peer_reduce_scatter_kernel(
     int64_t b, e;
     slice_range(n_vec, gridDim.x, blockIdx.x, b, e);
     const int64_t base = (int64_t)me.rank * n_per;
-    for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
-        float acc[V];
-        reduce16<T, kMC>(c, me, in_bufs.p, mc, base + i * V, acc);
+    for (int64_t i0 = b; i0 < e; i0 += (int64_t)kCommThreads * U) {
+        float acc[U][V];
+        int64_t off[U];
+        bool ok[U];
 #pragma unroll
-        for (int k = 0; k < V; ++k) { acc[k] *= mult; bad |= !isfinite(acc[k]); }
-        float* o = out + i * V;
-        if (accumulate) {
-#pragma unroll
-            for (int k = 0; k < V; k += 4) {
-                float4 t = *reinterpret_cast<float4*>(o + k);
-                t.x += acc[k]; t.y += acc[k + 1]; t.z += acc[k + 2]; t.w += acc[k + 3];
-                *reinterpret_cast<float4*>(o + k) = t;
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < V; k += 4)
-                *reinterpret_cast<float4*>(o + k) = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
+        for (int u = 0; u < U; ++u) {
+            const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+            ok[u] = i < e;
+            off[u] = base + i * V;
         }
+        reduce16_batch<T, kMC, WMAX, U>(me, in_bufs.p, mc, off, ok, acc);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (ok[u]) {
+#pragma unroll
+                for (int k = 0; k < V; ++k) { acc[u][k] *= mult; bad |= !isfinite(acc[u][k]); }
+                float* o = out + (off[u] - base);
+#pragma unroll
+                for (int k = 0; k < V; k += 4) {
+                    float4 t = make_float4(acc[u][k], acc[u][k + 1], acc[u][k + 2], acc[u][k + 3]);
+                    if (accumulate) {
+                        const float4 old = *reinterpret_cast<float4*>(o + k);
+                        t.x += old.x; t.y += old.y; t.z += old.z; t.w += old.w;
+                    }
+                    *reinterpret_cast<float4*>(o + k) = t;
+                }
+            }
     }
     cta_barrier_all_ranks(c, me);  // peers are done reading my input: it may be reused
     float* fi = (float*)found_inf.p[me.rank];
@@ -330,8 +381,15 @@ __global__ void __launch_bounds__(kCommThreads) peer_all_gather_kernel(b200dp_pe
     const int64_t base = (int64_t)me.rank * n_per;
     for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
         float f[V];
+        if (sizeof(TI) == 4) {
 #pragma unroll
-        for (int k = 0; k < V; ++k) f[k] = Cvt<TI>::to_f(src[i * V + k]);
+            for (int k = 0; k < V; k += 4) {
+                const float4 t = *reinterpret_cast<const float4*>((const float*)src + i * V + k);
+                f[k] = t.x; f[k + 1] = t.y; f[k + 2] = t.z; f[k + 3] = t.w;
+            }
+        } else {
+            Pack<TO>::unpack(*reinterpret_cast<const uint4*>((const TO*)src + i * V), f);
+        }
         const uint4 r = Pack<TO>::pack(f);
         if (kMC) {
             multimem_st((TO*)mc + base + i * V, r);
@@ -354,13 +412,14 @@ __global__ void __launch_bounds__(kCommThreads) peer_all_gather_kernel(b200dp_pe
 // values into every rank's parameter buffer (multicast store, or one peer store per rank).
 struct SegTable { int64_t s[B200DP_MAX_RANKS + 1]; };
 
-template <typename TW, bool kMC>   // TW: wire / parameter-buffer dtype
+template <typename TW, bool kMC, int WMAX>   // TW: wire / parameter-buffer dtype
 __global__ void __launch_bounds__(kCommThreads) peer_zero_adam_kernel(
     b200dp_peer_ctx c, PtrTable grad_bufs, void* grad_mc, PtrTable param_bufs, void* param_mc, SegTable seg,
     PtrTable master, PtrTable m_tab, PtrTable v_tab, b200dp_adam_hparams hp, CPtrTable step_tab, float pre_mult,
     CPtrTable mult_dev, CPtrTable found_inf, int prereduced, CPtrTable local_grad) {
     const Rank me(c);
     constexpr int V = 4;  // fp32 gradients: 4 per 16 bytes
+    constexpr int U = kMC ? 4 : (WMAX >= 8 ? 1 : 4 / WMAX);   // fewer in flight than the pure reduce: state traffic shares the registers
     const int64_t s0 = seg.s[me.rank], s1 = seg.s[me.rank + 1];
     const int64_t n_vec = (s1 - s0) / V;   // segments are padded to multiples of 8
     const float* md = (const float*)mult_dev.p[me.rank];
@@ -378,64 +437,82 @@ __global__ void __launch_bounds__(kCommThreads) peer_zero_adam_kernel(
     int64_t b, e;
     slice_range(n_vec, gridDim.x, blockIdx.x, b, e);
     if (!skip) {
-        for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
-            float g[V];
+        for (int64_t i0 = b; i0 < e; i0 += (int64_t)kCommThreads * U) {
+            float g[U][V];
+            int64_t off[U];
+            bool ok[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+                ok[u] = i < e;
+                off[u] = s0 + i * V;
+            }
             if (prereduced) {
-                const float4 t = reinterpret_cast<const float4*>((const float*)local_grad.p[me.rank])[i];
-                g[0] = t.x; g[1] = t.y; g[2] = t.z; g[3] = t.w;
-            } else {
-                reduce16<float, kMC>(c, me, grad_bufs.p, grad_mc, s0 + i * V, g);
-            }
-            float4 p4 = reinterpret_cast<float4*>(pm)[i], m4 = reinterpret_cast<float4*>(mm)[i],
-                   v4 = reinterpret_cast<float4*>(vm)[i];
-            float pv[V] = {p4.x, p4.y, p4.z, p4.w}, mv[V] = {m4.x, m4.y, m4.z, m4.w}, vv[V] = {v4.x, v4.y, v4.z, v4.w};
 #pragma unroll
-            for (int k = 0; k < V; ++k) {
-                const float gv = g[k] * mult + l2 * pv[k];
-                pv[k] *= decay;
-                mv[k] = hp.beta1 * mv[k] + (1.f - hp.beta1) * gv;
-                vv[k] = hp.beta2 * vv[k] + (1.f - hp.beta2) * gv * gv;
-                pv[k] -= step_size * (mv[k] / (sqrtf(vv[k]) * inv_sqrt_bc2 + hp.eps));
-            }
-            reinterpret_cast<float4*>(pm)[i] = make_float4(pv[0], pv[1], pv[2], pv[3]);
-            reinterpret_cast<float4*>(mm)[i] = make_float4(mv[0], mv[1], mv[2], mv[3]);
-            reinterpret_cast<float4*>(vm)[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
-            // publish (W3): fp32 wire = one 16-byte store per 4 values; 16-bit wire = 8 bytes
-            if (sizeof(TW) == 4) {
-                const uint4 r = Pack<float>::pack(pv);
-                if (kMC) multimem_st((float*)param_mc + s0 + i * V, r);
-                else {
-#pragma unroll
-                    for (int p = 0; p < B200DP_MAX_RANKS; ++p)
-                        if (p < me.world) st_peer16((float*)param_bufs.p[(me.rank + p) % me.world] + s0 + i * V, r);
-                }
-            } else {
-                TW w[V];
-#pragma unroll
-                for (int k = 0; k < V; ++k) w[k] = Cvt<TW>::from_f(pv[k]);
-                const uint2 r = *reinterpret_cast<const uint2*>(w);
-#pragma unroll
-                for (int p = 0; p < B200DP_MAX_RANKS; ++p)
-                    if (p < me.world) {
-                        TW* dst = (TW*)param_bufs.p[(me.rank + p) % me.world] + s0 + i * V;
-                        asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(dst), "r"(r.x), "r"(r.y) : "memory");
+                for (int u = 0; u < U; ++u)
+                    if (ok[u]) {
+                        const float4 t = *reinterpret_cast<const float4*>((const float*)local_grad.p[me.rank] + (off[u] - s0));
+                        g[u][0] = t.x; g[u][1] = t.y; g[u][2] = t.z; g[u][3] = t.w;
                     }
+            } else {
+                reduce16_batch<float, kMC, WMAX, U>(me, grad_bufs.p, grad_mc, off, ok, g);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!ok[u]) continue;
+                const int64_t li = off[u] - s0;     // element index inside the owned segment
+                float4 p4 = *reinterpret_cast<float4*>(pm + li), m4 = *reinterpret_cast<float4*>(mm + li),
+                       v4 = *reinterpret_cast<float4*>(vm + li);
+                float pv[V] = {p4.x, p4.y, p4.z, p4.w}, mv[V] = {m4.x, m4.y, m4.z, m4.w}, vv[V] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+                for (int k = 0; k < V; ++k) {
+                    const float gv = g[u][k] * mult + l2 * pv[k];
+                    pv[k] *= decay;
+                    mv[k] = hp.beta1 * mv[k] + (1.f - hp.beta1) * gv;
+                    vv[k] = hp.beta2 * vv[k] + (1.f - hp.beta2) * gv * gv;
+                    pv[k] -= step_size * (mv[k] / (sqrtf(vv[k]) * inv_sqrt_bc2 + hp.eps));
+                }
+                *reinterpret_cast<float4*>(pm + li) = make_float4(pv[0], pv[1], pv[2], pv[3]);
+                *reinterpret_cast<float4*>(mm + li) = make_float4(mv[0], mv[1], mv[2], mv[3]);
+                *reinterpret_cast<float4*>(vm + li) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+                // publish (W3): fp32 wire = one 16-byte store per 4 values; 16-bit wire = 8 bytes
+                if (sizeof(TW) == 4) {
+                    const uint4 r = Pack<float>::pack(pv);
+                    if (kMC) multimem_st((float*)param_mc + off[u], r);
+                    else {
+#pragma unroll
+                        for (int p = 0; p < WMAX; ++p)
+                            if (p < me.world) st_peer16((float*)param_bufs.p[(me.rank + p) % me.world] + off[u], r);
+                    }
+                } else {
+                    TW w[V];
+#pragma unroll
+                    for (int k = 0; k < V; ++k) w[k] = Cvt<TW>::from_f(pv[k]);
+                    const uint2 r = *reinterpret_cast<const uint2*>(w);
+#pragma unroll
+                    for (int p = 0; p < WMAX; ++p)
+                        if (p < me.world) {
+                            TW* dst = (TW*)param_bufs.p[(me.rank + p) % me.world] + off[u];
+                            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(dst), "r"(r.x), "r"(r.y) : "memory");
+                        }
+                }
             }
         }
     }
     cta_barrier_all_ranks(c, me);   // every rank's parameters are complete; gradients are free again
 }
 
-// reduce-to-owner only (used when clipping needs the global norm before the update):
-// local_out[rank][i] = mult * sum_p grad[p][seg[rank]+i]; per-CTA sum of squares -> partials
+// reduce-to-owner only (used when clipping / AMP need the global norm and inf flag before the
+// update): local_out[rank][i] = mult * sum_p grad[p][seg[rank]+i]; sum of squares -> norm_out
+template <int WMAX>
 __global__ void __launch_bounds__(kCommThreads) peer_reduce_to_owner_kernel(
     b200dp_peer_ctx c, PtrTable grad_bufs, SegTable seg, PtrTable local_out, float pre_mult, CPtrTable mult_dev,
-    PtrTable norm_out /* [sumsq, found_inf] per rank, accumulated with atomics-free last-CTA scheme */,
-    PtrTable partials, PtrTable counters) {
+    PtrTable norm_out, PtrTable partials, PtrTable counters) {
     __shared__ float red[32];
     __shared__ bool is_last;
     const Rank me(c);
     constexpr int V = 4;
+    constexpr int U = Unroll<false, WMAX>::U;
     const int64_t s0 = seg.s[me.rank], s1 = seg.s[me.rank + 1];
     const int64_t n_vec = (s1 - s0) / V;
     const float* md = (const float*)mult_dev.p[me.rank];
@@ -446,12 +523,24 @@ __global__ void __launch_bounds__(kCommThreads) peer_reduce_to_owner_kernel(
     slice_range(n_vec, gridDim.x, blockIdx.x, b, e);
     float acc2 = 0.f;
     bool bad = false;
-    for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
-        float g[V];
-        reduce16<float, false>(c, me, grad_bufs.p, nullptr, s0 + i * V, g);
+    for (int64_t i0 = b; i0 < e; i0 += (int64_t)kCommThreads * U) {
+        float g[U][V];
+        int64_t off[U];
+        bool ok[U];
 #pragma unroll
-        for (int k = 0; k < V; ++k) { g[k] *= mult; bad |= !isfinite(g[k]); acc2 += g[k] * g[k]; }
-        reinterpret_cast<float4*>(out)[i] = make_float4(g[0], g[1], g[2], g[3]);
+        for (int u = 0; u < U; ++u) {
+            const int64_t i = i0 + (int64_t)u * kCommThreads + threadIdx.x;
+            ok[u] = i < e;
+            off[u] = s0 + i * V;
+        }
+        reduce16_batch<float, false, WMAX, U>(me, grad_bufs.p, nullptr, off, ok, g);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (ok[u]) {
+#pragma unroll
+                for (int k = 0; k < V; ++k) { g[u][k] *= mult; bad |= !isfinite(g[u][k]); acc2 += g[u][k] * g[u][k]; }
+                *reinterpret_cast<float4*>(out + (off[u] - s0)) = make_float4(g[u][0], g[u][1], g[u][2], g[u][3]);
+            }
     }
     cta_barrier_all_ranks(c, me);
     const float tot = block_sum(acc2, red);
@@ -552,10 +641,13 @@ int b200dp_peer_allreduce(const b200dp_peer_ctx* ctx, void* const* bufs, void* m
     PtrTable tb, tf; CPtrTable tm;
     fill(tb, bufs); fill(tf, found_inf); fill(tm, mult_dev);
     cudaStream_t s = (cudaStream_t)stream;
-    B200DP_DISPATCH_DTYPE(dtype, T, {
-        if (mc != nullptr) rc = launch_comm(peer_allreduce_kernel<T, true>, *ctx, blocks, s, *ctx, tb, mc, n, pre_mult, tm, tf, 1);
-        else rc = launch_comm(peer_allreduce_kernel<T, false>, *ctx, blocks, s, *ctx, tb, mc, n, pre_mult, tm, tf, algo);
-    });
+#define AR(W)                                                                                                        \
+    B200DP_DISPATCH_DTYPE(dtype, T, {                                                                               \
+        if (mc != nullptr) rc = launch_comm(peer_allreduce_kernel<T, true, W>, *ctx, blocks, s, *ctx, tb, mc, n, pre_mult, tm, tf, 1); \
+        else rc = launch_comm(peer_allreduce_kernel<T, false, W>, *ctx, blocks, s, *ctx, tb, mc, n, pre_mult, tm, tf, algo); \
+    })
+    if (ctx->world <= 2) { AR(2); } else if (ctx->world <= 4) { AR(4); } else { AR(8); }
+#undef AR
     return rc;
 }
 
@@ -570,10 +662,13 @@ int b200dp_peer_reduce_scatter(const b200dp_peer_ctx* ctx, void* const* in_bufs,
     PtrTable ti, to, tf; CPtrTable tm;
     fill(ti, in_bufs); fill(to, outs); fill(tf, found_inf); fill(tm, mult_dev);
     cudaStream_t s = (cudaStream_t)stream;
-    B200DP_DISPATCH_DTYPE(dtype, T, {
-        if (mc != nullptr) rc = launch_comm(peer_reduce_scatter_kernel<T, true>, *ctx, blocks, s, *ctx, ti, mc, n_per_rank, to, pre_mult, tm, tf, accumulate);
-        else rc = launch_comm(peer_reduce_scatter_kernel<T, false>, *ctx, blocks, s, *ctx, ti, mc, n_per_rank, to, pre_mult, tm, tf, accumulate);
-    });
+#define RS(W)                                                                                                        \
+    B200DP_DISPATCH_DTYPE(dtype, T, {                                                                               \
+        if (mc != nullptr) rc = launch_comm(peer_reduce_scatter_kernel<T, true, W>, *ctx, blocks, s, *ctx, ti, mc, n_per_rank, to, pre_mult, tm, tf, accumulate); \
+        else rc = launch_comm(peer_reduce_scatter_kernel<T, false, W>, *ctx, blocks, s, *ctx, ti, mc, n_per_rank, to, pre_mult, tm, tf, accumulate); \
+    })
+    if (ctx->world <= 2) { RS(2); } else if (ctx->world <= 4) { RS(4); } else { RS(8); }
+#undef RS
     return rc;
 }
 
@@ -621,10 +716,13 @@ int b200dp_peer_zero_adam(const b200dp_peer_ctx* ctx, void* const* grad_bufs, vo
     cudaStream_t s = (cudaStream_t)stream;
     const bool mc = (grad_mc != nullptr || prereduced) && param_mc != nullptr && wire_dtype == B200DP_F32 && !ctx->emulate &&
                     (prereduced || grad_mc != nullptr);
-#define ZA(TW, MC) rc = launch_comm(peer_zero_adam_kernel<TW, MC>, *ctx, blocks, s, *ctx, tg, grad_mc, tp, param_mc, st, tma, tm_, tv, hp, ts, pre_mult, tmu, tfi, prereduced, tlg)
-    if (wire_dtype == B200DP_F32) { if (mc) { ZA(float, true); } else { ZA(float, false); } }
-    else if (wire_dtype == B200DP_F16) { ZA(__half, false); }
-    else { ZA(__nv_bfloat16, false); }
+#define ZA(TW, MC, W) rc = launch_comm(peer_zero_adam_kernel<TW, MC, W>, *ctx, blocks, s, *ctx, tg, grad_mc, tp, param_mc, st, tma, tm_, tv, hp, ts, pre_mult, tmu, tfi, prereduced, tlg)
+#define ZAW(W)                                                                              \
+    if (wire_dtype == B200DP_F32) { if (mc) { ZA(float, true, W); } else { ZA(float, false, W); } } \
+    else if (wire_dtype == B200DP_F16) { ZA(__half, false, W); }                            \
+    else { ZA(__nv_bfloat16, false, W); }
+    if (ctx->world <= 2) { ZAW(2) } else if (ctx->world <= 4) { ZAW(4) } else { ZAW(8) }
+#undef ZAW
 #undef ZA
     return rc;
 }
@@ -640,7 +738,10 @@ int b200dp_peer_reduce_to_owner(const b200dp_peer_ctx* ctx, void* const* grad_bu
     for (int i = 0; i <= B200DP_MAX_RANKS; ++i) st.s[i] = i <= ctx->world ? seg[i] : seg[ctx->world];
     PtrTable tg, tl, tn, tpa, tc; CPtrTable tmu;
     fill(tg, grad_bufs); fill(tl, local_out); fill(tn, norm_out); fill(tpa, partials); fill(tc, counters); fill(tmu, mult_dev);
-    return launch_comm(peer_reduce_to_owner_kernel, *ctx, blocks, (cudaStream_t)stream, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (ctx->world <= 2) return launch_comm(peer_reduce_to_owner_kernel<2>, *ctx, blocks, s, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
+    if (ctx->world <= 4) return launch_comm(peer_reduce_to_owner_kernel<4>, *ctx, blocks, s, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
+    return launch_comm(peer_reduce_to_owner_kernel<8>, *ctx, blocks, s, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
 }
 
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
