@@ -1,0 +1,387 @@
+// bf16 / fp16 GEMM on the 5th-generation tensor cores (W7 for 1x1 convolutions, K17 for
+// linears, and the compute half of W4).
+//
+//   C[M, N] (+bias[N]) = A(M x K) * B(N x K)^T,   fp32 accumulation in TMEM
+//
+// Each operand may be "K-major" (the reduction index is the contiguous one in global memory)
+// or "MN-major" (the output index is contiguous).  That covers forward, dgrad and wgrad of a
+// linear layer with no transposes:
+//     forward  Y[M,N]  = X[M,K]  W[N,K]^T     A = X  (K-major),   B = W  (K-major)
+//     dgrad    dX[M,K] = dY[M,N] W[N,K]       A = dY (K-major),   B = W  (MN-major)
+//     wgrad    dW[N,K] = dY[M,N]^T X[M,K]     A = dY (MN-major),  B = X  (MN-major)
+//
+// Structure (one CTA per SM, persistent over 128 x BN output tiles):
+//   warp 0      TMA producer: cp.async.bulk.tensor into a kStages-deep ring of 128B-swizzled
+//               smem tiles, completion signalled on "full" mbarriers (complete_tx bytes)
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma (M=128, N=BN, K=16) reading smem
+//               through UMMA descriptors, accumulating into one of two TMEM buffers;
+//               tcgen05.commit releases the smem stage ("empty") and finally hands the
+//               accumulator to the epilogue ("tmem_full")
+//   warp 2      allocates / frees the 2*BN TMEM columns
+//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp per step) -> bias ->
+//               16-bit pack -> 16-byte global stores; releases the accumulator ("tmem_empty")
+// The two accumulator buffers let the epilogue of tile i overlap the MMAs of tile i+1.
+// Ragged M / N / K edges: TMA zero-fills out-of-bounds reads, the epilogue masks the stores.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include "common.cuh"
+
+namespace b200dp {
+namespace gemm {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;          // 64 x 2 B = one 128-byte swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kThreads = 256;
+constexpr int kEpiWarp0 = 4;
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tm) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// UMMA shared-memory descriptor, 128-byte swizzle (SM100 format: version 1 in bits 46-47,
+// layout type 2 in bits 61-63; addresses and offsets in 16-byte units).
+//   K-major : rows of 128 B (64 elements of K); 8 rows form one 1024 B swizzle atom; SBO is the
+//             distance between 8-row groups (1024 B); LBO is unused (1).
+//   MN-major: each K index is a row of 128 B (64 elements of M/N); 8 K-rows form the atom;
+//             SBO = distance between 8-K groups (1024 B), LBO = distance between 64-wide M/N blocks.
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// Instruction descriptor for kind::f16: fp32 accumulate, A/B format (0 = fp16, 1 = bf16), majors, N>>3, M>>4.
+__host__ __device__ constexpr uint32_t make_idesc(int bf16, int a_mn, int b_mn, int M, int N) {
+    return (1u << 4) | ((uint32_t)bf16 << 7) | ((uint32_t)bf16 << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+           ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <int BN> struct Cfg {
+    static constexpr int kStages = BN == 256 ? 4 : 6;
+    static constexpr int kABytes = kBM * kBK * 2;   // 16 KB
+    static constexpr int kBBytes = BN * kBK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int kTmemCols = 2 * BN;        // two accumulators (power of two: 256 / 512)
+};
+
+template <int BN, bool kAMN, bool kBMN, typename TOut>
+__global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                           const __grid_constant__ CUtensorMap tmB, TOut* __restrict__ C,
+                                                           const float* __restrict__ bias, int M, int N, int K, int ldc,
+                                                           int is_bf16, int accumulate_c) {
+    using cfg = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemA = smem;
+    uint8_t* smemB = smem + cfg::kStages * cfg::kABytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + cfg::kStages * cfg::kStageBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + cfg::kStages;
+    uint64_t* tmem_full = bars + 2 * cfg::kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = (M + kBM - 1) / kBM, num_n = (N + BN - 1) / BN;
+    const int num_tiles = num_m * num_n;
+    const int num_kb = (K + kBK - 1) / kBK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < cfg::kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, cfg::kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile % num_m) * kBM, n0 = (tile / num_m) * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty + stage, phase ^ 1);
+                    mbar_expect_tx(full + stage, cfg::kStageBytes);
+                    uint8_t* a = smemA + stage * cfg::kABytes;
+                    uint8_t* b = smemB + stage * cfg::kBBytes;
+                    const int k0 = kb * kBK;
+                    if (kAMN) {
+#pragma unroll
+                        for (int j = 0; j < kBM / 64; ++j) tma_load_2d(a + j * (kBK * 128), &tmA, full + stage, m0 + j * 64, k0);
+                    } else {
+                        tma_load_2d(a, &tmA, full + stage, k0, m0);
+                    }
+                    if (kBMN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j) tma_load_2d(b + j * (kBK * 128), &tmB, full + stage, n0 + j * 64, k0);
+                    } else {
+                        tma_load_2d(b, &tmB, full + stage, k0, n0);
+                    }
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, kAMN ? 1 : 0, kBMN ? 1 : 0, kBM, BN);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full + stage, phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smemA + stage * cfg::kABytes);
+                    const uint32_t b_addr = smem_u32(smemB + stage * cfg::kBBytes);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k) {
+                        const uint64_t da = kAMN ? make_desc(a_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                 : make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
+                        const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                 : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
+                        umma_f16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(empty + stage);            // smem stage reusable once these MMAs retire
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tmem_full + acc);              // accumulator complete
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===== epilogue =====
+        const int quarter = warp - kEpiWarp0;              // TMEM lanes [32q, 32q+32) belong to warp q (mod 4)
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int m0 = (tile % num_m) * kBM, n0 = (tile / num_m) * BN;
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            const int row = m0 + quarter * 32 + lane;
+            TOut* crow = C + (size_t)row * ldc;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c * 32, r);
+                tmem_ld_wait();
+                const int col0 = n0 + c * 32;
+                if (row < M && col0 < N) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    if (bias != nullptr) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (col0 + j < N) ? __ldg(bias + col0 + j) : 0.f;
+                    }
+                    if (col0 + 32 <= N && (ldc % 8) == 0) {
+                        if (accumulate_c) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) v[j] += Cvt<TOut>::to_f(crow[col0 + j]);
+                        }
+                        if (sizeof(TOut) == 2) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 8) {
+                                float t[8] = {v[j], v[j + 1], v[j + 2], v[j + 3], v[j + 4], v[j + 5], v[j + 6], v[j + 7]};
+                                store8<TOut>(crow + col0 + j, t);
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4)
+                                *reinterpret_cast<float4*>((float*)crow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        }
+                    } else {
+                        for (int j = 0; j < 32 && col0 + j < N; ++j) {
+                            float o = v[j];
+                            if (accumulate_c) o += Cvt<TOut>::to_f(crow[col0 + j]);
+                            crow[col0 + j] = Cvt<TOut>::from_f(o);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + acc);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, cfg::kTmemCols);
+}
+
+// ---------------------------------------------------------------- host: tensor maps
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    }
+    return fn;
+}
+
+// 2-D row-major tensor [rows][cols] of 16-bit elements, row pitch ld elements; box = {box_cols, box_rows}
+static int make_tmap(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+                     int box_rows) {
+    auto enc = get_encode();
+    B200DP_REQUIRE(enc != nullptr, "gemm: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapDataType dt = is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    CUresult r = enc(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r == CUDA_ERROR_INVALID_CONTEXT || r == CUDA_ERROR_NOT_INITIALIZED) {
+        // called from a thread that has only used the runtime API lazily (e.g. an autograd worker):
+        // bind the primary context of the current device to this thread, then retry
+        cudaFree(nullptr);
+        r = enc(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    B200DP_REQUIRE(r == CUDA_SUCCESS, "gemm: cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld ld=%lld", (int)r,
+                   (long long)rows, (long long)cols, (long long)ld);
+    return 0;
+}
+
+template <int BN, bool kAMN, bool kBMN, typename TOut>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* C, const float* bias, int M, int N, int K, int ldc,
+                  int is_bf16, int accumulate_c, int sms, cudaStream_t s) {
+    auto kern = gemm_kernel<BN, kAMN, kBMN, TOut>;
+    static bool configured = false;
+    if (!configured) {
+        B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
+        configured = true;
+    }
+    const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+    const int grid = tiles < sms ? tiles : sms;
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, (TOut*)C, bias, M, N, K, ldc, is_bf16, accumulate_c);
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace gemm
+}  // namespace b200dp
+
+using namespace b200dp;
+using namespace b200dp::gemm;
+
+// C[M,N] (+)= A * B^T (+ bias).  a_mn / b_mn: 0 = operand is K-major ([rows][K], K contiguous),
+// 1 = MN-major ([K][rows], rows contiguous).  lda / ldb are the row pitches (elements) of the
+// arrays as stored.  out_dtype: B200DP_F16 / B200DP_BF16 (same as the inputs) or B200DP_F32.
+extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
+                           int ldc, int a_mn, int b_mn, b200dp_dtype in_dtype, b200dp_dtype out_dtype, int accumulate_c,
+                           void* stream) {
+    B200DP_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "gemm: bad arguments");
+    B200DP_REQUIRE(in_dtype == B200DP_F16 || in_dtype == B200DP_BF16, "gemm: inputs must be fp16 or bf16");
+    B200DP_REQUIRE(out_dtype == in_dtype || out_dtype == B200DP_F32, "gemm: output must match the inputs or be fp32");
+    B200DP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda / ldb must be multiples of 8 elements (16-byte TMA strides)");
+    B200DP_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: A and B must be 16-byte aligned");
+    const int is_bf16 = in_dtype == B200DP_BF16;
+    const int BN = (N >= 256 && (int64_t)M * N >= (int64_t)148 * 128 * 256) ? 256 : 128;
+    CUtensorMap ta, tb;
+    int rc;
+    // K-major operand [rows][K]: box = 64 (K) x tile rows.  MN-major [K][rows]: box = 64 (rows) x 64 (K).
+    rc = a_mn ? make_tmap(&ta, A, is_bf16, K, M, lda, 64, kBK) : make_tmap(&ta, A, is_bf16, M, K, lda, kBK, kBM);
+    if (rc) return rc;
+    rc = b_mn ? make_tmap(&tb, B, is_bf16, K, N, ldb, 64, kBK) : make_tmap(&tb, B, is_bf16, N, K, ldb, kBK, BN);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int sms = B200DP_SMS;
+#define GO(BNv, AM, BM_, T) return launch<BNv, AM, BM_, T>(ta, tb, C, bias, M, N, K, ldc, is_bf16, accumulate_c, sms, s)
+#define BY_OUT(BNv, AM, BM_)                                                      \
+    if (out_dtype == B200DP_F32) { GO(BNv, AM, BM_, float); }                     \
+    else if (is_bf16) { GO(BNv, AM, BM_, __nv_bfloat16); }                        \
+    else { GO(BNv, AM, BM_, __half); }
+#define BY_MAJOR(BNv)                                                             \
+    if (!a_mn && !b_mn) { BY_OUT(BNv, false, false) }                             \
+    else if (!a_mn && b_mn) { BY_OUT(BNv, false, true) }                          \
+    else if (a_mn && b_mn) { BY_OUT(BNv, true, true) }                            \
+    else { BY_OUT(BNv, true, false) }
+    if (BN == 256) { BY_MAJOR(256) } else { BY_MAJOR(128) }
+#undef BY_MAJOR
+#undef BY_OUT
+#undef GO
+    return 0;
+}

@@ -189,6 +189,21 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
                          const float* gamma, const float* mean, const float* rstd, float* scratch,
                          unsigned int* counter, float* dgamma, float* dbeta, void* stream);
 
+/* ------------------------------------------------------------------ tensor-core GEMM (tcgen05 / TMEM / TMA)
+ * C[M,N] (+)= A(MxK) * B(NxK)^T (+ bias[N]), 16-bit inputs, fp32 accumulation in TMEM.
+ *   a_mn / b_mn = 0: operand stored [rows][K] (K contiguous);  = 1: stored [K][rows] (rows
+ *   contiguous) — so forward, dgrad and wgrad of a linear layer need no transposes:
+ *     forward  Y  = X W^T      gemm(X,  W, M=rows, N=out, K=in,   a_mn=0, b_mn=0)
+ *     dgrad    dX = dY W       gemm(dY, W, M=rows, N=in,  K=out,  a_mn=0, b_mn=1)
+ *     wgrad    dW = dY^T X     gemm(dY, X, M=out,  N=in,  K=rows, a_mn=1, b_mn=1)
+ *   lda / ldb: row pitch in elements of A / B as stored (multiples of 8); ldc likewise for C.
+ *   out_dtype: the input dtype or B200DP_F32.  accumulate_c: C += instead of C =.
+ * Reference: the linear layers of the transformer models (Stoke-DDP.py:206-208) and the 1x1
+ * convolutions of the CNNs, which the reference leaves to cuBLAS / cuDNN. */
+int b200dp_gemm(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
+                int ldc, int a_mn, int b_mn, b200dp_dtype in_dtype, b200dp_dtype out_dtype, int accumulate_c,
+                void* stream);
+
 /* ------------------------------------------------------------------ peer-memory collectives
  * One kernel per rank; ranks meet at flag barriers in peer-mapped memory (csrc/collectives.cu
  * explains the protocol).  Every buffer argument is a table of B200DP_MAX_RANKS pointers:

@@ -62,7 +62,8 @@ def ln_supported(mod: Any, x: torch.Tensor) -> bool:
 
 
 def linear_supported(mod: Any, x: torch.Tensor) -> bool:
-    """tcgen05 GEMM envelope: fp16/bf16 compute (directly or under autocast), K % 64 == 0, N % 16 == 0."""
+    """tcgen05 GEMM envelope: fp16/bf16 compute (directly or under autocast), in/out features % 8 == 0
+    (16-byte TMA row pitches); ragged M/N/K tile edges are handled in the kernel."""
     if not (enabled("gemm") and _lib_ok()):
         return False
     from . import gemm
@@ -71,7 +72,7 @@ def linear_supported(mod: Any, x: torch.Tensor) -> bool:
     dt = _autocast_dtype(x)
     if dt not in _HALF:
         return False
-    return mod.in_features % 64 == 0 and mod.out_features % 16 == 0
+    return mod.in_features % 8 == 0 and mod.out_features % 8 == 0
 
 
 def conv_supported(mod: Any, x: torch.Tensor) -> bool:

@@ -103,6 +103,18 @@ class _FusedBase(Optimizer):
             return total
         return self.fused_unscale_clip(None, max_norm, None)
 
+    @staticmethod
+    def _bump_versions(params: List[torch.Tensor]) -> None:
+        """The kernels write parameters through raw pointers; tell autograd they changed."""
+        try:
+            torch.autograd.graph.increment_version(params)
+        except Exception:  # pragma: no cover - older torch: per-tensor signature
+            for p in params:
+                try:
+                    torch.autograd.graph.increment_version(p)
+                except Exception:
+                    return
+
     def _consume_grad_mult(self) -> Optional[torch.Tensor]:
         if getattr(self, "_use_grad_mult", False):
             self._use_grad_mult = False
@@ -172,6 +184,7 @@ class FusedAdamW(_FusedBase):
                                    float(group["weight_decay"]), self._adamw, int(bool(group.get("maximize", False))))
             fused.step_advance(step_t, found_inf)
             fused.multi_adam(tl, grads[0].dtype, torch.float16, hp, step_t, grad_mult, found_inf)
+            self._bump_versions(params)
         return loss
 
     def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
@@ -241,6 +254,7 @@ class FusedSGD(_FusedBase):
                 hp = fused.SGDHParams(float(group["lr"]), mom, float(group["dampening"]), float(group["weight_decay"]),
                                       int(bool(group["nesterov"])), int(bool(group.get("maximize", False))))
                 fused.multi_sgd(tl, grads[0].dtype, torch.float16, hp, first, grad_mult, found_inf)
+                self._bump_versions(ps)
         return loss
 
     def load_state_dict(self, state_dict: Dict[str, Any]) -> None:

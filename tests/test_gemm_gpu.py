@@ -1,0 +1,83 @@
+"""tcgen05 GEMM vs a plain PyTorch fp32 matmul of the same 16-bit operands."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+cuda = torch.device("cuda")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _lib():
+    from pytorch_distributedtraining_b200.ops import require_library
+    require_library()
+
+
+def _mk(rows, cols, dtype, seed):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(rows, cols, generator=g) * 0.5).to(dtype).to(cuda)
+
+
+SHAPES = [(128, 128, 64), (256, 256, 256), (512, 384, 192), (200, 136, 72), (1000, 1000, 520), (8, 8, 8),
+          (4096, 768, 3072), (197 * 8, 2304, 768), (130, 264, 4104)]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+def test_gemm_matches_fp32_reference(dtype, M, N, K, a_mn, b_mn):
+    from pytorch_distributedtraining_b200.ops.gemm import gemm
+    a = _mk(K, M, dtype, 1) if a_mn else _mk(M, K, dtype, 1)
+    b = _mk(K, N, dtype, 2) if b_mn else _mk(N, K, dtype, 2)
+    if (a.shape[1] % 8) or (b.shape[1] % 8):
+        pytest.skip("row pitch must be a multiple of 8 elements")
+    A = a.float().t() if a_mn else a.float()
+    B = b.float().t() if b_mn else b.float()
+    want = A @ B.t()
+    got = gemm(a, b, M, N, K, a_mn=a_mn, b_mn=b_mn)
+    torch.cuda.synchronize()
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * max(1.0, K ** 0.5 * 0.25))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_gemm_bias_fp32_out_and_accumulate(dtype):
+    from pytorch_distributedtraining_b200.ops.gemm import gemm
+    M, N, K = 300, 264, 136
+    a, b = _mk(M, K, dtype, 3), _mk(N, K, dtype, 4)
+    bias = torch.randn(N, device=cuda)
+    want = a.float() @ b.float().t() + bias
+    got = gemm(a, b, M, N, K, bias=bias, out_dtype=torch.float32)
+    torch.testing.assert_close(got, want, rtol=1e-3, atol=1e-3)
+    out = torch.ones(M, N, device=cuda)
+    gemm(a, b, M, N, K, out=out, accumulate=True)
+    torch.testing.assert_close(out, 1.0 + a.float() @ b.float().t(), rtol=1e-3, atol=1e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape,out_f", [((4, 197, 768), 3072), ((64, 512), 1000), ((3, 5, 7, 64), 24)])
+def test_linear_layer_forward_backward(dtype, shape, out_f):
+    from pytorch_distributedtraining_b200.ops.layers import Linear
+    torch.manual_seed(0)
+    lin = Linear(shape[-1], out_f).to(cuda)
+    x = torch.randn(*shape, device=cuda, requires_grad=True)
+    xr = x.detach().clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=dtype):
+        y = lin(x)
+    assert y.dtype == dtype
+    # reference: the same 16-bit rounding of inputs, fp32 math
+    w16, x16 = lin.weight.detach().to(dtype).float(), xr.to(dtype).float()
+    yr = F.linear(x16, w16, lin.bias.detach())
+    tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
+    torch.testing.assert_close(y.float(), yr, rtol=tol, atol=tol)
+    g = torch.randn_like(yr)
+    y.backward(g.to(dtype))
+    g16 = g.to(dtype).float()
+    dx = g16 @ w16
+    dw = g16.reshape(-1, out_f).t() @ x16.reshape(-1, shape[-1])
+    db = g16.reshape(-1, out_f).sum(0)
+    rows = x16.reshape(-1, shape[-1]).shape[0]
+    torch.testing.assert_close(x.grad, dx.view_as(x), rtol=tol, atol=tol * out_f ** 0.5)
+    torch.testing.assert_close(lin.weight.grad, dw, rtol=tol, atol=tol * rows ** 0.5)
+    torch.testing.assert_close(lin.bias.grad, db, rtol=tol, atol=tol * rows ** 0.5)
+    assert lin.weight.grad.dtype == torch.float32
