@@ -18,8 +18,10 @@
 //               tcgen05.commit releases the smem stage ("empty") and finally hands the
 //               accumulator to the epilogue ("tmem_full")
 //   warp 2      allocates / frees the 2*BN TMEM columns
-//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp per step) -> bias ->
-//               16-bit pack -> 16-byte global stores; releases the accumulator ("tmem_empty")
+//   warps 4-7   epilogue: tcgen05.ld (32 lanes x 32 columns per warp per step) -> bias -> pack ->
+//               128B-swizzled smem staging (double-buffered per warp) -> TMA store (or TMA
+//               reduce-add when accumulating into C); releases the accumulator ("tmem_empty")
+//               as soon as the tile has left TMEM
 // The two accumulator buffers let the epilogue of tile i overlap the MMAs of tile i+1.
 // Ragged M / N / K edges: TMA zero-fills out-of-bounds reads, the epilogue masks the stores.
 #include <cuda.h>
@@ -125,25 +127,43 @@ __host__ __device__ constexpr uint32_t make_idesc(int bf16, int a_mn, int b_mn, 
 }
 
 template <int BN> struct Cfg {
-    static constexpr int kStages = BN == 256 ? 4 : 6;
+    static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 5 : 7);
     static constexpr int kABytes = kBM * kBK * 2;   // 16 KB
     static constexpr int kBBytes = BN * kBK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
-    static constexpr int kTmemCols = 2 * BN;        // two accumulators (power of two: 256 / 512)
+    static constexpr int kEpiBufBytes = 32 * 128;   // 32 rows x 128 B per staging buffer
+    static constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;   // 4 warps x double buffer
+    static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int kTmemCols = 2 * BN;        // two accumulators (power of two: 128 / 256 / 512)
 };
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, const void* smem_src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(tm), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* tm, const void* smem_src, int c0, int c1) {
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(tm), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 template <int BN, bool kAMN, bool kBMN, typename TOut>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                           const __grid_constant__ CUtensorMap tmB, TOut* __restrict__ C,
-                                                           const float* __restrict__ bias, int M, int N, int K, int ldc,
+                                                           const __grid_constant__ CUtensorMap tmB,
+                                                           const __grid_constant__ CUtensorMap tmC,
+                                                           const float* __restrict__ bias, int M, int N, int K,
                                                            int is_bf16, int accumulate_c) {
     using cfg = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* smemA = smem;
     uint8_t* smemB = smem + cfg::kStages * cfg::kABytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + cfg::kStages * cfg::kStageBytes);
+    uint8_t* smemC = smem + cfg::kStages * cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + cfg::kEpiBytes);
     uint64_t* full = bars;
     uint64_t* empty = bars + cfg::kStages;
     uint64_t* tmem_full = bars + 2 * cfg::kStages;
@@ -158,6 +178,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmC);
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < cfg::kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
@@ -231,57 +252,69 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     } else if (warp >= kEpiWarp0) {
         // ===== epilogue =====
         const int quarter = warp - kEpiWarp0;              // TMEM lanes [32q, 32q+32) belong to warp q (mod 4)
+        constexpr int kChunkCols = 128 / (int)sizeof(TOut);     // columns per 128-byte staging row
+        constexpr int kLoadsPerChunk = kChunkCols / 32;         // tcgen05.ld.x32 per chunk (2 for 16-bit, 1 for fp32)
+        uint8_t* my_stage = smemC + quarter * 2 * cfg::kEpiBufBytes;
         int acc = 0; uint32_t acc_phase = 0;
+        uint32_t buf_idx = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const int m0 = (tile % num_m) * kBM, n0 = (tile / num_m) * BN;
             mbar_wait(tmem_full + acc, acc_phase);
             tc_fence_after();
-            const int row = m0 + quarter * 32 + lane;
-            TOut* crow = C + (size_t)row * ldc;
+            const int row0 = m0 + quarter * 32;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                uint32_t r[32];
-                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c * 32, r);
-                tmem_ld_wait();
-                const int col0 = n0 + c * 32;
-                if (row < M && col0 < N) {
+            for (int ch = 0; ch < BN / kChunkCols; ++ch) {
+                uint8_t* buf = my_stage + (buf_idx & 1) * cfg::kEpiBufBytes;
+                // the TMA store that last read this buffer (two chunks ago) must have drained it
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+#pragma unroll
+                for (int l = 0; l < kLoadsPerChunk; ++l) {
+                    uint32_t r[32];
+                    const int colbase = ch * kChunkCols + l * 32;
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + colbase, r);
+                    tmem_ld_wait();
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
                     if (bias != nullptr) {
+                        const int gcol = n0 + colbase;
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] += (col0 + j < N) ? __ldg(bias + col0 + j) : 0.f;
+                        for (int j = 0; j < 32; ++j) v[j] += (gcol + j < N) ? __ldg(bias + gcol + j) : 0.f;
                     }
-                    if (col0 + 32 <= N && (ldc % 8) == 0) {
-                        if (accumulate_c) {
+                    // 128-byte swizzle: 16-byte chunk j of row r lives at chunk (j ^ (r & 7))
+                    uint8_t* rowp = buf + lane * 128;
+                    if (sizeof(TOut) == 2) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) v[j] += Cvt<TOut>::to_f(crow[col0 + j]);
-                        }
-                        if (sizeof(TOut) == 2) {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 8) {
-                                float t[8] = {v[j], v[j + 1], v[j + 2], v[j + 3], v[j + 4], v[j + 5], v[j + 6], v[j + 7]};
-                                store8<TOut>(crow + col0 + j, t);
-                            }
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; j += 4)
-                                *reinterpret_cast<float4*>((float*)crow + col0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                        for (int q = 0; q < 4; ++q) {
+                            float t[8] = {v[q * 8], v[q * 8 + 1], v[q * 8 + 2], v[q * 8 + 3],
+                                          v[q * 8 + 4], v[q * 8 + 5], v[q * 8 + 6], v[q * 8 + 7]};
+                            const int j = l * 4 + q;
+                            store8<TOut>(reinterpret_cast<TOut*>(rowp + ((j ^ (lane & 7)) << 4)), t);
                         }
                     } else {
-                        for (int j = 0; j < 32 && col0 + j < N; ++j) {
-                            float o = v[j];
-                            if (accumulate_c) o += Cvt<TOut>::to_f(crow[col0 + j]);
-                            crow[col0 + j] = Cvt<TOut>::from_f(o);
-                        }
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(rowp + ((j ^ (lane & 7)) << 4)) =
+                                make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
                     }
                 }
+                fence_async_smem();        // generic-proxy smem writes -> visible to the TMA engine
+                __syncwarp();
+                if (lane == 0 && n0 + ch * kChunkCols < N && row0 < M) {
+                    if (accumulate_c) tma_reduce_add_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
+                    else tma_store_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
+                }
+                if (lane == 0) tma_store_commit();
+                ++buf_idx;
             }
+            // the accumulator has left TMEM: hand it back to the MMA warp before the stores finish
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tmem_empty + acc);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (lane == 0) tma_store_wait_read<0>();
     }
     tc_fence_before();
     __syncthreads();
@@ -303,14 +336,15 @@ static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
 
 // 2-D row-major tensor [rows][cols] of 16-bit elements, row pitch ld elements; box = {box_cols, box_rows}
 static int make_tmap(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t rows, int64_t cols, int64_t ld, int box_cols,
-                     int box_rows) {
+                     int box_rows, int elem_bytes = 2) {
     auto enc = get_encode();
     B200DP_REQUIRE(enc != nullptr, "gemm: cuTensorMapEncodeTiled is not available from the driver");
     cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
     cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    const CUtensorMapDataType dt = is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    const CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                   : (is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16);
     CUresult r = enc(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r == CUDA_ERROR_INVALID_CONTEXT || r == CUDA_ERROR_NOT_INITIALIZED) {
@@ -326,7 +360,7 @@ static int make_tmap(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t rows
 }
 
 template <int BN, bool kAMN, bool kBMN, typename TOut>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* C, const float* bias, int M, int N, int K, int ldc,
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias, int M, int N, int K,
                   int is_bf16, int accumulate_c, int sms, cudaStream_t s) {
     auto kern = gemm_kernel<BN, kAMN, kBMN, TOut>;
     static bool configured = false;
@@ -336,7 +370,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, void* C, const f
     }
     const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
     const int grid = tiles < sms ? tiles : sms;
-    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, (TOut*)C, bias, M, N, K, ldc, is_bf16, accumulate_c);
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c);
     B200DP_CHECK_LAUNCH();
     return 0;
 }
@@ -359,9 +393,14 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
     B200DP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda / ldb must be multiples of 8 elements (16-byte TMA strides)");
     B200DP_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: A and B must be 16-byte aligned");
     const int is_bf16 = in_dtype == B200DP_BF16;
-    const int BN = (N >= 256 && (int64_t)M * N >= (int64_t)148 * 128 * 256) ? 256 : 128;
-    CUtensorMap ta, tb;
+    B200DP_REQUIRE(((uintptr_t)C & 15) == 0 && (ldc * (out_dtype == B200DP_F32 ? 4 : 2)) % 16 == 0,
+                   "gemm: C must be 16-byte aligned with a 16-byte row pitch (TMA store)");
+    const int BN = N <= 64 ? 64 : ((N >= 256 && (int64_t)M * N >= (int64_t)148 * 128 * 256) ? 256 : 128);
+    CUtensorMap ta, tb, tc;
     int rc;
+    const int c_bytes = out_dtype == B200DP_F32 ? 4 : 2;
+    rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 128 / c_bytes, 32, c_bytes);   // staging rows are 128 B
+    if (rc) return rc;
     // K-major operand [rows][K]: box = 64 (K) x tile rows.  MN-major [K][rows]: box = 64 (rows) x 64 (K).
     rc = a_mn ? make_tmap(&ta, A, is_bf16, K, M, lda, 64, kBK) : make_tmap(&ta, A, is_bf16, M, K, lda, kBK, kBM);
     if (rc) return rc;
@@ -369,7 +408,7 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     const int sms = B200DP_SMS;
-#define GO(BNv, AM, BM_, T) return launch<BNv, AM, BM_, T>(ta, tb, C, bias, M, N, K, ldc, is_bf16, accumulate_c, sms, s)
+#define GO(BNv, AM, BM_, T) return launch<BNv, AM, BM_, T>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, sms, s)
 #define BY_OUT(BNv, AM, BM_)                                                      \
     if (out_dtype == B200DP_F32) { GO(BNv, AM, BM_, float); }                     \
     else if (is_bf16) { GO(BNv, AM, BM_, __nv_bfloat16); }                        \
@@ -379,7 +418,7 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
     else if (!a_mn && b_mn) { BY_OUT(BNv, false, true) }                          \
     else if (a_mn && b_mn) { BY_OUT(BNv, true, true) }                            \
     else { BY_OUT(BNv, true, false) }
-    if (BN == 256) { BY_MAJOR(256) } else { BY_MAJOR(128) }
+    if (BN == 256) { BY_MAJOR(256) } else if (BN == 128) { BY_MAJOR(128) } else { BY_MAJOR(64) }
 #undef BY_MAJOR
 #undef BY_OUT
 #undef GO
