@@ -54,6 +54,7 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--config", default="resnet50_ddp_amp", choices=sorted(CONFIGS))
     ap.add_argument("--batch-size", type=int, default=0, help="per-GPU batch (0: the config's default)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="disable CUDA-graph capture of the train step")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (config 1)")
     return ap.parse_args()
 
@@ -82,7 +83,7 @@ def build_ours(cfg: dict, args, world: int):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     configs = [AMPConfig(init_scale=2.0 ** 14), DDPConfig(local_rank=local_rank, backend="nccl" if gpu else "gloo"),
                FairscaleOSSConfig(broadcast_fp16=False), FairscaleFSDPConfig(mixed_precision=cfg["fp16"] is not None),
-               B200Config()]
+               B200Config(cuda_graph=gpu and not args.no_graph)]
     stoke = Stoke(
         model=model, verbose=(int(os.environ.get("RANK", "0")) == 0),
         optimizer=StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs=dict(ADAMW)),
@@ -94,10 +95,7 @@ def build_ours(cfg: dict, args, world: int):
     stoke.model_access.train()
 
     def step(x, y):
-        loss = stoke.loss(stoke.model(x), y)
-        stoke.backward(loss)
-        stoke.step()
-        return loss
+        return stoke.train_step(x, y)     # public API: forward + loss + backward + (optimizer step)
 
     return stoke, step, stoke.device
 
@@ -291,8 +289,18 @@ def main() -> None:
         if is_cuda:
             out["peak_mem_gb"] = round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)
         print(json.dumps(out))
+    # teardown: CUDA graphs first (they may hold collective kernels), then the process group; a
+    # watchdog makes sure a stuck teardown can never hold the GPUs after the result is printed
+    sys.stdout.flush()
+    import threading
+    threading.Timer(20.0, lambda: os._exit(0)).start()
+    if stoke is not None:
+        stoke.reset_graphs()
+    sync()
     if world > 1 and dist.is_initialized():
+        barrier()
         dist.destroy_process_group()
+    os._exit(0)
 
 
 if __name__ == "__main__":

@@ -431,8 +431,9 @@ __global__ void __launch_bounds__(kCommThreads) peer_zero_adam_kernel(
     float* vm = (float*)v_tab.p[me.rank];
     const float step = *(const float*)step_tab.p[me.rank];
     const float bc1 = 1.f - powf(hp.beta1, step), bc2 = 1.f - powf(hp.beta2, step);
-    const float step_size = hp.lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
-    const float decay = hp.adamw ? 1.f - hp.lr * hp.weight_decay : 1.f, l2 = hp.adamw ? 0.f : hp.weight_decay;
+    const float lr = hp.lr_dev ? *hp.lr_dev : hp.lr;
+    const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
+    const float decay = hp.adamw ? 1.f - lr * hp.weight_decay : 1.f, l2 = hp.adamw ? 0.f : hp.weight_decay;
     if (!prereduced) cta_barrier_all_ranks(c, me);   // all ranks' gradients are complete
     int64_t b, e;
     slice_range(n_vec, gridDim.x, blockIdx.x, b, e);
@@ -562,6 +563,32 @@ __global__ void __launch_bounds__(kCommThreads) peer_reduce_to_owner_kernel(
         s = block_sum(s, red);
         if (threadIdx.x == 0) { no[0] = s; *ctr = 0u; }
     }
+}
+
+// ---------------------------------------------------------------- broadcast (root -> all), raw bytes
+// Module buffers (BatchNorm running statistics) replicated from the root every forward
+// (K11 hot half): one multicast store per 16 bytes with NVLS, else one peer store per rank.
+template <bool kMC>
+__global__ void __launch_bounds__(kCommThreads) peer_broadcast_kernel(b200dp_peer_ctx c, PtrTable bufs, void* mc,
+                                                                     int64_t n_vec16, int root) {
+    const Rank me(c);
+    cta_barrier_all_ranks(c, me);            // everyone is done reading the previous contents
+    if (me.rank == root) {
+        int64_t b, e;
+        slice_range(n_vec16, gridDim.x, blockIdx.x, b, e);
+        const uint4* src = (const uint4*)bufs.p[root];
+        for (int64_t i = b + threadIdx.x; i < e; i += kCommThreads) {
+            const uint4 v = src[i];
+            if (kMC) {
+                multimem_st((uint4*)mc + i, v);
+            } else {
+#pragma unroll
+                for (int p = 0; p < B200DP_MAX_RANKS; ++p)
+                    if (p < me.world && p != root) st_peer16((uint4*)bufs.p[p] + i, v);
+            }
+        }
+    }
+    cta_barrier_all_ranks(c, me);            // the root's stores have landed everywhere
 }
 
 // ---------------------------------------------------------------- small one-shot all-reduce (<= 64 KB fp32)
@@ -742,6 +769,20 @@ int b200dp_peer_reduce_to_owner(const b200dp_peer_ctx* ctx, void* const* grad_bu
     if (ctx->world <= 2) return launch_comm(peer_reduce_to_owner_kernel<2>, *ctx, blocks, s, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
     if (ctx->world <= 4) return launch_comm(peer_reduce_to_owner_kernel<4>, *ctx, blocks, s, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
     return launch_comm(peer_reduce_to_owner_kernel<8>, *ctx, blocks, s, *ctx, tg, st, tl, pre_mult, tmu, tn, tpa, tc);
+}
+
+int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* mc, int64_t nbytes, int root, int blocks,
+                          void* stream) {
+    int rc = check_ctx(ctx, blocks);
+    if (rc) return rc;
+    B200DP_REQUIRE(bufs && nbytes > 0 && nbytes % 16 == 0, "peer_broadcast: size must be a positive multiple of 16 bytes");
+    B200DP_REQUIRE(root >= 0 && root < ctx->world, "peer_broadcast: bad root %d", root);
+    B200DP_REQUIRE(mc == nullptr || !ctx->emulate, "peer_broadcast: multicast cannot be emulated on one GPU");
+    PtrTable tb;
+    fill(tb, bufs);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (mc != nullptr) return launch_comm(peer_broadcast_kernel<true>, *ctx, blocks, s, *ctx, tb, mc, nbytes / 16, root);
+    return launch_comm(peer_broadcast_kernel<false>, *ctx, blocks, s, *ctx, tb, mc, nbytes / 16, root);
 }
 
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,

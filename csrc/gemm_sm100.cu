@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                                                            const __grid_constant__ CUtensorMap tmB,
                                                            const __grid_constant__ CUtensorMap tmC,
                                                            const float* __restrict__ bias, int M, int N, int K,
-                                                           int is_bf16, int accumulate_c) {
+                                                           int is_bf16, int accumulate_c, int splits) {
     using cfg = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -174,6 +174,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     const int num_m = (M + kBM - 1) / kBM, num_n = (N + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
     const int num_kb = (K + kBK - 1) / kBK;
+    // split-K: work item = (tile, split); split s reduces k-blocks [s*kb_per, min(num_kb, (s+1)*kb_per))
+    // and is added into C by TMA reduce-add (C pre-zeroed by the host unless accumulating)
+    const int kb_per = (num_kb + splits - 1) / splits;
+    const int num_items = num_tiles * splits;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -195,9 +199,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         // ===== TMA producer =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                const int tile = item % num_tiles, split = item / num_tiles;
                 const int m0 = (tile % num_m) * kBM, n0 = (tile / num_m) * BN;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                const int kb_begin = split * kb_per, kb_end = min(num_kb, kb_begin + kb_per);
+                for (int kb = kb_begin; kb < kb_end; ++kb) {
                     mbar_wait(empty + stage, phase ^ 1);
                     mbar_expect_tx(full + stage, cfg::kStageBytes);
                     uint8_t* a = smemA + stage * cfg::kABytes;
@@ -225,11 +231,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             const uint32_t idesc = make_idesc(is_bf16, kAMN ? 1 : 0, kBMN ? 1 : 0, kBM, BN);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                const int split = item / num_tiles;
+                const int kb_begin = split * kb_per, kb_end = min(num_kb, kb_begin + kb_per);
                 mbar_wait(tmem_empty + acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = kb_begin; kb < kb_end; ++kb) {
                     mbar_wait(full + stage, phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smemA + stage * cfg::kABytes);
@@ -240,7 +248,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                                                  : make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
                         const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
                                                  : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
-                        umma_f16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                        umma_f16(d_tmem, da, db, idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
                     }
                     umma_commit(empty + stage);            // smem stage reusable once these MMAs retire
                     if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
@@ -257,8 +265,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         uint8_t* my_stage = smemC + quarter * 2 * cfg::kEpiBufBytes;
         int acc = 0; uint32_t acc_phase = 0;
         uint32_t buf_idx = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+            const int tile = item % num_tiles, split = item / num_tiles;
             const int m0 = (tile % num_m) * kBM, n0 = (tile / num_m) * BN;
+            const bool add_bias = bias != nullptr && split == 0;
             mbar_wait(tmem_full + acc, acc_phase);
             tc_fence_after();
             const int row0 = m0 + quarter * 32;
@@ -277,7 +287,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (bias != nullptr) {
+                    if (add_bias) {
                         const int gcol = n0 + colbase;
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += (gcol + j < N) ? __ldg(bias + gcol + j) : 0.f;
@@ -302,7 +312,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                 fence_async_smem();        // generic-proxy smem writes -> visible to the TMA engine
                 __syncwarp();
                 if (lane == 0 && n0 + ch * kChunkCols < N && row0 < M) {
-                    if (accumulate_c) tma_reduce_add_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
+                    if (accumulate_c || splits > 1) tma_reduce_add_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
                     else tma_store_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
                 }
                 if (lane == 0) tma_store_commit();
@@ -361,16 +371,16 @@ static int make_tmap(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t rows
 
 template <int BN, bool kAMN, bool kBMN, typename TOut>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias, int M, int N, int K,
-                  int is_bf16, int accumulate_c, int sms, cudaStream_t s) {
+                  int is_bf16, int accumulate_c, int splits, int sms, cudaStream_t s) {
     auto kern = gemm_kernel<BN, kAMN, kBMN, TOut>;
     static bool configured = false;
     if (!configured) {
         B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
         configured = true;
     }
-    const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
-    const int grid = tiles < sms ? tiles : sms;
-    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c);
+    const int items = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * splits;
+    const int grid = items < sms ? items : sms;
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits);
     B200DP_CHECK_LAUNCH();
     return 0;
 }
@@ -393,6 +403,11 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
     B200DP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda / ldb must be multiples of 8 elements (16-byte TMA strides)");
     B200DP_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "gemm: A and B must be 16-byte aligned");
     const int is_bf16 = in_dtype == B200DP_BF16;
+    {   // driver-API calls (tensor-map encode) need the primary context bound to THIS thread; autograd
+        // worker threads only ever touched the runtime API lazily
+        static thread_local bool bound = false;
+        if (!bound) { cudaFree(nullptr); bound = true; }
+    }
     B200DP_REQUIRE(((uintptr_t)C & 15) == 0 && (ldc * (out_dtype == B200DP_F32 ? 4 : 2)) % 16 == 0,
                    "gemm: C must be 16-byte aligned with a 16-byte row pitch (TMA store)");
     const int BN = N <= 64 ? 64 : ((N >= 256 && (int64_t)M * N >= (int64_t)148 * 128 * 256) ? 256 : 128);
@@ -408,7 +423,23 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     const int sms = B200DP_SMS;
-#define GO(BNv, AM, BM_, T) return launch<BNv, AM, BM_, T>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, sms, s)
+    // split-K when the output has too few tiles to fill the GPU and the reduction is long (wgrad):
+    // fp32 outputs only (partial sums are combined by TMA reduce-add, whose order is not fixed)
+    int splits = 1;
+    {
+        const int tiles = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
+        const int num_kb = (K + kBK - 1) / kBK;
+        if (out_dtype == B200DP_F32 && tiles * 2 <= sms && num_kb >= 16) {
+            splits = sms / tiles;
+            if (splits > num_kb / 8) splits = num_kb / 8;     // at least 8 k-blocks per split
+            if (splits < 1) splits = 1;
+            const int kb_per = (num_kb + splits - 1) / splits;
+            splits = (num_kb + kb_per - 1) / kb_per;          // no empty split (an empty one would add garbage)
+        }
+        if (splits > 1 && !accumulate_c)
+            B200DP_CUDA(cudaMemsetAsync(C, 0, (size_t)M * ldc * 4, s));
+    }
+#define GO(BNv, AM, BM_, T) return launch<BNv, AM, BM_, T>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits, sms, s)
 #define BY_OUT(BNv, AM, BM_)                                                      \
     if (out_dtype == B200DP_F32) { GO(BNv, AM, BM_, float); }                     \
     else if (is_bf16) { GO(BNv, AM, BM_, __nv_bfloat16); }                        \

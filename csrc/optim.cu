@@ -38,11 +38,12 @@ __global__ void __launch_bounds__(kThreads) multi_adam_kernel(
 
     const float step = *step_p;
     const float gm = grad_mult_p ? *grad_mult_p : 1.f;
+    const float lr = hp.lr_dev ? *hp.lr_dev : hp.lr;
     const float bc1 = 1.f - powf(hp.beta1, step);
     const float bc2 = 1.f - powf(hp.beta2, step);
-    const float step_size = hp.lr / bc1;
+    const float step_size = lr / bc1;
     const float inv_sqrt_bc2 = rsqrtf(bc2);
-    const float decay = hp.adamw ? 1.f - hp.lr * hp.weight_decay : 1.f;
+    const float decay = hp.adamw ? 1.f - lr * hp.weight_decay : 1.f;
     const float l2 = hp.adamw ? 0.f : hp.weight_decay;
     const float sign = hp.maximize ? -1.f : 1.f;
     const float b1 = hp.beta1, b2 = hp.beta2, eps = hp.eps;
@@ -100,6 +101,7 @@ __global__ void __launch_bounds__(kThreads) multi_sgd_kernel(
     LT* lp = d.p_lp ? (LT*)d.p_lp + start : nullptr;
     const float gm = grad_mult_p ? *grad_mult_p : 1.f;
     const float sign = hp.maximize ? -1.f : 1.f;
+    const float lr = hp.lr_dev ? *hp.lr_dev : hp.lr;
     for (int64_t i = threadIdx.x; i < len; i += kThreads) {
         float pv = p[i];
         float gv = Cvt<GT>::to_f(g[i]) * gm * sign + hp.weight_decay * pv;
@@ -108,7 +110,7 @@ __global__ void __launch_bounds__(kThreads) multi_sgd_kernel(
             m[i] = mv;
             gv = hp.nesterov ? gv + hp.momentum * mv : mv;
         }
-        pv -= hp.lr * gv;
+        pv -= lr * gv;
         p[i] = pv;
         if (lp) lp[i] = Cvt<LT>::from_f(pv);
     }

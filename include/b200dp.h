@@ -50,12 +50,14 @@ typedef struct {
     float lr, beta1, beta2, eps, weight_decay;
     int adamw;            /* 1: decoupled weight decay (AdamW); 0: L2 (Adam)   */
     int maximize;
+    const float* lr_dev;  /* optional device scalar overriding lr (LR schedules under CUDA graphs) */
 } b200dp_adam_hparams;
 
 typedef struct {
     float lr, momentum, dampening, weight_decay;
     int nesterov;
     int maximize;
+    const float* lr_dev;  /* optional device scalar overriding lr */
 } b200dp_sgd_hparams;
 
 /* Fused AdamW over a tensor list (reference: AdamW built at Stoke-DDP.py:226-235 /
@@ -269,6 +271,12 @@ int b200dp_peer_reduce_to_owner(const b200dp_peer_ctx* ctx, void* const* grad_bu
                                 void* const* local_out, float pre_mult, const void* const* mult_dev,
                                 void* const* norm_out, void* const* partials, void* const* counters, int blocks,
                                 void* stream);
+
+/* Root's buffer (raw bytes, multiple of 16) replicated into every rank's buffer: module
+ * buffers such as BatchNorm running statistics, every forward (replaces the per-forward
+ * _broadcast_coalesced of the data-parallel wrappers). */
+int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* mc, int64_t nbytes, int root, int blocks,
+                          void* stream);
 
 /* In-place sum across ranks of n <= slot_floats fp32 values (SyncBN moments, loss, norm, inf
  * flag: W6 / W11).  staging[p]: 2*slot_floats floats of peer memory; call_counter: local uint32. */

@@ -104,6 +104,8 @@ class Stoke:
         self._ema_loss: Any = None
         self._loss_sync_calls = 0
         self._skipped_optimizer_steps = 0
+        self._agg_fresh = True
+        self._graphs: Dict[Any, Dict[str, Any]] = {}
 
         # 1. process group + device
         self._device = self._setup_device_and_group(gpu)
@@ -199,6 +201,10 @@ class Stoke:
             optim = opt_cls(model.parameters(), **opt_kwargs)
             self._attach_peer(engine, optim)
             return engine, optim
+        if self._b200.cuda_graph and st.gpu:
+            # graph capture needs gradient addresses that never change: alias them to flat buckets
+            engine = DistributedDataParallel(model, sync_models_at_startup=False)
+            return engine, opt_cls(model.parameters(), **opt_kwargs)
         return model, opt_cls(model.parameters(), **opt_kwargs)
 
     def _wrap_ddp(self, model: nn.Module) -> DistributedDataParallel:
@@ -268,12 +274,34 @@ class Stoke:
                 loss = self._loss(*args, **kwargs)
         if not self._unwrapped.training:
             return loss
-        det = _map_loss(lambda l: l.detach().float(), loss)
-        self._last_step_loss = det
-        self._agg_loss = det if self._agg_loss is None else self._zip(lambda a, b: a + b, self._agg_loss, det)
         w = self._ema_weight
-        self._ema_loss = det if self._ema_loss is None else self._zip(lambda e, l: e * (1.0 - w) + l * w,
-                                                                       self._ema_loss, det)
+        if isinstance(loss, torch.Tensor):
+            # persistent device scalars updated in place: no per-step allocations, no host reads, and
+            # a CUDA-graph replay keeps feeding the same buffers
+            det = loss.detach().float()
+            if self._last_step_loss is None or not isinstance(self._last_step_loss, torch.Tensor):
+                self._last_step_loss, self._agg_loss, self._ema_loss = det.clone(), det.clone(), det.clone()
+                self._agg_fresh = False
+            else:
+                self._last_step_loss.copy_(det)
+                if self._agg_loss is None:
+                    self._agg_loss = det.clone()
+                elif self._agg_fresh:
+                    self._agg_loss.copy_(det)
+                else:
+                    self._agg_loss.add_(det)
+                self._agg_fresh = False
+                if self._ema_loss is None:
+                    self._ema_loss = det.clone()
+                else:
+                    self._ema_loss.mul_(1.0 - w).add_(det, alpha=w)
+        else:
+            det = _map_loss(lambda l: l.detach().float(), loss)
+            self._last_step_loss = det
+            self._agg_loss = det if (self._agg_loss is None or self._agg_fresh) else self._zip(lambda a, b: a + b, self._agg_loss, det)
+            self._agg_fresh = False
+            self._ema_loss = det if self._ema_loss is None else self._zip(lambda e, l: e * (1.0 - w) + l * w,
+                                                                           self._ema_loss, det)
         if self.grad_accum > 1:
             return _map_loss(lambda l: l / self.grad_accum, loss)
         return loss
@@ -357,8 +385,93 @@ class Stoke:
             opt.step()
         self.zero_grads()
         self._grad_accum_counter = 0
-        self._agg_loss = None
+        self._agg_fresh = True          # the next training loss restarts the accumulation window
         self._optimizer_steps += 1
+
+    # ------------------------------------------------------------------ fused train step (+ CUDA graph)
+    def train_step(self, inputs: Any, targets: Any) -> Any:
+        """One micro-step as a single call: ``loss = self.loss(self.model(inputs), targets)``,
+        ``self.backward(loss)``, ``self.step()``.  Returns the detached (undivided) loss scalar,
+        a device tensor.
+
+        With ``B200Config(cuda_graph=True)`` on a GPU the micro-step is captured into a CUDA graph
+        after three eager warm-up calls and replayed afterwards: one launch instead of ~1000, so the
+        step stops being bound by Python / launch overhead.  Everything the step reads on the host
+        is baked in at capture time, except the learning rate (kept in a device scalar that is
+        refreshed before every replay, so LR schedulers keep working) — so change other
+        hyper-parameters, ``requires_grad`` flags or input shapes only via a new shape (new graph) or
+        ``reset_graphs()``.  Inputs are copied into static buffers before each replay.
+        """
+        args = inputs if isinstance(inputs, (tuple, list)) else (inputs,)
+        if not (self._b200.cuda_graph and self._status.gpu and self._unwrapped.training):
+            return self._eager_step(args, targets)
+        return self._graphed_step(args, targets)
+
+    def _eager_step(self, args: Any, targets: Any) -> Any:
+        loss = self.loss(self.model(*args), targets)
+        self.backward(loss)
+        self.step()
+        return self._last_step_loss
+
+    def reset_graphs(self) -> None:
+        self._graphs.clear()
+
+    def _sync_lr(self) -> None:
+        opt = self._optimizer.optim if isinstance(self._optimizer, OSS) else self._optimizer
+        if hasattr(opt, "sync_lr"):
+            if isinstance(self._optimizer, OSS):
+                self._optimizer._sync_param_groups(self._optimizer.param_groups, opt.param_groups)
+            opt.sync_lr()
+
+    def _graphed_step(self, args: Any, targets: Any) -> Any:
+        flat = [a for a in args if isinstance(a, torch.Tensor)] + ([targets] if isinstance(targets, torch.Tensor) else [])
+        key = (self._grad_accum_counter, tuple((tuple(t.shape), t.dtype, t.stride()) for t in flat))
+        ent = self._graphs.setdefault(key, {"calls": 0, "graph": None})
+        if ent["graph"] is None:
+            if ent["calls"] < 3:
+                ent["calls"] += 1
+                return self._eager_step(args, targets)
+            # ---- capture
+            ent["args"] = tuple(a.clone() if isinstance(a, torch.Tensor) else a for a in args)
+            ent["targets"] = targets.clone() if isinstance(targets, torch.Tensor) else targets
+            self._sync_lr()
+            counters = (self._backward_steps, self._optimizer_steps, self._grad_accum_counter, self._agg_fresh)
+            torch.cuda.synchronize(self._device)
+            graph = torch.cuda.CUDAGraph()
+            from .ops import _lib
+            launches0 = _lib.LAUNCHES
+            try:
+                with torch.cuda.graph(graph):
+                    self._eager_step(ent["args"], ent["targets"])
+            except Exception as e:  # this configuration cannot be captured: stay eager from here on
+                self._backward_steps, self._optimizer_steps, self._grad_accum_counter, self._agg_fresh = counters
+                self._b200.cuda_graph = False
+                self._graphs.clear()
+                torch.cuda.synchronize(self._device)
+                self.reset()
+                self.print(f"[b200] CUDA-graph capture failed ({type(e).__name__}: {str(e)[:160]}); continuing eagerly")
+                return self._eager_step(args, targets)
+            ent["launches"] = _lib.LAUNCHES - launches0    # b200dp kernels inside one replay
+            _lib.LAUNCHES = launches0
+            ent["delta"] = (self._backward_steps - counters[0], self._optimizer_steps - counters[1],
+                            self._grad_accum_counter, self._agg_fresh)
+            ent["graph"] = graph
+            # capture records, it does not execute: roll the host counters back and replay for real
+            self._backward_steps, self._optimizer_steps, self._grad_accum_counter, self._agg_fresh = counters
+        for dst, src in zip(ent["args"], args):
+            if isinstance(dst, torch.Tensor):
+                dst.copy_(src, non_blocking=True)
+        if isinstance(ent["targets"], torch.Tensor):
+            ent["targets"].copy_(targets, non_blocking=True)
+        self._sync_lr()
+        ent["graph"].replay()
+        from .ops import _lib
+        _lib.LAUNCHES += ent["launches"]
+        d = ent["delta"]
+        self._backward_steps += d[0]
+        self._optimizer_steps += d[1]
+        self._grad_accum_counter, self._agg_fresh = d[2], d[3]
+        return self._last_step_loss
 
     def _clip(self) -> None:
         """Clip dispatch."""
@@ -380,16 +493,19 @@ class Stoke:
             torch.nn.utils.clip_grad_norm_(params, gc.max_norm, gc.norm_type)
 
     def zero_grads(self) -> None:
-        if isinstance(self._model, (DistributedDataParallel, ShardedDataParallel)):
+        if isinstance(self._model, DistributedDataParallel):
             self._model.zero_grad()
+        elif isinstance(self._model, ShardedDataParallel):
+            self._model.zero_grad(set_to_none=not (self._b200.cuda_graph and self._status.gpu))
         else:
-            self._optimizer.zero_grad(set_to_none=True)
+            # under CUDA graphs gradient tensors must keep their addresses: zero in place
+            self._optimizer.zero_grad(set_to_none=not (self._b200.cuda_graph and self._status.gpu))
 
     def reset(self) -> None:
         """Drop gradients and accumulation state (e.g. after a manual interruption)."""
         self.zero_grads()
         self._grad_accum_counter = 0
-        self._agg_loss = None
+        self._agg_fresh = True
 
     def reset_ema(self) -> None:
         self._ema_loss = None
@@ -450,7 +566,7 @@ class Stoke:
         self.print(f"{prepend_msg}: " + (", ".join(f"{v:.3f}" for v in vals) if isinstance(vals, (list, tuple)) else f"{vals:.3f}"))
 
     def print_mean_accumulated_synced_loss(self, prepend_msg: str = "Mean Accumulated & Synced Loss") -> None:
-        if self._agg_loss is None:
+        if self._agg_loss is None or self._agg_fresh:
             return
         n = max(self._grad_accum_counter, 1)
         vals = self.detach_and_sync_loss(_map_loss(lambda t: t / n, self._agg_loss))

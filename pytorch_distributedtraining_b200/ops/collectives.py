@@ -126,6 +126,10 @@ class PeerContext:
                                                    ctypes.c_float(pre_mult), mult_dev, norm_out, partials, counters,
                                                    blocks, self._s(stream)), "peer_reduce_to_owner")
 
+    def broadcast(self, bufs: VoidPtrTable, mc: int, nbytes: int, root: int = 0, blocks: int = 8, stream=None) -> None:
+        check(self.lib.b200dp_peer_broadcast(ctypes.byref(self.c), bufs, ctypes.c_void_p(mc or None), ctypes.c_int64(nbytes),
+                                             root, blocks, self._s(stream)), "peer_broadcast")
+
     def small_allreduce(self, staging: VoidPtrTable, io: VoidPtrTable, n: int, slot_floats: int,
                         call_counter: VoidPtrTable, stream=None) -> None:
         check(self.lib.b200dp_peer_small_allreduce(ctypes.byref(self.c), staging, io, n, slot_floats, call_counter,

@@ -20,12 +20,13 @@ _DESC = np.dtype([("p", "<u8"), ("g", "<u8"), ("m", "<u8"), ("v", "<u8"), ("lp",
 class AdamHParams(ctypes.Structure):
     _fields_ = [("lr", ctypes.c_float), ("beta1", ctypes.c_float), ("beta2", ctypes.c_float),
                 ("eps", ctypes.c_float), ("weight_decay", ctypes.c_float), ("adamw", ctypes.c_int),
-                ("maximize", ctypes.c_int)]
+                ("maximize", ctypes.c_int), ("lr_dev", ctypes.c_void_p)]
 
 
 class SGDHParams(ctypes.Structure):
     _fields_ = [("lr", ctypes.c_float), ("momentum", ctypes.c_float), ("dampening", ctypes.c_float),
-                ("weight_decay", ctypes.c_float), ("nesterov", ctypes.c_int), ("maximize", ctypes.c_int)]
+                ("weight_decay", ctypes.c_float), ("nesterov", ctypes.c_int), ("maximize", ctypes.c_int),
+                ("lr_dev", ctypes.c_void_p)]
 
 
 def ptr(t: Optional[torch.Tensor]) -> ctypes.c_void_p:
@@ -101,6 +102,10 @@ class TensorList:
                  v: Optional[Sequence[Optional[torch.Tensor]]] = None,
                  lp: Optional[Sequence[Optional[torch.Tensor]]] = None):
         n = len(g)
+        if torch.cuda.is_available() and torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("a fused-kernel tensor table would have to be (re)built during CUDA-graph capture: "
+                               "parameter / gradient addresses changed since the warm-up steps (keep gradients "
+                               "allocated, e.g. zero_grad(set_to_none=False))")
         ref = next(t for t in list(g) + list(p) if t is not None)
         self.device = ref.device
         desc = np.zeros(n, dtype=_DESC)

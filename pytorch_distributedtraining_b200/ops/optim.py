@@ -115,6 +115,28 @@ class _FusedBase(Optimizer):
                 except Exception:
                     return
 
+    def _lr_tensor(self, gi: int, group: Dict[str, Any], device: torch.device) -> Optional[int]:
+        """Device copy of the group's learning rate, refreshed only when the host value changed
+        (outside CUDA-graph capture).  The kernels read the LR from it, so a captured step keeps
+        following an LR schedule."""
+        cache = self.__dict__.setdefault("_lr_cache", {})
+        ent = cache.get(gi)
+        lr = float(group["lr"])
+        if ent is None:
+            if torch.cuda.is_current_stream_capturing():
+                return None
+            ent = cache[gi] = [torch.full((), lr, dtype=torch.float32, device=device), lr]
+        elif ent[1] != lr and not torch.cuda.is_current_stream_capturing():
+            ent[0].fill_(lr)
+            ent[1] = lr
+        return ent[0].data_ptr()
+
+    def sync_lr(self) -> None:
+        """Push host-side LR changes (schedulers) to the device scalars; call before a graph replay."""
+        for gi, g in enumerate(self.param_groups):
+            if g["params"]:
+                self._lr_tensor(gi, g, g["params"][0].device)
+
     def _consume_grad_mult(self) -> Optional[torch.Tensor]:
         if getattr(self, "_use_grad_mult", False):
             self._use_grad_mult = False
@@ -181,7 +203,8 @@ class FusedAdamW(_FusedBase):
                     [self.state[p]["exp_avg_sq"] for p in params])
             b1, b2 = group["betas"]
             hp = fused.AdamHParams(float(group["lr"]), float(b1), float(b2), float(group["eps"]),
-                                   float(group["weight_decay"]), self._adamw, int(bool(group.get("maximize", False))))
+                                   float(group["weight_decay"]), self._adamw, int(bool(group.get("maximize", False))),
+                                   self._lr_tensor(gi, group, params[0].device))
             fused.step_advance(step_t, found_inf)
             fused.multi_adam(tl, grads[0].dtype, torch.float16, hp, step_t, grad_mult, found_inf)
             self._bump_versions(params)
@@ -252,7 +275,8 @@ class FusedSGD(_FusedBase):
                     tl = self._tables[tkey] = fused.TensorList(
                         ps, grads, [self.state[p].get("momentum_buffer") for p in ps] if mom != 0 else None)
                 hp = fused.SGDHParams(float(group["lr"]), mom, float(group["dampening"]), float(group["weight_decay"]),
-                                      int(bool(group["nesterov"])), int(bool(group.get("maximize", False))))
+                                      int(bool(group["nesterov"])), int(bool(group.get("maximize", False))),
+                                      self._lr_tensor(gi, group, ps[0].device))
                 fused.multi_sgd(tl, grads[0].dtype, torch.float16, hp, first, grad_mult, found_inf)
                 self._bump_versions(ps)
         return loss

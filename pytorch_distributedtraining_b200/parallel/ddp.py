@@ -202,9 +202,13 @@ class DistributedDataParallel(nn.Module):
     # ------------------------------------------------------------------ forward
     def forward(self, *inputs: Any, **kwargs: Any) -> Any:
         if self.broadcast_buffers and self.world_size > 1 and self.training:
-            bufs = [b.data for b in self.module.buffers()]
-            if bufs:
-                comm.broadcast_coalesced(bufs, src=0, group=self.process_group)
+            peer_sync = getattr(self._peer_allreduce, "sync_buffers", None)
+            if peer_sync is not None:
+                peer_sync()                      # one peer-memory kernel, no NCCL on the hot path
+            else:
+                bufs = [b.data for b in self.module.buffers()]
+                if bufs:
+                    comm.broadcast_coalesced(bufs, src=0, group=self.process_group)
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             for b in self.buckets:
                 b.reset()

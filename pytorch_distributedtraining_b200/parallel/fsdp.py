@@ -256,6 +256,11 @@ class FullyShardedDataParallel(nn.Module):
     def _reduce_grad(self, grad_full: torch.Tensor) -> Optional[torch.Tensor]:
         """Post-backward for this unit: (accumulate) → pre-divide → reduce-scatter →
         post-divide → fp32 shard gradient."""
+        # the module attributes still point at views of this iteration's autograd graph; swap them
+        # for history-free views so the graph (and its AccumulateGrad nodes, which would otherwise be
+        # re-used by the next iteration and break CUDA-graph capture) can be freed
+        if self._full is not None:
+            self._install_views(self._full.detach())
         if self.reshard_after_forward:
             self._free_full()
         if not self._require_backward_grad_sync:

@@ -174,7 +174,11 @@ class ShardedDataParallel(nn.Module):
         if self.auto_refresh_trainable and self._trainable_snapshot() != self._trainable_mask:
             self.refresh_trainable()
         if self.broadcast_buffers and self.world_size > 1 and self.training and any(True for _ in self.module.buffers()):
-            self.sync_buffers()
+            peer_sync = getattr(self._fused_engine, "sync_buffers", None)
+            if peer_sync is not None:
+                peer_sync()                      # one peer-memory kernel, no NCCL on the hot path
+            else:
+                self.sync_buffers()
         if self._fused_engine is not None:
             self._fused_engine.pre_forward()
         for b in self._buckets.values():

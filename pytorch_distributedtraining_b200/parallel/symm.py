@@ -121,6 +121,40 @@ class SmallAllReduce:
     small_allreduce = __call__
 
 
+# --------------------------------------------------------------------------- module buffers
+class PeerBufferSync:
+    """Module buffers re-homed into one flat piece of arena memory, so the per-forward
+    "broadcast buffers from rank 0" of the data-parallel wrappers is one peer-memory kernel
+    (root pushes, multicast when available) instead of an NCCL broadcast with pack / unpack."""
+
+    def __init__(self, arena: PeerArena, module: Any):
+        self.arena, self.ctx = arena, arena.context("main")
+        bufs = [b for b in module.buffers() if b is not None and b.is_cuda]
+        off, plan = 0, []
+        for b in bufs:
+            nbytes = b.numel() * b.element_size()
+            plan.append((b, off))
+            off += (nbytes + 15) // 16 * 16
+        self.nbytes = off
+        self.flat: Optional[SymmBuffer] = None
+        if off == 0:
+            return
+        self.flat = arena.alloc(off, torch.uint8)
+        storage = self.flat.tensor.untyped_storage()
+        base = self.flat.tensor.storage_offset()
+        with torch.no_grad():
+            for b, o in plan:
+                view = torch.empty(0, dtype=b.dtype, device=b.device).set_(
+                    storage, (base + o) // b.element_size(), b.shape, b.contiguous().stride())
+                view.copy_(b)
+                b.data = view
+
+    def __call__(self) -> None:
+        if self.flat is not None:
+            self.ctx.broadcast(self.flat.table, self.flat.mc, self.nbytes, root=0,
+                               blocks=int(min(8, max(1, self.nbytes // 65536))))
+
+
 # --------------------------------------------------------------------------- DDP
 class DDPPeerEngine:
     """Bucket all-reduce on a comm stream, fused with 1/world, the AMP unscale and the inf check."""
@@ -144,6 +178,7 @@ class DDPPeerEngine:
 
         ddp.rebuild_buckets(allocator)
         ddp.attach_peer_allreduce(self)
+        self.sync_buffers = PeerBufferSync(arena, ddp.module)
         torch.cuda.synchronize(arena.device)
         comm.barrier(arena.group)
 
@@ -279,6 +314,7 @@ class ZeroPeerEngine:
         self.grad_mult = torch.ones((), dtype=torch.float32, device=dev)
         self.total_norm = torch.zeros((), dtype=torch.float32, device=dev)
         self._clip_pending = False
+        self.sync_buffers = PeerBufferSync(arena, sddp.module)
         torch.cuda.synchronize(dev)
         comm.barrier(arena.group)
         oss.attach_flat_engine(self)
@@ -348,7 +384,7 @@ class ZeroPeerEngine:
         for gi, (g, pg) in enumerate(zip(self.groups, oss.param_groups)):
             b1, b2 = pg.get("betas", (0.9, 0.999))
             hp = fused.AdamHParams(float(pg["lr"]), float(b1), float(b2), float(pg.get("eps", 1e-8)),
-                                   float(pg.get("weight_decay", 0.0)), 1 if self._is_adamw() else 0, 0)
+                                   float(pg.get("weight_decay", 0.0)), 1 if self._is_adamw() else 0, 0, None)
             fused.step_advance(g["step"], found_inf)
             s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
             pbuf = self.P16 if self.P16 is not None else self.P
@@ -420,6 +456,7 @@ class ZeroPeerEngine:
 # --------------------------------------------------------------------------- attachment
 def _arena_bytes(engine: Any, optim: Any, status: Any) -> int:
     n_params = sum(p.numel() for p in engine.parameters())
+    n_params += sum(b.numel() * b.element_size() for b in engine.buffers()) // 4 + 64 * len(list(engine.buffers()))
     if status.fully_sharded:
         from .fsdp import FullyShardedDataParallel
         units = [u for u in engine.modules() if isinstance(u, FullyShardedDataParallel) and u.flat_param is not None]

@@ -12,7 +12,7 @@ ap.add_argument("--config", default="resnet50_ddp_amp")
 ap.add_argument("--batch-size", type=int, default=0)
 ap.add_argument("--out", default="gpurun_out/prof.txt")
 a = ap.parse_args()
-args = argparse.Namespace(cpu=False, batch_size=a.batch_size, impl=a.impl)
+args = argparse.Namespace(cpu=False, batch_size=a.batch_size, impl=a.impl, no_graph=True)
 cfg = dict(bench.CONFIGS[a.config])
 build = bench.build_ours if a.impl == "ours" else bench.build_torch
 stoke, step, device = build(cfg, args, 1)

@@ -108,7 +108,7 @@ def test_emulated_zero_adam_matches_torch_adamw(C, world, wire, prereduced):
     m = [torch.zeros(sizes[r], device=cuda) for r in range(world)]
     v = [torch.zeros(sizes[r], device=cuda) for r in range(world)]
     step = [torch.zeros((), device=cuda) for _ in range(world)]
-    hp = fused.AdamHParams(1e-2, 0.9, 0.99, 1e-8, 1e-2, 1, 0)
+    hp = fused.AdamHParams(1e-2, 0.9, 0.99, 1e-8, 1e-2, 1, 0, None)
     for it in range(3):
         grads = _rand(world, total, torch.float32, seed=100 + it)
         for r in range(world):
@@ -166,6 +166,19 @@ def test_emulated_reduce_to_owner_and_small_allreduce(C, world):
         for x in io:
             torch.testing.assert_close(x, want, rtol=1e-5, atol=1e-5)
     assert not em.timed_out() and all(c.item() == 5 for c in calls)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_emulated_broadcast(C, world):
+    em = C.EmulatedPeers(world, max_blocks=8)
+    nbytes = 16 * 4099
+    bufs = [torch.randint(0, 255, (nbytes,), dtype=torch.uint8, device=cuda) for _ in range(world)]
+    want = bufs[1].clone()
+    em.ctx.broadcast(C.table(bufs), 0, nbytes, root=1, blocks=4)
+    torch.cuda.synchronize()
+    assert not em.timed_out()
+    for b in bufs:
+        assert torch.equal(b, want)
 
 
 # ----------------------------------------------------------------------------- real multi-GPU

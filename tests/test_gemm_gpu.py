@@ -81,3 +81,17 @@ def test_linear_layer_forward_backward(dtype, shape, out_f):
     torch.testing.assert_close(lin.weight.grad, dw, rtol=tol, atol=tol * rows ** 0.5)
     torch.testing.assert_close(lin.bias.grad, db, rtol=tol, atol=tol * rows ** 0.5)
     assert lin.weight.grad.dtype == torch.float32
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K", [(64, 256, 100352), (256, 64, 50176), (768, 768, 25216), (2048, 512, 12544), (8, 16, 4096)])
+def test_gemm_split_k_wgrad_shapes(dtype, M, N, K):
+    """Few output tiles + long reduction: the kernel splits K and combines with TMA reduce-add."""
+    from pytorch_distributedtraining_b200.ops.gemm import gemm
+    a, b = _mk(K, M, dtype, 7), _mk(K, N, dtype, 8)          # both MN-major, like dW = dY^T X
+    want = a.float().t() @ b.float()
+    got = gemm(a, b, M, N, K, a_mn=True, b_mn=True, out_dtype=torch.float32)
+    torch.testing.assert_close(got, want, rtol=2e-3, atol=2e-3 * K ** 0.5 * 0.25)
+    out = torch.full((M, N), 2.0, device=cuda)
+    gemm(a, b, M, N, K, a_mn=True, b_mn=True, out=out, accumulate=True)
+    torch.testing.assert_close(out, want + 2.0, rtol=2e-3, atol=2e-3 * K ** 0.5 * 0.25)

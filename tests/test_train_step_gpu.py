@@ -1,0 +1,50 @@
+"""``Stoke.train_step`` with CUDA-graph capture must train exactly like the eager four-call API."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(graph: bool, accum: int, clip, steps: int = 10, sched: bool = True):
+    from pytorch_distributedtraining_b200 import AMPConfig, B200Config, ClipGradNormConfig, Stoke, StokeOptimizer
+    from pytorch_distributedtraining_b200.models import resnet18
+    from pytorch_distributedtraining_b200.ops.loss import cross_entropy
+    torch.manual_seed(0)
+    s = Stoke(model=resnet18(num_classes=10, small_input=True), verbose=False,
+              optimizer=StokeOptimizer(optimizer=torch.optim.AdamW,
+                                       optimizer_kwargs={"lr": 1e-3, "betas": (0.9, 0.99), "eps": 1e-8, "weight_decay": 1e-4}),
+              loss=cross_entropy, batch_size_per_device=32, gpu=True, fp16="amp", grad_accum_steps=accum,
+              grad_clip=None if clip is None else ClipGradNormConfig(max_norm=clip, norm_type=2.0),
+              configs=[AMPConfig(init_scale=2.0 ** 8), B200Config(cuda_graph=graph)])
+    s.model_access.train()
+    lr_sched = torch.optim.lr_scheduler.StepLR(s.optimizer, step_size=2, gamma=0.5) if sched else None
+    g = torch.Generator().manual_seed(5)
+    losses = []
+    for i in range(steps):
+        x = torch.randn(32, 3, 32, 32, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+        y = torch.randint(0, 10, (32,), generator=g).cuda()
+        if graph:
+            loss = s.train_step(x, y)
+        else:
+            l = s.loss(s.model(x), y)
+            s.backward(l)
+            s.step()
+            loss = s.step_loss
+        losses.append(float(loss))
+        if lr_sched is not None and (i + 1) % accum == 0:
+            lr_sched.step()
+    assert s.backward_steps == steps and s.optimizer_steps == steps // accum
+    return losses, [p.detach().clone() for p in s.model_access.parameters()], s
+
+
+@pytest.mark.parametrize("accum,clip", [(1, None), (2, 1.0)])
+def test_graphed_train_step_matches_eager(accum, clip):
+    l_e, p_e, _ = _run(False, accum, clip)
+    l_g, p_g, s = _run(True, accum, clip)
+    assert any(e["graph"] is not None for e in s._graphs.values()), "no CUDA graph was captured"
+    for a, b in zip(l_e, l_g):
+        assert abs(a - b) <= 2e-2 * max(1.0, abs(a)), (l_e, l_g)
+    num = sum(((a - b) ** 2).sum() for a, b in zip(p_g, p_e))
+    den = sum((b ** 2).sum() for b in p_e)
+    assert (num / den).sqrt().item() < 2e-3, (num, den)
+    assert float(s.ema_loss) == float(s.ema_loss) and s.ema_loss is not None
