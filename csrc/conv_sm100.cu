@@ -1,0 +1,566 @@
+// Implicit-GEMM convolution on tcgen05 / TMEM, operands fetched by TMA straight from the NHWC
+// activation tensor — no im2col buffer, no cuDNN (W7).
+//
+// The GEMM view:  M = output pixels (tiles of bn x bp x bq pixels, <= 128 rows),
+//                 N = output channels, K = (filter tap r,s) x (64-channel chunk).
+// For one k-block the A tile is "the input pixels seen by this tile of output pixels through
+// tap (r,s)": a box of the 4-D tensor [N][H][W][C] starting at (q0*stride + s - pad,
+// p0*stride + r - pad) and traversed with the convolution stride.  That is exactly what a tiled
+// TMA load with elementStrides = {1, stride, stride, 1} fetches; out-of-image pixels (padding,
+// ragged tiles) are zero-filled by the TMA unit.  Rows land in smem in (n, p, q) order with 128 B
+// per row (64 channels), i.e. the K-major SWIZZLE_128B layout the UMMA descriptor expects.
+//
+//   fprop  Y[n,p,q,co]  = sum_{r,s,ci} X[n, p*st+r-pad, q*st+s-pad, ci] * W[co,r,s,ci]
+//          A = X via 4-D TMA, B = W viewed as [Cout][R*S*Cin] (K-major)
+//   dgrad  dX[n,h,w,ci] = sum_{r,s,co} dY[n, h+pad-r, w+pad-s, co] * W[co,r,s,ci]     (stride 1)
+//          A = dY via 4-D TMA (tap offsets negated), B = W viewed as [Cout][R*S*Cin] read MN-major
+//   wgrad  dW[co,r,s,ci] = sum_{n,p,q} dY[n,p,q,co] * X[n, p*st+r-pad, q*st+s-pad, ci]
+//          both operands MN-major via 4-D TMA, K = pixels (exactly 64 per k-block), split over
+//          pixel tiles and combined with TMA reduce-add into the fp32 gradient
+//
+// Warp roles, pipeline and TMEM double buffering are those of gemm_sm100.cu.  The epilogue
+// stages 32 rows x 128 B per warp in swizzled smem and writes them out 4 rows per instruction
+// (8 lanes x 16 B per row) to the pixel's address, masking rows that fall outside the image.
+#include "tc_common.cuh"
+
+namespace b200dp {
+namespace conv {
+
+using namespace b200dp::tc;
+
+struct Geom {
+    int n_img, out_h, out_w;      // pixel space this pass writes (fprop: P,Q; dgrad: H,W)
+    int c_out, c_red;             // GEMM N and the per-tap reduction length
+    int R, S, stride;
+    int off_h, off_w, tap_sign;   // input coordinate = out*stride + off + tap_sign*tap
+    int bq, bp, bn;               // tile box (pixels): bq*bp*bn <= 128
+    int tiles_q, tiles_p, tiles_n;
+    int w_taps_ld;                // R*S*Cin: row pitch of the weight matrix view (elements)
+};
+
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+
+template <int BN> struct Cfg {
+    static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 5 : 7);
+    static constexpr int kABytes = kBM * kBK * 2;
+    static constexpr int kBBytes = BN * kBK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kEpiBufBytes = 32 * 128;
+    static constexpr int kEpiBytes = 4 * kEpiBufBytes;      // one staging buffer per epilogue warp
+    static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kEpiBytes + 1024 + 256;   // wgrad double-buffers its staging
+    static constexpr int kTmemCols = 2 * BN;
+};
+
+// fprop (kBMN = false) and stride-1 dgrad (kBMN = true)
+template <int BN, bool kBMN, typename TOut>
+__global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                              const __grid_constant__ CUtensorMap tmB,
+                                                              TOut* __restrict__ out, const float* __restrict__ bias,
+                                                              Geom g, int is_bf16) {
+    using cfg = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemA = smem;
+    uint8_t* smemB = smem + cfg::kStages * cfg::kABytes;
+    uint8_t* smemC = smem + cfg::kStages * cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + cfg::kEpiBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + cfg::kStages;
+    uint64_t* tmem_full = bars + 2 * cfg::kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = g.tiles_q * g.tiles_p * g.tiles_n;
+    const int num_n = (g.c_out + BN - 1) / BN;
+    const int num_tiles = num_m * num_n;
+    const int chunks = g.c_red / kBK;
+    const int num_kb = g.R * g.S * chunks;
+    const int rows_valid = g.bq * g.bp * g.bn;
+    const uint32_t a_bytes = (uint32_t)rows_valid * 128u;
+
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < cfg::kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, cfg::kTmemCols);
+    // rows of the A tile beyond rows_valid are never written by TMA: clear them once so the MMA
+    // reads zeros (their results are discarded, but NaN bit patterns must not linger in smem)
+    for (int i = threadIdx.x; i < cfg::kStages * cfg::kABytes / 16; i += kThreads)
+        reinterpret_cast<uint4*>(smemA)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode_m = [&](int mt, int& n0, int& p0, int& q0) {
+        q0 = (mt % g.tiles_q) * g.bq;
+        p0 = ((mt / g.tiles_q) % g.tiles_p) * g.bp;
+        n0 = (mt / (g.tiles_q * g.tiles_p)) * g.bn;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int n0, p0, q0;
+                decode_m(tile % num_m, n0, p0, q0);
+                const int nt0 = (tile / num_m) * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int tap = kb / chunks, c0 = (kb % chunks) * kBK;
+                    const int r = tap / g.S, s = tap % g.S;
+                    mbar_wait(empty + stage, phase ^ 1);
+                    mbar_expect_tx(full + stage, a_bytes + cfg::kBBytes);
+                    tma_load_4d(smemA + stage * cfg::kABytes, &tmA, full + stage, c0,
+                                q0 * g.stride + g.off_w + g.tap_sign * s, p0 * g.stride + g.off_h + g.tap_sign * r, n0);
+                    uint8_t* b = smemB + stage * cfg::kBBytes;
+                    if (kBMN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_2d(b + j * (kBK * 128), &tmB, full + stage, tap * g.c_out + nt0 + j * 64, c0);
+                    } else {
+                        tma_load_2d(b, &tmB, full + stage, tap * g.c_red + c0, nt0);
+                    }
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, 0, kBMN ? 1 : 0, kBM, BN);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full + stage, phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smemA + stage * cfg::kABytes);
+                    const uint32_t b_addr = smem_u32(smemB + stage * cfg::kBBytes);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k) {
+                        const uint64_t da = make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
+                        const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                 : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
+                        umma_f16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(empty + stage);
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tmem_full + acc);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        const int quarter = warp - kEpiWarp0;
+        uint8_t* buf = smemC + quarter * cfg::kEpiBufBytes;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            int n0, p0, q0;
+            decode_m(tile % num_m, n0, p0, q0);
+            const int nt0 = (tile / num_m) * BN;
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            // this lane's row of the tile -> output pixel
+            const int t = quarter * 32 + lane;
+            const int bq_i = t % g.bq, bp_i = (t / g.bq) % g.bp, bn_i = t / (g.bq * g.bp);
+            const int n = n0 + bn_i, p = p0 + bp_i, q = q0 + bq_i;
+            const bool valid = t < rows_valid && n < g.n_img && p < g.out_h && q < g.out_w;
+            const long long pix = valid ? (((long long)n * g.out_h + p) * g.out_w + q) : -1;
+#pragma unroll 1
+            for (int ch = 0; ch < BN / 64; ++ch) {
+                __syncwarp();
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+                    uint32_t r[32];
+                    const int colbase = ch * 64 + l * 32;
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + colbase, r);
+                    tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    if (bias != nullptr) {
+                        const int gcol = nt0 + colbase;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (gcol + j < g.c_out) ? __ldg(bias + gcol + j) : 0.f;
+                    }
+                    uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+                    for (int qd = 0; qd < 4; ++qd) {
+                        float tt[8] = {v[qd * 8], v[qd * 8 + 1], v[qd * 8 + 2], v[qd * 8 + 3],
+                                       v[qd * 8 + 4], v[qd * 8 + 5], v[qd * 8 + 6], v[qd * 8 + 7]};
+                        const int j = l * 4 + qd;
+                        store8<TOut>(reinterpret_cast<TOut*>(rowp + ((j ^ (lane & 7)) << 4)), tt);
+                    }
+                }
+                __syncwarp();
+                // write-out: 8 lanes per row, 4 rows per instruction, 128 contiguous bytes per row
+                const int col0 = nt0 + ch * 64;
+#pragma unroll
+                for (int rr = 0; rr < 32; rr += 4) {
+                    const int row = rr + (lane >> 3), chunk = lane & 7;
+                    const long long rpix = __shfl_sync(0xffffffffu, pix, row);
+                    const uint4 val = *reinterpret_cast<const uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4));
+                    if (rpix >= 0 && col0 + chunk * 8 < g.c_out)
+                        *reinterpret_cast<uint4*>(out + rpix * g.c_out + col0 + chunk * 8) = val;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + acc);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, cfg::kTmemCols);
+}
+
+
+// ---------------------------------------------------------------- wgrad
+// dW[co][tap][ci] += sum over a 64-pixel box of dY[pix][co] * X[pix shifted by tap][ci].
+// Work item = (tap, co tile, ci tile, split); a split walks its share of the pixel boxes.  Both
+// operands are MN-major (channels contiguous, pixels = K rows), fetched by 4-D TMA; out-of-image
+// pixels are zero-filled for both, so ragged edges and padding contribute nothing.
+struct WGeom {
+    int n_img, out_h, out_w;      // dY pixel space (P, Q)
+    int c_out, c_in, R, S, stride, pad;
+    int tiles_q, tiles_p;         // 8 x 8 pixel boxes per image
+    int splits, kb_per;           // pixel boxes per split
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1) conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY,
+                                                                 const __grid_constant__ CUtensorMap tmX,
+                                                                 const __grid_constant__ CUtensorMap tmDW, WGeom g,
+                                                                 int is_bf16) {
+    using cfg = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemA = smem;
+    uint8_t* smemB = smem + cfg::kStages * cfg::kABytes;
+    uint8_t* smemC = smem + cfg::kStages * cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + 2 * cfg::kEpiBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + cfg::kStages;
+    uint64_t* tmem_full = bars + 2 * cfg::kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = (g.c_out + kBM - 1) / kBM, num_n = (g.c_in + BN - 1) / BN;
+    const int taps = g.R * g.S;
+    const int boxes_per_img = g.tiles_p * g.tiles_q;
+    const int num_kb = g.n_img * boxes_per_img;
+    const int num_items = taps * num_m * num_n * g.splits;
+
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmDY); tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmDW); }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < cfg::kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, cfg::kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode = [&](int item, int& tap, int& m0, int& n0, int& kb0, int& kb1) {
+        const int split = item % g.splits;
+        int rest = item / g.splits;
+        n0 = (rest % num_n) * BN; rest /= num_n;
+        m0 = (rest % num_m) * kBM; rest /= num_m;
+        tap = rest;
+        kb0 = split * g.kb_per;
+        kb1 = min(num_kb, kb0 + g.kb_per);
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                int tap, m0, n0, kb0, kb1;
+                decode(item, tap, m0, n0, kb0, kb1);
+                const int r = tap / g.S, s = tap % g.S;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    const int img = kb / boxes_per_img, bx = kb % boxes_per_img;
+                    const int p0 = (bx / g.tiles_q) * 8, q0 = (bx % g.tiles_q) * 8;
+                    mbar_wait(empty + stage, phase ^ 1);
+                    mbar_expect_tx(full + stage, cfg::kStageBytes);
+                    uint8_t* a = smemA + stage * cfg::kABytes;
+                    uint8_t* b = smemB + stage * cfg::kBBytes;
+#pragma unroll
+                    for (int j = 0; j < kBM / 64; ++j) tma_load_4d(a + j * (kBK * 128), &tmDY, full + stage, m0 + j * 64, q0, p0, img);
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j)
+                        tma_load_4d(b + j * (kBK * 128), &tmX, full + stage, n0 + j * 64, q0 * g.stride + s - g.pad,
+                                    p0 * g.stride + r - g.pad, img);
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, 1, 1, kBM, BN);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                int tap, m0, n0, kb0, kb1;
+                decode(item, tap, m0, n0, kb0, kb1);
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(full + stage, phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smemA + stage * cfg::kABytes);
+                    const uint32_t b_addr = smem_u32(smemB + stage * cfg::kBBytes);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k) {
+                        const uint64_t da = make_desc(a_addr + k * (kUmmaK * 128), kBK * 128, 1024);
+                        const uint64_t db = make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024);
+                        umma_f16(d_tmem, da, db, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+                    }
+                    umma_commit(empty + stage);
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tmem_full + acc);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        const int quarter = warp - kEpiWarp0;
+        uint8_t* my_stage = smemC + quarter * 2 * cfg::kEpiBufBytes;
+        int acc = 0; uint32_t acc_phase = 0;
+        uint32_t buf_idx = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+            int tap, m0, n0, kb0, kb1;
+            decode(item, tap, m0, n0, kb0, kb1);
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            const int row0 = m0 + quarter * 32;
+#pragma unroll 1
+            for (int ch = 0; ch < BN / 32; ++ch) {
+                uint8_t* buf = my_stage + (buf_idx & 1) * cfg::kEpiBufBytes;
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + ch * 32, r);
+                tmem_ld_wait();
+                uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4)) = make_uint4(r[j * 4], r[j * 4 + 1], r[j * 4 + 2], r[j * 4 + 3]);
+                fence_async_smem();
+                __syncwarp();
+                const int col = n0 + ch * 32;
+                if (lane == 0 && col < g.c_in && row0 < g.c_out && kb1 > kb0)
+                    tma_reduce_add_2d(&tmDW, buf, tap * g.c_in + col, row0);
+                if (lane == 0) tma_store_commit();
+                ++buf_idx;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + acc);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (lane == 0) tma_store_wait_read<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, cfg::kTmemCols);
+}
+
+// ---------------------------------------------------------------- host
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn =
+        reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(driver_fn("cuTensorMapEncodeTiled"));
+    return fn;
+}
+
+// NHWC activation [N][H][W][C] as a 4-D map {C, W, H, N}; box = {64 ch, bq, bp, bn} pixels traversed with `stride`
+static int make_act_map(CUtensorMap* tm, const void* ptr, int is_bf16, int N, int H, int W, int C, int bq, int bp, int bn,
+                        int stride, int box_c = 64) {
+    auto enc = get_encode();
+    B200DP_REQUIRE(enc != nullptr, "conv: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    cuuint32_t box[4] = {(cuuint32_t)box_c, (cuuint32_t)((bq - 1) * stride + 1), (cuuint32_t)((bp - 1) * stride + 1),
+                         (cuuint32_t)bn};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    B200DP_REQUIRE(box[1] <= 256 && box[2] <= 256 && box[3] <= 256, "conv: TMA box too large (%u,%u,%u)", box[1], box[2], box[3]);
+    CUresult r = enc(tm, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200DP_REQUIRE(r == CUDA_SUCCESS, "conv: cuTensorMapEncodeTiled(4d) failed (%d) N=%d H=%d W=%d C=%d box=(%u,%u,%u,%u) stride=%d",
+                   (int)r, N, H, W, C, box[0], box[1], box[2], box[3], stride);
+    return 0;
+}
+
+static int make_mat_map(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+                        int box_rows) {
+    auto enc = get_encode();
+    B200DP_REQUIRE(enc != nullptr, "conv: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200DP_REQUIRE(r == CUDA_SUCCESS, "conv: cuTensorMapEncodeTiled(2d) failed (%d)", (int)r);
+    return 0;
+}
+
+// pick the pixel box: full rows when they fit, several rows / images per tile up to 128 pixels
+static void pick_box(int n_img, int out_h, int out_w, int stride, int& bq, int& bp, int& bn) {
+    const int max_span = stride == 1 ? 256 : 128;       // (b-1)*stride+1 <= 256
+    bq = out_w < 128 ? out_w : 128;
+    if (bq > max_span) bq = max_span;
+    bp = 128 / bq;
+    if (bp > out_h) bp = out_h;
+    if (bp < 1) bp = 1;
+    bn = 1;
+    if (bq == out_w && bp == out_h) {
+        bn = 128 / (bq * bp);
+        if (bn > n_img) bn = n_img;
+        if (bn < 1) bn = 1;
+    }
+}
+
+template <int BN, bool kBMN, typename TOut>
+static int launch_fd(const CUtensorMap& ta, const CUtensorMap& tb, void* out, const float* bias, const Geom& g, int is_bf16,
+                     cudaStream_t s) {
+    auto kern = conv_fd_kernel<BN, kBMN, TOut>;
+    static bool configured = false;
+    if (!configured) {
+        B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
+        configured = true;
+    }
+    const int tiles = g.tiles_q * g.tiles_p * g.tiles_n * ((g.c_out + BN - 1) / BN);
+    const int grid = tiles < B200DP_SMS ? tiles : B200DP_SMS;
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16);
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace conv
+}  // namespace b200dp
+
+using namespace b200dp;
+using namespace b200dp::conv;
+
+// NHWC convolution forward (mode 0) or stride-1 input gradient (mode 1).
+//   mode 0: x = input  [N][H][W][Cin],  y = output [N][P][Q][Cout]
+//   mode 1: x = dY     [N][P][Q][Cout], y = dX     [N][H][W][Cin]   (stride must be 1)
+//   w = [Cout][R][S][Cin] (channels-last weight), 16-bit like x.  Cin and Cout multiples of 64
+//   on the reduction side (Cin for fprop, Cout for dgrad) and of 8 on the output side.
+extern "C" int b200dp_conv2d(int mode, const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin,
+                             int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, void* stream) {
+    B200DP_REQUIRE(x && w && y, "conv2d: null argument");
+    B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "conv2d: fp16 / bf16 only");
+    B200DP_REQUIRE(mode == 0 || (mode == 1 && stride == 1), "conv2d: dgrad is implemented for stride 1");
+    B200DP_REQUIRE(stride >= 1 && stride <= 2 && R >= 1 && S >= 1, "conv2d: unsupported stride / filter");
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    const int c_red = mode == 0 ? Cin : Cout, c_out = mode == 0 ? Cout : Cin;
+    B200DP_REQUIRE(c_red % 64 == 0, "conv2d: the reduction channel count (%d) must be a multiple of 64", c_red);
+    B200DP_REQUIRE(c_out % 8 == 0, "conv2d: the output channel count (%d) must be a multiple of 8", c_out);
+    bind_context_once();
+    const int is_bf16 = dtype == B200DP_BF16;
+    Geom g;
+    g.n_img = N; g.R = R; g.S = S; g.c_out = c_out; g.c_red = c_red; g.w_taps_ld = R * S * Cin;
+    int src_h, src_w;
+    if (mode == 0) { g.out_h = P; g.out_w = Q; g.stride = stride; g.off_h = -pad; g.off_w = -pad; g.tap_sign = 1; src_h = H; src_w = W; }
+    else           { g.out_h = H; g.out_w = W; g.stride = 1; g.off_h = pad; g.off_w = pad; g.tap_sign = -1; src_h = P; src_w = Q; }
+    pick_box(N, g.out_h, g.out_w, g.stride, g.bq, g.bp, g.bn);
+    g.tiles_q = (g.out_w + g.bq - 1) / g.bq;
+    g.tiles_p = (g.out_h + g.bp - 1) / g.bp;
+    g.tiles_n = (N + g.bn - 1) / g.bn;
+    const int BN = c_out <= 64 ? 64 : (c_out >= 256 ? 256 : 128);
+    CUtensorMap ta, tb;
+    int rc = make_act_map(&ta, x, is_bf16, N, src_h, src_w, c_red, g.bq, g.bp, g.bn, g.stride);
+    if (rc) return rc;
+    // weights as a matrix [Cout][R*S*Cin]: fprop reads it K-major (box 64 x BN rows), dgrad MN-major (box 64 x 64)
+    rc = mode == 0 ? make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, kBK, BN)
+                   : make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, 64, kBK);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+#define GO(BNv, MN, T) return launch_fd<BNv, MN, T>(ta, tb, y, bias, g, is_bf16, s)
+#define BY_T(BNv, MN) if (is_bf16) { GO(BNv, MN, __nv_bfloat16); } else { GO(BNv, MN, __half); }
+#define BY_MODE(BNv) if (mode == 0) { BY_T(BNv, false) } else { BY_T(BNv, true) }
+    if (BN == 256) { BY_MODE(256) } else if (BN == 128) { BY_MODE(128) } else { BY_MODE(64) }
+#undef BY_MODE
+#undef BY_T
+#undef GO
+    return 0;
+}
+
+// Weight gradient: dw[Cout][R][S][Cin] (fp32, channels-last weight layout) = sum over pixels of
+// dy[N][P][Q][Cout] (x) x[N][H][W][Cin] shifted by the tap.  Cin and Cout multiples of 8; stride 1 or 2.
+// The result is accumulated with TMA reduce-add: dw is zeroed here first unless accumulate != 0.
+extern "C" int b200dp_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R,
+                                   int S, int stride, int pad, b200dp_dtype dtype, int accumulate, void* stream) {
+    B200DP_REQUIRE(x && dy && dw, "conv2d_wgrad: null argument");
+    B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "conv2d_wgrad: fp16 / bf16 only");
+    B200DP_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "conv2d_wgrad: channel counts must be multiples of 8");
+    B200DP_REQUIRE(stride >= 1 && stride <= 2, "conv2d_wgrad: stride 1 or 2");
+    B200DP_REQUIRE(((int64_t)R * S * Cin * 4) % 16 == 0, "conv2d_wgrad: weight row pitch must be a multiple of 16 bytes");
+    bind_context_once();
+    const int is_bf16 = dtype == B200DP_BF16;
+    const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
+    WGeom g;
+    g.n_img = N; g.out_h = P; g.out_w = Q; g.c_out = Cout; g.c_in = Cin; g.R = R; g.S = S; g.stride = stride; g.pad = pad;
+    g.tiles_q = (Q + 7) / 8; g.tiles_p = (P + 7) / 8;
+    const int BN = Cin <= 64 ? 64 : (Cin >= 256 ? 256 : 128);
+    const int num_kb = N * g.tiles_p * g.tiles_q;
+    const int base_items = R * S * ((Cout + kBM - 1) / kBM) * ((Cin + BN - 1) / BN);
+    int splits = (2 * B200DP_SMS + base_items - 1) / base_items;         // ~2 waves of work items
+    if (splits > num_kb / 4) splits = num_kb / 4;
+    if (splits < 1) splits = 1;
+    g.kb_per = (num_kb + splits - 1) / splits;
+    g.splits = (num_kb + g.kb_per - 1) / g.kb_per;
+    CUtensorMap tdy, tx, tdw;
+    int rc = make_act_map(&tdy, dy, is_bf16, N, P, Q, Cout, 8, 8, 1, 1);
+    if (rc) return rc;
+    rc = make_act_map(&tx, x, is_bf16, N, H, W, Cin, 8, 8, 1, stride);
+    if (rc) return rc;
+    {   // fp32 dW as a matrix [Cout][R*S*Cin]; staging rows are 128 B = 32 floats
+        auto enc = get_encode();
+        cuuint64_t dims[2] = {(cuuint64_t)R * S * Cin, (cuuint64_t)Cout};
+        cuuint64_t strides[1] = {(cuuint64_t)R * S * Cin * 4};
+        cuuint32_t box[2] = {32, 32};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult r = enc(&tdw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, dw, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        B200DP_REQUIRE(r == CUDA_SUCCESS, "conv2d_wgrad: cuTensorMapEncodeTiled(dW) failed (%d)", (int)r);
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!accumulate) B200DP_CUDA(cudaMemsetAsync(dw, 0, (size_t)Cout * R * S * Cin * 4, s));
+    const int items = base_items * g.splits;
+    const int grid = items < B200DP_SMS ? items : B200DP_SMS;
+#define WG(BNv)                                                                                                  \
+    {                                                                                                            \
+        auto kern = conv_wgrad_kernel<BNv>;                                                                      \
+        static bool configured = false;                                                                          \
+        if (!configured) {                                                                                       \
+            B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BNv>::kSmemBytes)); \
+            configured = true;                                                                                   \
+        }                                                                                                        \
+        kern<<<grid, kThreads, Cfg<BNv>::kSmemBytes, s>>>(tdy, tx, tdw, g, is_bf16);                             \
+    }
+    if (BN == 256) WG(256) else if (BN == 128) WG(128) else WG(64)
+#undef WG
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}

@@ -206,6 +206,22 @@ int b200dp_gemm(const void* A, const void* B, void* C, const float* bias, int M,
                 int ldc, int a_mn, int b_mn, b200dp_dtype in_dtype, b200dp_dtype out_dtype, int accumulate_c,
                 void* stream);
 
+/* Implicit-GEMM NHWC convolution on tcgen05, operands fetched by TMA straight from the
+ * activation tensor (no im2col buffer).  mode 0: forward, y[N][P][Q][Cout] = conv(x[N][H][W][Cin], w);
+ * mode 1: input gradient of a stride-1 convolution, y = dX[N][H][W][Cin] from x = dY[N][P][Q][Cout].
+ * w is [Cout][R][S][Cin] (channels-last weight), same 16-bit dtype as x.  The reduction-side channel
+ * count must be a multiple of 64, the output-side one a multiple of 8; stride 1 or 2; square padding.
+ * Reference: the convolutions of the CNN models (Fairscale-DDP.py:74), left to cuDNN there. */
+int b200dp_conv2d(int mode, const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin,
+                  int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, void* stream);
+
+/* Weight gradient of the same convolution: dw[Cout][R][S][Cin] (fp32) = sum over pixels of
+ * dy[N][P][Q][Cout] x x[N][H][W][Cin] shifted by the tap; both operands fetched by 4-D TMA as
+ * MN-major tiles (pixels are the reduction), split over pixel boxes and combined with TMA reduce-add
+ * (so the summation order is not fixed).  dw is zeroed first unless accumulate != 0. */
+int b200dp_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
+                        int stride, int pad, b200dp_dtype dtype, int accumulate, void* stream);
+
 /* ------------------------------------------------------------------ peer-memory collectives
  * One kernel per rank; ranks meet at flag barriers in peer-mapped memory (csrc/collectives.cu
  * explains the protocol).  Every buffer argument is a table of B200DP_MAX_RANKS pointers:

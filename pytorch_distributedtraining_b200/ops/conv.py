@@ -1,21 +1,28 @@
-"""Convolution front end.
+"""Convolution front end (W7).
 
-1x1 / stride-1 convolutions on channels-last activations ARE matrix products
-(``Y[rows, Cout] = X[rows, Cin] W[Cout, Cin]^T`` with ``rows = N*H*W``), so forward, dgrad and
-wgrad run on the tcgen05 GEMM of ``csrc/gemm_sm100.cu`` without any data movement (W7 for the
-1x1 case; 32 of ResNet-50's 53 convolutions).  Other shapes (3x3, 7x7, strided) go to the
-implicit-GEMM kernel when it supports them and otherwise stay on cuDNN — `dispatch.conv_supported`
-is the single place that decides, and DESIGN.md lists what is still on the library path.
+On channels-last 16-bit activations:
+  * 1x1 / stride-1 convolutions ARE matrix products (``Y[rows, Cout] = X[rows, Cin] W^T``): forward,
+    dgrad and wgrad run on the tcgen05 GEMM (``csrc/gemm_sm100.cu``) with no data movement;
+  * every other supported shape (3x3, strided 1x1, 5x5 ...; Cin % 64 == 0) runs forward — and, for
+    stride 1, the input gradient — on the implicit-GEMM kernel of ``csrc/conv_sm100.cu`` (TMA fetches
+    the shifted / strided pixel boxes directly from the NHWC tensor, zero-filling the padding);
+  * weight gradients of all of these run on the wgrad kernel of the same file (both operands
+    MN-major by 4-D TMA, pixels as the reduction, split-K with TMA reduce-add into fp32);
+  * what is not covered yet stays on cuDNN and is listed in DESIGN.md: input gradients of strided
+    convolutions and first-layer convolutions (Cin = 3).
 
+``dispatch.conv_supported`` is the single place that decides.
 Parity target: the convolutions inside the CNN models (Fairscale-DDP.py:74; BASELINE ResNets).
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Optional
 
 import torch
 
-from ._lib import library_available
+from ._lib import check, library_available, require_library
+from .fused import DT, ptr, stream_ptr
 from .gemm import gemm
 
 _HALF = (torch.float16, torch.bfloat16)
@@ -25,55 +32,109 @@ def available() -> bool:
     return library_available()
 
 
+def _is_1x1_s1(mod) -> bool:
+    return mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.padding == (0, 0)
+
+
 def shape_supported(mod, x) -> bool:
-    """1x1, stride 1, no padding, channel counts that keep TMA row pitches 16-byte aligned."""
-    return (mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.padding == (0, 0)
-            and mod.in_channels % 8 == 0 and mod.out_channels % 8 == 0 and x.dim() == 4
-            and x.is_contiguous(memory_format=torch.channels_last))
+    if x.dim() != 4 or not x.is_contiguous(memory_format=torch.channels_last):
+        return False
+    if mod.out_channels % 8 != 0:
+        return False
+    if _is_1x1_s1(mod):
+        return mod.in_channels % 8 == 0
+    return (mod.in_channels % 64 == 0 and mod.stride[0] == mod.stride[1] and mod.stride[0] in (1, 2)
+            and mod.padding[0] == mod.padding[1] and isinstance(mod.padding[0], int)
+            and x.shape[2] + 2 * mod.padding[0] >= mod.kernel_size[0])
 
 
-class _Conv1x1Fn(torch.autograd.Function):
+def conv2d_raw(mode: int, x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], n: int, h: int, wd: int, cin: int,
+               cout: int, r: int, s: int, stride: int, pad: int) -> torch.Tensor:
+    """Direct call of ``b200dp_conv2d`` on NHWC-contiguous 16-bit tensors; returns NCHW-shaped,
+    channels-last output."""
+    lib = require_library()
+    p, q = (h + 2 * pad - r) // stride + 1, (wd + 2 * pad - s) // stride + 1
+    if mode == 0:
+        out = torch.empty((n, p, q, cout), dtype=x.dtype, device=x.device)
+    else:
+        out = torch.empty((n, h, wd, cin), dtype=x.dtype, device=x.device)
+    check(lib.b200dp_conv2d(mode, ptr(x), ptr(w), ptr(out), ptr(bias), n, h, wd, cin, cout, r, s, stride, pad, DT[x.dtype],
+                            stream_ptr(x.device)), "conv2d")
+    return out.permute(0, 3, 1, 2)
+
+
+def conv2d_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, n: int, h: int, wd: int, cin: int, cout: int, r: int, s: int,
+                     stride: int, pad: int) -> torch.Tensor:
+    """fp32 weight gradient in the channels-last weight layout ([Cout][R][S][Cin] memory)."""
+    lib = require_library()
+    dw = torch.empty((cout, r, s, cin), dtype=torch.float32, device=x.device)
+    check(lib.b200dp_conv2d_wgrad(ptr(x), ptr(dy), ptr(dw), n, h, wd, cin, cout, r, s, stride, pad, DT[x.dtype], 0,
+                                  stream_ptr(x.device)), "conv2d_wgrad")
+    return dw.permute(0, 3, 1, 2)
+
+
+class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, dtype):  # type: ignore[override]
+    def forward(ctx, x, weight, bias, dtype, stride, pad):  # type: ignore[override]
         n, cin, h, w = x.shape
-        cout = weight.shape[0]
+        cout, _, r, s = weight.shape
         if x.dtype != dtype:
             x = x.to(dtype)
-        x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)            # a view: channels-last memory is [rows, Cin]
-        w16 = weight.reshape(cout, cin)
-        if w16.dtype != dtype:
-            w16 = w16.to(dtype)
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        w16 = weight.to(dtype) if weight.dtype != dtype else weight
+        if not w16.is_contiguous(memory_format=torch.channels_last):
+            w16 = w16.contiguous(memory_format=torch.channels_last)       # memory = [Cout][R][S][Cin]
         b32 = None if bias is None else bias.float()
-        y2 = gemm(x2, w16, x2.shape[0], cout, cin, bias=b32)
-        ctx.save_for_backward(x2, w16)
-        ctx.dims = (n, cin, h, w, cout)
-        ctx.w_shape, ctx.w_dtype, ctx.has_bias = weight.shape, weight.dtype, bias is not None
-        return y2.view(n, h, w, cout).permute(0, 3, 1, 2)     # logically NCHW, physically NHWC
+        one = r == 1 and s == 1 and stride == 1 and pad == 0
+        if one:
+            x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)
+            y = gemm(x2, w16.reshape(cout, cin), x2.shape[0], cout, cin, bias=b32).view(n, h, w, cout).permute(0, 3, 1, 2)
+        else:
+            y = conv2d_raw(0, x, w16, b32, n, h, w, cin, cout, r, s, stride, pad)
+        ctx.save_for_backward(x, w16)
+        ctx.geom = (n, cin, h, w, cout, r, s, stride, pad, one)
+        ctx.w_dtype, ctx.has_bias = weight.dtype, bias is not None
+        return y
 
     @staticmethod
     def backward(ctx, dy):  # type: ignore[override]
-        x2, w16 = ctx.saved_tensors
-        n, cin, h, w, cout = ctx.dims
+        x, w16 = ctx.saved_tensors
+        n, cin, h, w, cout, r, s, stride, pad, one = ctx.geom
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
-        dy2 = dy.permute(0, 2, 3, 1).reshape(-1, cout)
-        if dy2.dtype != x2.dtype:
-            dy2 = dy2.to(x2.dtype)
-        rows = x2.shape[0]
         dx = dw = db = None
-        if ctx.needs_input_grad[0]:
-            dx = gemm(dy2, w16, rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
-        if ctx.needs_input_grad[1]:
-            dw = gemm(dy2, x2, cout, cin, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
-            dw = dw.view(cout, 1, 1, cin).permute(0, 3, 1, 2)  # channels-last strides, like the parameter
-            if ctx.w_dtype != torch.float32:
-                dw = dw.to(ctx.w_dtype)
+        need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        if one:
+            x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)
+            dy2 = dy.permute(0, 2, 3, 1).reshape(-1, cout)
+            rows = x2.shape[0]
+            if need_dx:
+                dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
+            if need_dw:
+                dw = gemm(dy2, x2, cout, cin, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
+                dw = dw.view(cout, 1, 1, cin).permute(0, 3, 1, 2)
+        else:
+            ours_dx = need_dx and stride == 1 and cout % 64 == 0 and cin % 8 == 0
+            if ours_dx:
+                dx = conv2d_raw(1, dy, w16, None, n, h, w, cin, cout, r, s, 1, pad)
+            if need_dw:
+                dw = conv2d_wgrad_raw(x, dy, n, h, w, cin, cout, r, s, stride, pad)
+            if need_dx and not ours_dx:
+                # library path for what the implicit-GEMM kernels do not cover yet (DESIGN.md): the input
+                # gradient of strided convolutions
+                dx = torch.ops.aten.convolution_backward(dy, x, w16, None, (stride, stride), (pad, pad), (1, 1), False,
+                                                         (0, 0), 1, (True, False, False))[0]
+        if dw is not None and dw.dtype != ctx.w_dtype:
+            dw = dw.to(ctx.w_dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = torch.sum(dy2, dim=0, dtype=torch.float32)
-        return dx, dw, db, None
+            db = torch.sum(dy, dim=(0, 2, 3), dtype=torch.float32)
+        return dx, dw, db, None, None, None
 
 
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], stride, padding, dilation, groups):
     dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
     with torch.autocast("cuda", enabled=False):
-        return _Conv1x1Fn.apply(x, weight, bias, dtype)
+        return _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]))

@@ -1,0 +1,102 @@
+"""Implicit-GEMM convolution (tcgen05 + TMA) vs torch's convolution in fp32 on the same 16-bit data."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+cuda = torch.device("cuda")
+
+CASES = [
+    # N, H, W, Cin, Cout, R, stride, pad
+    (2, 56, 56, 64, 64, 3, 1, 1),
+    (3, 28, 28, 128, 128, 3, 1, 1),
+    (4, 14, 14, 256, 256, 3, 1, 1),
+    (5, 7, 7, 512, 512, 3, 1, 1),
+    (2, 56, 56, 128, 128, 3, 2, 1),
+    (2, 56, 56, 256, 512, 1, 2, 0),
+    (1, 17, 23, 64, 72, 3, 1, 1),
+    (2, 16, 16, 64, 40, 5, 1, 2),
+    (1, 130, 130, 64, 64, 3, 1, 1),
+    (2, 9, 9, 192, 264, 3, 2, 1),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad", CASES)
+def test_conv_forward_matches_reference(dtype, N, H, W, Cin, Cout, R, stride, pad):
+    from pytorch_distributedtraining_b200.ops.conv import conv2d_raw
+    g = torch.Generator().manual_seed(N * 1000 + H)
+    x = (torch.randn(N, Cin, H, W, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) * 0.1).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    b = torch.randn(Cout, generator=g).to(cuda)
+    want = F.conv2d(x.float(), w.float(), b, stride=stride, padding=pad)
+    got = conv2d_raw(0, x, w, b, N, H, W, Cin, Cout, R, R, stride, pad)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape and got.is_contiguous(memory_format=torch.channels_last)
+    tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * (Cin * R * R) ** 0.5 * 0.05)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad", [c for c in CASES if c[6] == 1 and c[4] % 64 == 0])
+def test_conv_dgrad_matches_reference(dtype, N, H, W, Cin, Cout, R, stride, pad):
+    from pytorch_distributedtraining_b200.ops.conv import conv2d_raw
+    g = torch.Generator().manual_seed(N * 77 + H)
+    P = (H + 2 * pad - R) + 1
+    Q = (W + 2 * pad - R) + 1
+    dy = (torch.randn(N, Cout, P, Q, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) * 0.1).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    want = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float(), dy.float(), stride=1, padding=pad)
+    got = conv2d_raw(1, dy, w, None, N, H, W, Cin, Cout, R, R, 1, pad)
+    torch.cuda.synchronize()
+    tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * (Cout * R * R) ** 0.5 * 0.05)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad", CASES)
+def test_conv_wgrad_matches_reference(dtype, N, H, W, Cin, Cout, R, stride, pad):
+    from pytorch_distributedtraining_b200.ops.conv import conv2d_wgrad_raw
+    g = torch.Generator().manual_seed(N * 31 + H)
+    P = (H + 2 * pad - R) // stride + 1
+    Q = (W + 2 * pad - R) // stride + 1
+    x = (torch.randn(N, Cin, H, W, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    dy = (torch.randn(N, Cout, P, Q, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    want = torch.nn.grad.conv2d_weight(x.float(), (Cout, Cin, R, R), dy.float(), stride=stride, padding=pad)
+    got = conv2d_wgrad_raw(x, dy, N, H, W, Cin, Cout, R, R, stride, pad)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape and got.dtype == torch.float32
+    rel = ((got - want).norm() / want.norm()).item()
+    assert rel < 2e-3, rel
+    torch.testing.assert_close(got, want, rtol=1e-2, atol=1e-2 * (N * P * Q) ** 0.5 * 0.25)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_conv_module_autograd(dtype):
+    """Conv2d modules through autocast: forward/backward vs the same modules on the library path."""
+    import copy
+    from pytorch_distributedtraining_b200.ops import dispatch
+    from pytorch_distributedtraining_b200.ops.layers import Conv2d
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(Conv2d(64, 128, 3, 1, 1, bias=False), torch.nn.ReLU(), Conv2d(128, 128, 3, 2, 1, bias=True),
+                              torch.nn.ReLU(), Conv2d(128, 64, 1, 1, 0, bias=False)).to(cuda).to(memory_format=torch.channels_last)
+    ref = copy.deepcopy(net)
+    x = torch.randn(4, 64, 20, 20, device=cuda).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    xr = x.detach().clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=dtype):
+        y = net(x)
+    dispatch.disable("conv")
+    try:
+        with torch.autocast("cuda", dtype=dtype):
+            yr = ref(xr)
+    finally:
+        dispatch.enable("conv")
+    tol = 4e-2 if dtype == torch.bfloat16 else 8e-3
+    torch.testing.assert_close(y.float(), yr.float(), rtol=tol, atol=tol)
+    gr = torch.randn_like(yr)
+    y.backward(gr.to(y.dtype)); yr.backward(gr)
+    torch.testing.assert_close(x.grad, xr.grad, rtol=tol, atol=tol * 4)
+    for a, b in zip(net.parameters(), ref.parameters()):
+        # weight gradients sum thousands of 16-bit products on both sides: compare in relative L2
+        rel = ((a.grad - b.grad).norm() / b.grad.norm()).item()
+        assert rel < tol, rel
