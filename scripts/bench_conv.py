@@ -3,7 +3,7 @@ import os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 import torch
 import torch.nn.functional as F
-from pytorch_distributedtraining_b200.ops.conv import conv2d_raw
+from pytorch_distributedtraining_b200.ops.conv import conv2d_raw, conv2d_wgrad_raw
 
 dev = torch.device("cuda")
 torch.backends.cudnn.benchmark = True
@@ -47,6 +47,15 @@ for (H, Cin, Cout, R, st, pad) in shapes:
             return torch.ops.aten.convolution_backward(dys[i[0] % 2], xs[0], w, None, (1, 1), (pad, pad), (1, 1), False, (0, 0), 1,
                                                        (True, False, False))[0]
         r["dgrad_ours_ms"], r["dgrad_cudnn_ms"] = timeit(ours_d), timeit(cudnn_d)
+    dyw = torch.randn(N, Cout, P, P, device=dev).half().contiguous(memory_format=torch.channels_last)
+    def ours_w():
+        i[0] += 1
+        return conv2d_wgrad_raw(xs[i[0] % 2], dyw, N, H, H, Cin, Cout, R, R, st, pad)
+    def cudnn_w():
+        i[0] += 1
+        return torch.ops.aten.convolution_backward(dyw, xs[i[0] % 2], w, None, (st, st), (pad, pad), (1, 1), False, (0, 0), 1,
+                                                   (False, True, False))[1]
+    r["wgrad_ours_ms"], r["wgrad_cudnn_ms"] = timeit(ours_w), timeit(cudnn_w)
     r["fwd_ours_tflops"] = fl / r["fwd_ours_ms"] / 1e9
     r["fwd_cudnn_tflops"] = fl / r["fwd_cudnn_ms"] / 1e9
     rows.append(r)
