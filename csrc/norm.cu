@@ -82,7 +82,7 @@ __device__ __forceinline__ void bn_reduce_tail(float (&a)[8], float (&b)[8], int
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kBNThreads) bn_reduce_kernel(const T* __restrict__ x, int64_t rows, int C,
+__global__ void __launch_bounds__(kBNThreads, 4) bn_reduce_kernel(const T* __restrict__ x, int64_t rows, int C,
                                                                int tpr, int cgb, int rpb,
                                                                float* __restrict__ scratch,
                                                                unsigned int* __restrict__ counters,
@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
     const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t rows, int C, int tpr, int cgb,
     int rpb, const float* __restrict__ sums, float count, const float* __restrict__ gamma,
     const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
-    float* __restrict__ running_var, float* __restrict__ mean_out, float* __restrict__ invstd_out, int relu) {
+    float* __restrict__ running_var, float* __restrict__ mean_out, float* __restrict__ invstd_out, int relu,
+    uint8_t* __restrict__ mask_out) {
     const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
     const int cg = blockIdx.x * cgb + cgl;
     if (!(rl < rpb && cg < tpr)) return;
@@ -152,7 +153,39 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
         sh[k] = beta[c0 + k] - mean * sc[k];
     }
     const int64_t rstep = (int64_t)gridDim.y * rpb;
-    for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
+    auto finish = [&](float (&v)[8], int64_t r) {
+        if (relu) {
+            if (mask_out != nullptr) {      // 1 bit per element: the backward never has to read y
+                unsigned m = 0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) m |= (v[k] > 0.f ? 1u : 0u) << k;
+                mask_out[r * tpr + cg] = (uint8_t)m;
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+        }
+        store8<T>(y + r * C + c0, v);
+    };
+    int64_t r = (int64_t)blockIdx.y * rpb + rl;
+    // two rows per iteration: four independent 16-byte loads in flight per thread
+    for (; r + rstep < rows; r += 2 * rstep) {
+        float v0[8], v1[8];
+        load8<T>(x + r * C + c0, v0);
+        load8<T>(x + (r + rstep) * C + c0, v1);
+        if (res != nullptr) {
+            float r0[8], r1[8];
+            load8<T>(res + r * C + c0, r0);
+            load8<T>(res + (r + rstep) * C + c0, r1);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { v0[k] = v0[k] * sc[k] + sh[k] + r0[k]; v1[k] = v1[k] * sc[k] + sh[k] + r1[k]; }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { v0[k] = v0[k] * sc[k] + sh[k]; v1[k] = v1[k] * sc[k] + sh[k]; }
+        }
+        finish(v0, r);
+        finish(v1, r + rstep);
+    }
+    for (; r < rows; r += rstep) {
         float v[8];
         load8<T>(x + r * C + c0, v);
         if (res != nullptr) {
@@ -164,86 +197,127 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] = v[k] * sc[k] + sh[k];
         }
-        if (relu) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
-        }
-        store8<T>(y + r * C + c0, v);
+        finish(v, r);
     }
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kBNThreads) bn_bwd_reduce_kernel(
+__global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_reduce_kernel(
     const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, int64_t rows, int C, int tpr,
     int cgb, int rpb, const float* __restrict__ mean, const float* __restrict__ invstd, int relu,
-    float* __restrict__ scratch, unsigned int* __restrict__ counters, float* __restrict__ dsums) {
+    float* __restrict__ scratch, unsigned int* __restrict__ counters, float* __restrict__ dsums,
+    const uint8_t* __restrict__ mask) {
     const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
     const int cg = blockIdx.x * cgb + cgl;
     const bool active = rl < rpb && cg < tpr;
     float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (active) {
         const int c0 = cg * 8;
-        float mu[8], is[8];
-#pragma unroll
-        for (int k = 0; k < 8; ++k) { mu[k] = mean[c0 + k]; is[k] = invstd[c0 + k]; }
         const int64_t rstep = (int64_t)gridDim.y * rpb;
-        for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
-            float d[8], xv[8];
-            load8<T>(dy + r * C + c0, d);
-            load8<T>(x + r * C + c0, xv);
-            if (relu) {
+        auto masked = [&](float (&d)[8], int64_t r) {
+            if (!relu) return;
+            if (mask != nullptr) {
+                const unsigned m = mask[r * tpr + cg];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) d[k] = ((m >> k) & 1u) ? d[k] : 0.f;
+            } else {
                 float yv[8];
                 load8<T>(y + r * C + c0, yv);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) d[k] = yv[k] > 0.f ? d[k] : 0.f;
             }
+        };
+        // The loop keeps only sum(dz) and sum(dz * x) (16 accumulators): sum(dz * xhat) is recovered as
+        // (sum(dz*x) - mean * sum(dz)) * invstd afterwards.  Few live registers => two rows (four 16-byte
+        // loads) in flight per thread at 4 CTAs/SM, which is what the HBM latency needs.
+        int64_t r = (int64_t)blockIdx.y * rpb + rl;
+        for (; r + rstep < rows; r += 2 * rstep) {
+            float d0[8], x0[8], d1[8], x1[8];
+            load8<T>(dy + r * C + c0, d0);
+            load8<T>(x + r * C + c0, x0);
+            load8<T>(dy + (r + rstep) * C + c0, d1);
+            load8<T>(x + (r + rstep) * C + c0, x1);
+            masked(d0, r);
+            masked(d1, r + rstep);
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
-                a[k] += d[k];
-                b[k] += d[k] * (xv[k] - mu[k]) * is[k];
+                a[k] += d0[k] + d1[k];
+                b[k] += d0[k] * x0[k] + d1[k] * x1[k];
             }
         }
+        for (; r < rows; r += rstep) {
+            float d[8], xv[8];
+            load8<T>(dy + r * C + c0, d);
+            load8<T>(x + r * C + c0, xv);
+            masked(d, r);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { a[k] += d[k]; b[k] += d[k] * xv[k]; }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) b[k] = (b[k] - mean[c0 + k] * a[k]) * invstd[c0 + k];
     }
     bn_reduce_tail(a, b, C, cgb, rpb, rl, cgl, cg, active, scratch, counters, dsums);
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kBNThreads) bn_bwd_apply_kernel(
+__global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_apply_kernel(
     const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ dx,
     T* __restrict__ dres, int64_t rows, int C, int tpr, int cgb, int rpb, const float* __restrict__ mean,
     const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ dsums,
-    float count, int relu) {
+    float count, int relu, const uint8_t* __restrict__ mask) {
     const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
     const int cg = blockIdx.x * cgb + cgl;
     if (!(rl < rpb && cg < tpr)) return;
     const int c0 = cg * 8;
-    float mu[8], is[8], ga[8], m1[8], m2[8];
+    // dx = ga*(dz - m1 - xhat*m2) with xhat = (x - mu)*is  ==  A*dz + B*x + K  (three constants per channel)
+    float A[8], B[8], K[8];
     const float inv_n = 1.f / count;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        mu[k] = mean[c0 + k];
-        is[k] = invstd[c0 + k];
-        ga[k] = gamma[c0 + k] * is[k];
-        m1[k] = dsums[c0 + k] * inv_n;
-        m2[k] = dsums[C + c0 + k] * inv_n;
+        const float mu = mean[c0 + k], is = invstd[c0 + k];
+        const float ga = gamma[c0 + k] * is;
+        const float m1 = dsums[c0 + k] * inv_n, m2 = dsums[C + c0 + k] * inv_n;
+        A[k] = ga;
+        B[k] = -ga * m2 * is;
+        K[k] = -ga * m1 - B[k] * mu;
     }
     const int64_t rstep = (int64_t)gridDim.y * rpb;
-    for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
-        float d[8], xv[8];
-        load8<T>(dy + r * C + c0, d);
-        load8<T>(x + r * C + c0, xv);
-        if (relu) {
+    auto masked = [&](float (&d)[8], int64_t r) {
+        if (!relu) return;
+        if (mask != nullptr) {
+            const unsigned m = mask[r * tpr + cg];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) d[k] = ((m >> k) & 1u) ? d[k] : 0.f;
+        } else {
             float yv[8];
             load8<T>(y + r * C + c0, yv);
 #pragma unroll
             for (int k = 0; k < 8; ++k) d[k] = yv[k] > 0.f ? d[k] : 0.f;
         }
+    };
+    int64_t r = (int64_t)blockIdx.y * rpb + rl;
+    for (; r + rstep < rows; r += 2 * rstep) {
+        float d0[8], x0[8], d1[8], x1[8];
+        load8<T>(dy + r * C + c0, d0);
+        load8<T>(x + r * C + c0, x0);
+        load8<T>(dy + (r + rstep) * C + c0, d1);
+        load8<T>(x + (r + rstep) * C + c0, x1);
+        masked(d0, r);
+        masked(d1, r + rstep);
+        if (dres != nullptr) { store8<T>(dres + r * C + c0, d0); store8<T>(dres + (r + rstep) * C + c0, d1); }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { d0[k] = A[k] * d0[k] + B[k] * x0[k] + K[k]; d1[k] = A[k] * d1[k] + B[k] * x1[k] + K[k]; }
+        store8<T>(dx + r * C + c0, d0);
+        store8<T>(dx + (r + rstep) * C + c0, d1);
+    }
+    for (; r < rows; r += rstep) {
+        float d[8], xv[8];
+        load8<T>(dy + r * C + c0, d);
+        load8<T>(x + r * C + c0, xv);
+        masked(d, r);
         if (dres != nullptr) store8<T>(dres + r * C + c0, d);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float xhat = (xv[k] - mu[k]) * is[k];
-            d[k] = ga[k] * (d[k] - m1[k] - xhat * m2[k]);
-        }
+        for (int k = 0; k < 8; ++k) d[k] = A[k] * d[k] + B[k] * xv[k] + K[k];
         store8<T>(dx + r * C + c0, d);
     }
 }
@@ -398,13 +472,13 @@ int b200dp_bn_reduce(const void* x, int64_t rows, int C, b200dp_dtype dtype, flo
 int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
                     const float* sums, float count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, float* mean_out,
-                    float* invstd_out, int relu, void* stream) {
+                    float* invstd_out, int relu, unsigned char* relu_mask, void* stream) {
     B200DP_REQUIRE(x && y && sums && gamma && beta && mean_out && invstd_out, "bn_apply: null argument");
     BN_COMMON_CHECKS("bn_apply")
     B200DP_DISPATCH_HALF(dtype, T, {
         bn_apply_kernel<T, true><<<grid, kBNThreads, 0, s>>>((const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr,
                                                              g.cgb, g.rpb, sums, count, gamma, beta, eps, momentum,
-                                                             running_mean, running_var, mean_out, invstd_out, relu);
+                                                             running_mean, running_var, mean_out, invstd_out, relu, relu_mask);
     });
     B200DP_CHECK_LAUNCH();
     return 0;
@@ -418,7 +492,7 @@ int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, 
     B200DP_DISPATCH_HALF(dtype, T, {
         bn_apply_kernel<T, false><<<grid, kBNThreads, 0, s>>>(
             (const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr, g.cgb, g.rpb, nullptr, 1.f, gamma, beta, eps,
-            0.f, const_cast<float*>(running_mean), const_cast<float*>(running_var), nullptr, nullptr, relu);
+            0.f, const_cast<float*>(running_mean), const_cast<float*>(running_var), nullptr, nullptr, relu, nullptr);
     });
     B200DP_CHECK_LAUNCH();
     return 0;
@@ -426,14 +500,14 @@ int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, 
 
 int b200dp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t rows, int C, b200dp_dtype dtype,
                          const float* mean, const float* invstd, int relu, float* scratch,
-                         unsigned int* counter, float* dsums, void* stream) {
+                         unsigned int* counter, float* dsums, const unsigned char* relu_mask, void* stream) {
     B200DP_REQUIRE(dy && x && mean && invstd && scratch && counter && dsums, "bn_bwd_reduce: null argument");
-    B200DP_REQUIRE(!relu || y, "bn_bwd_reduce: relu needs the forward output y");
+    B200DP_REQUIRE(!relu || y || relu_mask, "bn_bwd_reduce: relu needs the forward output y or the relu mask");
     BN_COMMON_CHECKS("bn_bwd_reduce")
     B200DP_DISPATCH_HALF(dtype, T, {
         bn_bwd_reduce_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, g.tpr,
                                                             g.cgb, g.rpb, mean, invstd, relu, scratch, counter,
-                                                            dsums);
+                                                            dsums, relu_mask);
     });
     B200DP_CHECK_LAUNCH();
     return 0;
@@ -441,14 +515,14 @@ int b200dp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t r
 
 int b200dp_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int64_t rows, int C,
                         b200dp_dtype dtype, const float* mean, const float* invstd, const float* gamma,
-                        const float* dsums, float count, int relu, void* stream) {
+                        const float* dsums, float count, int relu, const unsigned char* relu_mask, void* stream) {
     B200DP_REQUIRE(dy && x && dx && mean && invstd && gamma && dsums, "bn_bwd_apply: null argument");
-    B200DP_REQUIRE(!relu || y, "bn_bwd_apply: relu needs the forward output y");
+    B200DP_REQUIRE(!relu || y || relu_mask, "bn_bwd_apply: relu needs the forward output y or the relu mask");
     BN_COMMON_CHECKS("bn_bwd_apply")
     B200DP_DISPATCH_HALF(dtype, T, {
         bn_bwd_apply_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)y, (const T*)x, (T*)dx, (T*)dres,
                                                            rows, C, g.tpr, g.cgb, g.rpb, mean, invstd, gamma, dsums,
-                                                           count, relu);
+                                                           count, relu, relu_mask);
     });
     B200DP_CHECK_LAUNCH();
     return 0;

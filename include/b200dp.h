@@ -162,24 +162,37 @@ int b200dp_mse(const void* a, const void* b, int64_t n, b200dp_dtype dtype, void
  *      (multi-GPU: all-reduce `dsums`)
  *   4. b200dp_bn_bwd_apply     dx = gamma*invstd*(dz - mean(dz) - xhat*mean(dz*xhat)); dres = dz
  *
- * scratch for the two reductions: b200dp_bn_scratch_floats(rows, C) floats + one zeroed uint32. */
+ * relu_mask (optional, rows*C/8 bytes): bn_apply records y > 0 as one bit per element and the
+ * two backward kernels read that instead of y (1/16 of the bytes); pass NULL to use y itself.
+ * scratch for the two reductions: b200dp_bn_scratch_floats(rows, C) floats + 64 zeroed uint32
+ * completion counters (one per 256-channel column). */
 int64_t b200dp_bn_scratch_floats(int64_t rows, int C);
 int b200dp_bn_reduce(const void* x, int64_t rows, int C, b200dp_dtype dtype, float* scratch,
                      unsigned int* counter, float* sums, void* stream);
 int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
                     const float* sums, float count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, float* mean_out,
-                    float* invstd_out, int relu, void* stream);
+                    float* invstd_out, int relu, unsigned char* relu_mask, void* stream);
 /* inference: y = act(gamma*(x-running_mean)*rsqrt(running_var+eps) + beta + residual) */
 int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
                     const float* gamma, const float* beta, const float* running_mean,
                     const float* running_var, float eps, int relu, void* stream);
 int b200dp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t rows, int C,
                          b200dp_dtype dtype, const float* mean, const float* invstd, int relu,
-                         float* scratch, unsigned int* counter, float* dsums, void* stream);
+                         float* scratch, unsigned int* counter, float* dsums, const unsigned char* relu_mask,
+                         void* stream);
 int b200dp_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, void* dres, int64_t rows,
                         int C, b200dp_dtype dtype, const float* mean, const float* invstd,
-                        const float* gamma, const float* dsums, float count, int relu, void* stream);
+                        const float* gamma, const float* dsums, float count, int relu,
+                        const unsigned char* relu_mask, void* stream);
+
+/* NHWC max pooling (reference: the stem pooling of the CNN models).  The forward also writes one
+ * byte per output element — the winning tap's position in the window — which turns the backward
+ * into a gather with no index tensor, zero-fill or atomics.  C must be a multiple of 8. */
+int b200dp_maxpool_fwd(const void* x, void* y, unsigned char* idx, int N, int H, int W, int C, int K, int stride, int pad,
+                       b200dp_dtype dtype, void* stream);
+int b200dp_maxpool_bwd(const void* dy, const unsigned char* idx, void* dx, int N, int H, int W, int C, int K, int stride,
+                       int pad, b200dp_dtype dtype, void* stream);
 
 /* LayerNorm over the last dimension, x[rows, D] (reference: SwinIR / ViT blocks,
  * Stoke-DDP.py:206-208).  mean/rstd are float[rows].  dgamma/dbeta are accumulated via

@@ -19,7 +19,7 @@ from typing import Callable, List, Optional, Type, Union
 import torch
 import torch.nn as nn
 
-from ..ops.layers import BatchNormAct2d, Conv2d, Linear
+from ..ops.layers import BatchNormAct2d, Conv2d, Linear, MaxPool2d
 
 __all__ = ["ResNet", "resnet18", "resnet34", "resnet50", "resnet101"]
 
@@ -80,7 +80,7 @@ class ResNet(nn.Module):
             self.maxpool: nn.Module = nn.Identity()
         else:
             self.conv1 = Conv2d(3, 64, kernel_size=7, stride=2, padding=3, bias=False)
-            self.maxpool = nn.MaxPool2d(kernel_size=3, stride=2, padding=1)
+            self.maxpool = MaxPool2d(kernel_size=3, stride=2, padding=1)
         self.bn1 = BatchNormAct2d(64, act="relu")
         self.layer1 = self._make_layer(block, 64, layers[0])
         self.layer2 = self._make_layer(block, 128, layers[1], stride=2)

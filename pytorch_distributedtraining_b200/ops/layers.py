@@ -86,3 +86,48 @@ class LayerNorm(nn.LayerNorm):
             from . import norm as _norm
             return _norm.layer_norm(x, self.weight, self.bias, self.eps)
         return super().forward(x)
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):  # type: ignore[override]
+        import ctypes
+        from ._lib import check, require_library
+        from .fused import DT, ptr, stream_ptr
+        lib = require_library()
+        n, c, h, w = x.shape
+        p, q = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+        y = torch.empty((n, p, q, c), dtype=x.dtype, device=x.device)
+        idx = torch.empty((n, p, q, c), dtype=torch.uint8, device=x.device)
+        check(lib.b200dp_maxpool_fwd(ptr(x), ptr(y), ptr(idx), n, h, w, c, k, stride, pad, DT[x.dtype], stream_ptr(x.device)),
+              "maxpool_fwd")
+        ctx.save_for_backward(idx)
+        ctx.geom = (n, c, h, w, k, stride, pad)
+        return y.permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):  # type: ignore[override]
+        from ._lib import check, require_library
+        from .fused import DT, ptr, stream_ptr
+        lib = require_library()
+        (idx,) = ctx.saved_tensors
+        n, c, h, w, k, stride, pad = ctx.geom
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty((n, h, w, c), dtype=dy.dtype, device=dy.device)
+        check(lib.b200dp_maxpool_bwd(ptr(dy), ptr(idx), ptr(dx), n, h, w, c, k, stride, pad, DT[dy.dtype], stream_ptr(dy.device)),
+              "maxpool_bwd")
+        return dx.permute(0, 3, 1, 2), None, None, None
+
+
+class MaxPool2d(nn.MaxPool2d):
+    """Max pooling; fused NHWC kernels (1-byte argmax, gather backward) on CUDA channels-last 16-bit input."""
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        k, st, pd = self.kernel_size, self.stride, self.padding
+        simple = all(isinstance(v, int) for v in (k, st, pd)) and self.dilation == 1 and not self.ceil_mode \
+            and not self.return_indices
+        if (x.is_cuda and simple and x.dim() == 4 and x.dtype in (torch.float16, torch.bfloat16) and x.shape[1] % 8 == 0
+                and x.is_contiguous(memory_format=torch.channels_last) and dispatch.enabled("pool") and dispatch._lib_ok()):
+            return _MaxPoolFn.apply(x, k, st, pd)
+        return super().forward(x)

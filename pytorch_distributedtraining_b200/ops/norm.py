@@ -53,11 +53,12 @@ class _BatchNormActFn(torch.autograd.Function):
         y = torch.empty_like(x)
         mean = torch.empty(C, dtype=torch.float32, device=dev)
         invstd = torch.empty(C, dtype=torch.float32, device=dev)
+        mask = torch.empty(rows * (C // 8), dtype=torch.uint8, device=dev) if relu else None   # 1 bit / element
         check(lib.b200dp_bn_apply(ptr(x), ptr(residual), ptr(y), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(sums),
                                   ctypes.c_float(count), ptr(weight), ptr(bias), ctypes.c_float(eps),
                                   ctypes.c_float(momentum), ptr(running_mean), ptr(running_var), ptr(mean),
-                                  ptr(invstd), ctypes.c_int(int(relu)), st), "bn_apply")
-        ctx.save_for_backward(x, y if relu else None, weight, mean, invstd)
+                                  ptr(invstd), ctypes.c_int(int(relu)), ptr(mask), st), "bn_apply")
+        ctx.save_for_backward(x, mask, weight, mean, invstd)
         ctx.relu, ctx.group, ctx.world, ctx.count = relu, group, world, count
         ctx.has_res = residual is not None
         return y
@@ -65,7 +66,7 @@ class _BatchNormActFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):  # type: ignore[override]
         lib = require_library()
-        x, y, weight, mean, invstd = ctx.saved_tensors
+        x, mask, weight, mean, invstd = ctx.saved_tensors
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
         rows, C = _rows_view(x)
@@ -76,8 +77,8 @@ class _BatchNormActFn(torch.autograd.Function):
         dsums = torch.empty(2 * C, dtype=torch.float32, device=dev)
         st = stream_ptr(dev)
         relu = ctypes.c_int(int(ctx.relu))
-        check(lib.b200dp_bn_bwd_reduce(ptr(dy), ptr(y), ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(mean),
-                                       ptr(invstd), relu, ptr(scratch), ptr(ws.counters), ptr(dsums), st),
+        check(lib.b200dp_bn_bwd_reduce(ptr(dy), None, ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(mean),
+                                       ptr(invstd), relu, ptr(scratch), ptr(ws.counters), ptr(dsums), ptr(mask), st),
               "bn_bwd_reduce")
         # parameter gradients are the LOCAL sums (the data-parallel engine averages them)
         dbias = dsums[:C].clone()
@@ -86,9 +87,9 @@ class _BatchNormActFn(torch.autograd.Function):
             _allreduce_stats(dsums, ctx.group)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res else None
-        check(lib.b200dp_bn_bwd_apply(ptr(dy), ptr(y), ptr(x), ptr(dx), ptr(dres), ctypes.c_int64(rows), ctypes.c_int(C),
+        check(lib.b200dp_bn_bwd_apply(ptr(dy), None, ptr(x), ptr(dx), ptr(dres), ctypes.c_int64(rows), ctypes.c_int(C),
                                       dt, ptr(mean), ptr(invstd), ptr(weight), ptr(dsums), ctypes.c_float(ctx.count),
-                                      relu, st), "bn_bwd_apply")
+                                      relu, ptr(mask), st), "bn_bwd_apply")
         return dx, dres, dweight.to(weight.dtype), dbias.to(weight.dtype), None, None, None, None, None, None, None
 
 

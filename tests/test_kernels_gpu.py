@@ -265,3 +265,21 @@ def test_resnet18_fused_path_matches_stock_ops():
     print(f"grad rel err vs fp32: fused {e_fused:.4f}, stock fp16 {e_stock:.4f}")
     torch.testing.assert_close(l1, l3, rtol=2e-2, atol=2e-2)
     assert e_fused < max(1.5 * e_stock, 2e-2), (e_fused, e_stock)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape,k,st,pd", [((4, 64, 112, 112), 3, 2, 1), ((2, 16, 9, 11), 3, 2, 1), ((3, 8, 8, 8), 2, 2, 0),
+                                            ((2, 24, 13, 7), 3, 1, 1)])
+def test_maxpool_matches_torch_including_ties(dtype, shape, k, st, pd):
+    from pytorch_distributedtraining_b200.ops.layers import MaxPool2d
+    torch.manual_seed(3)
+    # post-ReLU style input: many exact ties (zeros), where the argmax convention matters
+    x = torch.relu(torch.randn(shape, device=cuda)).to(dtype).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    xr = x.detach().clone().requires_grad_(True)
+    pool = MaxPool2d(k, st, pd)
+    y = pool(x)
+    yr = F.max_pool2d(xr, k, st, pd)
+    assert torch.equal(y, yr)
+    g = torch.randn_like(yr)
+    y.backward(g); yr.backward(g)
+    torch.testing.assert_close(x.grad.float(), xr.grad.float(), rtol=1e-2, atol=1e-2)
