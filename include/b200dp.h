@@ -312,6 +312,20 @@ int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* m
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
                                 int slot_floats, void* const* call_counter, void* stream);
 
+/* All-gather fused into the consuming GEMM (W4): Y[M,N] = X[M,K] W^T (+bias) with W[N,K] row-sharded
+ * over the ranks (w_shards[p] = rank p's [rows_per_rank][K] shard in peer-mapped memory).  One kernel:
+ * the otherwise idle warp of every CTA pulls chunks of 1-8 weight rows over NVLink into the local copy
+ * w_full and bumps the arrival counter of the chunk's weight tile; the TMA producer waits until the
+ * tile it is about to consume is complete.
+ * Locally owned tiles are computed first, so remote transfers overlap the math; each remote byte is
+ * read once per rank.  tile_flags: ceil(N/128)+1 words, zero before the
+ * first call (the kernel leaves them zero again; one buffer per stream).  ctx == NULL: shards are
+ * local (tests).  Reference: FSDP's parameter all-gather / OSS's broadcast followed by the first
+ * consuming linear (Stoke fairscale_fsdp / fairscale_oss flags), two NCCL + cuBLAS calls there. */
+int b200dp_gemm_gather(const void* X, const void* const* w_shards, void* w_full, void* Y, const float* bias, int M, int N,
+                       int K, int ldx, int ldy, int world, int rank, int rows_per_rank, b200dp_dtype dtype,
+                       unsigned int* tile_flags, const b200dp_peer_ctx* ctx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -103,3 +103,30 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], 
     elif act == "relu":
         y = F.relu(y)
     return y
+
+
+_GATHER_FLAGS: dict = {}
+
+
+def gemm_gather(x: torch.Tensor, shard_ptrs, w_full: torch.Tensor, rank: int, world: int, rows_per_rank: int,
+                bias: Optional[torch.Tensor] = None, ctx=None, tile_flags: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``Y = X @ W.T (+ bias)`` with ``W`` row-sharded over ranks: the all-gather of ``W`` happens inside
+    the GEMM kernel (W4).  ``shard_ptrs``: per-rank shard addresses as mapped here (ints or tensors);
+    ``w_full``: local ``[N, K]`` buffer the kernel fills; ``ctx``: ``ops.collectives.PeerContext`` or
+    ``None`` when every shard is local."""
+    from .collectives import table
+    lib = require_library()
+    M, K = x.shape
+    N = w_full.shape[0]
+    assert x.dtype in _HALF and w_full.dtype == x.dtype and x.stride(1) == 1 and w_full.is_contiguous()
+    y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+    if tile_flags is None:
+        # arrival counters, one set per (device, stream): zero at creation, the kernel leaves them zero
+        key = (x.device.index, torch.cuda.current_stream(x.device).cuda_stream, (N + 127) // 128 + 1)
+        tile_flags = _GATHER_FLAGS.get(key)
+        if tile_flags is None:
+            tile_flags = _GATHER_FLAGS[key] = torch.zeros(key[2], dtype=torch.int32, device=x.device)
+    check(lib.b200dp_gemm_gather(ptr(x), table(shard_ptrs), ptr(w_full), ptr(y), ptr(bias), M, N, K, x.stride(0), y.stride(0),
+                                 world, rank, rows_per_rank, DT[x.dtype], ptr(tile_flags),
+                                 ctypes.byref(ctx.c) if ctx is not None else None, stream_ptr(x.device)), "gemm_gather")
+    return y

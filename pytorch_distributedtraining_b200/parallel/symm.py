@@ -45,7 +45,7 @@ class SymmBuffer:
 
 
 class PeerArena:
-    def __init__(self, group: Any, device: torch.device, nbytes: int, max_blocks: int = 128, timeout_s: float = 30.0):
+    def __init__(self, group: Any, device: torch.device, nbytes: int, max_blocks: int = 160, timeout_s: float = 30.0):
         import torch.distributed._symmetric_memory as symm_mem
         self.group, self.device = group, device
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)

@@ -190,7 +190,7 @@ def _w_real(rank, world):
     from pytorch_distributedtraining_b200.ops import collectives as C
     from pytorch_distributedtraining_b200.parallel.symm import PeerArena, SmallAllReduce
     dev = torch.device("cuda", rank)
-    arena = PeerArena(dist.group.WORLD, dev, 256 << 20, max_blocks=64, timeout_s=20.0)
+    arena = PeerArena(dist.group.WORLD, dev, 256 << 20, max_blocks=160, timeout_s=20.0)
     ctx = arena.context("main")
     ctx.barrier(blocks=16, rounds=10)
     for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 2e-2), (torch.float16, 2e-3)):
@@ -240,6 +240,23 @@ def _w_real(rank, world):
         assert small(v, None)
         torch.cuda.synchronize()
         assert torch.all(v == sum(r + k for r in range(world)))
+    # W4: all-gather of row-sharded weights fused into the GEMM, shards read over NVLink
+    from pytorch_distributedtraining_b200.ops.gemm import gemm_gather
+    N_, K_, M_ = 128 * 2 * world, 512, 2048
+    rpr = N_ // world
+    g = torch.Generator().manual_seed(5)
+    w_all = (torch.randn(N_, K_, generator=g) * 0.5).bfloat16().to(dev)
+    xg = (torch.randn(M_, K_, generator=g) * 0.5).bfloat16().to(dev)
+    shard = arena.alloc(rpr * K_, torch.bfloat16)
+    for it in range(2):
+        shard.tensor.copy_((w_all[rank * rpr:(rank + 1) * rpr] * (it + 1)).reshape(-1))
+        torch.cuda.synchronize(); dist.barrier()
+        w_full = torch.zeros(N_, K_, dtype=torch.bfloat16, device=dev)
+        y = gemm_gather(xg, shard.ptrs, w_full, rank, world, rpr, ctx=ctx)
+        torch.cuda.synchronize()
+        assert torch.equal(w_full, w_all * (it + 1))
+        torch.testing.assert_close(y.float(), xg.float() @ (w_all * (it + 1)).float().t(), rtol=2e-2, atol=0.3)
+        dist.barrier()
     assert not arena.timed_out()
     if rank == 0:
         print(f"[real] world={world} multicast={'yes' if arena.mc_base else 'no'} all peer collectives match NCCL")

@@ -95,3 +95,24 @@ def test_gemm_split_k_wgrad_shapes(dtype, M, N, K):
     out = torch.full((M, N), 2.0, device=cuda)
     gemm(a, b, M, N, K, a_mn=True, b_mn=True, out=out, accumulate=True)
     torch.testing.assert_close(out, want + 2.0, rtol=2e-3, atol=2e-3 * K ** 0.5 * 0.25)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K,world", [(4096, 3072, 768, 8), (1000, 768, 3072, 4), (300, 512, 264, 2), (25216, 2304, 768, 8)])
+def test_gemm_with_fused_gather_of_row_sharded_weights(dtype, M, N, K, world):
+    """W4 on one GPU: the shards are separate local buffers; the kernel must assemble W tile by tile
+    (flag per tile) while it computes, starting with the tiles "this rank" owns."""
+    from pytorch_distributedtraining_b200.ops.gemm import gemm_gather
+    x, w = _mk(M, K, dtype, 11), _mk(N, K, dtype, 12)
+    bias = torch.randn(N, device=cuda)
+    rpr = (N + world - 1) // world
+    shards = [w[r * rpr:(r + 1) * rpr].clone() for r in range(world)]
+    shards = [s if s.shape[0] == rpr else torch.cat([s, torch.zeros(rpr - s.shape[0], K, dtype=dtype, device=cuda)]) for s in shards]
+    want = x.float() @ w.float().t() + bias
+    for rank in (0, world - 1):
+        w_full = torch.full((N, K), float("nan"), dtype=dtype, device=cuda)
+        got = gemm_gather(x, shards, w_full, rank, world, rpr, bias=bias)
+        torch.cuda.synchronize()
+        assert torch.equal(w_full, w), "the gathered copy of W must be exact"
+        tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+        torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * max(1.0, K ** 0.5 * 0.25))
