@@ -87,6 +87,16 @@ __device__ __forceinline__ void store8<float>(float* p, const float (&in)[8]) {
     reinterpret_cast<float4*>(p)[1] = make_float4(in[4], in[5], in[6], in[7]);
 }
 
+// two packed 16-bit values -> float2 (the float instantiation exists only so templates compile)
+template <typename T> __device__ __forceinline__ float2 unpack2(uint32_t u);
+template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t u) {
+    return __half22float2(*reinterpret_cast<const __half2*>(&u));
+}
+template <> __device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t u) {
+    return make_float2(__uint_as_float(u << 16), __uint_as_float(u & 0xffff0000u));
+}
+template <> __device__ __forceinline__ float2 unpack2<float>(uint32_t u) { return make_float2(__uint_as_float(u), 0.f); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -56,12 +56,14 @@ template <int BN> struct Cfg {
     static constexpr int kTmemCols = 2 * BN;
 };
 
-// fprop (kBMN = false) and stride-1 dgrad (kBMN = true)
-template <int BN, bool kBMN, typename TOut>
+// fprop (kBMN = false) and stride-1 dgrad (kBMN = true).  kStats (fprop): the epilogue also adds the
+// per-channel sum / sum of squares of the stored values into colstats[0:Cout] / [Cout:2Cout] — the
+// batch statistics of the BatchNorm that follows — so that layer skips its own pass over the tensor.
+template <int BN, bool kBMN, typename TOut, bool kStats = false>
 __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_constant__ CUtensorMap tmA,
                                                               const __grid_constant__ CUtensorMap tmB,
                                                               TOut* __restrict__ out, const float* __restrict__ bias,
-                                                              Geom g, int is_bf16) {
+                                                              Geom g, int is_bf16, float* __restrict__ colstats) {
     using cfg = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -165,10 +167,35 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
         const int quarter = warp - kEpiWarp0;
         uint8_t* buf = smemC + quarter * cfg::kEpiBufBytes;
         int acc = 0; uint32_t acc_phase = 0;
+        constexpr int kChunks = BN / 64;
+        // channel statistics: lane l owns channels 2l, 2l+1 of every 64-channel chunk of the current channel tile
+        float st[kStats ? kChunks * 4 : 1];
+        int st_n0 = -1;
+#pragma unroll
+        for (int i = 0; i < (kStats ? kChunks * 4 : 1); ++i) st[i] = 0.f;
+        auto flush_stats = [&]() {
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) {
+                    const int col = st_n0 + ch * 64 + 2 * lane;
+                    if (col < g.c_out) {          // c_out is even (multiple of 8): col + 1 is valid too
+                        atomicAdd(colstats + col, st[ch * 4 + 0]);
+                        atomicAdd(colstats + col + 1, st[ch * 4 + 1]);
+                        atomicAdd(colstats + g.c_out + col, st[ch * 4 + 2]);
+                        atomicAdd(colstats + g.c_out + col + 1, st[ch * 4 + 3]);
+                    }
+                    st[ch * 4 + 0] = st[ch * 4 + 1] = st[ch * 4 + 2] = st[ch * 4 + 3] = 0.f;
+                }
+            }
+        };
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             int n0, p0, q0;
             decode_m(tile % num_m, n0, p0, q0);
             const int nt0 = (tile / num_m) * BN;
+            if (kStats && nt0 != st_n0) {
+                if (st_n0 >= 0) flush_stats();
+                st_n0 = nt0;
+            }
             mbar_wait(tmem_full + acc, acc_phase);
             tc_fence_after();
             // this lane's row of the tile -> output pixel
@@ -177,8 +204,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
             const int n = n0 + bn_i, p = p0 + bp_i, q = q0 + bq_i;
             const bool valid = t < rows_valid && n < g.n_img && p < g.out_h && q < g.out_w;
             const long long pix = valid ? (((long long)n * g.out_h + p) * g.out_w + q) : -1;
-#pragma unroll 1
-            for (int ch = 0; ch < BN / 64; ++ch) {
+            auto do_chunk = [&](const int ch) {
                 __syncwarp();
 #pragma unroll
                 for (int l = 0; l < 2; ++l) {
@@ -193,6 +219,10 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
                         const int gcol = nt0 + colbase;
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += (gcol + j < g.c_out) ? __ldg(bias + gcol + j) : 0.f;
+                    }
+                    if (kStats && !valid) {       // pixels outside the image must not count
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = 0.f;
                     }
                     uint8_t* rowp = buf + lane * 128;
 #pragma unroll
@@ -214,12 +244,33 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
                     if (rpix >= 0 && col0 + chunk * 8 < g.c_out)
                         *reinterpret_cast<uint4*>(out + rpix * g.c_out + col0 + chunk * 8) = val;
                 }
+                if constexpr (kStats) {
+                    // lane l sums the 4-byte word of channels 2l, 2l+1 over the 32 staged rows
+                    const int j = lane >> 2, w = lane & 3;
+                    float s0 = 0.f, s1 = 0.f, q0s = 0.f, q1s = 0.f;
+#pragma unroll 8
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const uint32_t u = *reinterpret_cast<const uint32_t*>(buf + rr * 128 + ((j ^ (rr & 7)) << 4) + w * 4);
+                        const float2 f = unpack2<TOut>(u);
+                        s0 += f.x; s1 += f.y;
+                        q0s = fmaf(f.x, f.x, q0s); q1s = fmaf(f.y, f.y, q1s);
+                    }
+                    st[ch * 4 + 0] += s0; st[ch * 4 + 1] += s1; st[ch * 4 + 2] += q0s; st[ch * 4 + 3] += q1s;
+                }
+            };
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
+            } else {
+#pragma unroll 1
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tmem_empty + acc);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (kStats && st_n0 >= 0) flush_stats();
     }
     tc_fence_before();
     __syncthreads();
@@ -382,6 +433,167 @@ __global__ void __launch_bounds__(kThreads, 1) conv_wgrad_kernel(const __grid_co
     if (warp == 2) tmem_dealloc(tmem_base, cfg::kTmemCols);
 }
 
+// ---------------------------------------------------------------- wgrad, 3 x S filters, stride 1
+// Row-grouped variant: one work item produces the THREE taps (r = 0,1,2) of one filter column s.
+// Per 8 x 8 pixel box it loads dY once and an X patch of 10 x 8 pixels (two halo rows); because a
+// patch row is 8 pixels x 128 B = 1024 B — one swizzle atom — the operand for tap r is the same
+// patch read from byte offset r * 1024, so the three MMAs of a k-step share both loads.  L2 -> SM
+// traffic per FLOP drops ~2.7x against the tap-at-a-time kernel above, which is what bounds it.
+// The 3 x BN fp32 accumulators fill TMEM (single-buffered); items are long (>= 16 k-blocks).
+template <int BN> struct WCfg {
+    static constexpr int kPatchBytes = 10 * 8 * 128;                    // per 64-channel chunk of X
+    static constexpr int kABytes = kBM * kBK * 2;
+    static constexpr int kBBytes = (BN / 64) * kPatchBytes;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = BN == 128 ? 5 : 7;
+    static constexpr int kEpiBufBytes = 32 * 128;
+    static constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 + 256;
+    static constexpr int kTmemCols = BN == 128 ? 512 : 256;             // 3 * BN rounded up to a power of two
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kThreads, 1) conv_wgrad_rows_kernel(const __grid_constant__ CUtensorMap tmDY,
+                                                                      const __grid_constant__ CUtensorMap tmX,
+                                                                      const __grid_constant__ CUtensorMap tmDW, WGeom g,
+                                                                      int is_bf16) {
+    using cfg = WCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemC = smem + cfg::kStages * cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + cfg::kEpiBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + cfg::kStages;
+    uint64_t* tmem_full = bars + 2 * cfg::kStages;
+    uint64_t* tmem_empty = tmem_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = (g.c_out + kBM - 1) / kBM, num_n = (g.c_in + BN - 1) / BN;
+    const int boxes_per_img = g.tiles_p * g.tiles_q;
+    const int num_kb = g.n_img * boxes_per_img;
+    const int num_items = g.S * num_m * num_n * g.splits;
+
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmDY); tma_prefetch_desc(&tmX); tma_prefetch_desc(&tmDW); }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < cfg::kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        mbar_init(tmem_full, 1);
+        mbar_init(tmem_empty, 4);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, cfg::kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode = [&](int item, int& s, int& m0, int& n0, int& kb0, int& kb1) {
+        const int split = item % g.splits;
+        int rest = item / g.splits;
+        n0 = (rest % num_n) * BN; rest /= num_n;
+        m0 = (rest % num_m) * kBM; rest /= num_m;
+        s = rest;
+        kb0 = split * g.kb_per;
+        kb1 = min(num_kb, kb0 + g.kb_per);
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                int s, m0, n0, kb0, kb1;
+                decode(item, s, m0, n0, kb0, kb1);
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    const int img = kb / boxes_per_img, bx = kb % boxes_per_img;
+                    const int p0 = (bx / g.tiles_q) * 8, q0 = (bx % g.tiles_q) * 8;
+                    mbar_wait(empty + stage, phase ^ 1);
+                    mbar_expect_tx(full + stage, cfg::kStageBytes);
+                    uint8_t* a = smem + stage * cfg::kStageBytes;
+                    uint8_t* b = a + cfg::kABytes;
+#pragma unroll
+                    for (int j = 0; j < kBM / 64; ++j) tma_load_4d(a + j * (kBK * 128), &tmDY, full + stage, m0 + j * 64, q0, p0, img);
+#pragma unroll
+                    for (int j = 0; j < BN / 64; ++j)
+                        tma_load_4d(b + j * cfg::kPatchBytes, &tmX, full + stage, n0 + j * 64, q0 + s - g.pad, p0 - g.pad, img);
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, 1, 1, kBM, BN);
+            int stage = 0; uint32_t phase = 0;
+            uint32_t acc_phase = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                int s, m0, n0, kb0, kb1;
+                decode(item, s, m0, n0, kb0, kb1);
+                mbar_wait(tmem_empty, acc_phase ^ 1);
+                tc_fence_after();
+                for (int kb = kb0; kb < kb1; ++kb) {
+                    mbar_wait(full + stage, phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + stage * cfg::kStageBytes);
+                    const uint32_t b_addr = a_addr + cfg::kABytes;
+#pragma unroll
+                    for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                        for (int k = 0; k < kBK / kUmmaK; ++k) {
+                            const uint64_t da = make_desc(a_addr + k * (kUmmaK * 128), kBK * 128, 1024);
+                            const uint64_t db = make_desc(b_addr + r * 1024 + k * (kUmmaK * 128), cfg::kPatchBytes, 1024);
+                            umma_f16(tmem_base + r * BN, da, db, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(empty + stage);
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tmem_full);
+                acc_phase ^= 1;
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        const int quarter = warp - kEpiWarp0;
+        uint8_t* my_stage = smemC + quarter * 2 * cfg::kEpiBufBytes;
+        uint32_t acc_phase = 0;
+        uint32_t buf_idx = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+            int s, m0, n0, kb0, kb1;
+            decode(item, s, m0, n0, kb0, kb1);
+            mbar_wait(tmem_full, acc_phase);
+            tc_fence_after();
+            const int row0 = m0 + quarter * 32;
+#pragma unroll 1
+            for (int ch = 0; ch < 3 * (BN / 32); ++ch) {
+                const int r = ch / (BN / 32), cc = ch % (BN / 32);
+                uint8_t* buf = my_stage + (buf_idx & 1) * cfg::kEpiBufBytes;
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + r * BN + cc * 32, v);
+                tmem_ld_wait();
+                uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4)) = make_uint4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
+                fence_async_smem();
+                __syncwarp();
+                const int col = n0 + cc * 32;
+                if (lane == 0 && col < g.c_in && row0 < g.c_out && kb1 > kb0)
+                    tma_reduce_add_2d(&tmDW, buf, (r * g.S + s) * g.c_in + col, row0);
+                if (lane == 0) tma_store_commit();
+                ++buf_idx;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty);
+            acc_phase ^= 1;
+        }
+        if (lane == 0) tma_store_wait_read<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, cfg::kTmemCols);
+}
+
 // ---------------------------------------------------------------- host
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
     static PFN_cuTensorMapEncodeTiled_v12000 fn =
@@ -423,6 +635,20 @@ static int make_mat_map(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t r
     return 0;
 }
 
+// fp32 dW as a matrix [Cout][R*S*Cin]; staging rows are 128 B = 32 floats
+static int make_dw_map(CUtensorMap* tm, float* dw, int c_out, int64_t row_len) {
+    auto enc = get_encode();
+    B200DP_REQUIRE(enc != nullptr, "conv: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {(cuuint64_t)row_len, (cuuint64_t)c_out};
+    cuuint64_t strides[1] = {(cuuint64_t)row_len * 4};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, dw, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200DP_REQUIRE(r == CUDA_SUCCESS, "conv2d_wgrad: cuTensorMapEncodeTiled(dW) failed (%d)", (int)r);
+    return 0;
+}
+
 // pick the pixel box: full rows when they fit, several rows / images per tile up to 128 pixels
 static void pick_box(int n_img, int out_h, int out_w, int stride, int& bq, int& bp, int& bn) {
     const int max_span = stride == 1 ? 256 : 128;       // (b-1)*stride+1 <= 256
@@ -439,10 +665,10 @@ static void pick_box(int n_img, int out_h, int out_w, int stride, int& bq, int& 
     }
 }
 
-template <int BN, bool kBMN, typename TOut>
+template <int BN, bool kBMN, typename TOut, bool kStats = false>
 static int launch_fd(const CUtensorMap& ta, const CUtensorMap& tb, void* out, const float* bias, const Geom& g, int is_bf16,
-                     cudaStream_t s) {
-    auto kern = conv_fd_kernel<BN, kBMN, TOut>;
+                     cudaStream_t s, float* colstats = nullptr) {
+    auto kern = conv_fd_kernel<BN, kBMN, TOut, kStats>;
     static bool configured = false;
     if (!configured) {
         B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
@@ -450,7 +676,7 @@ static int launch_fd(const CUtensorMap& ta, const CUtensorMap& tb, void* out, co
     }
     const int tiles = g.tiles_q * g.tiles_p * g.tiles_n * ((g.c_out + BN - 1) / BN);
     const int grid = tiles < B200DP_SMS ? tiles : B200DP_SMS;
-    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16);
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16, colstats);
     B200DP_CHECK_LAUNCH();
     return 0;
 }
@@ -466,8 +692,8 @@ using namespace b200dp::conv;
 //   mode 1: x = dY     [N][P][Q][Cout], y = dX     [N][H][W][Cin]   (stride must be 1)
 //   w = [Cout][R][S][Cin] (channels-last weight), 16-bit like x.  Cin and Cout multiples of 64
 //   on the reduction side (Cin for fprop, Cout for dgrad) and of 8 on the output side.
-extern "C" int b200dp_conv2d(int mode, const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin,
-                             int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, void* stream) {
+static int conv2d_impl(int mode, const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin,
+                       int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, float* colstats, void* stream) {
     B200DP_REQUIRE(x && w && y, "conv2d: null argument");
     B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "conv2d: fp16 / bf16 only");
     B200DP_REQUIRE(mode == 0 || (mode == 1 && stride == 1), "conv2d: dgrad is implemented for stride 1");
@@ -496,6 +722,15 @@ extern "C" int b200dp_conv2d(int mode, const void* x, const void* w, void* y, co
                    : make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, 64, kBK);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
+    if (colstats != nullptr) {
+#define GS(BNv)                                                                                               \
+    {                                                                                                         \
+        if (is_bf16) return launch_fd<BNv, false, __nv_bfloat16, true>(ta, tb, y, bias, g, 1, s, colstats);    \
+        return launch_fd<BNv, false, __half, true>(ta, tb, y, bias, g, 0, s, colstats);                        \
+    }
+        if (BN == 256) GS(256) else if (BN == 128) GS(128) else GS(64)
+#undef GS
+    }
 #define GO(BNv, MN, T) return launch_fd<BNv, MN, T>(ta, tb, y, bias, g, is_bf16, s)
 #define BY_T(BNv, MN) if (is_bf16) { GO(BNv, MN, __nv_bfloat16); } else { GO(BNv, MN, __half); }
 #define BY_MODE(BNv) if (mode == 0) { BY_T(BNv, false) } else { BY_T(BNv, true) }
@@ -504,6 +739,20 @@ extern "C" int b200dp_conv2d(int mode, const void* x, const void* w, void* y, co
 #undef BY_T
 #undef GO
     return 0;
+}
+
+extern "C" int b200dp_conv2d(int mode, const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin,
+                             int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, void* stream) {
+    return conv2d_impl(mode, x, w, y, bias, N, H, W, Cin, Cout, R, S, stride, pad, dtype, nullptr, stream);
+}
+
+// Forward convolution that also accumulates the per-channel sum / sum of squares of its output into
+// colstats[0:Cout] / colstats[Cout:2Cout] (fp32 atomics; the caller zeroes colstats).
+extern "C" int b200dp_conv2d_colstats(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin,
+                                      int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, float* colstats,
+                                      void* stream) {
+    B200DP_REQUIRE(colstats != nullptr, "conv2d_colstats: null statistics buffer");
+    return conv2d_impl(0, x, w, y, bias, N, H, W, Cin, Cout, R, S, stride, pad, dtype, colstats, stream);
 }
 
 // Weight gradient: dw[Cout][R][S][Cin] (fp32, channels-last weight layout) = sum over pixels of
@@ -522,8 +771,55 @@ extern "C" int b200dp_conv2d_wgrad(const void* x, const void* dy, float* dw, int
     WGeom g;
     g.n_img = N; g.out_h = P; g.out_w = Q; g.c_out = Cout; g.c_in = Cin; g.R = R; g.S = S; g.stride = stride; g.pad = pad;
     g.tiles_q = (Q + 7) / 8; g.tiles_p = (P + 7) / 8;
-    const int BN = Cin <= 64 ? 64 : (Cin >= 256 ? 256 : 128);
     const int num_kb = N * g.tiles_p * g.tiles_q;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (R == 3 && stride == 1 && Cin % 64 == 0 && num_kb >= 16) {
+        // row-grouped kernel: work item = (s, co tile, ci tile, split), three taps per item
+        const int BNr = Cin <= 64 ? 64 : 128;
+        const int base = S * ((Cout + kBM - 1) / kBM) * ((Cin + BNr - 1) / BNr);
+        // items are long on purpose (single-buffered accumulators): pick the split count that fills whole
+        // waves of 148 CTAs best while keeping >= 16 pixel boxes per item
+        int best_splits = 1; double best_eff = 0.0;
+        for (int w = 1; w <= 3; ++w) {
+            int sp = (B200DP_SMS * w) / base;
+            if (sp < 1) sp = 1;
+            if (sp > num_kb / 16) sp = num_kb / 16;
+            if (sp < 1) sp = 1;
+            const int kbp = (num_kb + sp - 1) / sp;
+            sp = (num_kb + kbp - 1) / kbp;
+            const int items = base * sp;
+            const int waves = (items + B200DP_SMS - 1) / B200DP_SMS;
+            const double eff = (double)items / ((double)waves * B200DP_SMS);
+            if (eff > best_eff + 0.02) { best_eff = eff; best_splits = sp; }
+        }
+        g.kb_per = (num_kb + best_splits - 1) / best_splits;
+        g.splits = (num_kb + g.kb_per - 1) / g.kb_per;
+        CUtensorMap tdy, tx, tdw;
+        int rc = make_act_map(&tdy, dy, is_bf16, N, P, Q, Cout, 8, 8, 1, 1);
+        if (rc) return rc;
+        rc = make_act_map(&tx, x, is_bf16, N, H, W, Cin, 8, 10, 1, 1);          // 8 x 10 pixel patch (two halo rows)
+        if (rc) return rc;
+        rc = make_dw_map(&tdw, dw, Cout, R * S * Cin);
+        if (rc) return rc;
+        if (!accumulate) B200DP_CUDA(cudaMemsetAsync(dw, 0, (size_t)Cout * R * S * Cin * 4, s));
+        const int items = base * g.splits;
+        const int grid = items < B200DP_SMS ? items : B200DP_SMS;
+#define WR(BNv)                                                                                                  \
+    {                                                                                                            \
+        auto kern = conv_wgrad_rows_kernel<BNv>;                                                                 \
+        static bool configured = false;                                                                          \
+        if (!configured) {                                                                                       \
+            B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WCfg<BNv>::kSmemBytes)); \
+            configured = true;                                                                                   \
+        }                                                                                                        \
+        kern<<<grid, kThreads, WCfg<BNv>::kSmemBytes, s>>>(tdy, tx, tdw, g, is_bf16);                            \
+    }
+        if (BNr == 128) WR(128) else WR(64)
+#undef WR
+        B200DP_CHECK_LAUNCH();
+        return 0;
+    }
+    const int BN = Cin <= 64 ? 64 : (Cin >= 256 ? 256 : 128);
     const int base_items = R * S * ((Cout + kBM - 1) / kBM) * ((Cin + BN - 1) / BN);
     int splits = (2 * B200DP_SMS + base_items - 1) / base_items;         // ~2 waves of work items
     if (splits > num_kb / 4) splits = num_kb / 4;
@@ -535,17 +831,8 @@ extern "C" int b200dp_conv2d_wgrad(const void* x, const void* dy, float* dw, int
     if (rc) return rc;
     rc = make_act_map(&tx, x, is_bf16, N, H, W, Cin, 8, 8, 1, stride);
     if (rc) return rc;
-    {   // fp32 dW as a matrix [Cout][R*S*Cin]; staging rows are 128 B = 32 floats
-        auto enc = get_encode();
-        cuuint64_t dims[2] = {(cuuint64_t)R * S * Cin, (cuuint64_t)Cout};
-        cuuint64_t strides[1] = {(cuuint64_t)R * S * Cin * 4};
-        cuuint32_t box[2] = {32, 32};
-        cuuint32_t estr[2] = {1, 1};
-        CUresult r = enc(&tdw, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, dw, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        B200DP_REQUIRE(r == CUDA_SUCCESS, "conv2d_wgrad: cuTensorMapEncodeTiled(dW) failed (%d)", (int)r);
-    }
-    cudaStream_t s = (cudaStream_t)stream;
+    rc = make_dw_map(&tdw, dw, Cout, R * S * Cin);
+    if (rc) return rc;
     if (!accumulate) B200DP_CUDA(cudaMemsetAsync(dw, 0, (size_t)Cout * R * S * Cin * 4, s));
     const int items = base_items * g.splits;
     const int grid = items < B200DP_SMS ? items : B200DP_SMS;

@@ -42,12 +42,18 @@ template <int BN> struct Cfg {
     static constexpr int kTmemCols = 2 * BN;        // two accumulators (power of two: 128 / 256 / 512)
 };
 
-template <int BN, bool kAMN, bool kBMN, typename TOut>
+// kStats: the epilogue also accumulates, per output column, the sum and the sum of squares of the
+// (rounded) values it stores — the batch statistics the BatchNorm that follows a 1x1 convolution
+// needs — so that layer does not have to read the activation once more (colstats[0:N] += sum,
+// colstats[N:2N] += sum of squares; per-lane register partials, one red.add per column per change
+// of column tile).
+template <int BN, bool kAMN, bool kBMN, typename TOut, bool kStats = false>
 __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant__ CUtensorMap tmA,
                                                            const __grid_constant__ CUtensorMap tmB,
                                                            const __grid_constant__ CUtensorMap tmC,
                                                            const float* __restrict__ bias, int M, int N, int K,
-                                                           int is_bf16, int accumulate_c, int splits) {
+                                                           int is_bf16, int accumulate_c, int splits,
+                                                           float* __restrict__ colstats) {
     using cfg = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -156,15 +162,41 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
         uint8_t* my_stage = smemC + quarter * 2 * cfg::kEpiBufBytes;
         int acc = 0; uint32_t acc_phase = 0;
         uint32_t buf_idx = 0;
+        constexpr int kChunks = BN / kChunkCols;
+        // column statistics: lane l owns columns 2l, 2l+1 of every 64-column chunk of the current column tile
+        float st[kStats ? kChunks * 4 : 1];
+        int st_n0 = -1;
+#pragma unroll
+        for (int i = 0; i < (kStats ? kChunks * 4 : 1); ++i) st[i] = 0.f;
+        auto flush_stats = [&]() {
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) {
+                    const int col = st_n0 + ch * kChunkCols + 2 * lane;
+                    if (col < N) {
+                        atomicAdd(colstats + col, st[ch * 4 + 0]);
+                        atomicAdd(colstats + N + col, st[ch * 4 + 2]);
+                    }
+                    if (col + 1 < N) {
+                        atomicAdd(colstats + col + 1, st[ch * 4 + 1]);
+                        atomicAdd(colstats + N + col + 1, st[ch * 4 + 3]);
+                    }
+                    st[ch * 4 + 0] = st[ch * 4 + 1] = st[ch * 4 + 2] = st[ch * 4 + 3] = 0.f;
+                }
+            }
+        };
         for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
             const int tile = item % num_tiles, split = item / num_tiles;
             const int m0 = (tile % num_m) * kBM, n0 = (tile / num_m) * BN;
             const bool add_bias = bias != nullptr && split == 0;
+            if (kStats && n0 != st_n0) {
+                if (st_n0 >= 0) flush_stats();
+                st_n0 = n0;
+            }
             mbar_wait(tmem_full + acc, acc_phase);
             tc_fence_after();
             const int row0 = m0 + quarter * 32;
-#pragma unroll 1
-            for (int ch = 0; ch < BN / kChunkCols; ++ch) {
+            auto do_chunk = [&](const int ch) {
                 uint8_t* buf = my_stage + (buf_idx & 1) * cfg::kEpiBufBytes;
                 // the TMA store that last read this buffer (two chunks ago) must have drained it
                 if (lane == 0) tma_store_wait_read<1>();
@@ -207,7 +239,29 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
                     else tma_store_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
                 }
                 if (lane == 0) tma_store_commit();
+                if constexpr (kStats && sizeof(TOut) == 2) {
+                    // column sums over this warp's 32 staged rows (rows past M hold zeros): lane l reads
+                    // the 4-byte word of columns 2l, 2l+1 in every row — one full 128-byte row per
+                    // request, no bank conflicts under the swizzle
+                    const int j = lane >> 2, w = lane & 3;
+                    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const uint32_t u = *reinterpret_cast<const uint32_t*>(buf + rr * 128 + ((j ^ (rr & 7)) << 4) + w * 4);
+                        const float2 f = unpack2<TOut>(u);
+                        s0 += f.x; s1 += f.y;
+                        q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
+                    }
+                    st[ch * 4 + 0] += s0; st[ch * 4 + 1] += s1; st[ch * 4 + 2] += q0; st[ch * 4 + 3] += q1;
+                }
                 ++buf_idx;
+            };
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
+            } else {
+#pragma unroll 1
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
             }
             // the accumulator has left TMEM: hand it back to the MMA warp before the stores finish
             tc_fence_before();
@@ -215,6 +269,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
             if (lane == 0) mbar_arrive(tmem_empty + acc);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (kStats && st_n0 >= 0) flush_stats();
         if (lane == 0) tma_store_wait_read<0>();
     }
     tc_fence_before();
@@ -254,10 +309,10 @@ static int make_tmap(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t rows
     return 0;
 }
 
-template <int BN, bool kAMN, bool kBMN, typename TOut>
+template <int BN, bool kAMN, bool kBMN, typename TOut, bool kStats = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias, int M, int N, int K,
-                  int is_bf16, int accumulate_c, int splits, int sms, cudaStream_t s) {
-    auto kern = gemm_kernel<BN, kAMN, kBMN, TOut>;
+                  int is_bf16, int accumulate_c, int splits, int sms, cudaStream_t s, float* colstats = nullptr) {
+    auto kern = gemm_kernel<BN, kAMN, kBMN, TOut, kStats>;
     static bool configured = false;
     if (!configured) {
         B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
@@ -265,7 +320,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     }
     const int items = ((M + kBM - 1) / kBM) * ((N + BN - 1) / BN) * splits;
     const int grid = items < sms ? items : sms;
-    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits);
+    kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits, colstats);
     B200DP_CHECK_LAUNCH();
     return 0;
 }
@@ -279,9 +334,9 @@ using namespace b200dp::gemm;
 // C[M,N] (+)= A * B^T (+ bias).  a_mn / b_mn: 0 = operand is K-major ([rows][K], K contiguous),
 // 1 = MN-major ([K][rows], rows contiguous).  lda / ldb are the row pitches (elements) of the
 // arrays as stored.  out_dtype: B200DP_F16 / B200DP_BF16 (same as the inputs) or B200DP_F32.
-extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
-                           int ldc, int a_mn, int b_mn, b200dp_dtype in_dtype, b200dp_dtype out_dtype, int accumulate_c,
-                           void* stream) {
+static int gemm_impl(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb, int ldc,
+                     int a_mn, int b_mn, b200dp_dtype in_dtype, b200dp_dtype out_dtype, int accumulate_c, float* colstats,
+                     void* stream) {
     B200DP_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "gemm: bad arguments");
     B200DP_REQUIRE(in_dtype == B200DP_F16 || in_dtype == B200DP_BF16, "gemm: inputs must be fp16 or bf16");
     B200DP_REQUIRE(out_dtype == in_dtype || out_dtype == B200DP_F32, "gemm: output must match the inputs or be fp32");
@@ -320,6 +375,16 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
         if (splits > 1 && !accumulate_c)
             B200DP_CUDA(cudaMemsetAsync(C, 0, (size_t)M * ldc * 4, s));
     }
+    if (colstats != nullptr) {
+        // statistics variant: K-major operands, 16-bit output, one pass over K (checked by the caller)
+#define GS(BNv)                                                                                                        \
+    {                                                                                                                  \
+        if (is_bf16) return launch<BNv, false, false, __nv_bfloat16, true>(ta, tb, tc, nullptr, M, N, K, 1, 0, 1, sms, s, colstats); \
+        return launch<BNv, false, false, __half, true>(ta, tb, tc, nullptr, M, N, K, 0, 0, 1, sms, s, colstats);        \
+    }
+        if (BN == 256) GS(256) else if (BN == 128) GS(128) else GS(64)
+#undef GS
+    }
 #define GO(BNv, AM, BM_, T) return launch<BNv, AM, BM_, T>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits, sms, s)
 #define BY_OUT(BNv, AM, BM_)                                                      \
     if (out_dtype == B200DP_F32) { GO(BNv, AM, BM_, float); }                     \
@@ -335,4 +400,18 @@ extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* b
 #undef BY_OUT
 #undef GO
     return 0;
+}
+
+extern "C" int b200dp_gemm(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
+                           int ldc, int a_mn, int b_mn, b200dp_dtype in_dtype, b200dp_dtype out_dtype, int accumulate_c,
+                           void* stream) {
+    return gemm_impl(A, B, C, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, in_dtype, out_dtype, accumulate_c, nullptr, stream);
+}
+
+// C[M,N] = A[M,K] B[N,K]^T (16-bit in / out) and, from the same epilogue, colstats[0:N] += column sums
+// of C, colstats[N:2N] += column sums of squares (fp32 atomics; the caller zeroes colstats).
+extern "C" int b200dp_gemm_colstats(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                                    b200dp_dtype dtype, float* colstats, void* stream) {
+    B200DP_REQUIRE(colstats != nullptr, "gemm_colstats: null statistics buffer");
+    return gemm_impl(A, B, C, nullptr, M, N, K, lda, ldb, ldc, 0, 0, dtype, dtype, 0, colstats, stream);
 }

@@ -312,6 +312,18 @@ int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* m
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
                                 int slot_floats, void* const* call_counter, void* stream);
 
+/* GEMM / forward convolution whose epilogue also accumulates, per output column (channel), the sum
+ * and the sum of squares of the values it stores: colstats[0:N] += sum, colstats[N:2N] += sum of
+ * squares (fp32 atomics from per-lane register partials; the caller zeroes colstats).  These are the
+ * batch statistics of the BatchNorm that follows the layer, which then skips its own reduction pass
+ * over the activation (b200dp_bn_reduce).  K-major 16-bit operands, 16-bit output, no bias for the
+ * GEMM form.  Reference: every conv -> BatchNorm pair of the CNN models (cuDNN conv + ATen batch_norm
+ * there, two passes over the activation). */
+int b200dp_gemm_colstats(const void* A, const void* B, void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                         b200dp_dtype dtype, float* colstats, void* stream);
+int b200dp_conv2d_colstats(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin, int Cout,
+                           int R, int S, int stride, int pad, b200dp_dtype dtype, float* colstats, void* stream);
+
 /* All-gather fused into the consuming GEMM (W4): Y[M,N] = X[M,K] W^T (+bias) with W[N,K] row-sharded
  * over the ranks (w_shards[p] = rank p's [rows_per_rank][K] shard in peer-mapped memory).  One kernel:
  * the otherwise idle warp of every CTA pulls chunks of 1-8 weight rows over NVLink into the local copy

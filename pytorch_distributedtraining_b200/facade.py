@@ -119,6 +119,10 @@ class Stoke:
                 model = model.to(memory_format=torch.channels_last)
         if self._status.is_distributed and self._ddp_cfg.convert_to_sync_batch_norm and self.world_size > 1:
             model = convert_sync_batchnorm(model)
+        if gpu and self._b200.fused_kernels:
+            # conv -> BatchNorm pairs: the convolution's epilogue emits the batch statistics
+            from .ops.layers import pair_conv_bn
+            pair_conv_bn(model)
         self._unwrapped = model
         # 3/4. optimizer + engine
         self._optimizer_spec = optimizer

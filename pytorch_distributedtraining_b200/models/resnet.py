@@ -89,6 +89,8 @@ class ResNet(nn.Module):
         self.avgpool = nn.AdaptiveAvgPool2d((1, 1))
         self.fc = Linear(512 * block.expansion, num_classes)
 
+        from ..ops.layers import pair_conv_bn
+        pair_conv_bn(self)          # conv epilogues emit the statistics of the BatchNorm that follows
         for m in self.modules():
             if isinstance(m, nn.Conv2d):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")

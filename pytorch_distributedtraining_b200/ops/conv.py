@@ -49,15 +49,21 @@ def shape_supported(mod, x) -> bool:
 
 
 def conv2d_raw(mode: int, x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], n: int, h: int, wd: int, cin: int,
-               cout: int, r: int, s: int, stride: int, pad: int) -> torch.Tensor:
+               cout: int, r: int, s: int, stride: int, pad: int, colstats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Direct call of ``b200dp_conv2d`` on NHWC-contiguous 16-bit tensors; returns NCHW-shaped,
-    channels-last output."""
+    channels-last output.  ``colstats`` (forward only; fp32, >= 2*cout, zeroed by the caller) receives
+    the per-channel sum / sum of squares of the output from the same epilogue."""
     lib = require_library()
     p, q = (h + 2 * pad - r) // stride + 1, (wd + 2 * pad - s) // stride + 1
     if mode == 0:
         out = torch.empty((n, p, q, cout), dtype=x.dtype, device=x.device)
     else:
         out = torch.empty((n, h, wd, cin), dtype=x.dtype, device=x.device)
+    if colstats is not None:
+        assert mode == 0 and colstats.dtype == torch.float32 and colstats.numel() >= 2 * cout
+        check(lib.b200dp_conv2d_colstats(ptr(x), ptr(w), ptr(out), ptr(bias), n, h, wd, cin, cout, r, s, stride, pad,
+                                         DT[x.dtype], ptr(colstats), stream_ptr(x.device)), "conv2d_colstats")
+        return out.permute(0, 3, 1, 2)
     check(lib.b200dp_conv2d(mode, ptr(x), ptr(w), ptr(out), ptr(bias), n, h, wd, cin, cout, r, s, stride, pad, DT[x.dtype],
                             stream_ptr(x.device)), "conv2d")
     return out.permute(0, 3, 1, 2)
@@ -75,7 +81,7 @@ def conv2d_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, n: int, h: int, wd: int,
 
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, dtype, stride, pad):  # type: ignore[override]
+    def forward(ctx, x, weight, bias, dtype, stride, pad, colstats=None):  # type: ignore[override]
         n, cin, h, w = x.shape
         cout, _, r, s = weight.shape
         if x.dtype != dtype:
@@ -89,9 +95,15 @@ class _ConvFn(torch.autograd.Function):
         one = r == 1 and s == 1 and stride == 1 and pad == 0
         if one:
             x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)
-            y = gemm(x2, w16.reshape(cout, cin), x2.shape[0], cout, cin, bias=b32).view(n, h, w, cout).permute(0, 3, 1, 2)
+            if colstats is not None and b32 is None:
+                y = gemm(x2, w16.reshape(cout, cin), x2.shape[0], cout, cin, colstats=colstats)
+            else:
+                y = gemm(x2, w16.reshape(cout, cin), x2.shape[0], cout, cin, bias=b32)
+                colstats = None
+            y = y.view(n, h, w, cout).permute(0, 3, 1, 2)
         else:
-            y = conv2d_raw(0, x, w16, b32, n, h, w, cin, cout, r, s, stride, pad)
+            y = conv2d_raw(0, x, w16, b32, n, h, w, cin, cout, r, s, stride, pad, colstats=colstats)
+        ctx.emitted_stats = colstats is not None
         ctx.save_for_backward(x, w16)
         ctx.geom = (n, cin, h, w, cout, r, s, stride, pad, one)
         ctx.w_dtype, ctx.has_bias = weight.dtype, bias is not None
@@ -131,10 +143,22 @@ class _ConvFn(torch.autograd.Function):
             dw = dw.to(ctx.w_dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = torch.sum(dy, dim=(0, 2, 3), dtype=torch.float32)
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
-def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], stride, padding, dilation, groups):
+BN_STATS_ATTR = "_b200dp_bn_sums"
+
+
+def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], stride, padding, dilation, groups,
+           emit_bn_stats: bool = False):
+    """``emit_bn_stats``: the convolution's epilogue also produces [sum(y), sum(y^2), (count slot)] per
+    output channel and hangs that vector on the returned tensor; the BatchNorm that consumes this very
+    tensor (``ops.norm.batch_norm_act``) then skips its own reduction pass over the activation."""
     dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
     with torch.autocast("cuda", enabled=False):
+        if emit_bn_stats and (bias is None or tuple(weight.shape[2:]) != (1, 1) or int(stride[0]) != 1):
+            sums = torch.zeros(2 * weight.shape[0] + 1, dtype=torch.float32, device=x.device)
+            y = _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]), sums)
+            setattr(y, BN_STATS_ATTR, sums)
+            return y
         return _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]))

@@ -25,9 +25,11 @@ def available() -> bool:
 
 def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, a_mn: bool = False, b_mn: bool = False,
          bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, out_dtype: Optional[torch.dtype] = None,
-         accumulate: bool = False) -> torch.Tensor:
+         accumulate: bool = False, colstats: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``C[M,N] (+)= A(MxK) @ B(NxK)^T (+ bias)``.  ``a`` / ``b`` are 2-D, row-major, 16-bit:
-    K-major operands are ``[rows, K]``, MN-major operands are ``[K, rows]``."""
+    K-major operands are ``[rows, K]``, MN-major operands are ``[K, rows]``.  ``colstats`` (fp32,
+    >= 2N, zeroed by the caller): the epilogue also adds the column sums / sums of squares of C into
+    it (the batch statistics for a BatchNorm that follows a 1x1 convolution)."""
     lib = require_library()
     assert a.dtype in _HALF and b.dtype == a.dtype and a.dim() == 2 and b.dim() == 2
     assert a.stride(1) == 1 and b.stride(1) == 1
@@ -37,6 +39,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, a_mn: bool = 
     assert out.stride(1) == 1 and out.shape == (M, N)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.is_contiguous()
+    if colstats is not None:
+        assert not (a_mn or b_mn or accumulate) and bias is None and out.dtype == a.dtype
+        assert colstats.dtype == torch.float32 and colstats.numel() >= 2 * N and colstats.is_contiguous()
+        check(lib.b200dp_gemm_colstats(ptr(a), ptr(b), ptr(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+                                       DT[a.dtype], ptr(colstats), stream_ptr(a.device)), "gemm_colstats")
+        return out
     check(lib.b200dp_gemm(ptr(a), ptr(b), ptr(out), ptr(bias), M, N, K, a.stride(0), b.stride(0), out.stride(0),
                           int(a_mn), int(b_mn), DT[a.dtype], DT[out.dtype], int(accumulate), stream_ptr(a.device)),
           "gemm")

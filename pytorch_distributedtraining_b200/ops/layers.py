@@ -25,10 +25,17 @@ class Conv2d(nn.Conv2d):
     """Convolution.  On CUDA channels-last fp16/bf16 the forward/dgrad/wgrad go through
     ``ops.conv`` (tcgen05 implicit GEMM) when the shape is supported; otherwise cuDNN."""
 
+    # set by ``pair_conv_bn``: a BatchNormAct2d consumes this layer's output directly, so in training
+    # the convolution's epilogue also emits the batch statistics that layer needs
+    emit_bn_stats: bool = False
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda and dispatch.conv_supported(self, x):
             from . import conv as _conv
-            return _conv.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
+            emit = self.emit_bn_stats and self.training and torch.is_grad_enabled() and dispatch.enabled("bn") \
+                and dispatch.enabled("convstats")
+            return _conv.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups,
+                                emit_bn_stats=emit)
         return super().forward(x)
 
 
@@ -78,6 +85,22 @@ class BatchNormAct2d(nn.BatchNorm2d):
         if self.act == "relu":
             y = F.relu(y)
         return y
+
+
+def pair_conv_bn(model: nn.Module) -> int:
+    """Mark every ``Conv2d`` that is registered immediately before a ``BatchNormAct2d`` in the same parent
+    (conv1/bn1, Sequential(conv, bn) ...) so that it emits the batch statistics from its epilogue.
+    The pairing is only a hint: the BatchNorm uses the vector only when it finds it on its own input
+    tensor, so a wrong guess costs a little epilogue work and nothing else.  Returns the pair count."""
+    pairs = 0
+    for parent in model.modules():
+        prev = None
+        for child in parent.children():
+            if isinstance(child, BatchNormAct2d) and isinstance(prev, Conv2d) and prev.out_channels == child.num_features:
+                prev.emit_bn_stats = True
+                pairs += 1
+            prev = child
+    return pairs
 
 
 class LayerNorm(nn.LayerNorm):

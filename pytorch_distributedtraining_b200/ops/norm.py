@@ -34,17 +34,21 @@ def _allreduce_stats(buf: torch.Tensor, group: Any) -> None:
 
 class _BatchNormActFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, group, world):  # type: ignore[override]
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, group, world,
+                pre_sums=None):  # type: ignore[override]
         lib = require_library()
         rows, C = _rows_view(x)
         dt = ctypes.c_int(DT[x.dtype])
         dev = x.device
         ws = Workspace.get(dev)
-        scratch = ws.scratch(int(lib.b200dp_bn_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
-        sums = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
         st = stream_ptr(dev)
-        check(lib.b200dp_bn_reduce(ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(scratch), ptr(ws.counters),
-                                   ptr(sums), st), "bn_reduce")
+        if pre_sums is not None:
+            sums = pre_sums            # produced by the epilogue of the convolution that wrote x
+        else:
+            scratch = ws.scratch(int(lib.b200dp_bn_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
+            sums = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)
+            check(lib.b200dp_bn_reduce(ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(scratch), ptr(ws.counters),
+                                       ptr(sums), st), "bn_reduce")
         count = float(rows)
         if world > 1:
             sums[2 * C] = count
@@ -90,7 +94,7 @@ class _BatchNormActFn(torch.autograd.Function):
         check(lib.b200dp_bn_bwd_apply(ptr(dy), None, ptr(x), ptr(dx), ptr(dres), ctypes.c_int64(rows), ctypes.c_int(C),
                                       dt, ptr(mean), ptr(invstd), ptr(weight), ptr(dsums), ctypes.c_float(ctx.count),
                                       relu, ptr(mask), st), "bn_bwd_apply")
-        return dx, dres, dweight.to(weight.dtype), dbias.to(weight.dtype), None, None, None, None, None, None, None
+        return dx, dres, dweight.to(weight.dtype), dbias.to(weight.dtype), None, None, None, None, None, None, None, None
 
 
 def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) -> torch.Tensor:
@@ -116,8 +120,11 @@ def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) 
     if mod.sync and dist.is_available() and dist.is_initialized():
         group = mod.process_group if mod.process_group is not None else dist.group.WORLD
         world = dist.get_world_size(group)
+    pre = getattr(x, "_b200dp_bn_sums", None)
+    if pre is not None and (pre.numel() != 2 * x.shape[1] + 1 or pre.device != x.device):
+        pre = None
     return _BatchNormActFn.apply(x, residual, mod.weight, mod.bias, mod.running_mean, mod.running_var, mod.eps,
-                                 momentum, relu, group, world)
+                                 momentum, relu, group, world, pre)
 
 
 class _LayerNormFn(torch.autograd.Function):

@@ -18,6 +18,8 @@ CASES = [
     (2, 16, 16, 64, 40, 5, 1, 2),
     (1, 130, 130, 64, 64, 3, 1, 1),
     (2, 9, 9, 192, 264, 3, 2, 1),
+    (32, 7, 7, 512, 512, 3, 1, 1),
+    (2, 20, 20, 192, 136, 3, 1, 1),
 ]
 
 
@@ -100,3 +102,71 @@ def test_conv_module_autograd(dtype):
         # weight gradients sum thousands of 16-bit products on both sides: compare in relative L2
         rel = ((a.grad - b.grad).norm() / b.grad.norm()).item()
         assert rel < tol, rel
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad", CASES)
+def test_conv_epilogue_emits_batchnorm_statistics(dtype, N, H, W, Cin, Cout, R, stride, pad):
+    """The forward kernel's optional epilogue output: per-channel sum and sum of squares of exactly the
+    values it stored (ragged tiles, strided and padded shapes included)."""
+    from pytorch_distributedtraining_b200.ops.conv import conv2d_raw
+    g = torch.Generator().manual_seed(N * 13 + H)
+    x = (torch.randn(N, Cin, H, W, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) * 0.1).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    stats = torch.zeros(2 * Cout + 1, device=cuda)
+    got = conv2d_raw(0, x, w, None, N, H, W, Cin, Cout, R, R, stride, pad, colstats=stats)
+    plain = conv2d_raw(0, x, w, None, N, H, W, Cin, Cout, R, R, stride, pad)
+    torch.cuda.synchronize()
+    assert torch.equal(got, plain), "the statistics epilogue must not change the stored output"
+    y = got.double()
+    torch.testing.assert_close(stats[:Cout].double(), y.sum(dim=(0, 2, 3)), rtol=2e-4, atol=2e-3)
+    torch.testing.assert_close(stats[Cout:2 * Cout].double(), (y * y).sum(dim=(0, 2, 3)), rtol=2e-4, atol=2e-3)
+    assert float(stats[2 * Cout]) == 0.0
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("M,N,K", [(4096, 256, 64), (3000, 72, 128), (25088, 512, 128), (130, 1024, 256)])
+def test_gemm_epilogue_emits_column_statistics(dtype, M, N, K):
+    from pytorch_distributedtraining_b200.ops.gemm import gemm
+    g = torch.Generator().manual_seed(M + N)
+    a = (torch.randn(M, K, generator=g) * 0.5).to(dtype).to(cuda)
+    b = (torch.randn(N, K, generator=g) * 0.2).to(dtype).to(cuda)
+    stats = torch.zeros(2 * N + 1, device=cuda)
+    got = gemm(a, b, M, N, K, colstats=stats)
+    plain = gemm(a, b, M, N, K)
+    torch.cuda.synchronize()
+    assert torch.equal(got, plain)
+    y = got.double()
+    torch.testing.assert_close(stats[:N].double(), y.sum(0), rtol=2e-4, atol=2e-3)
+    torch.testing.assert_close(stats[N:2 * N].double(), (y * y).sum(0), rtol=2e-4, atol=2e-3)
+
+
+def test_conv_bn_pair_matches_unfused_statistics():
+    """A bottleneck block trained with the conv -> BatchNorm statistics hand-over gives the same outputs,
+    running statistics and gradients as with the BatchNorm's own reduction pass."""
+    from pytorch_distributedtraining_b200.models.resnet import Bottleneck
+    from pytorch_distributedtraining_b200.ops import dispatch
+    from pytorch_distributedtraining_b200.ops.layers import BatchNormAct2d, Conv2d, pair_conv_bn
+    import torch.nn as nn
+    torch.manual_seed(3)
+    down = nn.Sequential(Conv2d(64, 256, 1, stride=2, bias=False), BatchNormAct2d(256, act=None))
+    blk = Bottleneck(64, 64, stride=2, downsample=down).to(cuda).to(memory_format=torch.channels_last)
+    assert pair_conv_bn(blk) == 4
+    x = torch.randn(8, 64, 30, 30, device=cuda).contiguous(memory_format=torch.channels_last)
+    res = {}
+    state = {k: v.clone() for k, v in blk.state_dict().items()}
+    for mode in ("fused", "plain"):
+        blk.load_state_dict(state)
+        blk.zero_grad(set_to_none=True)
+        if mode == "plain":
+            dispatch.disable("convstats")
+        try:
+            with torch.autocast("cuda", dtype=torch.float16):
+                y = blk(x)
+            (y.float() ** 2).mean().backward()
+        finally:
+            dispatch.enable("convstats")
+        res[mode] = (y.detach().float(), blk.bn2.running_var.clone(), blk.conv1.weight.grad.clone(),
+                     blk.bn3.weight.grad.clone())
+    for a, b in zip(res["fused"], res["plain"]):
+        torch.testing.assert_close(a, b, rtol=2e-3, atol=2e-3)
