@@ -166,38 +166,43 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
         }
         store8<T>(y + r * C + c0, v);
     };
+    // The tensor is walked from its END to its start: x was just written front-to-back by the producing
+    // convolution, so its tail is what is still resident in the 126 MB L2 when this kernel starts.
+    const int64_t last = rows - 1;
     int64_t r = (int64_t)blockIdx.y * rpb + rl;
     // two rows per iteration: four independent 16-byte loads in flight per thread
     for (; r + rstep < rows; r += 2 * rstep) {
+        const int64_t p0 = last - r, p1 = last - (r + rstep);
         float v0[8], v1[8];
-        load8<T>(x + r * C + c0, v0);
-        load8<T>(x + (r + rstep) * C + c0, v1);
+        load8<T>(x + p0 * C + c0, v0);
+        load8<T>(x + p1 * C + c0, v1);
         if (res != nullptr) {
             float r0[8], r1[8];
-            load8<T>(res + r * C + c0, r0);
-            load8<T>(res + (r + rstep) * C + c0, r1);
+            load8<T>(res + p0 * C + c0, r0);
+            load8<T>(res + p1 * C + c0, r1);
 #pragma unroll
             for (int k = 0; k < 8; ++k) { v0[k] = v0[k] * sc[k] + sh[k] + r0[k]; v1[k] = v1[k] * sc[k] + sh[k] + r1[k]; }
         } else {
 #pragma unroll
             for (int k = 0; k < 8; ++k) { v0[k] = v0[k] * sc[k] + sh[k]; v1[k] = v1[k] * sc[k] + sh[k]; }
         }
-        finish(v0, r);
-        finish(v1, r + rstep);
+        finish(v0, p0);
+        finish(v1, p1);
     }
     for (; r < rows; r += rstep) {
+        const int64_t p0 = last - r;
         float v[8];
-        load8<T>(x + r * C + c0, v);
+        load8<T>(x + p0 * C + c0, v);
         if (res != nullptr) {
             float rv[8];
-            load8<T>(res + r * C + c0, rv);
+            load8<T>(res + p0 * C + c0, rv);
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] = v[k] * sc[k] + sh[k] + rv[k];
         } else {
 #pragma unroll
             for (int k = 0; k < 8; ++k) v[k] = v[k] * sc[k] + sh[k];
         }
-        finish(v, r);
+        finish(v, p0);
     }
 }
 
@@ -214,15 +219,15 @@ __global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_reduce_kernel(
     if (active) {
         const int c0 = cg * 8;
         const int64_t rstep = (int64_t)gridDim.y * rpb;
-        auto masked = [&](float (&d)[8], int64_t r) {
+        auto masked = [&](float (&d)[8], int64_t off) {      // off = row * C + c0
             if (!relu) return;
             if (mask != nullptr) {
-                const unsigned m = mask[r * tpr + cg];
+                const unsigned m = mask[off >> 3];
 #pragma unroll
                 for (int k = 0; k < 8; ++k) d[k] = ((m >> k) & 1u) ? d[k] : 0.f;
             } else {
                 float yv[8];
-                load8<T>(y + r * C + c0, yv);
+                load8<T>(y + off, yv);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) d[k] = yv[k] > 0.f ? d[k] : 0.f;
             }
@@ -230,26 +235,32 @@ __global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_reduce_kernel(
         // The loop keeps only sum(dz) and sum(dz * x) (16 accumulators): sum(dz * xhat) is recovered as
         // (sum(dz*x) - mean * sum(dz)) * invstd afterwards.  Few live registers => two rows (four 16-byte
         // loads) in flight per thread at 4 CTAs/SM, which is what the HBM latency needs.
-        int64_t r = (int64_t)blockIdx.y * rpb + rl;
-        for (; r + rstep < rows; r += 2 * rstep) {
+        // Walked from the END of the tensor to its start: the tail of dy (just written front-to-back by the
+        // kernel before this one) is still in L2, and bn_bwd_apply, which runs next and walks front-to-back,
+        // then starts on the rows this kernel touched last.
+        // element offset of (row, c0); the mask byte of that group is at offset / 8
+        const int64_t rs = rstep * C;
+        int64_t left = rows - ((int64_t)blockIdx.y * rpb + rl);          // rows still ahead of this thread (incl. its current one)
+        int64_t off = (rows - 1 - ((int64_t)blockIdx.y * rpb + rl)) * C + c0;
+        for (; left > rstep; left -= 2 * rstep, off -= 2 * rs) {
             float d0[8], x0[8], d1[8], x1[8];
-            load8<T>(dy + r * C + c0, d0);
-            load8<T>(x + r * C + c0, x0);
-            load8<T>(dy + (r + rstep) * C + c0, d1);
-            load8<T>(x + (r + rstep) * C + c0, x1);
-            masked(d0, r);
-            masked(d1, r + rstep);
+            load8<T>(dy + off, d0);
+            load8<T>(x + off, x0);
+            load8<T>(dy + off - rs, d1);
+            load8<T>(x + off - rs, x1);
+            masked(d0, off);
+            masked(d1, off - rs);
 #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 a[k] += d0[k] + d1[k];
                 b[k] += d0[k] * x0[k] + d1[k] * x1[k];
             }
         }
-        for (; r < rows; r += rstep) {
+        if (left > 0) {
             float d[8], xv[8];
-            load8<T>(dy + r * C + c0, d);
-            load8<T>(x + r * C + c0, xv);
-            masked(d, r);
+            load8<T>(dy + off, d);
+            load8<T>(x + off, xv);
+            masked(d, off);
 #pragma unroll
             for (int k = 0; k < 8; ++k) { a[k] += d[k]; b[k] += d[k] * xv[k]; }
         }
