@@ -277,6 +277,166 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
     if (warp == 2) tmem_dealloc(tmem_base, cfg::kTmemCols);
 }
 
+// ---------------------------------------------------------------- CTA-pair kernel (cta_group::2)
+// C[M,N] = A[M,K] B[N,K]^T (+bias), K-major operands, 16-bit output.  Two CTAs of a cluster (one TPC)
+// work on one 256 x 256 output tile: each loads ITS 128 rows of A and ITS 128 rows of B per k-block
+// (32 KB instead of 48 KB per 128 x 256 x 64 of math — operand traffic from L2 and shared-memory
+// reads per FLOP both drop by a third), the leader's MMA thread issues one M = 256 tcgen05.mma for
+// the pair, and each CTA's tensor core accumulates its own 128 rows in its own TMEM.
+//   full[stage]      leader only; armed by the leader's producer with the pair's 64 KB, credited by both CTAs' TMA
+//   empty[stage]     one per CTA; the pair MMA's commit arrives on both
+//   tmem_full[acc]   one per CTA; commit multicast
+//   tmem_empty[acc]  leader only; the 8 epilogue warps of the pair arrive on it
+namespace pair {
+constexpr int kBN = 256;
+constexpr int kHalfN = 128;
+constexpr int kStages = 6;
+constexpr int kABytes = kBM * kBK * 2;
+constexpr int kBBytes = kHalfN * kBK * 2;
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kEpiBufBytes = 32 * 128;
+constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;
+constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 + 256;
+constexpr int kTmemCols = 512;
+}  // namespace pair
+
+template <typename TOut>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias, int M, int N, int K, int is_bf16) {
+    using namespace pair;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemA = smem;
+    uint8_t* smemB = smem + kStages * kABytes;
+    uint8_t* smemC = smem + kStages * kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + kEpiBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + kStages;
+    uint64_t* tmem_full = bars + 2 * kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t cta_rank = cluster_ctarank();
+    const bool leader = cta_rank == 0;
+    const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    const int num_m = (M + 2 * kBM - 1) / (2 * kBM), num_n = (N + kBN - 1) / kBN;
+    const int num_tiles = num_m * num_n;
+    const int num_kb = (K + kBK - 1) / kBK;
+
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); tma_prefetch_desc(&tmC); }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 8); }
+        fence_barrier_init();
+    }
+    cluster_sync_all();                       // both CTAs' barriers exist before anything remote touches them
+    if (warp == 2) tmem_alloc_pair(tmem_slot, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs) =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+                const int m0 = (tile % num_m) * (2 * kBM) + (int)cta_rank * kBM;
+                const int n0 = (tile / num_m) * kBN + (int)cta_rank * kHalfN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty + stage, phase ^ 1);
+                    if (leader) mbar_expect_tx(full + stage, 2 * kStageBytes);
+                    tma_load_2d_pair(smemA + stage * kABytes, &tmA, full + stage, kb * kBK, m0);
+                    tma_load_2d_pair(smemB + stage * kBBytes, &tmB, full + stage, kb * kBK, n0);
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (leader && lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, 0, 0, 2 * kBM, kBN);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * kBN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full + stage, phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smemA + stage * kABytes);
+                    const uint32_t b_addr = smem_u32(smemB + stage * kBBytes);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k)
+                        umma_f16_pair(d_tmem, make_desc(a_addr + k * (kUmmaK * 2), 16, 1024),
+                                      make_desc(b_addr + k * (kUmmaK * 2), 16, 1024), idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_commit_pair(empty + stage, 3);          // both CTAs' producers may refill this stage
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(tmem_full + acc, 3);            // both CTAs' epilogues may read their half
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // ===== epilogue (both CTAs; each drains its own 128 rows) =====
+        const int quarter = warp - kEpiWarp0;
+        uint8_t* my_stage = smemC + quarter * 2 * kEpiBufBytes;
+        int acc = 0; uint32_t acc_phase = 0;
+        uint32_t buf_idx = 0;
+        for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+            const int m0 = (tile % num_m) * (2 * kBM) + (int)cta_rank * kBM;
+            const int n0 = (tile / num_m) * kBN;
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            const int row0 = m0 + quarter * 32;
+#pragma unroll 1
+            for (int ch = 0; ch < kBN / 64; ++ch) {
+                uint8_t* buf = my_stage + (buf_idx & 1) * kEpiBufBytes;
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+                    uint32_t r[32];
+                    const int colbase = ch * 64 + l * 32;
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * kBN + colbase, r);
+                    tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    if (bias != nullptr) {
+                        const int gcol = n0 + colbase;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (gcol + j < N) ? __ldg(bias + gcol + j) : 0.f;
+                    }
+                    uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        float t[8] = {v[q * 8], v[q * 8 + 1], v[q * 8 + 2], v[q * 8 + 3],
+                                      v[q * 8 + 4], v[q * 8 + 5], v[q * 8 + 6], v[q * 8 + 7]};
+                        store8<TOut>(reinterpret_cast<TOut*>(rowp + (((l * 4 + q) ^ (lane & 7)) << 4)), t);
+                    }
+                }
+                fence_async_smem();
+                __syncwarp();
+                if (lane == 0 && n0 + ch * 64 < N && row0 < M) tma_store_2d(&tmC, buf, n0 + ch * 64, row0);
+                if (lane == 0) tma_store_commit();
+                ++buf_idx;
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tmem_empty + acc);     // the leader's MMA thread counts all 8 warps
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (lane == 0) tma_store_wait_read<0>();
+    }
+    tc_fence_before();
+    cluster_sync_all();                       // neither CTA frees TMEM / exits while its peer may still use it
+    if (warp == 2) tmem_dealloc_pair(tmem_base, kTmemCols);
+}
+
 // ---------------------------------------------------------------- host: tensor maps
 static PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
     static PFN_cuTensorMapEncodeTiled_v12000 fn =
@@ -325,6 +485,29 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     return 0;
 }
 
+template <typename TOut>
+static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias, int M, int N,
+                       int K, int is_bf16, int sms, cudaStream_t s) {
+    auto kern = gemm_pair_kernel<TOut>;
+    static bool configured = false;
+    if (!configured) {
+        B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::kSmemBytes));
+        configured = true;
+    }
+    const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + pair::kBN - 1) / pair::kBN);
+    int pairs = sms / 2;
+    if (tiles < pairs) pairs = tiles;
+    kern<<<2 * pairs, kThreads, pair::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16);
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+// B200DP_GEMM_PAIR=0 turns the cta_group::2 kernel off (A/B measurements)
+static bool pair_enabled() {
+    static const bool on = [] { const char* e = getenv("B200DP_GEMM_PAIR"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 }  // namespace gemm
 }  // namespace b200dp
 
@@ -349,6 +532,18 @@ static int gemm_impl(const void* A, const void* B, void* C, const float* bias, i
     const int BN = N <= 64 ? 64 : ((N >= 256 && (int64_t)M * N >= (int64_t)148 * 128 * 256) ? 256 : 128);
     CUtensorMap ta, tb, tc;
     int rc;
+    // large K-major x K-major products with a 16-bit result: the CTA-pair kernel (256 x 256 tiles)
+    if (!a_mn && !b_mn && out_dtype == in_dtype && !accumulate_c && colstats == nullptr && pair_enabled() && N >= 256 &&
+        (int64_t)((M + 255) / 256) * ((N + 255) / 256) >= 74) {
+        rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 64, 32, 2);
+        if (rc) return rc;
+        rc = make_tmap(&ta, A, is_bf16, M, K, lda, kBK, kBM);
+        if (rc) return rc;
+        rc = make_tmap(&tb, B, is_bf16, N, K, ldb, kBK, pair::kHalfN);
+        if (rc) return rc;
+        if (is_bf16) return launch_pair<__nv_bfloat16>(ta, tb, tc, bias, M, N, K, 1, B200DP_SMS, (cudaStream_t)stream);
+        return launch_pair<__half>(ta, tb, tc, bias, M, N, K, 0, B200DP_SMS, (cudaStream_t)stream);
+    }
     const int c_bytes = out_dtype == B200DP_F32 ? 4 : 2;
     rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 128 / c_bytes, 32, c_bytes);   // staging rows are 128 B
     if (rc) return rc;

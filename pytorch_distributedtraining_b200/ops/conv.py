@@ -123,17 +123,19 @@ class _ConvFn(torch.autograd.Function):
             x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)
             dy2 = dy.permute(0, 2, 3, 1).reshape(-1, cout)
             rows = x2.shape[0]
-            if need_dx:
-                dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
+            # weight gradient first: the input gradient is then the most recent tensor in L2 when the
+            # backward of the layer below (BatchNorm) starts reading it
             if need_dw:
                 dw = gemm(dy2, x2, cout, cin, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
                 dw = dw.view(cout, 1, 1, cin).permute(0, 3, 1, 2)
+            if need_dx:
+                dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
         else:
             ours_dx = need_dx and stride == 1 and cout % 64 == 0 and cin % 8 == 0
-            if ours_dx:
-                dx = conv2d_raw(1, dy, w16, None, n, h, w, cin, cout, r, s, 1, pad)
             if need_dw:
                 dw = conv2d_wgrad_raw(x, dy, n, h, w, cin, cout, r, s, stride, pad)
+            if ours_dx:
+                dx = conv2d_raw(1, dy, w16, None, n, h, w, cin, cout, r, s, 1, pad)
             if need_dx and not ours_dx:
                 # library path for what the implicit-GEMM kernels do not cover yet: the input
                 # gradient of strided convolutions

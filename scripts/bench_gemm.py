@@ -2,7 +2,10 @@
 iterations by rotating through operand sets larger than L2."""
 import os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
+import argparse
 import torch
+ap = argparse.ArgumentParser(); ap.add_argument("--fwd-only", action="store_true"); ap.add_argument("--out", default="gpurun_out/gemm_bench.jsonl")
+args = ap.parse_args()
 from pytorch_distributedtraining_b200.ops.gemm import gemm
 
 dev = torch.device("cuda")
@@ -11,6 +14,8 @@ shapes = [(8192, 8192, 8192), (4096, 4096, 4096), (25216, 3072, 768), (25216, 76
 rows = []
 for (M, N, K) in shapes:
     for a_mn, b_mn, name in ((False, False, "fwd TN"), (False, True, "dgrad"), (True, True, "wgrad")):
+        if args.fwd_only and (a_mn or b_mn):
+            continue
         nset = max(2, int(300e6 // ((M * K + N * K + M * N) * 2)) + 1)
         nset = min(nset, 8)
         As = [torch.randn((K, M) if a_mn else (M, K), device=dev).bfloat16() for _ in range(nset)]
@@ -38,5 +43,5 @@ for (M, N, K) in shapes:
         rows.append(r)
         print(json.dumps(r), flush=True)
 os.makedirs("gpurun_out", exist_ok=True)
-with open("gpurun_out/gemm_bench.jsonl", "w") as fh:
+with open(args.out, "w") as fh:
     for r in rows: fh.write(json.dumps(r) + "\n")

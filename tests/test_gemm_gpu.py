@@ -116,3 +116,21 @@ def test_gemm_with_fused_gather_of_row_sharded_weights(dtype, M, N, K, world):
         assert torch.equal(w_full, w), "the gathered copy of W must be exact"
         tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
         torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * max(1.0, K ** 0.5 * 0.25))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K,bias", [(8192, 4096, 512, False), (25216, 3072, 768, True), (4500, 4360, 136, True),
+                                        (19456, 256, 64, False)])
+def test_gemm_cta_pair_kernel(dtype, M, N, K, bias):
+    """Shapes large enough for the cta_group::2 kernel (256 x 256 tiles per CTA pair): ragged M / N / K
+    tails, with and without the bias epilogue."""
+    from pytorch_distributedtraining_b200.ops.gemm import gemm
+    a, b = _mk(M, K, dtype, 5), _mk(N, K, dtype, 6)
+    bv = torch.randn(N, device=cuda) if bias else None
+    want = a.float() @ b.float().t()
+    if bias:
+        want = want + bv
+    got = gemm(a, b, M, N, K, bias=bv)
+    torch.cuda.synchronize()
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * max(1.0, K ** 0.5 * 0.25))
