@@ -300,10 +300,11 @@ constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 + 256;
 constexpr int kTmemCols = 512;
 }  // namespace pair
 
-template <typename TOut>
+template <bool kAMN, bool kBMN, typename TOut>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias, int M, int N, int K, int is_bf16) {
+                 const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias, int M, int N, int K, int is_bf16,
+                 int accumulate_c, int splits) {
     using namespace pair;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -324,6 +325,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int num_m = (M + 2 * kBM - 1) / (2 * kBM), num_n = (N + kBN - 1) / kBN;
     const int num_tiles = num_m * num_n;
     const int num_kb = (K + kBK - 1) / kBK;
+    // split-K as in gemm_kernel: item = (tile, split), partial products combined by TMA reduce-add
+    const int kb_per = (num_kb + splits - 1) / splits;
+    const int num_items = num_tiles * splits;
 
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); tma_prefetch_desc(&tmC); }
     if (warp == 1 && lane == 0) {
@@ -342,14 +346,29 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         // ===== TMA producer (both CTAs) =====
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
-            for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+            for (int item = pair_id; item < num_items; item += num_pairs) {
+                const int tile = item % num_tiles, split = item / num_tiles;
                 const int m0 = (tile % num_m) * (2 * kBM) + (int)cta_rank * kBM;
                 const int n0 = (tile / num_m) * kBN + (int)cta_rank * kHalfN;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                const int kb_begin = split * kb_per, kb_end = min(num_kb, kb_begin + kb_per);
+                for (int kb = kb_begin; kb < kb_end; ++kb) {
                     mbar_wait(empty + stage, phase ^ 1);
                     if (leader) mbar_expect_tx(full + stage, 2 * kStageBytes);
-                    tma_load_2d_pair(smemA + stage * kABytes, &tmA, full + stage, kb * kBK, m0);
-                    tma_load_2d_pair(smemB + stage * kBBytes, &tmB, full + stage, kb * kBK, n0);
+                    uint8_t* a = smemA + stage * kABytes;
+                    uint8_t* b = smemB + stage * kBBytes;
+                    const int k0 = kb * kBK;
+                    if (kAMN) {
+#pragma unroll
+                        for (int j = 0; j < kBM / 64; ++j) tma_load_2d_pair(a + j * (kBK * 128), &tmA, full + stage, m0 + j * 64, k0);
+                    } else {
+                        tma_load_2d_pair(a, &tmA, full + stage, k0, m0);
+                    }
+                    if (kBMN) {
+#pragma unroll
+                        for (int j = 0; j < kHalfN / 64; ++j) tma_load_2d_pair(b + j * (kBK * 128), &tmB, full + stage, n0 + j * 64, k0);
+                    } else {
+                        tma_load_2d_pair(b, &tmB, full + stage, k0, n0);
+                    }
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -357,22 +376,28 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else if (warp == 1) {
         // ===== MMA issuer (leader CTA only) =====
         if (leader && lane == 0) {
-            const uint32_t idesc = make_idesc(is_bf16, 0, 0, 2 * kBM, kBN);
+            const uint32_t idesc = make_idesc(is_bf16, kAMN ? 1 : 0, kBMN ? 1 : 0, 2 * kBM, kBN);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
-            for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+            for (int item = pair_id; item < num_items; item += num_pairs) {
+                const int split = item / num_tiles;
+                const int kb_begin = split * kb_per, kb_end = min(num_kb, kb_begin + kb_per);
                 mbar_wait(tmem_empty + acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * kBN;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = kb_begin; kb < kb_end; ++kb) {
                     mbar_wait(full + stage, phase);
                     tc_fence_after();
                     const uint32_t a_addr = smem_u32(smemA + stage * kABytes);
                     const uint32_t b_addr = smem_u32(smemB + stage * kBBytes);
 #pragma unroll
-                    for (int k = 0; k < kBK / kUmmaK; ++k)
-                        umma_f16_pair(d_tmem, make_desc(a_addr + k * (kUmmaK * 2), 16, 1024),
-                                      make_desc(b_addr + k * (kUmmaK * 2), 16, 1024), idesc, (kb | k) != 0 ? 1u : 0u);
+                    for (int k = 0; k < kBK / kUmmaK; ++k) {
+                        const uint64_t da = kAMN ? make_desc(a_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                 : make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
+                        const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                 : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
+                        umma_f16_pair(d_tmem, da, db, idesc, (kb != kb_begin || k != 0) ? 1u : 0u);
+                    }
                     umma_commit_pair(empty + stage, 3);          // both CTAs' producers may refill this stage
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
@@ -383,45 +408,60 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else if (warp >= kEpiWarp0) {
         // ===== epilogue (both CTAs; each drains its own 128 rows) =====
         const int quarter = warp - kEpiWarp0;
+        constexpr int kChunkCols = 128 / (int)sizeof(TOut);
+        constexpr int kLoadsPerChunk = kChunkCols / 32;
         uint8_t* my_stage = smemC + quarter * 2 * kEpiBufBytes;
         int acc = 0; uint32_t acc_phase = 0;
         uint32_t buf_idx = 0;
-        for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+        for (int item = pair_id; item < num_items; item += num_pairs) {
+            const int tile = item % num_tiles, split = item / num_tiles;
             const int m0 = (tile % num_m) * (2 * kBM) + (int)cta_rank * kBM;
             const int n0 = (tile / num_m) * kBN;
+            const bool add_bias = bias != nullptr && split == 0;
+            const bool has_k = split * kb_per < num_kb;
             mbar_wait(tmem_full + acc, acc_phase);
             tc_fence_after();
             const int row0 = m0 + quarter * 32;
 #pragma unroll 1
-            for (int ch = 0; ch < kBN / 64; ++ch) {
+            for (int ch = 0; ch < kBN / kChunkCols; ++ch) {
                 uint8_t* buf = my_stage + (buf_idx & 1) * kEpiBufBytes;
                 if (lane == 0) tma_store_wait_read<1>();
                 __syncwarp();
 #pragma unroll
-                for (int l = 0; l < 2; ++l) {
+                for (int l = 0; l < kLoadsPerChunk; ++l) {
                     uint32_t r[32];
-                    const int colbase = ch * 64 + l * 32;
+                    const int colbase = ch * kChunkCols + l * 32;
                     tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * kBN + colbase, r);
                     tmem_ld_wait();
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (bias != nullptr) {
+                    if (add_bias) {
                         const int gcol = n0 + colbase;
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += (gcol + j < N) ? __ldg(bias + gcol + j) : 0.f;
                     }
                     uint8_t* rowp = buf + lane * 128;
+                    if (sizeof(TOut) == 2) {
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        float t[8] = {v[q * 8], v[q * 8 + 1], v[q * 8 + 2], v[q * 8 + 3],
-                                      v[q * 8 + 4], v[q * 8 + 5], v[q * 8 + 6], v[q * 8 + 7]};
-                        store8<TOut>(reinterpret_cast<TOut*>(rowp + (((l * 4 + q) ^ (lane & 7)) << 4)), t);
+                        for (int q = 0; q < 4; ++q) {
+                            float t[8] = {v[q * 8], v[q * 8 + 1], v[q * 8 + 2], v[q * 8 + 3],
+                                          v[q * 8 + 4], v[q * 8 + 5], v[q * 8 + 6], v[q * 8 + 7]};
+                            store8<TOut>(reinterpret_cast<TOut*>(rowp + (((l * 4 + q) ^ (lane & 7)) << 4)), t);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(rowp + ((j ^ (lane & 7)) << 4)) =
+                                make_float4(v[j * 4], v[j * 4 + 1], v[j * 4 + 2], v[j * 4 + 3]);
                     }
                 }
                 fence_async_smem();
                 __syncwarp();
-                if (lane == 0 && n0 + ch * 64 < N && row0 < M) tma_store_2d(&tmC, buf, n0 + ch * 64, row0);
+                if (lane == 0 && n0 + ch * kChunkCols < N && row0 < M && has_k) {
+                    if (accumulate_c || splits > 1) tma_reduce_add_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
+                    else tma_store_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
+                }
                 if (lane == 0) tma_store_commit();
                 ++buf_idx;
             }
@@ -485,19 +525,19 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     return 0;
 }
 
-template <typename TOut>
+template <bool kAMN, bool kBMN, typename TOut>
 static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias, int M, int N,
-                       int K, int is_bf16, int sms, cudaStream_t s) {
-    auto kern = gemm_pair_kernel<TOut>;
+                       int K, int is_bf16, int accumulate_c, int splits, int sms, cudaStream_t s) {
+    auto kern = gemm_pair_kernel<kAMN, kBMN, TOut>;
     static bool configured = false;
     if (!configured) {
         B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::kSmemBytes));
         configured = true;
     }
-    const int tiles = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + pair::kBN - 1) / pair::kBN);
+    const int items = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + pair::kBN - 1) / pair::kBN) * splits;
     int pairs = sms / 2;
-    if (tiles < pairs) pairs = tiles;
-    kern<<<2 * pairs, kThreads, pair::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16);
+    if (items < pairs) pairs = items;
+    kern<<<2 * pairs, kThreads, pair::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits);
     B200DP_CHECK_LAUNCH();
     return 0;
 }
@@ -532,17 +572,47 @@ static int gemm_impl(const void* A, const void* B, void* C, const float* bias, i
     const int BN = N <= 64 ? 64 : ((N >= 256 && (int64_t)M * N >= (int64_t)148 * 128 * 256) ? 256 : 128);
     CUtensorMap ta, tb, tc;
     int rc;
-    // large K-major x K-major products with a 16-bit result: the CTA-pair kernel (256 x 256 tiles)
-    if (!a_mn && !b_mn && out_dtype == in_dtype && !accumulate_c && colstats == nullptr && pair_enabled() && N >= 256 &&
-        (int64_t)((M + 255) / 256) * ((N + 255) / 256) >= 74) {
-        rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 64, 32, 2);
-        if (rc) return rc;
-        rc = make_tmap(&ta, A, is_bf16, M, K, lda, kBK, kBM);
-        if (rc) return rc;
-        rc = make_tmap(&tb, B, is_bf16, N, K, ldb, kBK, pair::kHalfN);
-        if (rc) return rc;
-        if (is_bf16) return launch_pair<__nv_bfloat16>(ta, tb, tc, bias, M, N, K, 1, B200DP_SMS, (cudaStream_t)stream);
-        return launch_pair<__half>(ta, tb, tc, bias, M, N, K, 0, B200DP_SMS, (cudaStream_t)stream);
+    // large products: the CTA-pair kernel (256 x 256 tiles).  16-bit results need >= one tile per pair;
+    // fp32 results (weight gradients: few tiles, long K) are split along K to give every pair work.
+    if (colstats == nullptr && pair_enabled() && M >= 256 && N >= 256) {
+        const int64_t tiles2 = (int64_t)((M + 255) / 256) * ((N + 255) / 256);
+        const int num_kb2 = (K + kBK - 1) / kBK;
+        int splits2 = 1;
+        bool use = false;
+        if (out_dtype == in_dtype) {
+            use = !accumulate_c && tiles2 >= 74;
+        } else {
+            if (tiles2 < 74) {
+                splits2 = (int)(74 / tiles2);
+                if (splits2 > num_kb2 / 8) splits2 = num_kb2 / 8;
+                if (splits2 < 1) splits2 = 1;
+                const int kbp = (num_kb2 + splits2 - 1) / splits2;
+                splits2 = (num_kb2 + kbp - 1) / kbp;
+            }
+            use = tiles2 * splits2 >= 56;
+        }
+        if (use) {
+            const int cb = out_dtype == B200DP_F32 ? 4 : 2;
+            rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 128 / cb, 32, cb);
+            if (rc) return rc;
+            rc = a_mn ? make_tmap(&ta, A, is_bf16, K, M, lda, 64, kBK) : make_tmap(&ta, A, is_bf16, M, K, lda, kBK, kBM);
+            if (rc) return rc;
+            rc = b_mn ? make_tmap(&tb, B, is_bf16, K, N, ldb, 64, kBK) : make_tmap(&tb, B, is_bf16, N, K, ldb, kBK, pair::kHalfN);
+            if (rc) return rc;
+            cudaStream_t ps = (cudaStream_t)stream;
+            if (splits2 > 1 && !accumulate_c) B200DP_CUDA(cudaMemsetAsync(C, 0, (size_t)M * ldc * 4, ps));
+#define GP(AM, BM_, T) return launch_pair<AM, BM_, T>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits2, B200DP_SMS, ps)
+#define GP_OUT(AM, BM_)                                          \
+    if (out_dtype == B200DP_F32) { GP(AM, BM_, float); }          \
+    else if (is_bf16) { GP(AM, BM_, __nv_bfloat16); }             \
+    else { GP(AM, BM_, __half); }
+            if (!a_mn && !b_mn) { GP_OUT(false, false) }
+            else if (!a_mn && b_mn) { GP_OUT(false, true) }
+            else if (a_mn && b_mn) { GP_OUT(true, true) }
+            else { GP_OUT(true, false) }
+#undef GP_OUT
+#undef GP
+        }
     }
     const int c_bytes = out_dtype == B200DP_F32 ? 4 : 2;
     rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 128 / c_bytes, 32, c_bytes);   // staging rows are 128 B

@@ -29,8 +29,9 @@ class Attention(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B, S, D = x.shape
-        qkv = self.in_proj(x).view(B, S, 3, self.heads, D // self.heads).permute(2, 0, 3, 1, 4)
-        o = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2])
+        # unbind (one stacked gradient) rather than three selects (three zero-filled full-size gradients)
+        q, k, v = self.in_proj(x).view(B, S, 3, self.heads, D // self.heads).permute(2, 0, 3, 1, 4).unbind(0)
+        o = F.scaled_dot_product_attention(q, k, v)
         return self.out_proj(o.transpose(1, 2).reshape(B, S, D))
 
 

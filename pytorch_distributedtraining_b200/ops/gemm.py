@@ -85,16 +85,22 @@ class _LinearFn(torch.autograd.Function):
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         dx = dw = db = None
-        if ctx.needs_input_grad[0]:
-            dx = gemm(dy2, w16, rows, in_f, out_f, a_mn=False, b_mn=True).view(ctx.x_shape)
+        # parameter gradients first, the input gradient last: it is then the most recent tensor in L2 for
+        # the backward of the layer below
         if ctx.needs_input_grad[1]:
             dw = gemm(dy2, x2, out_f, in_f, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
             if ctx.w_dtype != torch.float32:
                 dw = dw.to(ctx.w_dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = torch.sum(dy2, dim=0, dtype=torch.float32)
+            if out_f % 8 == 0 and out_f <= 16384 and rows >= 64:
+                from .norm import column_sums
+                db = column_sums(dy2)
+            else:
+                db = torch.sum(dy2, dim=0, dtype=torch.float32)
             if ctx.b_dtype != torch.float32:
                 db = db.to(ctx.b_dtype)
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, w16, rows, in_f, out_f, a_mn=False, b_mn=True).view(ctx.x_shape)
         return dx, dw, db, None
 
 

@@ -134,3 +134,30 @@ def test_gemm_cta_pair_kernel(dtype, M, N, K, bias):
     torch.cuda.synchronize()
     tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
     torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * max(1.0, K ** 0.5 * 0.25))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn,f32", [
+    (25216, 768, 3072, False, True, False),      # dgrad of fc1 (weights read MN-major)
+    (8192, 2304, 768, False, True, False),
+    (3072, 768, 25216, True, True, True),        # wgrad of fc1: 36 tiles, split along K, fp32 reduce-add
+    (768, 3072, 12000, True, True, True),
+    (2304, 768, 4104, True, True, True),
+    (4096, 4096, 520, True, False, False),
+])
+def test_gemm_cta_pair_kernel_operand_layouts(dtype, M, N, K, a_mn, b_mn, f32):
+    from pytorch_distributedtraining_b200.ops.gemm import gemm
+    a = _mk(K, M, dtype, 7) if a_mn else _mk(M, K, dtype, 7)
+    b = _mk(K, N, dtype, 8) if b_mn else _mk(N, K, dtype, 8)
+    A = a.float().t() if a_mn else a.float()
+    B = b.float().t() if b_mn else b.float()
+    want = A @ B.t()
+    got = gemm(a, b, M, N, K, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32 if f32 else None)
+    torch.cuda.synchronize()
+    tol = (2e-3 if f32 else (2e-2 if dtype == torch.bfloat16 else 4e-3))
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * max(1.0, K ** 0.5 * 0.25))
+    if f32:
+        # accumulate into an existing gradient
+        got2 = gemm(a, b, M, N, K, a_mn=a_mn, b_mn=b_mn, out=got.clone(), out_dtype=torch.float32, accumulate=True)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(got2, 2 * want, rtol=2 * tol, atol=2 * tol * max(1.0, K ** 0.5 * 0.25))
