@@ -312,6 +312,13 @@ int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* m
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
                                 int slot_floats, void* const* call_counter, void* stream);
 
+/* Attention layout moves (ViT / SwinIR): W per-head tensors [B][H][S][d] <-> one token-major tensor
+ * [B][S][W][H][d] in one streaming pass (W = 3: packed q/k/v gradient; W = 1: merge heads).  Rows of
+ * d elements must be multiples of 16 bytes.  Reference: the reshape / permute / stack chains around
+ * nn.MultiheadAttention in the transformer models (ATen copies there). */
+int b200dp_heads_to_tokens(const void* const* srcs, void* out, int B, int H, int S, int d, int W, int elem_bytes, void* stream);
+int b200dp_tokens_to_heads(const void* in, void* const* dsts, int B, int H, int S, int d, int W, int elem_bytes, void* stream);
+
 /* GEMM / forward convolution whose epilogue also accumulates, per output column (channel), the sum
  * and the sum of squares of the values it stores: colstats[0:N] += sum, colstats[N:2N] += sum of
  * squares (fp32 atomics from per-lane register partials; the caller zeroes colstats).  These are the

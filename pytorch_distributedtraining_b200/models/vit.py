@@ -15,6 +15,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops.attention import merge_heads, split_qkv
 from ..ops.layers import LayerNorm, Linear
 
 __all__ = ["VisionTransformer", "vit_b_16", "vit_s_16", "vit_tiny"]
@@ -29,10 +30,8 @@ class Attention(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B, S, D = x.shape
-        # unbind (one stacked gradient) rather than three selects (three zero-filled full-size gradients)
-        q, k, v = self.in_proj(x).view(B, S, 3, self.heads, D // self.heads).permute(2, 0, 3, 1, 4).unbind(0)
-        o = F.scaled_dot_product_attention(q, k, v)
-        return self.out_proj(o.transpose(1, 2).reshape(B, S, D))
+        q, k, v = split_qkv(self.in_proj(x), self.heads)
+        return self.out_proj(merge_heads(F.scaled_dot_product_attention(q, k, v)))
 
 
 class MLP(nn.Module):
