@@ -9,9 +9,11 @@ namespace b200dp {
 struct HeadSrc { const void* p[3]; };
 struct HeadDst { void* p[3]; };
 
-// out[b][s][w][h][:] = src_w[b][h][s][:]      (W sources, each [B][H][S][d])
+// out[b][s][w][h][:] = src_w[b][h][s][:]      (W sources, each logically [B][H][S][d] with element strides
+// (sb, sh, ss) and a contiguous last dimension — contiguous per-head tensors and token-major views alike)
 __global__ void __launch_bounds__(256) heads_to_tokens_kernel(HeadSrc src, uint4* __restrict__ out, int B, int H, int S,
-                                                              int W, int vpr /* 16-byte vectors per head row */) {
+                                                              int W, int vpr /* 16-byte vectors per head row */,
+                                                              long long sb, long long sh, long long ss /* in vectors */) {
     const long long total = (long long)B * S * W * H * vpr;
     for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += (long long)gridDim.x * blockDim.x) {
         const int v = (int)(o % vpr);
@@ -21,7 +23,7 @@ __global__ void __launch_bounds__(256) heads_to_tokens_kernel(HeadSrc src, uint4
         const int s = (int)(t % S);
         const int b = (int)(t / S);
         const uint4* sp = reinterpret_cast<const uint4*>(src.p[w]);
-        out[o] = __ldg(sp + (((long long)b * H + h) * S + s) * vpr + v);
+        out[o] = __ldg(sp + b * sb + h * sh + s * ss + v);
     }
 }
 
@@ -47,7 +49,7 @@ __global__ void __launch_bounds__(256) tokens_to_heads_kernel(const uint4* __res
 using namespace b200dp;
 
 extern "C" int b200dp_heads_to_tokens(const void* const* srcs, void* out, int B, int H, int S, int d, int W, int elem_bytes,
-                                      void* stream) {
+                                      long long stride_b, long long stride_h, long long stride_s, void* stream) {
     B200DP_REQUIRE(srcs && out && W >= 1 && W <= 3, "heads_to_tokens: bad arguments");
     B200DP_REQUIRE((d * elem_bytes) % 16 == 0, "heads_to_tokens: head rows must be multiples of 16 bytes");
     HeadSrc s;
@@ -57,7 +59,11 @@ extern "C" int b200dp_heads_to_tokens(const void* const* srcs, void* out, int B,
     if (total == 0) return 0;
     long long blocks = (total + 255) / 256;
     if (blocks > B200DP_SMS * 16) blocks = B200DP_SMS * 16;
-    heads_to_tokens_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(s, (uint4*)out, B, H, S, W, vpr);
+    const long long epv = 16 / elem_bytes;      // elements per vector
+    B200DP_REQUIRE(stride_b % epv == 0 && stride_h % epv == 0 && stride_s % epv == 0,
+                   "heads_to_tokens: source strides must be multiples of 16 bytes");
+    heads_to_tokens_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(s, (uint4*)out, B, H, S, W, vpr, stride_b / epv,
+                                                                               stride_h / epv, stride_s / epv);
     B200DP_CHECK_LAUNCH();
     return 0;
 }

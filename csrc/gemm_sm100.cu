@@ -589,7 +589,7 @@ static int gemm_impl(const void* A, const void* B, void* C, const float* bias, i
                 const int kbp = (num_kb2 + splits2 - 1) / splits2;
                 splits2 = (num_kb2 + kbp - 1) / kbp;
             }
-            use = tiles2 * splits2 >= 56;
+            use = tiles2 * splits2 >= 40;
         }
         if (use) {
             const int cb = out_dtype == B200DP_F32 ? 4 : 2;

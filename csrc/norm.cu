@@ -382,71 +382,119 @@ __global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwd_kernel(
     }
 }
 
-template <typename T>
-__global__ void __launch_bounds__(kLNWarps * 32) layernorm_bwd_dx_kernel(
+// Fused LayerNorm backward: ONE pass over dy and x produces dx and the parameter gradients.  Persistent
+// warps walk the rows (warp per row, lane owns chunks lane, lane+32, ... of 8 columns, as in the
+// forward), so each lane's share of dbeta = sum dy and dgamma = sum dy * xhat stays in registers across
+// all its rows; the CTA's warps combine in shared memory and write one partial per CTA, which a small
+// second kernel adds in a fixed order (deterministic, no float atomics).
+template <typename T, int NCH>
+__global__ void __launch_bounds__(kLNWarps * 32) layernorm_bwd_fused_kernel(
     const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t rows, int D,
-    const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd) {
-    const int lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * kLNWarps + (threadIdx.x >> 5);
-    if (row >= rows) return;
+    const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
+    float* __restrict__ scratch /* one [dbeta(D) | dgamma(D)] partial per CTA */) {
+    __shared__ float red[2 * NCH * 256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nchunk = D / 8;
-    const float mu = mean[row], rs = rstd[row];
-    float g[kLNMaxChunks][8], xh[kLNMaxChunks][8];
-    float c1 = 0.f, c2 = 0.f;
+    float pa[NCH][8], pb[NCH][8];
 #pragma unroll
-    for (int j = 0; j < kLNMaxChunks; ++j) {
-        const int ch = lane + j * 32;
-        if (ch < nchunk) {
-            float d[8], xv[8], ga[8];
-            load8<T>(dy + row * D + ch * 8, d);
-            load8<T>(x + row * D + ch * 8, xv);
-            load8<float>(gamma + ch * 8, ga);
+    for (int j = 0; j < NCH; ++j)
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                xh[j][k] = (xv[k] - mu) * rs;
-                g[j][k] = d[k] * ga[k];
-                c1 += g[j][k] * xh[j][k];
-                c2 += g[j][k];
+        for (int k = 0; k < 8; ++k) { pa[j][k] = 0.f; pb[j][k] = 0.f; }
+
+    for (int64_t row = (int64_t)blockIdx.x * kLNWarps + warp; row < rows; row += (int64_t)gridDim.x * kLNWarps) {
+        const float mu = mean[row], rs = rstd[row];
+        Vec8<T> dv[NCH], xv[NCH];
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int ch = lane + j * 32;
+            if (ch < nchunk) {
+                dv[j] = *reinterpret_cast<const Vec8<T>*>(dy + row * D + ch * 8);
+                xv[j] = *reinterpret_cast<const Vec8<T>*>(x + row * D + ch * 8);
+            }
+        }
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int ch = lane + j * 32;
+            if (ch < nchunk) {
+                float ga[8];
+                load8<float>(gamma + ch * 8, ga);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float d = Cvt<T>::to_f(dv[j].v[k]);
+                    const float xh = (Cvt<T>::to_f(xv[j].v[k]) - mu) * rs;
+                    const float g = d * ga[k];
+                    c1 += g * xh;
+                    c2 += g;
+                    pa[j][k] += d;
+                    pb[j][k] += d * xh;
+                }
+            }
+        }
+        c1 = warp_sum(c1) / D;
+        c2 = warp_sum(c2) / D;
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int ch = lane + j * 32;
+            if (ch < nchunk) {
+                float ga[8], o[8];
+                load8<float>(gamma + ch * 8, ga);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const float xh = (Cvt<T>::to_f(xv[j].v[k]) - mu) * rs;
+                    o[k] = rs * (Cvt<T>::to_f(dv[j].v[k]) * ga[k] - c2 - xh * c1);
+                }
+                store8<T>(dx + row * D + ch * 8, o);
             }
         }
     }
-    c1 = warp_sum(c1) / D;
-    c2 = warp_sum(c2) / D;
+    // combine the CTA's warps (fixed order), publish the CTA partial
+    for (int w = 0; w < kLNWarps; ++w) {
+        if (warp == w) {
 #pragma unroll
-    for (int j = 0; j < kLNMaxChunks; ++j) {
-        const int ch = lane + j * 32;
-        if (ch < nchunk) {
-            float o[8];
+            for (int j = 0; j < NCH; ++j) {
+                const int ch = lane + j * 32;
+                if (ch < nchunk) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) o[k] = rs * (g[j][k] - c2 - xh[j][k] * c1);
-            store8<T>(dx + row * D + ch * 8, o);
+                    for (int k = 0; k < 8; ++k) {
+                        const int c = ch * 8 + k;
+                        red[c] = (w == 0 ? 0.f : red[c]) + pa[j][k];
+                        red[D + c] = (w == 0 ? 0.f : red[D + c]) + pb[j][k];
+                    }
+                }
+            }
         }
+        __syncthreads();
     }
+    float* mine = scratch + (size_t)blockIdx.x * 2 * D;
+    for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) mine[i] = red[i];
 }
 
-// dgamma = sum_rows dy * xhat, dbeta = sum_rows dy: same column-reduction shape as BatchNorm.
-template <typename T>
-__global__ void __launch_bounds__(kBNThreads) layernorm_bwd_dparams_kernel(
-    const T* __restrict__ dy, const T* __restrict__ x, int64_t rows, int D, int tpr, int cgb, int rpb,
-    const float* __restrict__ mean, const float* __restrict__ rstd, float* __restrict__ scratch,
-    unsigned int* __restrict__ counters, float* __restrict__ out /* [dbeta(D) | dgamma(D)] */) {
-    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
-    const int cg = blockIdx.x * cgb + cgl;
-    const bool active = rl < rpb && cg < tpr;
-    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (active) {
-        const int c0 = cg * 8;
-        const int64_t rstep = (int64_t)gridDim.y * rpb;
-        for (int64_t r = (int64_t)blockIdx.y * rpb + rl; r < rows; r += rstep) {
-            float d[8], xv[8];
-            load8<T>(dy + r * D + c0, d);
-            load8<T>(x + r * D + c0, xv);
-            const float mu = mean[r], rs = rstd[r];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { a[k] += d[k]; b[k] += d[k] * (xv[k] - mu) * rs; }
+// out[c] = sum over the CTA partials of column c, in a fixed order: 32 columns x 8 partial slices per CTA
+__global__ void __launch_bounds__(256) ln_partials_reduce_kernel(const float* __restrict__ scratch, int parts, int cols,
+                                                                 float* __restrict__ out) {
+    __shared__ float sm[8][33];
+    const int cl = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    if (c < cols) {
+        int p = sl;
+        for (; p + 24 < parts; p += 32) {
+            a0 += scratch[(size_t)p * cols + c];
+            a1 += scratch[(size_t)(p + 8) * cols + c];
+            a2 += scratch[(size_t)(p + 16) * cols + c];
+            a3 += scratch[(size_t)(p + 24) * cols + c];
         }
+        for (; p < parts; p += 8) a0 += scratch[(size_t)p * cols + c];
     }
-    bn_reduce_tail(a, b, D, cgb, rpb, rl, cgl, cg, active, scratch, counters, out);
+    sm[sl][cl] = (a0 + a1) + (a2 + a3);
+    __syncthreads();
+    if (sl == 0 && c < cols) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sm[i][cl];
+        out[c] = t;
+    }
 }
 
 }  // namespace b200dp
@@ -539,7 +587,14 @@ int b200dp_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, 
     return 0;
 }
 
-int64_t b200dp_ln_scratch_floats(int64_t rows, int D) { return b200dp_bn_scratch_floats(rows, D); }
+static unsigned ln_bwd_grid(int64_t rows) {
+    const int64_t want = (rows + kLNWarps - 1) / kLNWarps;
+    const int64_t cap = (int64_t)B200DP_SMS * 4;
+    return (unsigned)(want < cap ? want : cap);
+}
+
+// one [dbeta | dgamma] partial per CTA of the fused backward
+int64_t b200dp_ln_scratch_floats(int64_t rows, int D) { return rows <= 0 || D <= 0 ? 0 : (int64_t)ln_bwd_grid(rows) * 2 * D; }
 
 int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dtype dtype, const float* gamma,
                          const float* beta, float eps, float* mean, float* rstd, void* stream) {
@@ -563,15 +618,18 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
     B200DP_REQUIRE(dgamma == dbeta + D, "layernorm_bwd: dbeta and dgamma must be one buffer [dbeta(D) | dgamma(D)]");
     B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_bwd: D must be a multiple of 8, <= %d",
                    kLNMaxChunks * 256);
-    const int C = D;
-    BN_COMMON_CHECKS("layernorm_bwd")
-    const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
-    B200DP_DISPATCH_DTYPE(dtype, T, {
-        layernorm_bwd_dx_kernel<T><<<blocks, kLNWarps * 32, 0, s>>>((const T*)dy, (const T*)x, (T*)dx, rows, D, gamma,
-                                                                    mean, rstd);
-        layernorm_bwd_dparams_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)x, rows, D, g.tpr, g.cgb,
-                                                                    g.rpb, mean, rstd, scratch, counter, dbeta);
-    });
+    cudaStream_t s = (cudaStream_t)stream;
+    const unsigned grid = ln_bwd_grid(rows);
+    const int nch = (D + 255) / 256;
+#define LNB(N_)                                                                                                     \
+    B200DP_DISPATCH_DTYPE(dtype, T, {                                                                               \
+        layernorm_bwd_fused_kernel<T, N_><<<grid, kLNWarps * 32, 0, s>>>((const T*)dy, (const T*)x, (T*)dx, rows, D, \
+                                                                         gamma, mean, rstd, scratch);       \
+    })
+    if (nch <= 1) LNB(1) else if (nch <= 2) LNB(2) else if (nch <= 3) LNB(3) else if (nch <= 4) LNB(4)
+    else if (nch <= 6) LNB(6) else LNB(8)
+#undef LNB
+    ln_partials_reduce_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(scratch, (int)grid, 2 * D, dbeta);
     B200DP_CHECK_LAUNCH();
     return 0;
 }

@@ -316,7 +316,8 @@ int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging
  * [B][S][W][H][d] in one streaming pass (W = 3: packed q/k/v gradient; W = 1: merge heads).  Rows of
  * d elements must be multiples of 16 bytes.  Reference: the reshape / permute / stack chains around
  * nn.MultiheadAttention in the transformer models (ATen copies there). */
-int b200dp_heads_to_tokens(const void* const* srcs, void* out, int B, int H, int S, int d, int W, int elem_bytes, void* stream);
+int b200dp_heads_to_tokens(const void* const* srcs, void* out, int B, int H, int S, int d, int W, int elem_bytes,
+                           long long stride_b, long long stride_h, long long stride_s /* source strides, elements */, void* stream);
 int b200dp_tokens_to_heads(const void* in, void* const* dsts, int B, int H, int S, int d, int W, int elem_bytes, void* stream);
 
 /* GEMM / forward convolution whose epilogue also accumulates, per output column (channel), the sum

@@ -33,12 +33,22 @@ def _kernels_ok(t: torch.Tensor, d: int) -> bool:
         and dispatch._lib_ok()
 
 
+def _packable(srcs, d: int) -> bool:
+    """Same strides on every source, contiguous last dimension, 16-byte aligned rows."""
+    s0 = srcs[0]
+    epv = 16 // s0.element_size()
+    return all(t.stride() == s0.stride() and t.stride(3) == 1 and t.data_ptr() % 16 == 0 for t in srcs) \
+        and all(st % epv == 0 for st in s0.stride()[:3])
+
+
 def _heads_to_tokens(srcs, B: int, H: int, S: int, d: int) -> torch.Tensor:
-    """W contiguous ``[B, H, S, d]`` tensors -> ``[B, S, W, H, d]``."""
+    """W ``[B, H, S, d]`` tensors (any strides with a contiguous last dimension) -> ``[B, S, W, H, d]``."""
     lib = require_library()
     W = len(srcs)
     out = torch.empty((B, S, W, H, d), dtype=srcs[0].dtype, device=srcs[0].device)
+    sb, sh, ss, _ = srcs[0].stride()
     check(lib.b200dp_heads_to_tokens(table(list(srcs)), ptr(out), B, H, S, d, W, srcs[0].element_size(),
+                                     ctypes.c_longlong(sb), ctypes.c_longlong(sh), ctypes.c_longlong(ss),
                                      stream_ptr(out.device)), "heads_to_tokens")
     return out
 
@@ -65,7 +75,7 @@ class _SplitQKV(torch.autograd.Function):
     def backward(ctx, dq, dk, dv):  # type: ignore[override]
         B, S, H, d = ctx.geom
         grads = (dq, dk, dv)
-        if all(g.is_contiguous() for g in grads) and _kernels_ok(dq, d):
+        if _kernels_ok(dq, d) and _packable(grads, d):
             return _heads_to_tokens(grads, B, H, S, d).view(B, S, 3 * H * d), None
         # token-major or arbitrary gradients: one strided copy per tensor into the packed buffer
         out = torch.empty((B, S, 3, H, d), dtype=dq.dtype, device=dq.device)
@@ -82,7 +92,7 @@ class _MergeHeads(torch.autograd.Function):
         if o.transpose(1, 2).is_contiguous():
             ctx.mode = "view"
             return o.transpose(1, 2).reshape(B, S, H * d)
-        if o.is_contiguous() and _kernels_ok(o, d):
+        if _kernels_ok(o, d) and _packable((o,), d):
             ctx.mode = "kernel"
             return _heads_to_tokens((o,), B, H, S, d).view(B, S, H * d)
         ctx.mode = "copy"
