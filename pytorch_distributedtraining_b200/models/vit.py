@@ -15,10 +15,19 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops import dispatch
+from ..ops import gemm as _gemm
 from ..ops.attention import merge_heads, split_qkv
 from ..ops.layers import LayerNorm, Linear
 
 __all__ = ["VisionTransformer", "vit_b_16", "vit_s_16", "vit_tiny"]
+
+
+class _PatchProj:
+    """Shape carrier for ``dispatch.linear_supported``."""
+
+    def __init__(self, in_features: int, out_features: int):
+        self.in_features, self.out_features = in_features, out_features
 
 
 class Attention(nn.Module):
@@ -78,13 +87,29 @@ class VisionTransformer(nn.Module):
                     nn.init.zeros_(m.bias)
         nn.init.zeros_(self.head.weight)
 
+    def _embed_patches(self, x: torch.Tensor) -> torch.Tensor:
+        """The stride-p p x p convolution of the patch embedding IS a matrix product over non-overlapping
+        patches: one permute-copy of the image into ``[B*gh*gw, C*p*p]`` rows, then the tcgen05 GEMM with
+        the convolution weight viewed as ``[D, C*p*p]`` (same parameter, same state-dict key)."""
+        B, C, Hh, Ww = x.shape
+        p = self.patch_size
+        gh, gw = Hh // p, Ww // p
+        w = self.conv_proj.weight
+        probe = _PatchProj(w.shape[1] * p * p, w.shape[0])
+        if not (x.is_cuda and dispatch.linear_supported(probe, x)):
+            return self.conv_proj(x).flatten(2).transpose(1, 2)
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
+        rows = x.to(dt).view(B, C, gh, p, gw, p).permute(0, 2, 4, 1, 3, 5).reshape(B * gh * gw, C * p * p)
+        return _gemm.linear(rows, w.view(w.shape[0], -1), self.conv_proj.bias).view(B, gh * gw, w.shape[0])
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B = x.shape[0]
-        x = self.conv_proj(x).flatten(2).transpose(1, 2)          # [B, S-1, D]
+        x = self._embed_patches(x)                                 # [B, S-1, D]
         x = torch.cat([self.class_token.expand(B, -1, -1).to(x.dtype), x], dim=1) + self.pos_embedding.to(x.dtype)
         for blk in self.layers:
             x = blk(x)
-        return self.head(self.ln(x)[:, 0])
+        # LayerNorm is per token: normalise only the class token that feeds the head
+        return self.head(self.ln(x[:, 0]))
 
 
 def vit_b_16(num_classes: int = 1000, image_size: int = 224) -> VisionTransformer:
