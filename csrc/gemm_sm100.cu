@@ -580,7 +580,7 @@ static int gemm_impl(const void* A, const void* B, void* C, const float* bias, i
         int splits2 = 1;
         bool use = false;
         if (out_dtype == in_dtype) {
-            use = !accumulate_c && tiles2 >= 74;
+            use = tiles2 >= 74;              // accumulate_c: the epilogue's TMA store becomes a reduce-add
         } else {
             if (tiles2 < 74) {
                 splits2 = (int)(74 / tiles2);

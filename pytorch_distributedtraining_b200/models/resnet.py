@@ -63,9 +63,10 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        # conv1 hands the block input back for the bypass branch (ops.layers.Conv2d.forward_carry)
+        out, x = self.conv1.forward_carry(x)
         identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x))
-        out = self.bn2(self.conv2(out))
+        out = self.bn2(self.conv2(self.bn1(out)))
         return self.bn3(self.conv3(out), residual=identity)
 
 

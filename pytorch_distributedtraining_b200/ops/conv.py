@@ -81,7 +81,8 @@ def conv2d_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, n: int, h: int, wd: int,
 
 class _ConvFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, dtype, stride, pad, colstats=None):  # type: ignore[override]
+    def forward(ctx, x, weight, bias, dtype, stride, pad, colstats=None, carry=False):  # type: ignore[override]
+        x_in = x
         n, cin, h, w = x.shape
         cout, _, r, s = weight.shape
         if x.dtype != dtype:
@@ -107,10 +108,15 @@ class _ConvFn(torch.autograd.Function):
         ctx.save_for_backward(x, w16)
         ctx.geom = (n, cin, h, w, cout, r, s, stride, pad, one)
         ctx.w_dtype, ctx.has_bias = weight.dtype, bias is not None
+        if carry:
+            # second output: the input itself, for the branch that bypasses this convolution (residual
+            # identity / downsample).  Its gradient comes back into THIS backward, where the input
+            # gradient is accumulated straight into it — autograd never runs a separate add kernel.
+            return y, x_in.view_as(x_in)
         return y
 
     @staticmethod
-    def backward(ctx, dy):  # type: ignore[override]
+    def backward(ctx, dy, d_carry=None):  # type: ignore[override]
         x, w16 = ctx.saved_tensors
         n, cin, h, w, cout, r, s, stride, pad, one = ctx.geom
         if dy.dtype != x.dtype:
@@ -129,7 +135,14 @@ class _ConvFn(torch.autograd.Function):
                 dw = gemm(dy2, x2, cout, cin, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
                 dw = dw.view(cout, 1, 1, cin).permute(0, 3, 1, 2)
             if need_dx:
-                dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
+                acc = _accumulable(d_carry, x)
+                if acc:
+                    # dX += dY W, added onto the bypass branch's gradient by the epilogue (TMA reduce-add)
+                    gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True,
+                         out=d_carry.permute(0, 2, 3, 1).reshape(rows, cin), accumulate=True)
+                    dx, d_carry = d_carry, None
+                else:
+                    dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
         else:
             ours_dx = need_dx and stride == 1 and cout % 64 == 0 and cin % 8 == 0
             if need_dw:
@@ -141,26 +154,37 @@ class _ConvFn(torch.autograd.Function):
                 # gradient of strided convolutions
                 dx = torch.ops.aten.convolution_backward(dy, x, w16, None, (stride, stride), (pad, pad), (1, 1), False,
                                                          (0, 0), 1, (True, False, False))[0]
+        if d_carry is not None:
+            dx = d_carry if dx is None else dx + d_carry.to(dx.dtype)
         if dw is not None and dw.dtype != ctx.w_dtype:
             dw = dw.to(ctx.w_dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = torch.sum(dy, dim=(0, 2, 3), dtype=torch.float32)
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
+
+
+def _accumulable(d_carry, x) -> bool:
+    """The bypass gradient can take the input gradient in place: same dtype / shape, dense NHWC, not a view."""
+    return (d_carry is not None and d_carry.dtype == x.dtype and d_carry.shape == x.shape and d_carry._base is None
+            and d_carry.is_contiguous(memory_format=torch.channels_last) and d_carry.data_ptr() % 16 == 0)
 
 
 BN_STATS_ATTR = "_b200dp_bn_sums"
 
 
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], stride, padding, dilation, groups,
-           emit_bn_stats: bool = False):
+           emit_bn_stats: bool = False, carry: bool = False):
     """``emit_bn_stats``: the convolution's epilogue also produces [sum(y), sum(y^2), (count slot)] per
     output channel and hangs that vector on the returned tensor; the BatchNorm that consumes this very
-    tensor (``ops.norm.batch_norm_act``) then skips its own reduction pass over the activation."""
+    tensor (``ops.norm.batch_norm_act``) then skips its own reduction pass over the activation.
+    ``carry``: also return the input (for a bypass branch); see ``_ConvFn.forward``."""
     dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
     with torch.autocast("cuda", enabled=False):
+        sums = None
         if emit_bn_stats and (bias is None or tuple(weight.shape[2:]) != (1, 1) or int(stride[0]) != 1):
             sums = torch.zeros(2 * weight.shape[0] + 1, dtype=torch.float32, device=x.device)
-            y = _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]), sums)
+        out = _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]), sums, carry)
+        y = out[0] if carry else out
+        if sums is not None:
             setattr(y, BN_STATS_ATTR, sums)
-            return y
-        return _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]))
+        return out

@@ -29,14 +29,21 @@ class Conv2d(nn.Conv2d):
     # the convolution's epilogue also emits the batch statistics that layer needs
     emit_bn_stats: bool = False
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, carry: bool = False):
         if x.is_cuda and dispatch.conv_supported(self, x):
             from . import conv as _conv
             emit = self.emit_bn_stats and self.training and torch.is_grad_enabled() and dispatch.enabled("bn") \
                 and dispatch.enabled("convstats")
             return _conv.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups,
-                                emit_bn_stats=emit)
-        return super().forward(x)
+                                emit_bn_stats=emit, carry=carry)
+        y = super().forward(x)
+        return (y, x) if carry else y
+
+    def forward_carry(self, x: torch.Tensor):
+        """``(conv(x), x)``: use the second value for the branch that bypasses this layer (residual identity,
+        downsample).  On the kernel path its gradient is routed back through this layer's backward and the
+        input gradient is accumulated into it in the GEMM epilogue, which removes autograd's add kernel."""
+        return self.forward(x, carry=True)
 
 
 class Linear(nn.Linear):

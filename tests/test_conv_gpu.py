@@ -172,3 +172,34 @@ def test_conv_bn_pair_matches_unfused_statistics():
     # rounding of an activation two layers later, so compare at a few fp16 ulps
     for a, b in zip(res["fused"], res["plain"]):
         torch.testing.assert_close(a, b, rtol=1e-2, atol=1e-2)
+
+
+def test_residual_gradient_accumulates_in_the_dgrad_epilogue():
+    """Bottleneck blocks route the bypass branch through conv1 (``forward_carry``): conv1's input gradient
+    is reduce-added onto the bypass gradient by the GEMM epilogue.  Same gradients as the plain autograd
+    formulation where the engine adds the two branches itself."""
+    from pytorch_distributedtraining_b200.models.resnet import Bottleneck
+    from pytorch_distributedtraining_b200.ops.layers import BatchNormAct2d, Conv2d
+    import torch.nn as nn
+    torch.manual_seed(5)
+    blocks = [Bottleneck(256, 64).to(cuda).to(memory_format=torch.channels_last),
+              Bottleneck(64, 64, stride=1, downsample=nn.Sequential(Conv2d(64, 256, 1, bias=False), BatchNormAct2d(256, act=None))
+                         ).to(cuda).to(memory_format=torch.channels_last)]
+    for blk in blocks:
+        cin = blk.conv1.in_channels
+        x0 = torch.randn(32, cin, 28, 28, device=cuda).half().contiguous(memory_format=torch.channels_last)
+        res = []
+        for plain in (False, True):
+            x = x0.clone().requires_grad_(True)
+            blk.zero_grad(set_to_none=True)
+            if plain:
+                blk.conv1.forward_carry = lambda t, c=blk.conv1: (c.forward(t), t)      # engine adds the branches
+            with torch.autocast("cuda", dtype=torch.float16):
+                y = blk(x * 1.0)
+            (y.float() ** 2).mean().backward()
+            if plain:
+                del blk.conv1.forward_carry
+            res.append((x.grad.float().clone(), blk.conv1.weight.grad.clone()))
+        scale = res[1][0].abs().max()
+        torch.testing.assert_close(res[0][0], res[1][0], rtol=2e-2, atol=float(scale) * 4e-3)
+        torch.testing.assert_close(res[0][1], res[1][1], rtol=2e-2, atol=float(res[1][1].abs().max()) * 1e-2)
