@@ -286,25 +286,75 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_kernel(const __grid_constant
 //   full[stage]      leader only; armed by the leader's producer with the pair's 64 KB, credited by both CTAs' TMA
 //   empty[stage]     one per CTA; the pair MMA's commit arrives on both
 //   tmem_full[acc]   one per CTA; commit multicast
-//   tmem_empty[acc]  leader only; the 8 epilogue warps of the pair arrive on it
+//   tmem_empty[acc]  leader only; the 16 epilogue warps of the pair arrive on it
 namespace pair {
 constexpr int kBN = 256;
 constexpr int kHalfN = 128;
-constexpr int kStages = 6;
+constexpr int kStages = 5;
 constexpr int kABytes = kBM * kBK * 2;
 constexpr int kBBytes = kHalfN * kBK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
 constexpr int kEpiBufBytes = 32 * 128;
-constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;
+// EIGHT epilogue warps per CTA: two per TMEM lane quarter, splitting the column chunks between them.  With
+// short reductions (K = 768: ~6k MMA cycles per tile) four warps cannot drain a 128 x 256 accumulator in
+// the time the tensor core needs for the next one; eight can, also with a GELU in the epilogue.
+constexpr int kEpiWarps = 8;
+constexpr int kPairThreads = (kEpiWarp0 + kEpiWarps) * 32;
+constexpr int kEpiBytes = kEpiWarps * 2 * kEpiBufBytes;
 constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + 1024 + 256;
 constexpr int kTmemCols = 512;
 }  // namespace pair
 
-template <bool kAMN, bool kBMN, typename TOut>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+// Epilogue variants (16-bit outputs), all applied to the fp32 accumulator before it is rounded:
+//   kEpiGeluDual  C = acc (+bias) AND C2 = gelu(C): the pre-activation the backward needs and the activation
+//                 the next layer reads leave the same epilogue (exact erf GELU)
+//   kEpiDGelu     C = acc * gelu'(aux): the input gradient of the layer after a GELU becomes the gradient of
+//                 the pre-activation on the way out (aux = saved pre-activation, [M][ld_aux])
+//   kEpiAddAux    C = acc (+bias) + aux: residual add
+enum : int { kEpiNone = 0, kEpiGeluDual = 1, kEpiDGelu = 2, kEpiAddAux = 3 };
+
+// GELU pieces by Abramowitz-Stegun 7.1.26 (|erf error| < 1.5e-7, far below 16-bit output rounding) with the
+// hardware approximations for the reciprocal and the exponential: ~17 instructions per element, no branches
+// (erff is ~40 with a slow path).  With x = |z| / sqrt(2):  w = poly(t) * exp(-x^2), t = 1 / (1 + p x), and
+//   Phi(z) = 1 - w/2 (z >= 0),  w/2 (z < 0);   gelu(z) = z Phi(z);   gelu'(z) = Phi(z) + z * pdf(z),
+// where exp(-x^2) = exp(-z^2 / 2) is also the Gaussian factor of pdf(z).
+__device__ __forceinline__ float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fast_ex2(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void gelu_parts(float z, float& half_w, float& gauss) {
+    const float t = fast_rcp(fmaf(0.3275911f * 0.70710678118654752f, fabsf(z), 1.f));
+    gauss = fast_ex2(z * z * (-0.5f * 1.4426950408889634f));
+    float p = fmaf(t, 1.061405429f, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    half_w = 0.5f * p * t * gauss;
+}
+__device__ __forceinline__ float gelu_f(float z) {
+    float hw, g;
+    gelu_parts(z, hw, g);
+    return z >= 0.f ? fmaf(-z, hw, z) : z * hw;
+}
+__device__ __forceinline__ float dgelu_f(float z) {
+    float hw, g;
+    gelu_parts(z, hw, g);
+    const float phi = z >= 0.f ? 1.f - hw : hw;
+    return fmaf(z * 0.39894228040143268f, g, phi);
+}
+
+template <bool kAMN, bool kBMN, typename TOut, int kEpi = kEpiNone>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(pair::kPairThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const float* __restrict__ bias, int M, int N, int K, int is_bf16,
-                 int accumulate_c, int splits) {
+                 int accumulate_c, int splits, const __grid_constant__ CUtensorMap tmC2, const TOut* __restrict__ aux,
+                 int ld_aux) {
     using namespace pair;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -332,7 +382,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); tma_prefetch_desc(&tmC); }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 8); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 2 * kEpiWarps); }
         fence_barrier_init();
     }
     cluster_sync_all();                       // both CTAs' barriers exist before anything remote touches them
@@ -407,10 +457,12 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
     } else if (warp >= kEpiWarp0) {
         // ===== epilogue (both CTAs; each drains its own 128 rows) =====
-        const int quarter = warp - kEpiWarp0;
+        const int ew = warp - kEpiWarp0;                   // 0..7
+        const int quarter = ew & 3;                        // TMEM lanes [32q, 32q+32) are reachable from warps with warp % 4 == q
+        const int half = ew >> 2;                          // which of the two warps of this lane quarter: even / odd chunks
         constexpr int kChunkCols = 128 / (int)sizeof(TOut);
         constexpr int kLoadsPerChunk = kChunkCols / 32;
-        uint8_t* my_stage = smemC + quarter * 2 * kEpiBufBytes;
+        uint8_t* my_stage = smemC + ew * 2 * kEpiBufBytes;
         int acc = 0; uint32_t acc_phase = 0;
         uint32_t buf_idx = 0;
         for (int item = pair_id; item < num_items; item += num_pairs) {
@@ -419,13 +471,22 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int n0 = (tile / num_m) * kBN;
             const bool add_bias = bias != nullptr && split == 0;
             const bool has_k = split * kb_per < num_kb;
+            const int row0 = m0 + quarter * 32;
+            if constexpr (kEpi == kEpiDGelu || kEpi == kEpiAddAux) {
+                // pull this lane's aux rows for the tile towards L2 while the tensor core is still busy
+                if (row0 + lane < M) {
+                    for (int ch = half; ch < kBN / kChunkCols; ch += 2)
+                        if (n0 + ch * kChunkCols < N)
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(aux + (size_t)(row0 + lane) * ld_aux + n0 + ch * kChunkCols));
+                }
+            }
             mbar_wait(tmem_full + acc, acc_phase);
             tc_fence_after();
-            const int row0 = m0 + quarter * 32;
 #pragma unroll 1
-            for (int ch = 0; ch < kBN / kChunkCols; ++ch) {
+            for (int ch = half; ch < kBN / kChunkCols; ch += 2) {
                 uint8_t* buf = my_stage + (buf_idx & 1) * kEpiBufBytes;
-                if (lane == 0) tma_store_wait_read<1>();
+                uint8_t* buf2 = my_stage + ((buf_idx & 1) ^ 1) * kEpiBufBytes;      // kEpiGeluDual: second output
+                if (lane == 0) { if (kEpi == kEpiGeluDual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
                 __syncwarp();
 #pragma unroll
                 for (int l = 0; l < kLoadsPerChunk; ++l) {
@@ -441,6 +502,25 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] += (gcol + j < N) ? __ldg(bias + gcol + j) : 0.f;
                     }
+                    if constexpr (kEpi == kEpiDGelu || kEpi == kEpiAddAux) {
+                        // this lane's row of the aux matrix, 32 columns = 64 bytes
+                        const int grow = row0 + lane, gcol = n0 + colbase;
+                        if (grow < M) {
+                            const TOut* ap = aux + (size_t)grow * ld_aux + gcol;
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                if (gcol + q * 8 < N) {
+                                    float a8[8];
+                                    load8<TOut>(ap + q * 8, a8);
+#pragma unroll
+                                    for (int e = 0; e < 8; ++e) {
+                                        if (kEpi == kEpiDGelu) v[q * 8 + e] *= dgelu_f(a8[e]);
+                                        else v[q * 8 + e] += a8[e];
+                                    }
+                                }
+                            }
+                        }
+                    }
                     uint8_t* rowp = buf + lane * 128;
                     if (sizeof(TOut) == 2) {
 #pragma unroll
@@ -448,6 +528,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                             float t[8] = {v[q * 8], v[q * 8 + 1], v[q * 8 + 2], v[q * 8 + 3],
                                           v[q * 8 + 4], v[q * 8 + 5], v[q * 8 + 6], v[q * 8 + 7]};
                             store8<TOut>(reinterpret_cast<TOut*>(rowp + (((l * 4 + q) ^ (lane & 7)) << 4)), t);
+                            if constexpr (kEpi == kEpiGeluDual) {
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) t[e] = gelu_f(t[e]);
+                                store8<TOut>(reinterpret_cast<TOut*>(buf2 + lane * 128 + (((l * 4 + q) ^ (lane & 7)) << 4)), t);
+                            }
                         }
                     } else {
 #pragma unroll
@@ -461,13 +546,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 if (lane == 0 && n0 + ch * kChunkCols < N && row0 < M && has_k) {
                     if (accumulate_c || splits > 1) tma_reduce_add_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
                     else tma_store_2d(&tmC, buf, n0 + ch * kChunkCols, row0);
+                    if (kEpi == kEpiGeluDual) tma_store_2d(&tmC2, buf2, n0 + ch * kChunkCols, row0);
                 }
                 if (lane == 0) tma_store_commit();
                 ++buf_idx;
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_leader(tmem_empty + acc);     // the leader's MMA thread counts all 8 warps
+            if (lane == 0) mbar_arrive_leader(tmem_empty + acc);     // the leader's MMA thread counts all 16 warps
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (lane == 0) tma_store_wait_read<0>();
@@ -525,10 +611,11 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     return 0;
 }
 
-template <bool kAMN, bool kBMN, typename TOut>
+template <bool kAMN, bool kBMN, typename TOut, int kEpi = kEpiNone>
 static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const float* bias, int M, int N,
-                       int K, int is_bf16, int accumulate_c, int splits, int sms, cudaStream_t s) {
-    auto kern = gemm_pair_kernel<kAMN, kBMN, TOut>;
+                       int K, int is_bf16, int accumulate_c, int splits, int sms, cudaStream_t s,
+                       const CUtensorMap* tc2 = nullptr, const void* aux = nullptr, int ld_aux = 0) {
+    auto kern = gemm_pair_kernel<kAMN, kBMN, TOut, kEpi>;
     static bool configured = false;
     if (!configured) {
         B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::kSmemBytes));
@@ -537,7 +624,8 @@ static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     const int items = ((M + 2 * kBM - 1) / (2 * kBM)) * ((N + pair::kBN - 1) / pair::kBN) * splits;
     int pairs = sms / 2;
     if (items < pairs) pairs = items;
-    kern<<<2 * pairs, kThreads, pair::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits);
+    kern<<<2 * pairs, pair::kPairThreads, pair::kSmemBytes, s>>>(ta, tb, tc, bias, M, N, K, is_bf16, accumulate_c, splits,
+                                                       tc2 ? *tc2 : tc, (const TOut*)aux, ld_aux);
     B200DP_CHECK_LAUNCH();
     return 0;
 }
@@ -679,4 +767,44 @@ extern "C" int b200dp_gemm_colstats(const void* A, const void* B, void* C, int M
                                     b200dp_dtype dtype, float* colstats, void* stream) {
     B200DP_REQUIRE(colstats != nullptr, "gemm_colstats: null statistics buffer");
     return gemm_impl(A, B, C, nullptr, M, N, K, lda, ldb, ldc, 0, 0, dtype, dtype, 0, colstats, stream);
+}
+
+// Large-product GEMM with a fused epilogue (CTA-pair kernel only; see the kEpi* modes above):
+//   mode 1  C = A B^T (+bias), C2 = gelu(C)            (b_mn must be 0)
+//   mode 2  C = (A B^T) * gelu'(aux)                    (dgrad form: b_mn = 1)
+//   mode 3  C = A B^T (+bias) + aux                     (b_mn = 0)
+// 16-bit operands and outputs, A K-major.  Returns B200DP_ERR_INVALID when the shape is below the pair
+// kernel's envelope (M, N >= 256 and at least 74 output tiles of 256 x 256) — b200dp_gemm_fused_supported tells.
+extern "C" int b200dp_gemm_fused_supported(int M, int N) {
+    return pair_enabled() && M >= 256 && N >= 256 && (int64_t)((M + 255) / 256) * ((N + 255) / 256) >= 74;
+}
+
+extern "C" int b200dp_gemm_fused(const void* A, const void* B, void* C, void* C2, const float* bias, const void* aux, int M,
+                                 int N, int K, int lda, int ldb, int ldc, int ldc2, int ld_aux, int b_mn, b200dp_dtype dtype,
+                                 int mode, void* stream) {
+    B200DP_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, "gemm_fused: bad arguments");
+    B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "gemm_fused: fp16 / bf16 only");
+    B200DP_REQUIRE(mode >= 1 && mode <= 3, "gemm_fused: mode must be 1 (gelu dual), 2 (dgelu) or 3 (add)");
+    B200DP_REQUIRE(b200dp_gemm_fused_supported(M, N), "gemm_fused: shape %d x %d is below the CTA-pair kernel's envelope", M, N);
+    B200DP_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0 && N % 8 == 0, "gemm_fused: pitches and N must be multiples of 8");
+    B200DP_REQUIRE((mode == 1) == (C2 != nullptr) && (mode == 1 || aux != nullptr), "gemm_fused: C2 / aux do not match the mode");
+    B200DP_REQUIRE((mode == 2) == (b_mn != 0), "gemm_fused: mode 2 is the dgrad form (b_mn = 1), modes 1 / 3 the forward form");
+    B200DP_REQUIRE(mode == 1 || (ld_aux % 8 == 0 && ((uintptr_t)aux & 15) == 0), "gemm_fused: aux must be 16-byte aligned rows");
+    bind_context_once();
+    const int is_bf16 = dtype == B200DP_BF16;
+    CUtensorMap ta, tb, tc, tc2;
+    int rc = make_tmap(&tc, C, is_bf16, M, N, ldc, 64, 32, 2);
+    if (rc) return rc;
+    if (mode == 1) { rc = make_tmap(&tc2, C2, is_bf16, M, N, ldc2, 64, 32, 2); if (rc) return rc; }
+    rc = make_tmap(&ta, A, is_bf16, M, K, lda, kBK, kBM);
+    if (rc) return rc;
+    rc = b_mn ? make_tmap(&tb, B, is_bf16, K, N, ldb, 64, kBK) : make_tmap(&tb, B, is_bf16, N, K, ldb, kBK, pair::kHalfN);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+#define GF(BM_, T, E) return launch_pair<false, BM_, T, E>(ta, tb, tc, bias, M, N, K, is_bf16, 0, 1, B200DP_SMS, s, &tc2, aux, ld_aux)
+    if (mode == 1) { if (is_bf16) GF(false, __nv_bfloat16, kEpiGeluDual); else GF(false, __half, kEpiGeluDual); }
+    if (mode == 2) { if (is_bf16) GF(true, __nv_bfloat16, kEpiDGelu); else GF(true, __half, kEpiDGelu); }
+    if (is_bf16) GF(false, __nv_bfloat16, kEpiAddAux); else GF(false, __half, kEpiAddAux);
+#undef GF
+    return 0;
 }

@@ -388,10 +388,11 @@ __global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwd_kernel(
 // all its rows; the CTA's warps combine in shared memory and write one partial per CTA, which a small
 // second kernel adds in a fixed order (deterministic, no float atomics).
 template <typename T, int NCH>
-__global__ void __launch_bounds__(kLNWarps * 32) layernorm_bwd_fused_kernel(
+__global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd_fused_kernel(
     const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t rows, int D,
     const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
-    float* __restrict__ scratch /* one [dbeta(D) | dgamma(D)] partial per CTA */) {
+    float* __restrict__ scratch /* one [dbeta(D) | dgamma(D)] partial per CTA */,
+    const T* __restrict__ add_in /* optional: gradient of a branch that bypassed the layer, added to dx */) {
     __shared__ float red[2 * NCH * 256];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nchunk = D / 8;
@@ -403,13 +404,14 @@ __global__ void __launch_bounds__(kLNWarps * 32) layernorm_bwd_fused_kernel(
 
     for (int64_t row = (int64_t)blockIdx.x * kLNWarps + warp; row < rows; row += (int64_t)gridDim.x * kLNWarps) {
         const float mu = mean[row], rs = rstd[row];
-        Vec8<T> dv[NCH], xv[NCH];
+        Vec8<T> dv[NCH], xv[NCH], av[NCH];
 #pragma unroll
         for (int j = 0; j < NCH; ++j) {
             const int ch = lane + j * 32;
             if (ch < nchunk) {
                 dv[j] = *reinterpret_cast<const Vec8<T>*>(dy + row * D + ch * 8);
                 xv[j] = *reinterpret_cast<const Vec8<T>*>(x + row * D + ch * 8);
+                if (add_in != nullptr) av[j] = *reinterpret_cast<const Vec8<T>*>(add_in + row * D + ch * 8);   // in flight with the rest
             }
         }
         float c1 = 0.f, c2 = 0.f;
@@ -443,6 +445,10 @@ __global__ void __launch_bounds__(kLNWarps * 32) layernorm_bwd_fused_kernel(
                 for (int k = 0; k < 8; ++k) {
                     const float xh = (Cvt<T>::to_f(xv[j].v[k]) - mu) * rs;
                     o[k] = rs * (Cvt<T>::to_f(dv[j].v[k]) * ga[k] - c2 - xh * c1);
+                }
+                if (add_in != nullptr) {
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) o[k] += Cvt<T>::to_f(av[j].v[k]);
                 }
                 store8<T>(dx + row * D + ch * 8, o);
             }
@@ -587,9 +593,12 @@ int b200dp_bn_bwd_apply(const void* dy, const void* y, const void* x, void* dx, 
     return 0;
 }
 
+// persistent grid: never more CTAs than are resident at once (a second, partial wave would double the time);
+// 3 per SM is what the heaviest instantiation (D = 768 with the bypass gradient) fits
+constexpr int kLNBwdCtasPerSM = 3;
 static unsigned ln_bwd_grid(int64_t rows) {
     const int64_t want = (rows + kLNWarps - 1) / kLNWarps;
-    const int64_t cap = (int64_t)B200DP_SMS * 4;
+    const int64_t cap = (int64_t)B200DP_SMS * kLNBwdCtasPerSM;
     return (unsigned)(want < cap ? want : cap);
 }
 
@@ -610,9 +619,9 @@ int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dty
     return 0;
 }
 
-int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
-                         const float* gamma, const float* mean, const float* rstd, float* scratch,
-                         unsigned int* counter, float* dgamma, float* dbeta, void* stream) {
+static int layernorm_bwd_impl(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
+                              const float* gamma, const float* mean, const float* rstd, float* scratch,
+                              unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream) {
     B200DP_REQUIRE(dy && x && dx && gamma && mean && rstd && scratch && counter && dgamma && dbeta,
                    "layernorm_bwd: null argument");
     B200DP_REQUIRE(dgamma == dbeta + D, "layernorm_bwd: dbeta and dgamma must be one buffer [dbeta(D) | dgamma(D)]");
@@ -624,7 +633,7 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
 #define LNB(N_)                                                                                                     \
     B200DP_DISPATCH_DTYPE(dtype, T, {                                                                               \
         layernorm_bwd_fused_kernel<T, N_><<<grid, kLNWarps * 32, 0, s>>>((const T*)dy, (const T*)x, (T*)dx, rows, D, \
-                                                                         gamma, mean, rstd, scratch);       \
+                                                                         gamma, mean, rstd, scratch, (const T*)add_in); \
     })
     if (nch <= 1) LNB(1) else if (nch <= 2) LNB(2) else if (nch <= 3) LNB(3) else if (nch <= 4) LNB(4)
     else if (nch <= 6) LNB(6) else LNB(8)
@@ -632,6 +641,20 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
     ln_partials_reduce_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(scratch, (int)grid, 2 * D, dbeta);
     B200DP_CHECK_LAUNCH();
     return 0;
+}
+
+int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
+                         const float* gamma, const float* mean, const float* rstd, float* scratch,
+                         unsigned int* counter, float* dgamma, float* dbeta, void* stream) {
+    return layernorm_bwd_impl(dy, x, dx, rows, D, dtype, gamma, mean, rstd, scratch, counter, dgamma, dbeta, nullptr, stream);
+}
+
+// Same, plus dx += add_in: the gradient of a branch that bypassed the LayerNorm (the residual stream of a
+// transformer block) is folded into the input gradient instead of a separate add kernel.
+int b200dp_layernorm_bwd_add(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
+                             const float* gamma, const float* mean, const float* rstd, float* scratch,
+                             unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream) {
+    return layernorm_bwd_impl(dy, x, dx, rows, D, dtype, gamma, mean, rstd, scratch, counter, dgamma, dbeta, add_in, stream);
 }
 
 }  // extern "C"

@@ -203,6 +203,10 @@ int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dty
 int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
                          const float* gamma, const float* mean, const float* rstd, float* scratch,
                          unsigned int* counter, float* dgamma, float* dbeta, void* stream);
+/* dx += add_in (gradient of a branch that bypassed the layer, e.g. the residual stream) in the same pass */
+int b200dp_layernorm_bwd_add(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
+                             const float* gamma, const float* mean, const float* rstd, float* scratch,
+                             unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream);
 
 /* ------------------------------------------------------------------ tensor-core GEMM (tcgen05 / TMEM / TMA)
  * C[M,N] (+)= A(MxK) * B(NxK)^T (+ bias[N]), 16-bit inputs, fp32 accumulation in TMEM.
@@ -331,6 +335,16 @@ int b200dp_gemm_colstats(const void* A, const void* B, void* C, int M, int N, in
                          b200dp_dtype dtype, float* colstats, void* stream);
 int b200dp_conv2d_colstats(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin, int Cout,
                            int R, int S, int stride, int pad, b200dp_dtype dtype, float* colstats, void* stream);
+
+/* Large-product GEMM with a fused epilogue on the CTA-pair (cta_group::2) kernel; 16-bit in / out, A K-major:
+ *   mode 1  C = A B^T (+bias), C2 = gelu(C)      pre-activation and activation from one epilogue (b_mn = 0)
+ *   mode 2  C = (A B^T) * gelu'(aux)              input gradient through a GELU (dgrad form, b_mn = 1)
+ *   mode 3  C = A B^T (+bias) + aux               residual add (b_mn = 0)
+ * b200dp_gemm_fused_supported(M, N) says whether the shape is inside the kernel's envelope.
+ * Reference: nn.Linear + nn.GELU + the residual adds of the transformer blocks (separate ATen kernels there). */
+int b200dp_gemm_fused_supported(int M, int N);
+int b200dp_gemm_fused(const void* A, const void* B, void* C, void* C2, const float* bias, const void* aux, int M, int N, int K,
+                      int lda, int ldb, int ldc, int ldc2, int ld_aux, int b_mn, b200dp_dtype dtype, int mode, void* stream);
 
 /* All-gather fused into the consuming GEMM (W4): Y[M,N] = X[M,K] W^T (+bias) with W[N,K] row-sharded
  * over the ranks (w_shards[p] = rank p's [rows_per_rank][K] shard in peer-mapped memory).  One kernel:

@@ -11,6 +11,8 @@ GELU epilogue on CUDA), LayerNorm through the fused kernel, attention through
 """
 from __future__ import annotations
 
+from typing import Optional
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -37,10 +39,9 @@ class Attention(nn.Module):
         self.in_proj = Linear(dim, 3 * dim)
         self.out_proj = Linear(dim, dim)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        B, S, D = x.shape
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
         q, k, v = split_qkv(self.in_proj(x), self.heads)
-        return self.out_proj(merge_heads(F.scaled_dot_product_attention(q, k, v)))
+        return self.out_proj(merge_heads(F.scaled_dot_product_attention(q, k, v)), residual=residual)
 
 
 class MLP(nn.Module):
@@ -49,8 +50,10 @@ class MLP(nn.Module):
         self.fc1 = Linear(dim, hidden, act="gelu")
         self.fc2 = Linear(hidden, dim)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        return self.fc2(self.fc1(x))
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        if _gemm.mlp_supported(x, self.fc1.weight, self.fc2.weight):
+            return _gemm.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias, residual)
+        return self.fc2(self.fc1(x), residual=residual)
 
 
 class EncoderBlock(nn.Module):
@@ -62,8 +65,13 @@ class EncoderBlock(nn.Module):
         self.mlp = MLP(dim, mlp_dim)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = x + self.self_attention(self.ln_1(x))
-        return x + self.mlp(self.ln_2(x))
+        # the residual stream rides through the kernels: LayerNorm hands its input back for the bypass
+        # (forward_carry), the closing GEMM of each half adds it in its epilogue, and in the backward the
+        # bypass gradient is folded into the LayerNorm backward — no stand-alone add kernels either way
+        h, x = self.ln_1.forward_carry(x)
+        x = self.self_attention(h, residual=x)
+        h, x = self.ln_2.forward_carry(x)
+        return self.mlp(h, residual=x)
 
 
 class VisionTransformer(nn.Module):

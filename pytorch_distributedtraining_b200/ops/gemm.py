@@ -51,27 +51,70 @@ def gemm(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, a_mn: bool = 
     return out
 
 
+def fused_supported(M: int, N: int) -> bool:
+    """Is ``[M, N]`` inside the envelope of the CTA-pair kernel's fused epilogues (``b200dp_gemm_fused``)?"""
+    return bool(require_library().b200dp_gemm_fused_supported(int(M), int(N)))
+
+
+def gemm_fused(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, mode: int, bias: Optional[torch.Tensor] = None,
+               aux: Optional[torch.Tensor] = None):
+    """Large-product GEMM with a fused epilogue (``include/b200dp.h``): mode 1 returns ``(C, gelu(C))``,
+    mode 2 ``(A B) * gelu'(aux)`` with ``b`` given MN-major (``[K, N]``, the dgrad form), mode 3
+    ``A B^T (+bias) + aux``."""
+    lib = require_library()
+    assert a.dtype in _HALF and b.dtype == a.dtype and a.stride(1) == 1 and b.stride(1) == 1
+    c = torch.empty((M, N), dtype=a.dtype, device=a.device)
+    c2 = torch.empty((M, N), dtype=a.dtype, device=a.device) if mode == 1 else None
+    if aux is not None:
+        assert aux.dtype == a.dtype and aux.shape == (M, N) and aux.stride(1) == 1
+    check(lib.b200dp_gemm_fused(ptr(a), ptr(b), ptr(c), ptr(c2), ptr(bias), ptr(aux), M, N, K, a.stride(0), b.stride(0),
+                                c.stride(0), N, aux.stride(0) if aux is not None else 0, int(mode == 2), DT[a.dtype], mode,
+                                stream_ptr(a.device)), "gemm_fused")
+    return (c, c2) if mode == 1 else c
+
+
+def _as_rows(t: torch.Tensor, cols: int, dtype: torch.dtype) -> torch.Tensor:
+    t2 = t.reshape(-1, cols)
+    if t2.dtype != dtype:
+        t2 = t2.to(dtype)
+    return t2 if t2.is_contiguous() else t2.contiguous()
+
+
+def _w16(w: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    w = w if w.dtype == dtype else w.to(dtype)
+    return w if w.is_contiguous() else w.contiguous()
+
+
+def _bias_grad(dy2: torch.Tensor) -> torch.Tensor:
+    rows, out_f = dy2.shape
+    if out_f % 8 == 0 and out_f <= 16384 and rows >= 64:
+        from .norm import column_sums
+        return column_sums(dy2)
+    return torch.sum(dy2, dim=0, dtype=torch.float32)
+
+
 class _LinearFn(torch.autograd.Function):
-    """y = x W^T + b with 16-bit compute; ``weight`` / ``bias`` are the fp32 parameters, so dW
-    and db come out in fp32 directly (no cast kernels on the gradient path)."""
+    """y = x W^T + b (+ residual) with 16-bit compute; ``weight`` / ``bias`` are the fp32 parameters, so dW
+    and db come out in fp32 directly (no cast kernels on the gradient path).  The residual add is part of
+    the GEMM epilogue when the shape is inside the CTA-pair kernel's envelope."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, dtype):  # type: ignore[override]
+    def forward(ctx, x, weight, bias, dtype, residual=None):  # type: ignore[override]
         in_f = weight.shape[1]
-        x2 = x.reshape(-1, in_f)
-        if x2.dtype != dtype:
-            x2 = x2.to(dtype)
-        if not x2.is_contiguous():
-            x2 = x2.contiguous()
-        w16 = weight if weight.dtype == dtype else weight.to(dtype)
-        if not w16.is_contiguous():
-            w16 = w16.contiguous()
+        x2 = _as_rows(x, in_f, dtype)
+        w16 = _w16(weight, dtype)
         b32 = None if bias is None else (bias if bias.dtype == torch.float32 else bias.float())
         rows, out_f = x2.shape[0], weight.shape[0]
-        y = gemm(x2, w16, rows, out_f, in_f, bias=b32)
+        if residual is not None and fused_supported(rows, out_f):
+            y = gemm_fused(x2, w16, rows, out_f, in_f, 3, bias=b32, aux=_as_rows(residual, out_f, dtype))
+        else:
+            y = gemm(x2, w16, rows, out_f, in_f, bias=b32)
+            if residual is not None:
+                y += residual.reshape(rows, out_f)
         ctx.save_for_backward(x2, w16)
         ctx.x_shape, ctx.has_bias, ctx.w_dtype = x.shape, bias is not None, weight.dtype
         ctx.b_dtype = None if bias is None else bias.dtype
+        ctx.res_meta = None if residual is None else (residual.shape, residual.dtype)
         return y.view(*x.shape[:-1], out_f)
 
     @staticmethod
@@ -79,12 +122,8 @@ class _LinearFn(torch.autograd.Function):
         x2, w16 = ctx.saved_tensors
         rows, in_f = x2.shape
         out_f = w16.shape[0]
-        dy2 = dy.reshape(rows, out_f)
-        if dy2.dtype != x2.dtype:
-            dy2 = dy2.to(x2.dtype)
-        if not dy2.is_contiguous():
-            dy2 = dy2.contiguous()
-        dx = dw = db = None
+        dy2 = _as_rows(dy, out_f, x2.dtype)
+        dx = dw = db = dres = None
         # parameter gradients first, the input gradient last: it is then the most recent tensor in L2 for
         # the backward of the layer below
         if ctx.needs_input_grad[1]:
@@ -92,31 +131,103 @@ class _LinearFn(torch.autograd.Function):
             if ctx.w_dtype != torch.float32:
                 dw = dw.to(ctx.w_dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            if out_f % 8 == 0 and out_f <= 16384 and rows >= 64:
-                from .norm import column_sums
-                db = column_sums(dy2)
-            else:
-                db = torch.sum(dy2, dim=0, dtype=torch.float32)
+            db = _bias_grad(dy2)
             if ctx.b_dtype != torch.float32:
                 db = db.to(ctx.b_dtype)
         if ctx.needs_input_grad[0]:
             dx = gemm(dy2, w16, rows, in_f, out_f, a_mn=False, b_mn=True).view(ctx.x_shape)
-        return dx, dw, db, None
+        if ctx.res_meta is not None and ctx.needs_input_grad[4]:
+            dres = dy.reshape(ctx.res_meta[0])          # the residual's gradient IS dy (no copy)
+            if dres.dtype != ctx.res_meta[1]:
+                dres = dres.to(ctx.res_meta[1])
+        return dx, dw, db, None, dres
 
 
-def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act: Optional[str] = None) -> torch.Tensor:
+class _MLPFn(torch.autograd.Function):
+    """``y = fc2(gelu(fc1(x))) (+ residual)`` of a transformer block as ONE autograd node over four GEMM
+    launches forward and five backward, with every elementwise step inside a GEMM epilogue:
+    fc1 writes the pre-activation and its GELU from the same epilogue, fc2 adds the residual in its
+    epilogue, and in the backward the input gradient of fc2 is multiplied by gelu'(pre-activation) on
+    its way out of the tensor core.  (Reference: the MLP of the ViT / SwinIR blocks, Stoke-DDP.py:206-208;
+    Linear, GELU and add are separate kernels there.)"""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, dtype, residual=None):  # type: ignore[override]
+        in_f, hid, out_f = w1.shape[1], w1.shape[0], w2.shape[0]
+        x2 = _as_rows(x, in_f, dtype)
+        rows = x2.shape[0]
+        w1h, w2h = _w16(w1, dtype), _w16(w2, dtype)
+        b1f = None if b1 is None else b1.float()
+        b2f = None if b2 is None else b2.float()
+        z, a = gemm_fused(x2, w1h, rows, hid, in_f, 1, bias=b1f)
+        if residual is not None and fused_supported(rows, out_f):
+            y = gemm_fused(a, w2h, rows, out_f, hid, 3, bias=b2f, aux=_as_rows(residual, out_f, dtype))
+        else:
+            y = gemm(a, w2h, rows, out_f, hid, bias=b2f)
+            if residual is not None:
+                y += residual.reshape(rows, out_f)
+        ctx.save_for_backward(x2, z, a, w1h, w2h)
+        ctx.meta = (x.shape, w1.dtype, w2.dtype, None if b1 is None else b1.dtype, None if b2 is None else b2.dtype,
+                    None if residual is None else (residual.shape, residual.dtype))
+        return y.view(*x.shape[:-1], out_f)
+
+    @staticmethod
+    def backward(ctx, dy):  # type: ignore[override]
+        x2, z, a, w1h, w2h = ctx.saved_tensors
+        x_shape, w1_dt, w2_dt, b1_dt, b2_dt, res_meta = ctx.meta
+        rows, in_f = x2.shape
+        hid, out_f = w1h.shape[0], w2h.shape[0]
+        dy2 = _as_rows(dy, out_f, x2.dtype)
+        dw2 = gemm(dy2, a, out_f, hid, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
+        db2 = None if b2_dt is None else _bias_grad(dy2).to(b2_dt)
+        # dz = (dy W2) * gelu'(z), straight out of the dgrad epilogue
+        dz = gemm_fused(dy2, w2h, rows, hid, out_f, 2, aux=z)
+        dw1 = gemm(dz, x2, hid, in_f, rows, a_mn=True, b_mn=True, out_dtype=torch.float32)
+        db1 = None if b1_dt is None else _bias_grad(dz).to(b1_dt)
+        dx = gemm(dz, w1h, rows, in_f, hid, a_mn=False, b_mn=True).view(x_shape) if ctx.needs_input_grad[0] else None
+        dres = None
+        if res_meta is not None and ctx.needs_input_grad[6]:
+            dres = dy.reshape(res_meta[0])
+            if dres.dtype != res_meta[1]:
+                dres = dres.to(res_meta[1])
+        return dx, dw1.to(w1_dt), db1, dw2.to(w2_dt), db2, None, dres
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], act: Optional[str] = None,
+           residual: Optional[torch.Tensor] = None) -> torch.Tensor:
     dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
     if dtype not in _HALF:
         y = F.linear(x, weight, bias)
     else:
         # the function does its own casting; keep autocast from re-casting the fp32 parameters
         with torch.autocast("cuda", enabled=False):
-            y = _LinearFn.apply(x, weight, bias, dtype)
+            y = _LinearFn.apply(x, weight, bias, dtype, residual if act is None else None)
+        if act is None:
+            return y
     if act == "gelu":
         y = F.gelu(y)
     elif act == "relu":
         y = F.relu(y)
-    return y
+    return y if residual is None else y + residual
+
+
+def mlp_supported(x: torch.Tensor, w1: torch.Tensor, w2: torch.Tensor) -> bool:
+    """Fused transformer MLP: 16-bit compute on CUDA and both products inside the CTA-pair envelope."""
+    from . import dispatch
+    if not (x.is_cuda and dispatch.enabled("gemm") and dispatch.enabled("mlp") and dispatch._lib_ok()):
+        return False
+    dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
+    rows = x.numel() // x.shape[-1]
+    return (dtype in _HALF and all(d % 8 == 0 for d in (*w1.shape, *w2.shape))
+            and fused_supported(rows, w1.shape[0]) and fused_supported(rows, w1.shape[1]))
+
+
+def mlp(x: torch.Tensor, w1: torch.Tensor, b1: Optional[torch.Tensor], w2: torch.Tensor, b2: Optional[torch.Tensor],
+        residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``fc2(gelu(fc1(x))) (+ residual)``; caller checks ``mlp_supported`` first."""
+    dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
+    with torch.autocast("cuda", enabled=False):
+        return _MLPFn.apply(x, w1, b1, w2, b2, dtype, residual)
 
 
 _GATHER_FLAGS: dict = {}

@@ -54,16 +54,17 @@ class Linear(nn.Linear):
         super().__init__(in_features, out_features, bias, device=device, dtype=dtype)
         self.act = act
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``act(x W^T + b) (+ residual)``; on the kernel path the residual add is part of the GEMM epilogue."""
         if x.is_cuda and dispatch.linear_supported(self, x):
             from . import gemm as _gemm
-            return _gemm.linear(x, self.weight, self.bias, act=self.act)
+            return _gemm.linear(x, self.weight, self.bias, act=self.act, residual=residual)
         y = F.linear(x, self.weight, self.bias)
         if self.act == "gelu":
             y = F.gelu(y)
         elif self.act == "relu":
             y = F.relu(y)
-        return y
+        return y if residual is None else y + residual
 
 
 class BatchNormAct2d(nn.BatchNorm2d):
@@ -111,11 +112,17 @@ def pair_conv_bn(model: nn.Module) -> int:
 
 
 class LayerNorm(nn.LayerNorm):
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, carry: bool = False):
         if x.is_cuda and dispatch.ln_supported(self, x):
             from . import norm as _norm
-            return _norm.layer_norm(x, self.weight, self.bias, self.eps)
-        return super().forward(x)
+            return _norm.layer_norm(x, self.weight, self.bias, self.eps, carry=carry)
+        y = super().forward(x)
+        return (y, x) if carry else y
+
+    def forward_carry(self, x: torch.Tensor):
+        """``(LN(x), x)``: feed the second value to the residual add that closes the block.  On the kernel
+        path the residual's gradient is folded into the LayerNorm backward (no separate add kernel)."""
+        return self.forward(x, carry=True)
 
 
 class _MaxPoolFn(torch.autograd.Function):

@@ -142,7 +142,7 @@ def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) 
 
 class _LayerNormFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, eps):  # type: ignore[override]
+    def forward(ctx, x, weight, bias, eps, carry=False):  # type: ignore[override]
         lib = require_library()
         shape = x.shape
         D = shape[-1]
@@ -158,10 +158,14 @@ class _LayerNormFn(torch.autograd.Function):
                                        stream_ptr(x.device)), "layernorm_fwd")
         ctx.save_for_backward(x2, weight, mean, rstd)
         ctx.shape = shape
+        if carry:
+            # second output: the input itself, for the residual branch that bypasses the block; its gradient
+            # comes back into this backward and is added to dx inside the kernel
+            return y.view(shape), x.view_as(x)
         return y.view(shape)
 
     @staticmethod
-    def backward(ctx, dy):  # type: ignore[override]
+    def backward(ctx, dy, d_carry=None):  # type: ignore[override]
         lib = require_library()
         x2, weight, mean, rstd = ctx.saved_tensors
         rows, D = x2.shape
@@ -170,16 +174,25 @@ class _LayerNormFn(torch.autograd.Function):
             dy2 = dy2.contiguous()
         if dy2.dtype != x2.dtype:
             dy2 = dy2.to(x2.dtype)
+        add_in = None
+        if d_carry is not None:
+            add_in = d_carry.reshape(rows, D)
+            if add_in.dtype != x2.dtype:
+                add_in = add_in.to(x2.dtype)
+            if not add_in.is_contiguous():
+                add_in = add_in.contiguous()
         dx = torch.empty_like(x2)
         ws = Workspace.get(x2.device)
         scratch = ws.scratch(int(lib.b200dp_ln_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(D))))
         dparams = torch.empty(2 * D, dtype=torch.float32, device=x2.device)  # [dbeta | dgamma]
-        check(lib.b200dp_layernorm_bwd(ptr(dy2), ptr(x2), ptr(dx), ctypes.c_int64(rows), ctypes.c_int(D),
-                                       ctypes.c_int(DT[x2.dtype]), ptr(weight), ptr(mean), ptr(rstd), ptr(scratch),
-                                       ptr(ws.counters), ptr(dparams[D:]), ptr(dparams[:D]), stream_ptr(x2.device)),
+        check(lib.b200dp_layernorm_bwd_add(ptr(dy2), ptr(x2), ptr(dx), ctypes.c_int64(rows), ctypes.c_int(D),
+                                           ctypes.c_int(DT[x2.dtype]), ptr(weight), ptr(mean), ptr(rstd), ptr(scratch),
+                                           ptr(ws.counters), ptr(dparams[D:]), ptr(dparams[:D]), ptr(add_in),
+                                           stream_ptr(x2.device)),
               "layernorm_bwd", launches=2)
-        return dx.view(ctx.shape), dparams[D:].to(weight.dtype), dparams[:D].to(weight.dtype), None
+        return dx.view(ctx.shape), dparams[D:].to(weight.dtype), dparams[:D].to(weight.dtype), None, None
 
 
-def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float) -> torch.Tensor:
-    return _LayerNormFn.apply(x, weight.float(), bias.float(), eps)
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float, carry: bool = False):
+    """``carry=True`` returns ``(LN(x), x)``: use the second value as the residual that bypasses the block."""
+    return _LayerNormFn.apply(x, weight.float(), bias.float(), eps, carry)

@@ -161,3 +161,65 @@ def test_gemm_cta_pair_kernel_operand_layouts(dtype, M, N, K, a_mn, b_mn, f32):
         got2 = gemm(a, b, M, N, K, a_mn=a_mn, b_mn=b_mn, out=got.clone(), out_dtype=torch.float32, accumulate=True)
         torch.cuda.synchronize()
         torch.testing.assert_close(got2, 2 * want, rtol=2 * tol, atol=2 * tol * max(1.0, K ** 0.5 * 0.25))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_gemm_fused_epilogues(dtype):
+    """GELU-dual, dGELU and residual-add epilogues of the CTA-pair kernel vs the unfused fp32 formulation."""
+    from pytorch_distributedtraining_b200.ops.gemm import fused_supported, gemm_fused
+    M, N, K = 25216, 3072, 768
+    assert fused_supported(M, N) and not fused_supported(128, 128)
+    a, b = _mk(M, K, dtype, 21), (_mk(N, K, dtype, 22) * 0.2)
+    bias = torch.randn(N, device=cuda) * 0.1
+    z_ref = a.float() @ b.float().t() + bias
+    z, g = gemm_fused(a, b, M, N, K, 1, bias=bias)
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    torch.testing.assert_close(z.float(), z_ref, rtol=tol, atol=tol * 4)
+    torch.testing.assert_close(g.float(), F.gelu(z_ref), rtol=tol, atol=tol * 4)
+    res = _mk(M, N, dtype, 23)
+    y = gemm_fused(a, b, M, N, K, 3, bias=bias, aux=res)
+    torch.testing.assert_close(y.float(), z_ref + res.float(), rtol=tol, atol=tol * 4)
+    # dgrad form: dz[M, K'] = (dy[M, N'] W[N', K']) * gelu'(zsaved[M, K']) with W read MN-major
+    dy, w = _mk(M, 768, dtype, 24), (_mk(768, N, dtype, 25) * 0.2)
+    zs = _mk(M, N, dtype, 26)
+    zf = zs.float().requires_grad_(True)
+    F.gelu(zf).backward(dy.float() @ w.float())
+    dz = gemm_fused(dy, w, M, N, 768, 2, aux=zs)
+    torch.testing.assert_close(dz.float(), zf.grad, rtol=tol, atol=tol * 4)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_fused_transformer_mlp_and_residual_stream(dtype):
+    """One ViT encoder block with the fused MLP / residual epilogues / LayerNorm carry vs the same block in
+    fp32 torch ops: output and every gradient."""
+    from pytorch_distributedtraining_b200.models.vit import EncoderBlock
+    torch.manual_seed(11)
+    blk = EncoderBlock(768, 12, 3072).to(cuda)
+    x0 = torch.randn(128, 197, 768, device=cuda) * 0.5
+    x = x0.clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=dtype):
+        y = blk(x)
+    gy = torch.randn_like(y) * 0.1
+    y.backward(gy)
+    got = {n: p.grad.float().clone() for n, p in blk.named_parameters()}
+    gx = x.grad.float().clone()
+
+    def ref_block(t):
+        h = F.layer_norm(t, (768,), blk.ln_1.weight, blk.ln_1.bias, 1e-6)
+        B, S, D = h.shape
+        qkv = F.linear(h, blk.self_attention.in_proj.weight, blk.self_attention.in_proj.bias).view(B, S, 3, 12, 64).permute(2, 0, 3, 1, 4)
+        o = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2]).transpose(1, 2).reshape(B, S, D)
+        t = t + F.linear(o, blk.self_attention.out_proj.weight, blk.self_attention.out_proj.bias)
+        h = F.layer_norm(t, (768,), blk.ln_2.weight, blk.ln_2.bias, 1e-6)
+        return t + F.linear(F.gelu(F.linear(h, blk.mlp.fc1.weight, blk.mlp.fc1.bias)), blk.mlp.fc2.weight, blk.mlp.fc2.bias)
+
+    blk.zero_grad(set_to_none=True)
+    xr = x0.clone().requires_grad_(True)
+    yr = ref_block(xr)
+    yr.backward(gy.float())
+    tol = 4e-2 if dtype == torch.bfloat16 else 1e-2
+    torch.testing.assert_close(y.float(), yr, rtol=tol, atol=tol)
+    torch.testing.assert_close(gx, xr.grad, rtol=tol, atol=tol * float(xr.grad.abs().max()))
+    for n, p in blk.named_parameters():
+        ref = p.grad.float()
+        torch.testing.assert_close(got[n], ref, rtol=tol, atol=tol * float(ref.abs().max()) + 1e-4), n
