@@ -13,6 +13,10 @@ from typing import Any
 import torch
 
 _DISABLED = {s.strip() for s in os.environ.get("B200DP_DISABLE", "").split(",") if s.strip()}
+if os.environ.get("B200DP_DETERMINISTIC", "0") not in ("", "0"):
+    # run-to-run reproducible kernels only: the conv -> BatchNorm statistics epilogue accumulates with float
+    # atomics, so BatchNorm goes back to its own two-stage (fixed-order) reduction
+    _DISABLED.add("convstats")
 _HALF = (torch.float16, torch.bfloat16)
 
 

@@ -274,7 +274,12 @@ def _w_facade_peer(rank, world, mode):
     from pytorch_distributedtraining_b200 import (AMPConfig, B200Config, ClipGradNormConfig, DDPConfig,
                                                   FairscaleFSDPConfig, FairscaleOSSConfig, Stoke, StokeOptimizer)
     from pytorch_distributedtraining_b200.models import resnet18, vit_tiny
+    from pytorch_distributedtraining_b200.ops import dispatch
     from pytorch_distributedtraining_b200.ops.loss import cross_entropy
+    # two separate runs are compared, and AdamW turns 1e-7 differences in near-zero gradients into lr-sized
+    # parameter differences: keep the compute path run-to-run reproducible (the conv -> BatchNorm statistics
+    # epilogue accumulates with float atomics) so that what is compared is the collectives
+    dispatch.disable("convstats")
 
     def run(peer):
         torch.manual_seed(0)
