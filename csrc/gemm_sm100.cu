@@ -488,6 +488,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 uint8_t* buf2 = my_stage + ((buf_idx & 1) ^ 1) * kEpiBufBytes;      // kEpiGeluDual: second output
                 if (lane == 0) { if (kEpi == kEpiGeluDual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
                 __syncwarp();
+                if constexpr (kEpi == kEpiDGelu || kEpi == kEpiAddAux) {
+                    // the aux chunk (32 rows x 128 B) goes straight into the staging buffer with 16-byte async
+                    // copies — 8 lanes per row, fully coalesced, same swizzle as the output — while the
+                    // accumulator is still on its way out of TMEM
+#pragma unroll
+                    for (int rr = 0; rr < 32; rr += 4) {
+                        const int row = rr + (lane >> 3), c = lane & 7;
+                        const int grow = row0 + row, gcol = n0 + ch * kChunkCols + c * 8;
+                        if (grow < M && gcol < N)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(buf + row * 128 + ((c ^ (row & 7)) << 4))),
+                                         "l"(aux + (size_t)grow * ld_aux + gcol) : "memory");
+                    }
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+                }
 #pragma unroll
                 for (int l = 0; l < kLoadsPerChunk; ++l) {
                     uint32_t r[32];
@@ -503,21 +517,20 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for (int j = 0; j < 32; ++j) v[j] += (gcol + j < N) ? __ldg(bias + gcol + j) : 0.f;
                     }
                     if constexpr (kEpi == kEpiDGelu || kEpi == kEpiAddAux) {
-                        // this lane's row of the aux matrix, 32 columns = 64 bytes
-                        const int grow = row0 + lane, gcol = n0 + colbase;
-                        if (grow < M) {
-                            const TOut* ap = aux + (size_t)grow * ld_aux + gcol;
+                        if (l == 0) {
+                            asm volatile("cp.async.wait_group 0;" ::: "memory");
+                            __syncwarp();
+                        }
+                        // this lane's row of the aux chunk, read back from the staging buffer (rows past M / columns
+                        // past N hold stale bytes: their results are clipped by the TMA store)
 #pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                if (gcol + q * 8 < N) {
-                                    float a8[8];
-                                    load8<TOut>(ap + q * 8, a8);
+                        for (int q = 0; q < 4; ++q) {
+                            float a8[8];
+                            load8<TOut>(reinterpret_cast<const TOut*>(buf + lane * 128 + (((l * 4 + q) ^ (lane & 7)) << 4)), a8);
 #pragma unroll
-                                    for (int e = 0; e < 8; ++e) {
-                                        if (kEpi == kEpiDGelu) v[q * 8 + e] *= dgelu_f(a8[e]);
-                                        else v[q * 8 + e] += a8[e];
-                                    }
-                                }
+                            for (int e = 0; e < 8; ++e) {
+                                if (kEpi == kEpiDGelu) v[q * 8 + e] *= dgelu_f(a8[e]);
+                                else v[q * 8 + e] += a8[e];
                             }
                         }
                     }
