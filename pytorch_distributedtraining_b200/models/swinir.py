@@ -21,6 +21,10 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops import gemm as _gemm
+from ..ops.attention import merge_heads, split_qkv
+from ..ops.layers import LayerNorm, Linear
+
 __all__ = ["SwinIR"]
 
 
@@ -40,12 +44,16 @@ def window_reverse(windows: torch.Tensor, ws: int, H: int, W: int) -> torch.Tens
 class Mlp(nn.Module):
     def __init__(self, dim: int, hidden: int, drop: float = 0.0):
         super().__init__()
-        self.fc1 = nn.Linear(dim, hidden)
+        # ops.layers.Linear: tcgen05 GEMM when the widths are multiples of 8 (16-byte TMA rows), stock
+        # otherwise (the reference's embed_dim = 60 is not); same parameter names either way
+        self.fc1 = Linear(dim, hidden)
         self.act = nn.GELU()
-        self.fc2 = nn.Linear(hidden, dim)
+        self.fc2 = Linear(hidden, dim)
         self.drop = nn.Dropout(drop)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if (self.drop.p == 0.0 or not self.training) and _gemm.mlp_supported(x, self.fc1.weight, self.fc2.weight):
+            return _gemm.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias)
         return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
 
 
@@ -63,16 +71,15 @@ class WindowAttention(nn.Module):
         rel[:, :, 1] += ww - 1
         rel[:, :, 0] *= 2 * ww - 1
         self.register_buffer("relative_position_index", rel.sum(-1))
-        self.qkv = nn.Linear(dim, dim * 3, bias=qkv_bias)
+        self.qkv = Linear(dim, dim * 3, bias=qkv_bias)
         self.attn_drop = nn.Dropout(attn_drop)
-        self.proj = nn.Linear(dim, dim)
+        self.proj = Linear(dim, dim)
         self.proj_drop = nn.Dropout(proj_drop)
         nn.init.trunc_normal_(self.relative_position_bias_table, std=0.02)
 
     def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         B_, N, C = x.shape
-        qkv = self.qkv(x).reshape(B_, N, 3, self.num_heads, C // self.num_heads).permute(2, 0, 3, 1, 4)
-        q, k, v = qkv[0], qkv[1], qkv[2]
+        q, k, v = split_qkv(self.qkv(x), self.num_heads)      # strided per-head views; packed gradient in one pass
         bias = self.relative_position_bias_table[self.relative_position_index.view(-1)].view(N, N, -1)
         bias = bias.permute(2, 0, 1).unsqueeze(0).to(q.dtype)            # [1, heads, N, N]
         if mask is not None:
@@ -84,13 +91,13 @@ class WindowAttention(nn.Module):
         # one fused attention call: softmax(q k^T * scale + bias) v
         o = F.scaled_dot_product_attention(q, k, v, attn_mask=bias,
                                            dropout_p=self.attn_drop.p if self.training else 0.0, scale=self.scale)
-        return self.proj_drop(self.proj(o.transpose(1, 2).reshape(B_, N, C)))
+        return self.proj_drop(self.proj(merge_heads(o)))
 
 
 class SwinTransformerBlock(nn.Module):
     def __init__(self, dim: int, input_resolution: Tuple[int, int], num_heads: int, window_size: int = 7,
                  shift_size: int = 0, mlp_ratio: float = 4.0, qkv_bias: bool = True, qk_scale=None, drop: float = 0.0,
-                 attn_drop: float = 0.0, drop_path: float = 0.0, norm_layer=nn.LayerNorm):
+                 attn_drop: float = 0.0, drop_path: float = 0.0, norm_layer=LayerNorm):
         super().__init__()
         self.dim, self.input_resolution, self.num_heads = dim, input_resolution, num_heads
         self.window_size, self.shift_size = window_size, shift_size
@@ -147,7 +154,7 @@ class SwinTransformerBlock(nn.Module):
 
 class BasicLayer(nn.Module):
     def __init__(self, dim, input_resolution, depth, num_heads, window_size, mlp_ratio=4.0, qkv_bias=True, qk_scale=None,
-                 drop=0.0, attn_drop=0.0, drop_path=0.0, norm_layer=nn.LayerNorm, use_checkpoint=False):
+                 drop=0.0, attn_drop=0.0, drop_path=0.0, norm_layer=LayerNorm, use_checkpoint=False):
         super().__init__()
         self.use_checkpoint = use_checkpoint
         self.blocks = nn.ModuleList([
@@ -190,7 +197,7 @@ class RSTB(nn.Module):
     """Residual Swin Transformer Block: Swin layers + conv, with a skip connection."""
 
     def __init__(self, dim, input_resolution, depth, num_heads, window_size, mlp_ratio=4.0, qkv_bias=True, qk_scale=None,
-                 drop=0.0, attn_drop=0.0, drop_path=0.0, norm_layer=nn.LayerNorm, use_checkpoint=False,
+                 drop=0.0, attn_drop=0.0, drop_path=0.0, norm_layer=LayerNorm, use_checkpoint=False,
                  resi_connection="1conv"):
         super().__init__()
         self.residual_group = BasicLayer(dim, input_resolution, depth, num_heads, window_size, mlp_ratio, qkv_bias,
@@ -236,7 +243,7 @@ class SwinIR(nn.Module):
     def __init__(self, img_size: int = 64, patch_size: int = 1, in_chans: int = 3, embed_dim: int = 96,
                  depths: Sequence[int] = (6, 6, 6, 6), num_heads: Sequence[int] = (6, 6, 6, 6), window_size: int = 7,
                  mlp_ratio: float = 4.0, qkv_bias: bool = True, qk_scale=None, drop_rate: float = 0.0,
-                 attn_drop_rate: float = 0.0, drop_path_rate: float = 0.1, norm_layer=nn.LayerNorm, ape: bool = False,
+                 attn_drop_rate: float = 0.0, drop_path_rate: float = 0.1, norm_layer=LayerNorm, ape: bool = False,
                  patch_norm: bool = True, use_checkpoint: bool = False, upscale: int = 2, img_range: float = 1.0,
                  upsampler: str = "", resi_connection: str = "1conv", **_kw):
         super().__init__()
