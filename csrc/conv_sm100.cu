@@ -278,6 +278,255 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
 }
 
 
+// ---------------------------------------------------------------- fprop / dgrad, CTA pair (cta_group::2)
+// Same implicit GEMM with two CTAs of a cluster on one 256-pixel x BN tile: each CTA fetches ITS 128 pixels
+// and only HALF of the weight tile per k-block, the leader issues one M = 256 tcgen05.mma for the pair.
+// The weight tile is the larger operand for BN >= 128, so L2 -> SM operand traffic drops 25-33 %, which is
+// what bounds these kernels (protocol as in gemm_sm100.cu: leader-only full / tmem_empty barriers, multicast
+// commits).
+template <int BN> struct PCfg {
+    static constexpr int kABytes = kBM * kBK * 2;
+    static constexpr int kBBytes = (BN / 2) * kBK * 2;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = BN == 256 ? 6 : 8;
+    static constexpr int kEpiBufBytes = 32 * 128;
+    static constexpr int kEpiBytes = 4 * kEpiBufBytes;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 2 * kEpiBytes + 1024 + 256;
+    static constexpr int kTmemCols = 2 * BN;
+};
+
+__device__ __forceinline__ void tma_load_4d_pair(void* smem_dst, const CUtensorMap* tm, uint64_t* leader_bar, int c0, int c1,
+                                                 int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tm), "r"(smem_u32(leader_bar) & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+
+template <int BN, bool kBMN, typename TOut, bool kStats = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_fd_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TOut* __restrict__ out,
+                    const float* __restrict__ bias, Geom g, int is_bf16, float* __restrict__ colstats) {
+    using cfg = PCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemA = smem;
+    uint8_t* smemB = smem + cfg::kStages * cfg::kABytes;
+    uint8_t* smemC = smem + cfg::kStages * cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + cfg::kEpiBytes);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + cfg::kStages;
+    uint64_t* tmem_full = bars + 2 * cfg::kStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = g.tiles_q * g.tiles_p * g.tiles_n;
+    const int num_n = (g.c_out + BN - 1) / BN;
+    const uint32_t cta_rank = cluster_ctarank();
+    const bool leader = cta_rank == 0;
+    const int pair_id = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    const int num_mp = (num_m + 1) / 2;                  // pixel tiles are handed out two at a time
+    const int num_tiles = num_mp * num_n;
+    const int chunks = g.c_red / kBK;
+    const int num_kb = g.R * g.S * chunks;
+    const int rows_valid = g.bq * g.bp * g.bn;
+    const uint32_t a_bytes = (uint32_t)rows_valid * 128u;
+
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < cfg::kStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 8); }
+        fence_barrier_init();
+    }
+    // rows of the A tile beyond rows_valid are never written by TMA: clear them once so the MMA
+    // reads zeros (their results are discarded, but NaN bit patterns must not linger in smem)
+    for (int i = threadIdx.x; i < cfg::kStages * cfg::kABytes / 16; i += kThreads)
+        reinterpret_cast<uint4*>(smemA)[i] = make_uint4(0, 0, 0, 0);
+    fence_async_smem();
+    cluster_sync_all();                       // both CTAs' barriers exist before anything remote touches them
+    if (warp == 2) tmem_alloc_pair(tmem_slot, cfg::kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode_m = [&](int mt, int& n0, int& p0, int& q0) {
+        q0 = (mt % g.tiles_q) * g.bq;
+        p0 = ((mt / g.tiles_q) % g.tiles_p) * g.bp;
+        n0 = (mt / (g.tiles_q * g.tiles_p)) * g.bn;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+                int n0, p0, q0;
+                decode_m(2 * (tile % num_mp) + (int)cta_rank, n0, p0, q0);      // an index past the last tile decodes to n0 >= n_img: all rows out of range
+                const int nt0 = (tile / num_mp) * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int tap = kb / chunks, c0 = (kb % chunks) * kBK;
+                    const int r = tap / g.S, s = tap % g.S;
+                    mbar_wait(empty + stage, phase ^ 1);
+                    if (leader) mbar_expect_tx(full + stage, 2 * (a_bytes + cfg::kBBytes));
+                    tma_load_4d_pair(smemA + stage * cfg::kABytes, &tmA, full + stage, c0,
+                                q0 * g.stride + g.off_w + g.tap_sign * s, p0 * g.stride + g.off_h + g.tap_sign * r, n0);
+                    uint8_t* b = smemB + stage * cfg::kBBytes;
+                    if (kBMN) {
+#pragma unroll
+                        for (int j = 0; j < BN / 128; ++j)
+                            tma_load_2d_pair(b + j * (kBK * 128), &tmB, full + stage,
+                                             tap * g.c_out + nt0 + (int)cta_rank * (BN / 2) + j * 64, c0);
+                    } else {
+                        tma_load_2d_pair(b, &tmB, full + stage, tap * g.c_red + c0, nt0 + (int)cta_rank * (BN / 2));
+                    }
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (leader && lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, 0, kBMN ? 1 : 0, 2 * kBM, BN);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full + stage, phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smemA + stage * cfg::kABytes);
+                    const uint32_t b_addr = smem_u32(smemB + stage * cfg::kBBytes);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUmmaK; ++k) {
+                        const uint64_t da = make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
+                        const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                 : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
+                        umma_f16_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit_pair(empty + stage, 3);
+                    if (++stage == cfg::kStages) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(tmem_full + acc, 3);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        const int quarter = warp - kEpiWarp0;
+        uint8_t* buf = smemC + quarter * cfg::kEpiBufBytes;
+        int acc = 0; uint32_t acc_phase = 0;
+        constexpr int kChunks = BN / 64;
+        // channel statistics: lane l owns channels 2l, 2l+1 of every 64-channel chunk of the current channel tile
+        float st[kStats ? kChunks * 4 : 1];
+        int st_n0 = -1;
+#pragma unroll
+        for (int i = 0; i < (kStats ? kChunks * 4 : 1); ++i) st[i] = 0.f;
+        auto flush_stats = [&]() {
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) {
+                    const int col = st_n0 + ch * 64 + 2 * lane;
+                    if (col < g.c_out) {          // c_out is even (multiple of 8): col + 1 is valid too
+                        atomicAdd(colstats + col, st[ch * 4 + 0]);
+                        atomicAdd(colstats + col + 1, st[ch * 4 + 1]);
+                        atomicAdd(colstats + g.c_out + col, st[ch * 4 + 2]);
+                        atomicAdd(colstats + g.c_out + col + 1, st[ch * 4 + 3]);
+                    }
+                    st[ch * 4 + 0] = st[ch * 4 + 1] = st[ch * 4 + 2] = st[ch * 4 + 3] = 0.f;
+                }
+            }
+        };
+        for (int tile = pair_id; tile < num_tiles; tile += num_pairs) {
+            int n0, p0, q0;
+            decode_m(2 * (tile % num_mp) + (int)cta_rank, n0, p0, q0);      // an index past the last tile decodes to n0 >= n_img: all rows out of range
+            const int nt0 = (tile / num_mp) * BN;
+            if (kStats && nt0 != st_n0) {
+                if (st_n0 >= 0) flush_stats();
+                st_n0 = nt0;
+            }
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            // this lane's row of the tile -> output pixel
+            const int t = quarter * 32 + lane;
+            const int bq_i = t % g.bq, bp_i = (t / g.bq) % g.bp, bn_i = t / (g.bq * g.bp);
+            const int n = n0 + bn_i, p = p0 + bp_i, q = q0 + bq_i;
+            const bool valid = t < rows_valid && n < g.n_img && p < g.out_h && q < g.out_w;
+            const long long pix = valid ? (((long long)n * g.out_h + p) * g.out_w + q) : -1;
+            auto do_chunk = [&](const int ch) {
+                __syncwarp();
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+                    uint32_t r[32];
+                    const int colbase = ch * 64 + l * 32;
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + colbase, r);
+                    tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    if (bias != nullptr) {
+                        const int gcol = nt0 + colbase;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (gcol + j < g.c_out) ? __ldg(bias + gcol + j) : 0.f;
+                    }
+                    if (kStats && !valid) {       // pixels outside the image must not count
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+                    }
+                    uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+                    for (int qd = 0; qd < 4; ++qd) {
+                        float tt[8] = {v[qd * 8], v[qd * 8 + 1], v[qd * 8 + 2], v[qd * 8 + 3],
+                                       v[qd * 8 + 4], v[qd * 8 + 5], v[qd * 8 + 6], v[qd * 8 + 7]};
+                        const int j = l * 4 + qd;
+                        store8<TOut>(reinterpret_cast<TOut*>(rowp + ((j ^ (lane & 7)) << 4)), tt);
+                    }
+                }
+                __syncwarp();
+                // write-out: 8 lanes per row, 4 rows per instruction, 128 contiguous bytes per row
+                const int col0 = nt0 + ch * 64;
+#pragma unroll
+                for (int rr = 0; rr < 32; rr += 4) {
+                    const int row = rr + (lane >> 3), chunk = lane & 7;
+                    const long long rpix = __shfl_sync(0xffffffffu, pix, row);
+                    const uint4 val = *reinterpret_cast<const uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4));
+                    if (rpix >= 0 && col0 + chunk * 8 < g.c_out)
+                        *reinterpret_cast<uint4*>(out + rpix * g.c_out + col0 + chunk * 8) = val;
+                }
+                if constexpr (kStats) {
+                    // lane l sums the 4-byte word of channels 2l, 2l+1 over the 32 staged rows
+                    const int j = lane >> 2, w = lane & 3;
+                    float s0 = 0.f, s1 = 0.f, q0s = 0.f, q1s = 0.f;
+#pragma unroll 8
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const uint32_t u = *reinterpret_cast<const uint32_t*>(buf + rr * 128 + ((j ^ (rr & 7)) << 4) + w * 4);
+                        const float2 f = unpack2<TOut>(u);
+                        s0 += f.x; s1 += f.y;
+                        q0s = fmaf(f.x, f.x, q0s); q1s = fmaf(f.y, f.y, q1s);
+                    }
+                    st[ch * 4 + 0] += s0; st[ch * 4 + 1] += s1; st[ch * 4 + 2] += q0s; st[ch * 4 + 3] += q1s;
+                }
+            };
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
+            } else {
+#pragma unroll 1
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tmem_empty + acc);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (kStats && st_n0 >= 0) flush_stats();
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 2) tmem_dealloc_pair(tmem_base, cfg::kTmemCols);
+}
+
+
+
 // ---------------------------------------------------------------- wgrad
 // dW[co][tap][ci] += sum over a 64-pixel box of dY[pix][co] * X[pix shifted by tap][ci].
 // Work item = (tap, co tile, ci tile, split); a split walks its share of the pixel boxes.  Both
@@ -681,6 +930,30 @@ static int launch_fd(const CUtensorMap& ta, const CUtensorMap& tb, void* out, co
     return 0;
 }
 
+template <int BN, bool kBMN, typename TOut, bool kStats = false>
+static int launch_fd_pair(const CUtensorMap& ta, const CUtensorMap& tb, void* out, const float* bias, const Geom& g, int is_bf16,
+                          cudaStream_t s, float* colstats = nullptr) {
+    auto kern = conv_fd_pair_kernel<BN, kBMN, TOut, kStats>;
+    static bool configured = false;
+    if (!configured) {
+        B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PCfg<BN>::kSmemBytes));
+        configured = true;
+    }
+    const int num_m = g.tiles_q * g.tiles_p * g.tiles_n;
+    const int tiles = ((num_m + 1) / 2) * ((g.c_out + BN - 1) / BN);
+    int pairs = B200DP_SMS / 2;
+    if (tiles < pairs) pairs = tiles;
+    kern<<<2 * pairs, kThreads, PCfg<BN>::kSmemBytes, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16, colstats);
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+// B200DP_CONV_PAIR=0 turns the cta_group::2 convolution off (A/B measurements)
+static bool conv_pair_enabled() {
+    static const bool on = [] { const char* e = getenv("B200DP_CONV_PAIR"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 }  // namespace conv
 }  // namespace b200dp
 
@@ -717,6 +990,28 @@ static int conv2d_impl(int mode, const void* x, const void* w, void* y, const fl
     CUtensorMap ta, tb;
     int rc = make_act_map(&ta, x, is_bf16, N, src_h, src_w, c_red, g.bq, g.bp, g.bn, g.stride);
     if (rc) return rc;
+    {
+        const int num_m_tiles = g.tiles_q * g.tiles_p * g.tiles_n;
+        // measured (scripts/bench_conv.py, batch 256): 5-15 % faster than the single-CTA kernel for 256-channel
+        // tiles, no gain at 128 (there the activation operand, not the weights, is the larger load)
+        if (BN == 256 && conv_pair_enabled() && ((num_m_tiles + 1) / 2) * ((c_out + BN - 1) / BN) >= 74) {
+            // CTA-pair kernel: each CTA of a pair fetches half of the weight tile (box of BN/2 rows / 64-column boxes)
+            rc = mode == 0 ? make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, kBK, BN / 2)
+                           : make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, 64, kBK);
+            if (rc) return rc;
+            cudaStream_t ps = (cudaStream_t)stream;
+#define GP(BNv, MN, T, ST) return launch_fd_pair<BNv, MN, T, ST>(ta, tb, y, bias, g, is_bf16, ps, colstats)
+#define GP_T(BNv, MN, ST) if (is_bf16) { GP(BNv, MN, __nv_bfloat16, ST); } else { GP(BNv, MN, __half, ST); }
+#define GP_MODE(BNv)                                           \
+    if (mode == 0 && colstats != nullptr) { GP_T(BNv, false, true) } \
+    else if (mode == 0) { GP_T(BNv, false, false) }             \
+    else { GP_T(BNv, true, false) }
+            if (BN == 256) { GP_MODE(256) } else { GP_MODE(128) }
+#undef GP_MODE
+#undef GP_T
+#undef GP
+        }
+    }
     // weights as a matrix [Cout][R*S*Cin]: fprop reads it K-major (box 64 x BN rows), dgrad MN-major (box 64 x 64)
     rc = mode == 0 ? make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, kBK, BN)
                    : make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, 64, kBK);

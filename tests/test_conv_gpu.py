@@ -203,3 +203,40 @@ def test_residual_gradient_accumulates_in_the_dgrad_epilogue():
         scale = res[1][0].abs().max()
         torch.testing.assert_close(res[0][0], res[1][0], rtol=2e-2, atol=float(scale) * 4e-3)
         torch.testing.assert_close(res[0][1], res[1][1], rtol=2e-2, atol=float(res[1][1].abs().max()) * 1e-2)
+
+
+PAIR_CASES = [
+    # batches large enough for the cta_group::2 kernel (>= 74 pairs of 128-pixel tiles)
+    (64, 28, 28, 128, 128, 3, 1, 1),
+    (128, 14, 14, 256, 256, 3, 1, 1),
+    (130, 14, 14, 256, 512, 1, 2, 0),
+    (67, 27, 29, 128, 192, 3, 1, 1),          # ragged pixel tiles, odd tile count, ragged channel tile
+    (128, 28, 28, 256, 256, 3, 2, 1),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad", PAIR_CASES)
+def test_conv_cta_pair_kernel(dtype, N, H, W, Cin, Cout, R, stride, pad):
+    """Forward (+ statistics epilogue) and stride-1 input gradient on the CTA-pair implicit-GEMM kernel."""
+    from pytorch_distributedtraining_b200.ops.conv import conv2d_raw
+    g = torch.Generator().manual_seed(N + H)
+    x = (torch.randn(N, Cin, H, W, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) * 0.1).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    want = F.conv2d(x.float(), w.float(), None, stride=stride, padding=pad)
+    stats = torch.zeros(2 * Cout + 1, device=cuda)
+    got = conv2d_raw(0, x, w, None, N, H, W, Cin, Cout, R, R, stride, pad, colstats=stats)
+    plain = conv2d_raw(0, x, w, None, N, H, W, Cin, Cout, R, R, stride, pad)
+    torch.cuda.synchronize()
+    tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * (Cin * R * R) ** 0.5 * 0.05)
+    assert torch.equal(got, plain)
+    y = got.double()
+    torch.testing.assert_close(stats[:Cout].double(), y.sum(dim=(0, 2, 3)), rtol=2e-4, atol=2e-2)
+    torch.testing.assert_close(stats[Cout:2 * Cout].double(), (y * y).sum(dim=(0, 2, 3)), rtol=2e-4, atol=2e-2)
+    if stride == 1 and Cout % 64 == 0:
+        dy = (torch.randn(want.shape, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+        want_dx = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float(), dy.float(), stride=1, padding=pad)
+        got_dx = conv2d_raw(1, dy, w, None, N, H, W, Cin, Cout, R, R, 1, pad)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(got_dx.float(), want_dx, rtol=tol, atol=tol * (Cout * R * R) ** 0.5 * 0.05)
