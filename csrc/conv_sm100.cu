@@ -278,6 +278,305 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
 }
 
 
+// ---------------------------------------------------------------- fprop / dgrad, 3 x 3 stride 1, row-grouped
+// The tap-at-a-time kernel above is bound by operand traffic on the shallow layers (64 / 128 channels: few
+// MMA cycles per byte loaded; ~64 B/clk/SM is what TMA + L2 deliver).  Here one activation PATCH of
+// (bp + 2) x bq pixels (bq a multiple of 8) is loaded once per filter column s and 64-channel chunk, and the
+// A operand of filter row r is that same patch read from byte offset r * bq * 128 — a multiple of the
+// 1024-byte swizzle atom, so the UMMA descriptor just starts there.  Activation traffic drops ~2.5x.
+// Two rings: activation patches (kRowsAStages) and per-tap weight tiles (kRowsBStages).
+constexpr int kRowsAStages = 3;
+constexpr int kRowsBStages = 8;
+constexpr int kRowsEpiBufBytes = 32 * 128;
+constexpr int kRowsEpiWarps = 8;
+constexpr int kRowsThreads = (kEpiWarp0 + kRowsEpiWarps) * 32;
+constexpr int kRowsEpiBytes = kRowsEpiWarps * kRowsEpiBufBytes;
+template <int BN> struct RCfg {
+    static constexpr int kBBytes = BN * kBK * 2;                      // one tap's weight tile
+    static constexpr int kBStages = BN == 128 ? 6 : kRowsBStages;
+    // patch: up to (2 + 2) * 64 = 256 rows of 128 B; sized by the host per geometry (a_patch_bytes)
+    static int smem_bytes(int a_patch_bytes, int b_tiles) { return kRowsAStages * a_patch_bytes + b_tiles * kBBytes + kRowsEpiBytes + 1024 + 256; }
+};
+
+template <int BN, bool kBMN, typename TOut, bool kStats = false>
+__global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                const __grid_constant__ CUtensorMap tmB,
+                                                                TOut* __restrict__ out, const float* __restrict__ bias,
+                                                                Geom g, int is_bf16, float* __restrict__ colstats,
+                                                                int a_patch_bytes, int w_resident) {
+    using cfg = RCfg<BN>;
+    // P partial accumulators per tile (k-step residue -> accumulator, summed by the epilogue) were tried against
+    // the idea that back-to-back MMAs on one accumulator serialise: no measurable change (ncu: the tensor pipe
+    // sits at ~22 % on the 64-channel layer because only three activation patches — one tile — can be in
+    // flight next to the resident filter, and a patch takes ~2 us to arrive).  Kept at 1.
+    constexpr int P = 1;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemA = smem;
+    uint8_t* smemB = smem + kRowsAStages * a_patch_bytes;
+    uint8_t* smemC = smemB + (w_resident ? 9 * (g.c_red / kBK) : cfg::kBStages) * cfg::kBBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + kRowsEpiBytes);
+    uint64_t* a_full = bars;
+    uint64_t* a_empty = a_full + kRowsAStages;
+    uint64_t* b_full = a_empty + kRowsAStages;
+    uint64_t* b_empty = b_full + cfg::kBStages;
+    uint64_t* tmem_full = b_empty + cfg::kBStages;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_m = g.tiles_q * g.tiles_p * g.tiles_n;
+    const int num_n = (g.c_out + BN - 1) / BN;
+    const int num_tiles = num_m * num_n;
+    const int chunks = g.c_red / kBK;
+    const int rows_valid = g.bq * g.bp * g.bn;           // == 128 here
+    const uint32_t a_bytes = (uint32_t)(g.bp + 2) * g.bq * 128u;
+
+    if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kRowsAStages; ++i) { mbar_init(a_full + i, 1); mbar_init(a_empty + i, 1); }
+        for (int i = 0; i < cfg::kBStages; ++i) { mbar_init(b_full + i, 1); mbar_init(b_empty + i, 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 2 * P * BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode_m = [&](int mt, int& n0, int& p0, int& q0) {
+        q0 = (mt % g.tiles_q) * g.bq;
+        p0 = ((mt / g.tiles_q) % g.tiles_p) * g.bp;
+        n0 = (mt / (g.tiles_q * g.tiles_p)) * g.bn;
+    };
+    // input row seen by output row p through filter row r: p + off_h + tap_sign * r.  The patch starts at the
+    // lowest of the three; filter row r then sits r (fprop) or 2 - r (dgrad, tap_sign = -1) patch rows down.
+    const int patch_dh = g.tap_sign > 0 ? 0 : -2;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int sa = 0; uint32_t pa = 0;
+            int sb = 0; uint32_t pb = 0;
+            if (w_resident) {
+                // the whole filter (9 taps x chunks weight tiles, one channel tile) fits next to the patches:
+                // fetch it once per CTA, tile (tap, chunk) at smemB + (tap * chunks + chunk) * kBBytes
+                mbar_expect_tx(b_full, (uint32_t)(9 * chunks) * cfg::kBBytes);
+                for (int tap = 0; tap < 9; ++tap)
+                    for (int ck = 0; ck < chunks; ++ck) {
+                        uint8_t* b = smemB + (tap * chunks + ck) * cfg::kBBytes;
+                        if (kBMN) {
+#pragma unroll
+                            for (int j = 0; j < BN / 64; ++j)
+                                tma_load_2d(b + j * (kBK * 128), &tmB, b_full, tap * g.c_out + j * 64, ck * kBK);
+                        } else {
+                            tma_load_2d(b, &tmB, b_full, tap * g.c_red + ck * kBK, 0);
+                        }
+                    }
+            }
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int n0, p0, q0;
+                decode_m(tile % num_m, n0, p0, q0);
+                const int nt0 = (tile / num_m) * BN;
+                for (int s = 0; s < 3; ++s) {
+                    for (int ck = 0; ck < chunks; ++ck) {
+                        const int c0 = ck * kBK;
+                        mbar_wait(a_empty + sa, pa ^ 1);
+                        mbar_expect_tx(a_full + sa, a_bytes);
+                        tma_load_4d(smemA + sa * a_patch_bytes, &tmA, a_full + sa, c0, q0 + g.off_w + g.tap_sign * s,
+                                    p0 + g.off_h + patch_dh, n0);
+                        if (++sa == kRowsAStages) { sa = 0; pa ^= 1; }
+                        for (int r = 0; r < 3 && !w_resident; ++r) {
+                            const int tap = r * 3 + s;
+                            mbar_wait(b_empty + sb, pb ^ 1);
+                            mbar_expect_tx(b_full + sb, cfg::kBBytes);
+                            uint8_t* b = smemB + sb * cfg::kBBytes;
+                            if (kBMN) {
+#pragma unroll
+                                for (int j = 0; j < BN / 64; ++j)
+                                    tma_load_2d(b + j * (kBK * 128), &tmB, b_full + sb, tap * g.c_out + nt0 + j * 64, c0);
+                            } else {
+                                tma_load_2d(b, &tmB, b_full + sb, tap * g.c_red + c0, nt0);
+                            }
+                            if (++sb == cfg::kBStages) { sb = 0; pb ^= 1; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc(is_bf16, 0, kBMN ? 1 : 0, kBM, BN);
+            int sa = 0; uint32_t pa = 0;
+            int sb = 0; uint32_t pb = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            if (w_resident) { mbar_wait(b_full, 0); tc_fence_after(); }
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(tmem_empty + acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * (P * BN);
+                bool first = true;
+                for (int grp = 0; grp < 3 * chunks; ++grp) {
+                    mbar_wait(a_full + sa, pa);
+                    tc_fence_after();
+                    const uint32_t a_base = smem_u32(smemA + sa * a_patch_bytes);
+                    for (int r = 0; r < 3; ++r) {
+                        if (!w_resident) {
+                            mbar_wait(b_full + sb, pb);
+                            tc_fence_after();
+                        }
+                        const uint32_t a_addr = a_base + (uint32_t)((g.tap_sign > 0 ? r : 2 - r) * g.bq) * 128u;
+                        // producer order: s outermost, then chunk: grp = s * chunks + chunk
+                        const uint32_t b_addr = w_resident
+                            ? smem_u32(smemB + ((r * 3 + grp / chunks) * chunks + grp % chunks) * cfg::kBBytes)
+                            : smem_u32(smemB + sb * cfg::kBBytes);
+#pragma unroll
+                        for (int k = 0; k < kBK / kUmmaK; ++k) {
+                            const uint64_t da = make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
+                            const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
+                                                     : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
+                            umma_f16(d_tmem + (k % P) * BN, da, db, idesc, (first && k < P) ? 0u : 1u);
+                        }
+                        first = false;
+                        if (!w_resident) {
+                            umma_commit(b_empty + sb);
+                            if (++sb == cfg::kBStages) { sb = 0; pb ^= 1; }
+                        }
+                    }
+                    umma_commit(a_empty + sa);
+                    if (++sa == kRowsAStages) { sa = 0; pa ^= 1; }
+                }
+                umma_commit(tmem_full + acc);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else if (warp >= kEpiWarp0) {
+        // EIGHT epilogue warps: warps 4-7 drain the tiles that land in accumulator 0 (this CTA's even tiles),
+        // warps 8-11 those in accumulator 1 — with K as short as 9 x 64 a tile's MMAs take ~1.2k cycles, far
+        // less than one warp set needs to convert, store and sum a 128 x BN tile
+        const int ew = warp - kEpiWarp0;
+        const int quarter = ew & 3, eset = ew >> 2;
+        uint8_t* buf = smemC + ew * kRowsEpiBufBytes;
+        const int acc = eset; uint32_t acc_phase = 0;
+        constexpr int kChunks = BN / 64;
+        // channel statistics: lane l owns channels 2l, 2l+1 of every 64-channel chunk of the current channel tile
+        float st[kStats ? kChunks * 4 : 1];
+        int st_n0 = -1;
+#pragma unroll
+        for (int i = 0; i < (kStats ? kChunks * 4 : 1); ++i) st[i] = 0.f;
+        auto flush_stats = [&]() {
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) {
+                    const int col = st_n0 + ch * 64 + 2 * lane;
+                    if (col < g.c_out) {          // c_out is even (multiple of 8): col + 1 is valid too
+                        atomicAdd(colstats + col, st[ch * 4 + 0]);
+                        atomicAdd(colstats + col + 1, st[ch * 4 + 1]);
+                        atomicAdd(colstats + g.c_out + col, st[ch * 4 + 2]);
+                        atomicAdd(colstats + g.c_out + col + 1, st[ch * 4 + 3]);
+                    }
+                    st[ch * 4 + 0] = st[ch * 4 + 1] = st[ch * 4 + 2] = st[ch * 4 + 3] = 0.f;
+                }
+            }
+        };
+        for (int tile = blockIdx.x + eset * gridDim.x; tile < num_tiles; tile += 2 * gridDim.x) {
+            int n0, p0, q0;
+            decode_m(tile % num_m, n0, p0, q0);
+            const int nt0 = (tile / num_m) * BN;
+            if (kStats && nt0 != st_n0) {
+                if (st_n0 >= 0) flush_stats();
+                st_n0 = nt0;
+            }
+            mbar_wait(tmem_full + acc, acc_phase);
+            tc_fence_after();
+            // this lane's row of the tile -> output pixel
+            const int t = quarter * 32 + lane;
+            const int bq_i = t % g.bq, bp_i = (t / g.bq) % g.bp, bn_i = t / (g.bq * g.bp);
+            const int n = n0 + bn_i, p = p0 + bp_i, q = q0 + bq_i;
+            const bool valid = t < rows_valid && n < g.n_img && p < g.out_h && q < g.out_w;
+            const long long pix = valid ? (((long long)n * g.out_h + p) * g.out_w + q) : -1;
+            auto do_chunk = [&](const int ch) {
+                __syncwarp();
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+                    uint32_t r[32];
+                    const int colbase = ch * 64 + l * 32;
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (P * BN) + colbase, r);
+                    tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+#pragma unroll
+                    for (int pp = 1; pp < P; ++pp) {
+                        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (P * BN) + pp * BN + colbase, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += __uint_as_float(r[j]);
+                    }
+                    if (bias != nullptr) {
+                        const int gcol = nt0 + colbase;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] += (gcol + j < g.c_out) ? __ldg(bias + gcol + j) : 0.f;
+                    }
+                    if (kStats && !valid) {       // pixels outside the image must not count
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = 0.f;
+                    }
+                    uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+                    for (int qd = 0; qd < 4; ++qd) {
+                        float tt[8] = {v[qd * 8], v[qd * 8 + 1], v[qd * 8 + 2], v[qd * 8 + 3],
+                                       v[qd * 8 + 4], v[qd * 8 + 5], v[qd * 8 + 6], v[qd * 8 + 7]};
+                        const int j = l * 4 + qd;
+                        store8<TOut>(reinterpret_cast<TOut*>(rowp + ((j ^ (lane & 7)) << 4)), tt);
+                    }
+                }
+                __syncwarp();
+                // write-out: 8 lanes per row, 4 rows per instruction, 128 contiguous bytes per row
+                const int col0 = nt0 + ch * 64;
+#pragma unroll
+                for (int rr = 0; rr < 32; rr += 4) {
+                    const int row = rr + (lane >> 3), chunk = lane & 7;
+                    const long long rpix = __shfl_sync(0xffffffffu, pix, row);
+                    const uint4 val = *reinterpret_cast<const uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4));
+                    if (rpix >= 0 && col0 + chunk * 8 < g.c_out)
+                        *reinterpret_cast<uint4*>(out + rpix * g.c_out + col0 + chunk * 8) = val;
+                }
+                if constexpr (kStats) {
+                    // lane l sums the 4-byte word of channels 2l, 2l+1 over the 32 staged rows
+                    const int j = lane >> 2, w = lane & 3;
+                    float s0 = 0.f, s1 = 0.f, q0s = 0.f, q1s = 0.f;
+#pragma unroll 8
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const uint32_t u = *reinterpret_cast<const uint32_t*>(buf + rr * 128 + ((j ^ (rr & 7)) << 4) + w * 4);
+                        const float2 f = unpack2<TOut>(u);
+                        s0 += f.x; s1 += f.y;
+                        q0s = fmaf(f.x, f.x, q0s); q1s = fmaf(f.y, f.y, q1s);
+                    }
+                    st[ch * 4 + 0] += s0; st[ch * 4 + 1] += s1; st[ch * 4 + 2] += q0s; st[ch * 4 + 3] += q1s;
+                }
+            };
+            if constexpr (kStats) {
+#pragma unroll
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
+            } else {
+#pragma unroll 1
+                for (int ch = 0; ch < kChunks; ++ch) do_chunk(ch);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tmem_empty + acc);
+            acc_phase ^= 1;
+        }
+        if (kStats && st_n0 >= 0) flush_stats();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 2 * P * BN);
+}
+
+
+
 // ---------------------------------------------------------------- fprop / dgrad, CTA pair (cta_group::2)
 // Same implicit GEMM with two CTAs of a cluster on one 256-pixel x BN tile: each CTA fetches ITS 128 pixels
 // and only HALF of the weight tile per k-block, the leader issues one M = 256 tcgen05.mma for the pair.
@@ -948,6 +1247,46 @@ static int launch_fd_pair(const CUtensorMap& ta, const CUtensorMap& tb, void* ou
     return 0;
 }
 
+template <int BN, bool kBMN, typename TOut, bool kStats = false>
+static int launch_rows(const CUtensorMap& ta, const CUtensorMap& tb, void* out, const float* bias, const Geom& g, int is_bf16,
+                       cudaStream_t s, float* colstats, int a_patch_bytes) {
+    auto kern = conv_rows_kernel<BN, kBMN, TOut, kStats>;
+    static bool configured = false;
+    if (!configured) {
+        B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448));
+        configured = true;
+    }
+    const int tiles = g.tiles_q * g.tiles_p * g.tiles_n * ((g.c_out + BN - 1) / BN);
+    const int grid = tiles < B200DP_SMS ? tiles : B200DP_SMS;
+    // weights stay resident in shared memory when the whole filter of the (single) channel tile fits
+    const int chunks = g.c_red / kBK, all_tiles = 9 * chunks;
+    const int w_resident = (g.c_out <= BN && RCfg<BN>::smem_bytes(a_patch_bytes, all_tiles) <= 232448) ? 1 : 0;
+    const int smem = RCfg<BN>::smem_bytes(a_patch_bytes, w_resident ? all_tiles : RCfg<BN>::kBStages);
+    kern<<<grid, kRowsThreads, smem, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16, colstats, a_patch_bytes, w_resident);
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+// pixel tile for the row-grouped kernel: bq x bp = 128 with bq a multiple of 8; the shape that wastes the
+// fewest rows on ragged edges wins (ties: the narrower one, its halo patch is smaller).  Returns the fraction
+// of useful rows.
+static double pick_rows_box(int out_h, int out_w, int& bq, int& bp) {
+    double best = 0.0;
+    bq = 8; bp = 16;
+    for (int q = 8; q <= 64; q *= 2) {
+        const int p = 128 / q;
+        const double u = ((double)out_w / (((out_w + q - 1) / q) * q)) * ((double)out_h / (((out_h + p - 1) / p) * p));
+        if (u > best + 1e-9) { best = u; bq = q; bp = p; }
+    }
+    return best;
+}
+
+// B200DP_CONV_ROWS=0 turns the row-grouped fprop / dgrad kernel off, B200DP_CONV_PAIR=0 the cta_group::2 one
+static bool conv_rows_enabled() {
+    static const bool on = [] { const char* e = getenv("B200DP_CONV_ROWS"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
 // B200DP_CONV_PAIR=0 turns the cta_group::2 convolution off (A/B measurements)
 static bool conv_pair_enabled() {
     static const bool on = [] { const char* e = getenv("B200DP_CONV_PAIR"); return !(e && e[0] == '0'); }();
@@ -982,6 +1321,35 @@ static int conv2d_impl(int mode, const void* x, const void* w, void* y, const fl
     int src_h, src_w;
     if (mode == 0) { g.out_h = P; g.out_w = Q; g.stride = stride; g.off_h = -pad; g.off_w = -pad; g.tap_sign = 1; src_h = H; src_w = W; }
     else           { g.out_h = H; g.out_w = W; g.stride = 1; g.off_h = pad; g.off_w = pad; g.tap_sign = -1; src_h = P; src_w = Q; }
+    if (R == 3 && S == 3 && stride == 1 && c_out < 256 && conv_rows_enabled()) {
+        // shallow 3x3 layers: row-grouped kernel (one haloed activation patch feeds the three filter rows)
+        int rq, rp;
+        if (pick_rows_box(g.out_h, g.out_w, rq, rp) >= 0.75) {
+            g.bq = rq; g.bp = rp; g.bn = 1;
+            g.tiles_q = (g.out_w + g.bq - 1) / g.bq;
+            g.tiles_p = (g.out_h + g.bp - 1) / g.bp;
+            g.tiles_n = N;
+            const int BNr = c_out <= 64 ? 64 : 128;
+            const int a_patch_bytes = (g.bp + 2) * g.bq * 128;
+            CUtensorMap ta, tb;
+            int rc = make_act_map(&ta, x, is_bf16, N, src_h, src_w, c_red, g.bq, g.bp + 2, 1, 1);
+            if (rc) return rc;
+            rc = mode == 0 ? make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, kBK, BNr)
+                           : make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, 64, kBK);
+            if (rc) return rc;
+            cudaStream_t rs = (cudaStream_t)stream;
+#define GR(BNv, MN, T, ST) return launch_rows<BNv, MN, T, ST>(ta, tb, y, bias, g, is_bf16, rs, colstats, a_patch_bytes)
+#define GR_T(BNv, MN, ST) if (is_bf16) { GR(BNv, MN, __nv_bfloat16, ST); } else { GR(BNv, MN, __half, ST); }
+#define GR_MODE(BNv)                                                 \
+    if (mode == 0 && colstats != nullptr) { GR_T(BNv, false, true) }  \
+    else if (mode == 0) { GR_T(BNv, false, false) }                   \
+    else { GR_T(BNv, true, false) }
+            if (BNr == 128) { GR_MODE(128) } else { GR_MODE(64) }
+#undef GR_MODE
+#undef GR_T
+#undef GR
+        }
+    }
     pick_box(N, g.out_h, g.out_w, g.stride, g.bq, g.bp, g.bn);
     g.tiles_q = (g.out_w + g.bq - 1) / g.bq;
     g.tiles_p = (g.out_h + g.bp - 1) / g.bp;
