@@ -189,9 +189,12 @@ def main() -> None:
     n_pool = 2
     host = [(torch.randn((B, *cfg["shape"]), generator=g), torch.randint(0, cfg["classes"], (B,), generator=g))
             for _ in range(n_pool)]
-    if is_cuda:
-        host = [(x.pin_memory(), y.pin_memory()) for x, y in host]
     cl = is_cuda and cfg["model"].startswith("resnet")
+    if is_cuda:
+        from pytorch_distributedtraining_b200.data import pin_channels_last
+        # pinned host batches; for the CNNs stored NHWC on the host (decoded-image order), so the H2D copy
+        # lands in the channels-last layout directly
+        host = [((pin_channels_last(x) if cl else x.pin_memory()), y.pin_memory()) for x, y in host]
 
     def to_dev(x, y):
         x = x.to(device, non_blocking=True)
@@ -250,11 +253,26 @@ def main() -> None:
             for i in range(n):
                 yield host[i % n_pool]
 
+        loss_host = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        loss_evt = [torch.cuda.Event() for _ in range(2)]
+
         def run_e2e(n):
-            last = 0.0
-            for x, y in DevicePrefetcher(host_batches(n * accum), device, channels_last=cl):
+            # every step's loss is copied device -> pinned host and READ on the host; the read of step i happens
+            # after step i+1 has been enqueued (what a training loop that logs its loss does), so the GPU never
+            # idles on the host round trip
+            last, pending = 0.0, None
+            for i, (x, y) in enumerate(DevicePrefetcher(host_batches(n * accum), device, channels_last=cl)):
                 loss = step(x, y)
-                last = float(loss.detach().float().item())      # D2H read of the step result
+                slot = i & 1
+                loss_host[slot].copy_(loss.detach().float(), non_blocking=True)      # D2H of this step's result
+                loss_evt[slot].record()
+                if pending is not None:
+                    loss_evt[pending].synchronize()
+                    last = float(loss_host[pending])
+                pending = slot
+            if pending is not None:
+                loss_evt[pending].synchronize()
+                last = float(loss_host[pending])
             return last
 
         run_e2e(2)

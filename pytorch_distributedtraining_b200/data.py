@@ -26,7 +26,7 @@ import torch
 from torch.utils.data import DataLoader, Dataset, Sampler
 from torch.utils.data.distributed import DistributedSampler as _TorchDistributedSampler
 
-__all__ = ["StokeDataLoader", "DevicePrefetcher", "DistributedSampler", "BucketedDistributedSampler", "SyntheticImageDataset",
+__all__ = ["StokeDataLoader", "DevicePrefetcher", "pin_channels_last", "DistributedSampler", "BucketedDistributedSampler", "SyntheticImageDataset",
            "SyntheticPairedDataset", "PairedImageDataset", "CustomDataset", "to_device"]
 
 
@@ -44,6 +44,17 @@ def to_device(batch: Any, device: torch.device, non_blocking: bool = True, chann
     if isinstance(batch, (list, tuple)):
         return type(batch)(to_device(v, device, non_blocking, channels_last) for v in batch)
     return batch
+
+
+def pin_channels_last(x: torch.Tensor) -> torch.Tensor:
+    """Pinned host copy of an NCHW-shaped batch stored NHWC (the order decoded images come in): the H2D copy
+    then lands directly in the channels-last layout the kernels read, with no permute pass on the device."""
+    if x.dim() != 4:
+        return x.pin_memory() if torch.cuda.is_available() else x
+    n, c, h, w = x.shape
+    buf = torch.empty((n, h, w, c), dtype=x.dtype, pin_memory=torch.cuda.is_available()).permute(0, 3, 1, 2)
+    buf.copy_(x)
+    return buf
 
 
 def _record_stream(batch: Any, stream: "torch.cuda.Stream") -> None:
