@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
 // A operand of filter row r is that same patch read from byte offset r * bq * 128 — a multiple of the
 // 1024-byte swizzle atom, so the UMMA descriptor just starts there.  Activation traffic drops ~2.5x.
 // Two rings: activation patches (kRowsAStages) and per-tap weight tiles (kRowsBStages).
-constexpr int kRowsAStages = 3;
+constexpr int kRowsMaxAStages = 8;     // activation patches in flight: as many as fit (host decides), at most 8
 constexpr int kRowsBStages = 8;
 constexpr int kRowsEpiBufBytes = 32 * 128;
 constexpr int kRowsEpiWarps = 8;
@@ -295,7 +295,7 @@ template <int BN> struct RCfg {
     static constexpr int kBBytes = BN * kBK * 2;                      // one tap's weight tile
     static constexpr int kBStages = BN == 128 ? 6 : kRowsBStages;
     // patch: up to (2 + 2) * 64 = 256 rows of 128 B; sized by the host per geometry (a_patch_bytes)
-    static int smem_bytes(int a_patch_bytes, int b_tiles) { return kRowsAStages * a_patch_bytes + b_tiles * kBBytes + kRowsEpiBytes + 1024 + 256; }
+    static int smem_bytes(int a_stages, int a_patch_bytes, int b_tiles) { return a_stages * a_patch_bytes + b_tiles * kBBytes + kRowsEpiBytes + 1024 + 512; }
 };
 
 template <int BN, bool kBMN, typename TOut, bool kStats = false>
@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
                                                                 const __grid_constant__ CUtensorMap tmB,
                                                                 TOut* __restrict__ out, const float* __restrict__ bias,
                                                                 Geom g, int is_bf16, float* __restrict__ colstats,
-                                                                int a_patch_bytes, int w_resident) {
+                                                                int a_patch_bytes, int w_resident, int a_stages) {
     using cfg = RCfg<BN>;
     // P partial accumulators per tile (k-step residue -> accumulator, summed by the epilogue) were tried against
     // the idea that back-to-back MMAs on one accumulator serialise: no measurable change (ncu: the tensor pipe
@@ -313,12 +313,12 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* smemA = smem;
-    uint8_t* smemB = smem + kRowsAStages * a_patch_bytes;
+    uint8_t* smemB = smem + a_stages * a_patch_bytes;
     uint8_t* smemC = smemB + (w_resident ? 9 * (g.c_red / kBK) : cfg::kBStages) * cfg::kBBytes;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smemC + kRowsEpiBytes);
     uint64_t* a_full = bars;
-    uint64_t* a_empty = a_full + kRowsAStages;
-    uint64_t* b_full = a_empty + kRowsAStages;
+    uint64_t* a_empty = a_full + kRowsMaxAStages;
+    uint64_t* b_full = a_empty + kRowsMaxAStages;
     uint64_t* b_empty = b_full + cfg::kBStages;
     uint64_t* tmem_full = b_empty + cfg::kBStages;
     uint64_t* tmem_empty = tmem_full + 2;
@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
 
     if (warp == 0 && lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
     if (warp == 1 && lane == 0) {
-        for (int i = 0; i < kRowsAStages; ++i) { mbar_init(a_full + i, 1); mbar_init(a_empty + i, 1); }
+        for (int i = 0; i < a_stages; ++i) { mbar_init(a_full + i, 1); mbar_init(a_empty + i, 1); }
         for (int i = 0; i < cfg::kBStages; ++i) { mbar_init(b_full + i, 1); mbar_init(b_empty + i, 1); }
         for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
         fence_barrier_init();
@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
                         mbar_expect_tx(a_full + sa, a_bytes);
                         tma_load_4d(smemA + sa * a_patch_bytes, &tmA, a_full + sa, c0, q0 + g.off_w + g.tap_sign * s,
                                     p0 + g.off_h + patch_dh, n0);
-                        if (++sa == kRowsAStages) { sa = 0; pa ^= 1; }
+                        if (++sa == a_stages) { sa = 0; pa ^= 1; }
                         for (int r = 0; r < 3 && !w_resident; ++r) {
                             const int tap = r * 3 + s;
                             mbar_wait(b_empty + sb, pb ^ 1);
@@ -444,7 +444,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
                         }
                     }
                     umma_commit(a_empty + sa);
-                    if (++sa == kRowsAStages) { sa = 0; pa ^= 1; }
+                    if (++sa == a_stages) { sa = 0; pa ^= 1; }
                 }
                 umma_commit(tmem_full + acc);
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -1258,11 +1258,17 @@ static int launch_rows(const CUtensorMap& ta, const CUtensorMap& tb, void* out, 
     }
     const int tiles = g.tiles_q * g.tiles_p * g.tiles_n * ((g.c_out + BN - 1) / BN);
     const int grid = tiles < B200DP_SMS ? tiles : B200DP_SMS;
-    // weights stay resident in shared memory when the whole filter of the (single) channel tile fits
+    // weights stay resident in shared memory when the whole filter of the (single) channel tile fits next to at
+    // least three activation patches; whatever shared memory is left goes to more patches in flight (the
+    // shallow layers are bound by the TMA round trip, not by bandwidth)
     const int chunks = g.c_red / kBK, all_tiles = 9 * chunks;
-    const int w_resident = (g.c_out <= BN && RCfg<BN>::smem_bytes(a_patch_bytes, all_tiles) <= 232448) ? 1 : 0;
-    const int smem = RCfg<BN>::smem_bytes(a_patch_bytes, w_resident ? all_tiles : RCfg<BN>::kBStages);
-    kern<<<grid, kRowsThreads, smem, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16, colstats, a_patch_bytes, w_resident);
+    const int w_resident = (g.c_out <= BN && RCfg<BN>::smem_bytes(3, a_patch_bytes, all_tiles) <= 232448) ? 1 : 0;
+    const int b_tiles = w_resident ? all_tiles : RCfg<BN>::kBStages;
+    int a_stages = (232448 - RCfg<BN>::smem_bytes(0, a_patch_bytes, b_tiles)) / a_patch_bytes;
+    if (a_stages > kRowsMaxAStages) a_stages = kRowsMaxAStages;
+    B200DP_REQUIRE(a_stages >= 2, "conv2d: activation patch of %d bytes does not fit twice in shared memory", a_patch_bytes);
+    const int smem = RCfg<BN>::smem_bytes(a_stages, a_patch_bytes, b_tiles);
+    kern<<<grid, kRowsThreads, smem, s>>>(ta, tb, (TOut*)out, bias, g, is_bf16, colstats, a_patch_bytes, w_resident, a_stages);
     B200DP_CHECK_LAUNCH();
     return 0;
 }

@@ -105,3 +105,57 @@ def test_example_scripts_run_offline(script, args, tmp_path):
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-3000:]
     if script == "stoke_ddp.py":
         assert os.path.isdir(tmp_path / "checkpoint") and any(f.endswith(".pt") for f in os.listdir(tmp_path / "checkpoint"))
+
+
+def test_conv_bn_pairing_and_carry_fallbacks_on_cpu():
+    """The kernel-path hooks must be inert off the GPU: pairing only sets a flag, forward_carry returns the
+    input itself, and a bottleneck block gives the same gradients as the textbook formulation."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from pytorch_distributedtraining_b200.models.resnet import Bottleneck
+    from pytorch_distributedtraining_b200.ops.layers import BatchNormAct2d, Conv2d, LayerNorm, Linear, pair_conv_bn
+    torch.manual_seed(0)
+    blk = Bottleneck(16, 4)
+    assert pair_conv_bn(blk) == 3 and blk.conv1.emit_bn_stats and blk.conv3.emit_bn_stats
+    x = torch.randn(2, 16, 8, 8, requires_grad=True)
+    y = blk(x)
+    y.square().mean().backward()
+    gx = x.grad.clone()
+    x.grad = None
+    out = blk.bn1(blk.conv1(x))
+    out = blk.bn2(blk.conv2(out))
+    ref = blk.bn3(blk.conv3(out), residual=x)
+    torch.testing.assert_close(y, ref)
+    ref.square().mean().backward()
+    torch.testing.assert_close(gx, x.grad)
+    c = Conv2d(4, 4, 1)
+    t = torch.randn(1, 4, 3, 3)
+    yc, same = c.forward_carry(t)
+    assert same is t and torch.equal(yc, c(t))
+    ln = LayerNorm(8)
+    u = torch.randn(3, 8)
+    yl, same = ln.forward_carry(u)
+    assert same is u and torch.equal(yl, ln(u))
+    lin = Linear(8, 8)
+    torch.testing.assert_close(lin(u, residual=u), F.linear(u, lin.weight, lin.bias) + u)
+
+
+def test_attention_layout_and_host_layout_helpers_on_cpu():
+    import torch.nn.functional as F
+    from pytorch_distributedtraining_b200.data import pin_channels_last
+    from pytorch_distributedtraining_b200.ops.attention import merge_heads, split_qkv
+    torch.manual_seed(1)
+    B, S, H, d = 2, 5, 3, 8
+    x = torch.randn(B, S, 3 * H * d, requires_grad=True)
+    q, k, v = split_qkv(x, H)
+    y = merge_heads(F.scaled_dot_product_attention(q, k, v))
+    y.square().sum().backward()
+    g1, x.grad = x.grad.clone(), None
+    qkv = x.view(B, S, 3, H, d).permute(2, 0, 3, 1, 4)
+    y2 = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2]).transpose(1, 2).reshape(B, S, H * d)
+    y2.square().sum().backward()
+    torch.testing.assert_close(y, y2)
+    torch.testing.assert_close(g1, x.grad)
+    img = torch.randn(2, 3, 4, 5)
+    p = pin_channels_last(img)
+    assert torch.equal(p, img) and p.is_contiguous(memory_format=torch.channels_last)
