@@ -144,6 +144,30 @@ class BucketedDistributedSampler(Sampler[int]):
         return iter([i for b in batches for i in b])
 
 
+class _ChannelsLastCollate:
+    """Collate, then store image batches NHWC on the host (picklable, so it works with worker processes).
+    ``pin_memory`` keeps the strides, so the H2D copy lands in the channels-last layout the kernels read and
+    the device never runs a permute pass over the input."""
+
+    def __init__(self, base: Any = None):
+        from torch.utils.data import default_collate
+        self.base = base if base is not None else default_collate
+
+    def _fix(self, b: Any) -> Any:
+        if isinstance(b, torch.Tensor):
+            return b.contiguous(memory_format=torch.channels_last) if b.dim() == 4 and b.is_floating_point() else b
+        if isinstance(b, dict):
+            return {k: self._fix(v) for k, v in b.items()}
+        if isinstance(b, tuple) and hasattr(b, "_fields"):
+            return type(b)(*(self._fix(v) for v in b))
+        if isinstance(b, (list, tuple)):
+            return type(b)(self._fix(v) for v in b)
+        return b
+
+    def __call__(self, samples: Any) -> Any:
+        return self._fix(self.base(samples))
+
+
 class StokeDataLoader(DataLoader):
     """``DataLoader`` that forces the facade's per-device batch size and yields batches
     already resident on the training device."""
@@ -159,6 +183,8 @@ class StokeDataLoader(DataLoader):
                 "rank reads a disjoint slice of the dataset")
         if gpu:
             kwargs.setdefault("pin_memory", True)
+        if channels_last and kwargs.get("batch_sampler") is None:
+            kwargs["collate_fn"] = _ChannelsLastCollate(kwargs.get("collate_fn"))
         if kwargs.get("num_workers", 0) == 0:
             kwargs.pop("multiprocessing_context", None)
             kwargs.pop("prefetch_factor", None)

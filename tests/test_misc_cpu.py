@@ -159,3 +159,12 @@ def test_attention_layout_and_host_layout_helpers_on_cpu():
     img = torch.randn(2, 3, 4, 5)
     p = pin_channels_last(img)
     assert torch.equal(p, img) and p.is_contiguous(memory_format=torch.channels_last)
+
+
+def test_dataloader_collates_channels_last_on_the_host():
+    from pytorch_distributedtraining_b200.data import StokeDataLoader, SyntheticImageDataset
+    ds = SyntheticImageDataset(16, shape=(3, 8, 8), num_classes=4)
+    plain = next(iter(StokeDataLoader(ds, batch_size=4)))
+    cl = next(iter(StokeDataLoader(ds, batch_size=4, channels_last=True)))
+    assert torch.equal(plain[0], cl[0]) and torch.equal(plain[1], cl[1])
+    assert cl[0].is_contiguous(memory_format=torch.channels_last) and not plain[0].is_contiguous(memory_format=torch.channels_last)
