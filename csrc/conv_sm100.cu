@@ -36,6 +36,12 @@ struct Geom {
     int bq, bp, bn;               // tile box (pixels): bq*bp*bn <= 128
     int tiles_q, tiles_p, tiles_n;
     int w_taps_ld;                // R*S*Cin: row pitch of the weight matrix view (elements)
+    // Strided input gradient, one launch per output parity class (conv_fd_kernel only): ntaps > 0 selects an
+    // explicit tap list — weight tap index and the (unit-stride) dY offset it reads — and the pass writes
+    // pixel (p * out_mul + out_off_h, q * out_mul + out_off_w) of a full_h x full_w image.
+    int ntaps;
+    int out_mul, out_off_h, out_off_w, full_h, full_w;
+    signed char tap_id[16], tap_dh[16], tap_dw[16];
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2,
@@ -82,7 +88,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
     const int num_n = (g.c_out + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
     const int chunks = g.c_red / kBK;
-    const int num_kb = g.R * g.S * chunks;
+    const int num_kb = (g.ntaps > 0 ? g.ntaps : g.R * g.S) * chunks;
     const int rows_valid = g.bq * g.bp * g.bn;
     const uint32_t a_bytes = (uint32_t)rows_valid * 128u;
 
@@ -117,12 +123,21 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
                 decode_m(tile % num_m, n0, p0, q0);
                 const int nt0 = (tile / num_m) * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    const int tap = kb / chunks, c0 = (kb % chunks) * kBK;
-                    const int r = tap / g.S, s = tap % g.S;
+                    const int t = kb / chunks, c0 = (kb % chunks) * kBK;
+                    int tap, cw, chh;
+                    if (g.ntaps > 0) {                  // parity class of a strided dgrad: explicit tap list
+                        tap = g.tap_id[t];
+                        cw = q0 + g.tap_dw[t];
+                        chh = p0 + g.tap_dh[t];
+                    } else {
+                        tap = t;
+                        const int r = tap / g.S, s = tap % g.S;
+                        cw = q0 * g.stride + g.off_w + g.tap_sign * s;
+                        chh = p0 * g.stride + g.off_h + g.tap_sign * r;
+                    }
                     mbar_wait(empty + stage, phase ^ 1);
                     mbar_expect_tx(full + stage, a_bytes + cfg::kBBytes);
-                    tma_load_4d(smemA + stage * cfg::kABytes, &tmA, full + stage, c0,
-                                q0 * g.stride + g.off_w + g.tap_sign * s, p0 * g.stride + g.off_h + g.tap_sign * r, n0);
+                    tma_load_4d(smemA + stage * cfg::kABytes, &tmA, full + stage, c0, cw, chh, n0);
                     uint8_t* b = smemB + stage * cfg::kBBytes;
                     if (kBMN) {
 #pragma unroll
@@ -203,7 +218,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_fd_kernel(const __grid_const
             const int bq_i = t % g.bq, bp_i = (t / g.bq) % g.bp, bn_i = t / (g.bq * g.bp);
             const int n = n0 + bn_i, p = p0 + bp_i, q = q0 + bq_i;
             const bool valid = t < rows_valid && n < g.n_img && p < g.out_h && q < g.out_w;
-            const long long pix = valid ? (((long long)n * g.out_h + p) * g.out_w + q) : -1;
+            const long long pix = valid ? (((long long)n * g.full_h + p * g.out_mul + g.out_off_h) * g.full_w + q * g.out_mul + g.out_off_w) : -1;
             auto do_chunk = [&](const int ch) {
                 __syncwarp();
 #pragma unroll
@@ -1314,7 +1329,8 @@ static int conv2d_impl(int mode, const void* x, const void* w, void* y, const fl
                        int Cout, int R, int S, int stride, int pad, b200dp_dtype dtype, float* colstats, void* stream) {
     B200DP_REQUIRE(x && w && y, "conv2d: null argument");
     B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "conv2d: fp16 / bf16 only");
-    B200DP_REQUIRE(mode == 0 || (mode == 1 && stride == 1), "conv2d: dgrad is implemented for stride 1");
+    B200DP_REQUIRE(mode == 0 || mode == 1, "conv2d: mode 0 (forward) or 1 (input gradient)");
+    B200DP_REQUIRE(mode == 0 || stride == 1 || (R <= 7 && S <= 7), "conv2d: strided dgrad supports filters up to 7 x 7");
     B200DP_REQUIRE(stride >= 1 && stride <= 2 && R >= 1 && S >= 1, "conv2d: unsupported stride / filter");
     const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
     const int c_red = mode == 0 ? Cin : Cout, c_out = mode == 0 ? Cout : Cin;
@@ -1322,11 +1338,65 @@ static int conv2d_impl(int mode, const void* x, const void* w, void* y, const fl
     B200DP_REQUIRE(c_out % 8 == 0, "conv2d: the output channel count (%d) must be a multiple of 8", c_out);
     bind_context_once();
     const int is_bf16 = dtype == B200DP_BF16;
-    Geom g;
+    Geom g{};
     g.n_img = N; g.R = R; g.S = S; g.c_out = c_out; g.c_red = c_red; g.w_taps_ld = R * S * Cin;
+    g.ntaps = 0; g.out_mul = 1; g.out_off_h = 0; g.out_off_w = 0;
     int src_h, src_w;
     if (mode == 0) { g.out_h = P; g.out_w = Q; g.stride = stride; g.off_h = -pad; g.off_w = -pad; g.tap_sign = 1; src_h = H; src_w = W; }
     else           { g.out_h = H; g.out_w = W; g.stride = 1; g.off_h = pad; g.off_w = pad; g.tap_sign = -1; src_h = P; src_w = Q; }
+    g.full_h = g.out_h; g.full_w = g.out_w;
+    if (mode == 1 && stride == 2) {
+        // Strided input gradient = four stride-1 problems, one per parity class (ph, pw) of the input pixel:
+        //   dX[n, 2a+ph, 2b+pw] = sum over taps (r, s) with (ph+pad-r), (pw+pad-s) even of
+        //                         dY[n, a + (ph+pad-r)/2, b + (pw+pad-s)/2] * W[:, r, s, :]
+        // Each class runs the dgrad kernel over dY with its own tap list and writes every second pixel.
+        CUtensorMap tb;
+        int rc = make_mat_map(&tb, w, is_bf16, Cout, (int64_t)R * S * Cin, (int64_t)R * S * Cin, 64, kBK);
+        if (rc) return rc;
+        cudaStream_t cs = (cudaStream_t)stream;
+        const int BNc = c_out <= 64 ? 64 : (c_out >= 256 ? 256 : 128);
+        const int esz = 2;
+        int nonempty = 0;
+        for (int ph = 0; ph < 2; ++ph)
+            for (int pw = 0; pw < 2; ++pw) {
+                int cnt = 0;
+                for (int r = 0; r < R; ++r) for (int q = 0; q < S; ++q)
+                    if (((ph + pad - r) & 1) == 0 && ((pw + pad - q) & 1) == 0) ++cnt;
+                if (cnt > 0 && (H - ph + 1) / 2 > 0 && (W - pw + 1) / 2 > 0) ++nonempty;
+            }
+        if (nonempty < 4) B200DP_CUDA(cudaMemsetAsync(y, 0, (size_t)N * H * W * Cin * esz, cs));
+        for (int ph = 0; ph < 2; ++ph)
+            for (int pw = 0; pw < 2; ++pw) {
+                Geom gc = g;
+                gc.stride = 1; gc.out_mul = 2; gc.out_off_h = ph; gc.out_off_w = pw; gc.full_h = H; gc.full_w = W;
+                gc.out_h = (H - ph + 1) / 2; gc.out_w = (W - pw + 1) / 2;
+                gc.ntaps = 0;
+                for (int r = 0; r < R; ++r)
+                    for (int q = 0; q < S; ++q) {
+                        const int eh = ph + pad - r, ew = pw + pad - q;
+                        if ((eh & 1) || (ew & 1)) continue;
+                        gc.tap_id[gc.ntaps] = (signed char)(r * S + q);
+                        gc.tap_dh[gc.ntaps] = (signed char)(eh / 2);
+                        gc.tap_dw[gc.ntaps] = (signed char)(ew / 2);
+                        ++gc.ntaps;
+                    }
+                if (gc.ntaps == 0 || gc.out_h <= 0 || gc.out_w <= 0) continue;
+                pick_box(N, gc.out_h, gc.out_w, 1, gc.bq, gc.bp, gc.bn);
+                gc.tiles_q = (gc.out_w + gc.bq - 1) / gc.bq;
+                gc.tiles_p = (gc.out_h + gc.bp - 1) / gc.bp;
+                gc.tiles_n = (N + gc.bn - 1) / gc.bn;
+                CUtensorMap ta;
+                rc = make_act_map(&ta, x, is_bf16, N, P, Q, c_red, gc.bq, gc.bp, gc.bn, 1);
+                if (rc) return rc;
+#define GC(BNv)                                                                                          \
+    { rc = is_bf16 ? launch_fd<BNv, true, __nv_bfloat16>(ta, tb, y, nullptr, gc, 1, cs)                    \
+                   : launch_fd<BNv, true, __half>(ta, tb, y, nullptr, gc, 0, cs); }
+                if (BNc == 256) GC(256) else if (BNc == 128) GC(128) else GC(64)
+#undef GC
+                if (rc) return rc;
+            }
+        return 0;
+    }
     if (R == 3 && S == 3 && stride == 1 && c_out < 256 && conv_rows_enabled()) {
         // shallow 3x3 layers: row-grouped kernel (one haloed activation patch feeds the three filter rows)
         int rq, rp;

@@ -8,8 +8,9 @@ On channels-last 16-bit activations:
     the shifted / strided pixel boxes directly from the NHWC tensor, zero-filling the padding);
   * weight gradients of all of these run on the wgrad kernel of the same file (both operands
     MN-major by 4-D TMA, pixels as the reduction, split-K with TMA reduce-add into fp32);
-  * what is not covered yet stays on cuDNN and is listed in DESIGN.md: input gradients of strided
-    convolutions and first-layer convolutions (Cin = 3).
+  * the input gradient of a stride-2 convolution is four stride-1 problems, one per parity class of the
+    input pixel, each with its own tap list, run on the same dgrad kernel;
+  * what is not covered stays on cuDNN and is listed in DESIGN.md: first-layer convolutions (Cin = 3).
 
 ``dispatch.conv_supported`` is the single place that decides.
 Parity target: the convolutions inside the CNN models (Fairscale-DDP.py:74; BASELINE ResNets).
@@ -144,14 +145,14 @@ class _ConvFn(torch.autograd.Function):
                 else:
                     dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
         else:
-            ours_dx = need_dx and stride == 1 and cout % 64 == 0 and cin % 8 == 0
+            ours_dx = need_dx and stride in (1, 2) and cout % 64 == 0 and cin % 8 == 0
             if need_dw:
                 dw = conv2d_wgrad_raw(x, dy, n, h, w, cin, cout, r, s, stride, pad)
             if ours_dx:
-                dx = conv2d_raw(1, dy, w16, None, n, h, w, cin, cout, r, s, 1, pad)
+                dx = conv2d_raw(1, dy, w16, None, n, h, w, cin, cout, r, s, stride, pad)
             if need_dx and not ours_dx:
-                # library path for what the implicit-GEMM kernels do not cover yet: the input
-                # gradient of strided convolutions
+                # library path for what the implicit-GEMM kernels do not cover: input gradients
+                # whose reduction width (Cout) is not a multiple of 64
                 dx = torch.ops.aten.convolution_backward(dy, x, w16, None, (stride, stride), (pad, pad), (1, 1), False,
                                                          (0, 0), 1, (True, False, False))[0]
         if d_carry is not None:

@@ -240,3 +240,24 @@ def test_conv_cta_pair_kernel(dtype, N, H, W, Cin, Cout, R, stride, pad):
         got_dx = conv2d_raw(1, dy, w, None, N, H, W, Cin, Cout, R, R, 1, pad)
         torch.cuda.synchronize()
         torch.testing.assert_close(got_dx.float(), want_dx, rtol=tol, atol=tol * (Cout * R * R) ** 0.5 * 0.05)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,pad", [
+    (2, 56, 56, 128, 128, 3, 1),
+    (2, 56, 56, 256, 512, 1, 0),        # downsample 1x1: three of the four parity classes are empty (zero-filled)
+    (3, 15, 17, 64, 128, 3, 1),         # odd sizes: the classes have different extents
+    (2, 28, 28, 256, 256, 3, 1),
+    (1, 16, 16, 64, 64, 5, 2),
+])
+def test_conv_strided_dgrad_by_parity_classes(dtype, N, H, W, Cin, Cout, R, pad):
+    from pytorch_distributedtraining_b200.ops.conv import conv2d_raw
+    g = torch.Generator().manual_seed(N * 5 + H)
+    P, Q = (H + 2 * pad - R) // 2 + 1, (W + 2 * pad - R) // 2 + 1
+    dy = (torch.randn(N, Cout, P, Q, generator=g) * 0.5).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(Cout, Cin, R, R, generator=g) * 0.1).to(dtype).to(cuda).contiguous(memory_format=torch.channels_last)
+    want = torch.nn.grad.conv2d_input((N, Cin, H, W), w.float(), dy.float(), stride=2, padding=pad)
+    got = conv2d_raw(1, dy, w, None, N, H, W, Cin, Cout, R, R, 2, pad)
+    torch.cuda.synchronize()
+    tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
+    torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * (Cout * R * R) ** 0.5 * 0.05)
