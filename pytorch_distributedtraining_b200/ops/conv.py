@@ -145,7 +145,8 @@ class _ConvFn(torch.autograd.Function):
                 else:
                     dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
         else:
-            ours_dx = need_dx and stride in (1, 2) and cout % 64 == 0 and cin % 8 == 0
+            from . import dispatch
+            ours_dx = need_dx and (stride == 1 or (stride == 2 and dispatch.enabled("dgrad_s2"))) and cout % 64 == 0 and cin % 8 == 0
             if need_dw:
                 dw = conv2d_wgrad_raw(x, dy, n, h, w, cin, cout, r, s, stride, pad)
             if ours_dx:
