@@ -190,7 +190,9 @@ class _LayerNormFn(torch.autograd.Function):
                                            ptr(ws.counters), ptr(dparams[D:]), ptr(dparams[:D]), ptr(add_in),
                                            stream_ptr(x2.device)),
               "layernorm_bwd", launches=2)
-        return dx.view(ctx.shape), dparams[D:].to(weight.dtype), dparams[:D].to(weight.dtype), None, None
+        if dparams.dtype != weight.dtype:
+            dparams = dparams.to(weight.dtype)          # one cast for both parameter gradients
+        return dx.view(ctx.shape), dparams[D:], dparams[:D], None, None
 
 
 def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float, carry: bool = False):
