@@ -144,6 +144,10 @@ class _LayerNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, eps, carry=False):  # type: ignore[override]
         lib = require_library()
+        # parameters arrive in their own dtype (bf16 under FSDP mixed precision); the kernels read fp32.  Casting
+        # here instead of in the caller keeps autograd from adding one cast-backward kernel per parameter.
+        ctx.p_dtype = weight.dtype
+        weight, bias = weight.float(), bias.float()
         shape = x.shape
         D = shape[-1]
         x2 = x.reshape(-1, D)
@@ -190,11 +194,11 @@ class _LayerNormFn(torch.autograd.Function):
                                            ptr(ws.counters), ptr(dparams[D:]), ptr(dparams[:D]), ptr(add_in),
                                            stream_ptr(x2.device)),
               "layernorm_bwd", launches=2)
-        if dparams.dtype != weight.dtype:
-            dparams = dparams.to(weight.dtype)          # one cast for both parameter gradients
+        if dparams.dtype != ctx.p_dtype:
+            dparams = dparams.to(ctx.p_dtype)           # one cast for both parameter gradients
         return dx.view(ctx.shape), dparams[D:], dparams[:D], None, None
 
 
 def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float, carry: bool = False):
     """``carry=True`` returns ``(LN(x), x)``: use the second value as the residual that bypasses the block."""
-    return _LayerNormFn.apply(x, weight.float(), bias.float(), eps, carry)
+    return _LayerNormFn.apply(x, weight, bias, eps, carry)
