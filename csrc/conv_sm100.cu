@@ -320,11 +320,8 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
                                                                 Geom g, int is_bf16, float* __restrict__ colstats,
                                                                 int a_patch_bytes, int w_resident, int a_stages) {
     using cfg = RCfg<BN>;
-    // P partial accumulators per tile (k-step residue -> accumulator, summed by the epilogue) were tried against
-    // the idea that back-to-back MMAs on one accumulator serialise: no measurable change (ncu: the tensor pipe
-    // sits at ~22 % on the 64-channel layer because only three activation patches — one tile — can be in
-    // flight next to the resident filter, and a patch takes ~2 us to arrive).  Kept at 1.
-    constexpr int P = 1;
+    // (Splitting a tile's k-steps over several TMEM accumulators — in case back-to-back MMAs on one accumulator
+    // serialised — was tried and changed nothing; ncu shows the tensor pipe waiting on operands instead.)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* smemA = smem;
@@ -354,7 +351,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
         for (int i = 0; i < 2; ++i) { mbar_init(tmem_full + i, 1); mbar_init(tmem_empty + i, 4); }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_slot, 2 * P * BN);
+    if (warp == 2) tmem_alloc(tmem_slot, 2 * BN);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -429,7 +426,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 mbar_wait(tmem_empty + acc, acc_phase ^ 1);
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * (P * BN);
+                const uint32_t d_tmem = tmem_base + acc * BN;
                 bool first = true;
                 for (int grp = 0; grp < 3 * chunks; ++grp) {
                     mbar_wait(a_full + sa, pa);
@@ -450,7 +447,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
                             const uint64_t da = make_desc(a_addr + k * (kUmmaK * 2), 16, 1024);
                             const uint64_t db = kBMN ? make_desc(b_addr + k * (kUmmaK * 128), kBK * 128, 1024)
                                                      : make_desc(b_addr + k * (kUmmaK * 2), 16, 1024);
-                            umma_f16(d_tmem + (k % P) * BN, da, db, idesc, (first && k < P) ? 0u : 1u);
+                            umma_f16(d_tmem, da, db, idesc, (first && k == 0) ? 0u : 1u);
                         }
                         first = false;
                         if (!w_resident) {
@@ -516,18 +513,11 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
                 for (int l = 0; l < 2; ++l) {
                     uint32_t r[32];
                     const int colbase = ch * 64 + l * 32;
-                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (P * BN) + colbase, r);
+                    tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + colbase, r);
                     tmem_ld_wait();
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-#pragma unroll
-                    for (int pp = 1; pp < P; ++pp) {
-                        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (P * BN) + pp * BN + colbase, r);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] += __uint_as_float(r[j]);
-                    }
                     if (bias != nullptr) {
                         const int gcol = nt0 + colbase;
 #pragma unroll
@@ -587,7 +577,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1) conv_rows_kernel(const __grid
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) tmem_dealloc(tmem_base, 2 * P * BN);
+    if (warp == 2) tmem_dealloc(tmem_base, 2 * BN);
 }
 
 

@@ -195,8 +195,9 @@ int b200dp_maxpool_bwd(const void* dy, const unsigned char* idx, void* dx, int N
                        int pad, b200dp_dtype dtype, void* stream);
 
 /* LayerNorm over the last dimension, x[rows, D] (reference: SwinIR / ViT blocks,
- * Stoke-DDP.py:206-208).  mean/rstd are float[rows].  dgamma/dbeta are accumulated via
- * scratch of b200dp_ln_scratch_floats(rows, D) floats + one zeroed uint32. */
+ * Stoke-DDP.py:206-208).  mean/rstd are float[rows].  The backward is ONE pass over dy and x: dx plus
+ * one [dbeta | dgamma] partial per CTA in `scratch` (b200dp_ln_scratch_floats(rows, D) floats), summed
+ * in a fixed order by a second small kernel; `counter` is unused (kept for ABI stability). */
 int64_t b200dp_ln_scratch_floats(int64_t rows, int D);
 int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dtype dtype, const float* gamma,
                          const float* beta, float eps, float* mean, float* rstd, void* stream);
