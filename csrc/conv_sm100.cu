@@ -18,6 +18,18 @@
 //          both operands MN-major via 4-D TMA, K = pixels (exactly 64 per k-block), split over
 //          pixel tiles and combined with TMA reduce-add into the fp32 gradient
 //
+//          stride 2: four stride-1 problems, one per parity class of the input pixel, each with an
+//          explicit tap list (Geom::ntaps / tap_id / tap_dh / tap_dw) and a strided output mapping
+//
+// Kernels in this file:
+//   conv_fd_kernel          fprop / dgrad, one tap and one 64-channel chunk per k-block (any filter, stride 1/2)
+//   conv_rows_kernel        3x3 stride-1 fprop / dgrad for < 256 output channels: one haloed activation patch
+//                           feeds the three filter rows (patch ring + weight ring, or the filter resident)
+//   conv_fd_pair_kernel     fprop / dgrad for 256-channel tiles on a CTA pair (cta_group::2)
+//   conv_wgrad_kernel       weight gradient, one tap per work item
+//   conv_wgrad_rows_kernel  3x3 stride-1 weight gradient, three taps per work item from one dY box + one X patch
+// fprop kernels can also emit the per-channel sum / sum of squares of their output (kStats).
+//
 // Warp roles, pipeline and TMEM double buffering are those of gemm_sm100.cu.  The epilogue
 // stages 32 rows x 128 B per warp in swizzled smem and writes them out 4 rows per instruction
 // (8 lanes x 16 B per row) to the pixel's address, masking rows that fall outside the image.

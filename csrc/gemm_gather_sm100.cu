@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_gather_kernel(
 
     if (warp == 3) {
         // ===== gather engine =====
-        // W is fetched in chunks of kChunkRows rows; chunk j (in the order the weight tiles will be
+        // W is fetched in chunks of chunk_rows rows; chunk j (in the order the weight tiles will be
         // consumed, locally owned tiles first) is copied by the gather warp of CTA j mod grid, so all
         // ~148 gather warps pull in parallel (16 x 16 B in flight per lane) and every tile is complete
         // after a few microseconds; each finished chunk bumps its tile's counter.
