@@ -97,10 +97,11 @@ class _BatchNormActFn(torch.autograd.Function):
         check(lib.b200dp_bn_bwd_reduce(ptr(dy), None, ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(mean),
                                        ptr(invstd), relu, ptr(scratch), ptr(ws.counters), ptr(dsums), ptr(mask), st),
               "bn_bwd_reduce")
-        # parameter gradients are the LOCAL sums (the data-parallel engine averages them)
-        dbias = dsums[:C].clone()
-        dweight = dsums[C:].clone()
+        # parameter gradients are the LOCAL sums (the data-parallel engine averages them); they only need
+        # their own storage when the cross-rank exchange is about to overwrite dsums
+        dbias, dweight = dsums[:C], dsums[C:]
         if ctx.world > 1:
+            dbias, dweight = dbias.clone(), dweight.clone()
             _allreduce_stats(dsums, ctx.group)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res else None
