@@ -168,3 +168,27 @@ def test_dataloader_collates_channels_last_on_the_host():
     cl = next(iter(StokeDataLoader(ds, batch_size=4, channels_last=True)))
     assert torch.equal(plain[0], cl[0]) and torch.equal(plain[1], cl[1])
     assert cl[0].is_contiguous(memory_format=torch.channels_last) and not plain[0].is_contiguous(memory_format=torch.channels_last)
+
+
+def test_c_host_links_against_the_kernel_library(tmp_path):
+    """The kernel library is a plain C ABI: a C program compiles against include/b200dp.h, links the in-tree
+    .so and can plan (scratch sizes, envelopes) and get error text without Python, torch or a GPU."""
+    import os, shutil, subprocess
+    from pytorch_distributedtraining_b200.ops import _lib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    so = _lib.lib_path()
+    if not os.path.exists(so):
+        _lib.build_library()
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None or not os.path.isdir("/usr/local/cuda/lib64"):
+        import pytest
+        pytest.skip("no C compiler / CUDA runtime library on this box")
+    exe = str(tmp_path / "b200dp_host")
+    cmd = [cc, "-I", os.path.join(root, "include"), os.path.join(root, "examples", "c_host", "main.c"),
+           "-L", os.path.dirname(so), "-lb200dp", "-L", "/usr/local/cuda/lib64", "-lcudart",
+           "-Wl,-rpath," + os.path.dirname(so), "-Wl,-rpath,/usr/local/cuda/lib64", "-o", exe]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "b200dp version" in r.stdout and "bad arguments" in r.stdout
