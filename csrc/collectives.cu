@@ -128,6 +128,13 @@ struct Rank {
 // All threads of the CTA call this.  Orders everything the CTA wrote before the barrier
 // ahead of everything peers read after it, and vice versa.
 __device__ __forceinline__ void cta_barrier_all_ranks(const b200dp_peer_ctx& c, const Rank& me) {
+    if (c.skew_ns != 0 && threadIdx.x == 0) {
+        // stress mode (tests): shuffle the arrival order of ranks and CTAs at every barrier
+        uint32_t h = (uint32_t)me.rank * 2654435761u ^ blockIdx.x * 40503u ^ (c.epochs[me.rank][blockIdx.x] + 1u) * 2246822519u;
+        h ^= h >> 15; h *= 2654435761u; h ^= h >> 13;
+        const uint64_t wait = h % c.skew_ns, t0 = globaltimer_ns();
+        while (globaltimer_ns() - t0 < wait) __nanosleep(64);
+    }
     __syncthreads();
     __shared__ uint32_t s_epoch;
     if (threadIdx.x == 0) {

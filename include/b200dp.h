@@ -226,7 +226,8 @@ int b200dp_gemm(const void* A, const void* B, void* C, const float* bias, int M,
 
 /* Implicit-GEMM NHWC convolution on tcgen05, operands fetched by TMA straight from the
  * activation tensor (no im2col buffer).  mode 0: forward, y[N][P][Q][Cout] = conv(x[N][H][W][Cin], w);
- * mode 1: input gradient of a stride-1 convolution, y = dX[N][H][W][Cin] from x = dY[N][P][Q][Cout].
+ * mode 1: input gradient, y = dX[N][H][W][Cin] from x = dY[N][P][Q][Cout] (stride 2 runs as four stride-1
+ * problems, one per parity class of the input pixel).
  * w is [Cout][R][S][Cin] (channels-last weight), same 16-bit dtype as x.  The reduction-side channel
  * count must be a multiple of 64, the output-side one a multiple of 8; stride 1 or 2; square padding.
  * Reference: the convolutions of the CNN models (Fairscale-DDP.py:74), left to cuDNN there. */
@@ -264,6 +265,8 @@ typedef struct {
     uint32_t* epochs[B200DP_MAX_RANKS];  /* [max_blocks] per-CTA barrier counters (local entry used)      */
     uint32_t* status[B200DP_MAX_RANKS];  /* one word per rank: non-zero after a barrier timed out         */
     uint64_t timeout_ns; /* spin limit per barrier; 0 = wait forever                              */
+    uint64_t skew_ns;    /* stress knob, 0 in production: before every barrier each (rank, CTA) first
+                            idles a pseudo-random time below this, so arrival orders are shuffled  */
 } b200dp_peer_ctx;
 
 /* `rounds` barriers back to back (protocol self-test / latency probe). */

@@ -24,7 +24,8 @@ class PeerCtxStruct(ctypes.Structure):
     _fields_ = [("rank", ctypes.c_int), ("world", ctypes.c_int), ("emulate", ctypes.c_int),
                 ("max_blocks", ctypes.c_int),
                 ("flags", ctypes.c_void_p * MAX_RANKS), ("epochs", ctypes.c_void_p * MAX_RANKS),
-                ("status", ctypes.c_void_p * MAX_RANKS), ("timeout_ns", ctypes.c_uint64)]
+                ("status", ctypes.c_void_p * MAX_RANKS), ("timeout_ns", ctypes.c_uint64),
+                ("skew_ns", ctypes.c_uint64)]
 
 
 def table(ptrs: Optional[Sequence[Optional[int]]]) -> Optional[VoidPtrTable]:

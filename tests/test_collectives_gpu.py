@@ -323,3 +323,35 @@ def _w_facade_peer(rank, world, mode):
 def test_real_facade_peer_matches_nccl(mode):
     from pytorch_distributedtraining_b200.utils.testing import spawn
     spawn(_w_facade_peer, 2, (mode,), backend="nccl")
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_emulated_collectives_under_random_rank_skew(C, world):
+    """Flag-protocol stress (sanitizers do not see cross-rank races): with ctx.skew_ns set, every (rank, CTA)
+    idles a pseudo-random time before each barrier, so ranks arrive in a different order every round; results
+    must stay exact and no barrier may time out."""
+    em = C.EmulatedPeers(world, max_blocks=8)
+    em.ctx.c.skew_ns = 30_000
+    n = 8 * 1024 + 64
+    for it in range(6):
+        xs = _rand(world, n, torch.float32, seed=50 + it)
+        want = torch.stack(xs).sum(0) / world
+        for algo in (0, 1):
+            bufs = [x.clone() for x in xs]
+            em.ctx.allreduce(C.table(bufs), 0, n, torch.float32, pre_mult=1.0 / world, mult_dev=None, found_inf=None,
+                             algo=algo, blocks=8)
+            torch.cuda.synchronize()
+            for b in bufs:
+                torch.testing.assert_close(b, want, rtol=1e-5, atol=1e-6)
+                assert torch.equal(b, bufs[0])
+        n_per = 2048
+        ins = _rand(world, n_per * world, torch.bfloat16, seed=70 + it)
+        outs = [torch.zeros(n_per, device=cuda) for _ in range(world)]
+        em.ctx.reduce_scatter(C.table(ins), 0, n_per, torch.bfloat16, C.table(outs), pre_mult=1.0, accumulate=False, blocks=8)
+        torch.cuda.synchronize()
+        total = torch.stack([x.float() for x in ins]).sum(0)
+        for r in range(world):
+            torch.testing.assert_close(outs[r], total[r * n_per:(r + 1) * n_per], rtol=2e-2, atol=2e-2)
+    em.ctx.barrier(blocks=8, rounds=200)
+    torch.cuda.synchronize()
+    assert not em.timed_out()
