@@ -205,6 +205,11 @@ class B200Config:
     channels_last     run convolutional models in NHWC.
     loss_sync_every   how often ``detach_and_sync_loss`` drains to the host
                       (1 keeps the reference's per-batch ``.item()`` semantics).
+    watchdog_timeout_s  spin limit of the in-kernel cross-rank barriers (a stuck peer raises a
+                      status word instead of hanging the GPU).
+    step_watchdog_s   host-side hang guard: if no optimizer step finishes for this many seconds
+                      every thread's stack is dumped and, with ``step_watchdog_abort``, the process
+                      exits non-zero so the launcher tears the job down (0 = off).
     """
 
     fused_kernels: bool = True
@@ -213,6 +218,8 @@ class B200Config:
     channels_last: bool = True
     loss_sync_every: int = 1
     watchdog_timeout_s: float = 120.0
+    step_watchdog_s: float = 0.0
+    step_watchdog_abort: bool = False
 
 
 ALL_CONFIG_TYPES = (

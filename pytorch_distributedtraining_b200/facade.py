@@ -97,6 +97,11 @@ class Stoke:
         # counters (checkpointed)
         self._backward_steps = 0
         self._optimizer_steps = 0
+        # host-side hang guard (utils.watchdog): beats once per train_step / optimizer step
+        self._watchdog = None
+        if self._b200.step_watchdog_s > 0:
+            from .utils.watchdog import StepWatchdog
+            self._watchdog = StepWatchdog(self._b200.step_watchdog_s, abort=self._b200.step_watchdog_abort)
         self._grad_accum_counter = 0
         # loss tracking, device scalars
         self._last_step_loss: Any = None
@@ -391,6 +396,8 @@ class Stoke:
         self._grad_accum_counter = 0
         self._agg_fresh = True          # the next training loss restarts the accumulation window
         self._optimizer_steps += 1
+        if self._watchdog is not None:
+            self._watchdog.beat()
 
     # ------------------------------------------------------------------ fused train step (+ CUDA graph)
     def train_step(self, inputs: Any, targets: Any) -> Any:
@@ -407,6 +414,8 @@ class Stoke:
         ``reset_graphs()``.  Inputs are copied into static buffers before each replay.
         """
         args = inputs if isinstance(inputs, (tuple, list)) else (inputs,)
+        if self._watchdog is not None:
+            self._watchdog.beat()
         if not (self._b200.cuda_graph and self._status.gpu and self._unwrapped.training):
             return self._eager_step(args, targets)
         return self._graphed_step(args, targets)
@@ -690,6 +699,12 @@ class Stoke:
     @property
     def optimizer_steps(self) -> int:
         return self._optimizer_steps
+
+    @property
+    def watchdog(self) -> Any:
+        """The host-side ``StepWatchdog`` (``B200Config.step_watchdog_s > 0``) or None; ``pause()`` it around
+        legitimately long phases (evaluation, checkpoint upload)."""
+        return self._watchdog
 
     @property
     def gpu(self) -> bool:

@@ -192,3 +192,37 @@ def test_c_host_links_against_the_kernel_library(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "b200dp version" in r.stdout and "bad arguments" in r.stdout
+
+
+def test_step_watchdog_fires_only_when_steps_stop():
+    import io, time
+    from pytorch_distributedtraining_b200.utils.watchdog import StepWatchdog
+    hits, log = [], io.StringIO()
+    with StepWatchdog(0.4, on_timeout=hits.append, stream=log) as wd:
+        for _ in range(8):                      # steady progress: never fires
+            time.sleep(0.1)
+            wd.beat()
+        assert wd.fired == 0 and wd.beats == 8
+        wd.pause()
+        time.sleep(0.7)                         # paused (e.g. checkpointing): silent
+        assert wd.fired == 0
+        wd.resume()
+        time.sleep(0.9)                         # stuck: fires, dumps stacks, calls back
+        assert wd.fired >= 1 and hits and hits[0] >= 0.4
+    assert "no training step finished" in log.getvalue() and "Thread" in log.getvalue()
+
+
+def test_facade_starts_the_step_watchdog_on_request():
+    import torch.nn as nn
+    from pytorch_distributedtraining_b200 import B200Config, Stoke, StokeOptimizer
+    model = nn.Linear(4, 2)
+    s = Stoke(model=model, verbose=False, optimizer=StokeOptimizer(optimizer=torch.optim.SGD, optimizer_kwargs={"lr": 0.1}),
+              loss=nn.MSELoss(), batch_size_per_device=2, gpu=False, configs=[B200Config(step_watchdog_s=30.0)])
+    assert s.watchdog is not None and s.watchdog.beats == 0
+    x, y = torch.randn(2, 4), torch.randn(2, 2)
+    s.train_step(x, y)
+    assert s.watchdog.beats >= 1
+    s.watchdog.close()
+    s2 = Stoke(model=nn.Linear(4, 2), verbose=False, optimizer=StokeOptimizer(optimizer=torch.optim.SGD, optimizer_kwargs={"lr": 0.1}),
+               loss=nn.MSELoss(), batch_size_per_device=2, gpu=False)
+    assert s2.watchdog is None
