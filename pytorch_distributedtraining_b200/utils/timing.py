@@ -105,3 +105,42 @@ class ClockSampler:
             "reasons": sorted(reasons),
             "samples": len(sm),
         }
+
+
+def exposed_comm_ms(engine: Any, fwd_bwd: Any, iters: int = 10, warmup: int = 3) -> Dict[str, float]:
+    """Communication that is NOT hidden behind compute, in ms per forward+backward.
+
+    ``engine`` is a data-parallel wrapper with ``no_sync()`` (DDP, ShardedDDP, FSDP), ``fwd_bwd()`` runs one
+    forward + backward through it (and should clear the gradients itself if it wants to).  The same work is
+    timed with gradient synchronisation on and, under ``no_sync()``, off; the difference is what the collectives
+    add to the critical path.  Device-timed with CUDA events on a GPU, wall-clock on the CPU; max over ranks.
+    """
+    cuda = torch.cuda.is_available() and any(p.is_cuda for p in engine.parameters())
+    dev = next((p.device for p in engine.parameters()), torch.device("cpu"))
+
+    def timed(n: int) -> float:
+        if cuda:
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                fwd_bwd()
+            e1.record()
+            e1.synchronize()
+            return e0.elapsed_time(e1) / n
+        t0 = time.perf_counter()
+        for _ in range(n):
+            fwd_bwd()
+        return (time.perf_counter() - t0) * 1e3 / n
+
+    for _ in range(warmup):
+        fwd_bwd()
+    sync_ms = timed(iters)
+    with engine.no_sync():
+        for _ in range(max(1, warmup // 2)):
+            fwd_bwd()
+        nosync_ms = timed(iters)
+    fwd_bwd()          # one synchronising pass so replicas leave with reduced gradients again
+    sync_ms = max_over_ranks(sync_ms, dev if cuda else None)
+    nosync_ms = max_over_ranks(nosync_ms, dev if cuda else None)
+    return {"sync_ms": sync_ms, "no_sync_ms": nosync_ms, "exposed_comm_ms": max(sync_ms - nosync_ms, 0.0)}

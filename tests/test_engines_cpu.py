@@ -301,3 +301,30 @@ def _w_scaler(rank, world):
 
 def test_sharded_grad_scaler_skips_on_any_rank_inf():
     spawn(_w_scaler, 2)
+
+
+def _w_exposed_comm(rank, world):
+    import torch.nn as nn
+    from pytorch_distributedtraining_b200.parallel.ddp import DistributedDataParallel
+    from pytorch_distributedtraining_b200.utils.timing import exposed_comm_ms
+    torch.manual_seed(0)
+    model = DistributedDataParallel(nn.Sequential(nn.Linear(64, 64), nn.ReLU(), nn.Linear(64, 8)))
+    x = torch.randn(16, 64)
+
+    def fwd_bwd():
+        model.zero_grad(set_to_none=True)
+        model(x).square().mean().backward()
+
+    r = exposed_comm_ms(model, fwd_bwd, iters=3, warmup=2)
+    assert set(r) == {"sync_ms", "no_sync_ms", "exposed_comm_ms"}
+    assert r["sync_ms"] > 0 and r["no_sync_ms"] > 0 and r["exposed_comm_ms"] >= 0
+    # the helper must leave the replicas synchronised: gradients equal on every rank
+    g = torch.cat([p.grad.flatten() for p in model.parameters()])
+    ref = g.clone()
+    torch.distributed.broadcast(ref, src=0)
+    assert torch.allclose(g, ref)
+
+
+def test_exposed_comm_helper_runs_under_gloo():
+    from pytorch_distributedtraining_b200.utils.testing import spawn
+    spawn(_w_exposed_comm, 2)
