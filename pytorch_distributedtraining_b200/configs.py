@@ -16,7 +16,7 @@ distinct type with no inheritance between the siblings.
 from __future__ import annotations
 
 import dataclasses
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from enum import Enum
 from typing import Any, Dict, List, Optional, Type, TypedDict
 

@@ -14,7 +14,7 @@ the same modules fall back to stock torch ops, which is what the gloo tests exer
 """
 from __future__ import annotations
 
-from typing import Callable, List, Optional, Type, Union
+from typing import List, Optional, Type, Union
 
 import torch
 import torch.nn as nn

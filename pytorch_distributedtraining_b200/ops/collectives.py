@@ -9,7 +9,7 @@ tensors, ``emulate=True``).
 from __future__ import annotations
 
 import ctypes
-from typing import List, Optional, Sequence
+from typing import Optional, Sequence
 
 import torch
 

@@ -17,7 +17,6 @@ Parity target: the convolutions inside the CNN models (Fairscale-DDP.py:74; BASE
 """
 from __future__ import annotations
 
-import ctypes
 from typing import Optional
 
 import torch

@@ -128,7 +128,6 @@ class LayerNorm(nn.LayerNorm):
 class _MaxPoolFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, k, stride, pad):  # type: ignore[override]
-        import ctypes
         from ._lib import check, require_library
         from .fused import DT, ptr, stream_ptr
         lib = require_library()

@@ -11,7 +11,6 @@ saved gradient by the upstream scalar (which carries the AMP loss scale).
 from __future__ import annotations
 
 import ctypes
-from typing import Optional
 
 import torch
 import torch.nn.functional as F

@@ -20,7 +20,7 @@ B200-first differences
 from __future__ import annotations
 
 import contextlib
-from typing import Any, Callable, Dict, Generator, List, Optional, Tuple
+from typing import Any, Callable, Dict, Generator, List, Optional
 
 import torch
 import torch.distributed as dist

@@ -27,13 +27,11 @@ fused into the consuming GEMM's operand fetch for linears, W4); with gloo/NCCL t
 from __future__ import annotations
 
 import contextlib
-import functools
 from typing import Any, Callable, Dict, Generator, Iterator, List, Optional, Set, Tuple
 
 import torch
 import torch.distributed as dist
 import torch.nn as nn
-from torch.autograd import Variable
 
 from . import comm
 

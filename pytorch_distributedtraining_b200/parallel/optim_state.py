@@ -6,7 +6,7 @@ tensors so a checkpoint is independent of the world size.
 """
 from __future__ import annotations
 
-from typing import Any, Dict, Optional
+from typing import Any, Dict
 
 import torch
 import torch.distributed as dist

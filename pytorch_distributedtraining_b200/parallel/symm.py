@@ -23,8 +23,7 @@ Engines (attached by ``attach()`` from the facade):
 """
 from __future__ import annotations
 
-import math
-from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
+from typing import Any, Callable, Dict, List, Optional, Tuple
 
 import torch
 import torch.distributed as dist

@@ -6,7 +6,6 @@ a free port, Fairscale-DDP.py:122-133), wrapped so a test is one function call.
 from __future__ import annotations
 
 import os
-import traceback
 from typing import Any, Callable
 
 import torch
