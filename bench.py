@@ -56,6 +56,8 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="disable CUDA-graph capture of the train step")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (config 1)")
+    ap.add_argument("--no-standin", action="store_true", help="skip the same-session torch stand-in arm")
+    ap.add_argument("--no-exposed", action="store_true", help="skip the exposed-communication measurement (N > 1)")
     return ap.parse_args()
 
 
@@ -83,7 +85,7 @@ def build_ours(cfg: dict, args, world: int):
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     configs = [AMPConfig(init_scale=2.0 ** 14), DDPConfig(local_rank=local_rank, backend="nccl" if gpu else "gloo"),
                FairscaleOSSConfig(broadcast_fp16=False), FairscaleFSDPConfig(mixed_precision=cfg["fp16"] is not None),
-               B200Config(cuda_graph=gpu and not args.no_graph)]
+               B200Config(cuda_graph=gpu and not args.no_graph, strict=gpu)]
     stoke = Stoke(
         model=model, verbose=(int(os.environ.get("RANK", "0")) == 0),
         optimizer=StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs=dict(ADAMW)),
@@ -162,47 +164,45 @@ def build_torch(cfg: dict, args, world: int):
     return None, step, device
 
 
-def main() -> None:
-    args = parse()
-    if args.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable":
-                          "reference is two scripts with no setup.py/pyproject (pip: 'not installable'); its "
-                          "fairscale/stoke/wandb deps and 5 local modules are absent and there is no network"}))
-        return
-    maybe_relaunch(args)
+# fwd+bwd model FLOPs per image (2 x MACs x 3: forward + input gradient + weight gradient), for the roofline line
+MODEL_GFLOP_PER_IMAGE = {"resnet50": 24.6, "resnet18": 10.9, "vit_b_16": 105.4}
+
+
+def graph_torch_step(step, x, y, device):
+    """Whole-step CUDA-graph capture of the stand-in (single process only), so the comparison with the
+    graph-captured arm isolates kernels instead of launch overhead.  Returns a replay callable."""
+    import torch
+    sx, sy = x.clone(), y.clone()
+    side = torch.cuda.Stream(device=device)
+    side.wait_stream(torch.cuda.current_stream(device))
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            step(sx, sy)
+    torch.cuda.current_stream(device).wait_stream(side)
+    torch.cuda.synchronize(device)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        out = step(sx, sy)
+
+    def replay(x, y):
+        sx.copy_(x, non_blocking=True)
+        sy.copy_(y, non_blocking=True)
+        g.replay()
+        return out
+
+    return replay
+
+
+def measure(step, args, cfg, device, world, rank, host, dev_pool, cl, want_e2e, count_launches):
+    """Device-timed steps (CUDA events, barrier + synchronize on both sides, max over ranks), then the same
+    through the host path: pinned batch -> H2D every step, loss -> D2H every step."""
     import torch
     import torch.distributed as dist
-
-    cfg = dict(CONFIGS[args.config])
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    if args.cpu and world == 1 and args.gpus > 1:
-        world = 1
-    build = build_ours if args.impl == "ours" else build_torch
-    stoke, step, device = build(cfg, args, world)
+    from pytorch_distributedtraining_b200.ops import _lib
+    from pytorch_distributedtraining_b200.utils.timing import ClockSampler, max_over_ranks
     is_cuda = device.type == "cuda"
     B = args.batch_size or cfg["batch"]
-    accum = cfg["accum"]
-
-    # ---- synthetic data of the named shape (random-init weights, no datasets on the box)
-    g = torch.Generator().manual_seed(1234 + rank)
-    n_pool = 2
-    host = [(torch.randn((B, *cfg["shape"]), generator=g), torch.randint(0, cfg["classes"], (B,), generator=g))
-            for _ in range(n_pool)]
-    cl = is_cuda and cfg["model"].startswith("resnet")
-    if is_cuda:
-        from pytorch_distributedtraining_b200.data import pin_channels_last
-        # pinned host batches; for the CNNs stored NHWC on the host (decoded-image order), so the H2D copy
-        # lands in the channels-last layout directly
-        host = [((pin_channels_last(x) if cl else x.pin_memory()), y.pin_memory()) for x, y in host]
-
-    def to_dev(x, y):
-        x = x.to(device, non_blocking=True)
-        if cl:
-            x = x.contiguous(memory_format=torch.channels_last)
-        return x, y.to(device, non_blocking=True)
-
-    dev_pool = [to_dev(x, y) for x, y in host]
+    accum, n_pool = cfg["accum"], len(dev_pool)
 
     def sync():
         if is_cuda:
@@ -212,14 +212,13 @@ def main() -> None:
         if world > 1:
             dist.barrier(device_ids=[device.index]) if is_cuda else dist.barrier()
 
-    from pytorch_distributedtraining_b200.ops import _lib
-    from pytorch_distributedtraining_b200.utils.timing import ClockSampler, max_over_ranks
-
     # one timed "step" = one optimizer step = `accum` micro-batches
     def run_device_steps(n):
+        loss = None
         for i in range(n * accum):
             x, y = dev_pool[i % n_pool]
-            step(x, y)
+            loss = step(x, y)
+        return loss
 
     run_device_steps(max(args.warmup, 3))
     sync(); barrier(); sync()
@@ -229,7 +228,7 @@ def main() -> None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
     t0 = time.perf_counter()
-    run_device_steps(args.steps)
+    last = run_device_steps(args.steps)
     if is_cuda:
         e1.record()
         e1.synchronize()
@@ -237,16 +236,16 @@ def main() -> None:
     else:
         ms = (time.perf_counter() - t0) * 1e3
     sync(); barrier(); sync()
-    launches = _lib.LAUNCHES - launches0
+    launches = _lib.LAUNCHES - launches0 if count_launches else 0
     clocks = sampler.stop() if sampler is not None else None
     ms = max_over_ranks(ms, device if is_cuda else None)
     images = B * accum * world * args.steps
-    value = images / (ms / 1e3)
+    res = {"value": images / (ms / 1e3), "ms_per_step": ms / args.steps, "launches": launches, "clocks": clocks,
+           "final_loss": float(last.detach().float()) if last is not None else None, "e2e": None}
 
     # ---- end to end: pinned host batch -> H2D every step (prefetched one step ahead on a
     #      copy stream, as StokeDataLoader does) and a D2H read of the loss every step
-    e2e = None
-    if is_cuda and not args.no_e2e:
+    if is_cuda and want_e2e:
         from pytorch_distributedtraining_b200.data import DevicePrefetcher
 
         def host_batches(n):
@@ -283,14 +282,106 @@ def main() -> None:
         ms_e = max_over_ranks(e0.elapsed_time(e1), device)
         sync(); barrier()
         x0, y0 = host[0]
-        e2e = {"value": images / (ms_e / 1e3), "unit": "images/sec",
-               "h2d_bytes_per_step": int((x0.numel() * x0.element_size() + y0.numel() * y0.element_size()) * accum),
-               "d2h_bytes_per_step": 4 * accum, "ms_per_step": ms_e / args.steps}
+        res["e2e"] = {"value": images / (ms_e / 1e3), "unit": "images/sec",
+                      "h2d_bytes_per_step": int((x0.numel() * x0.element_size() + y0.numel() * y0.element_size()) * accum),
+                      "d2h_bytes_per_step": 4 * accum, "ms_per_step": ms_e / args.steps}
+    return res
+
+
+def main() -> None:
+    args = parse()
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "reference is two scripts with no setup.py/pyproject (pip: 'not installable'); its "
+                          "fairscale/stoke/wandb deps and 5 local modules are absent and there is no network"}))
+        return
+    maybe_relaunch(args)
+    import torch
+    import torch.distributed as dist
+
+    cfg = dict(CONFIGS[args.config])
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    if args.cpu and world == 1 and args.gpus > 1:
+        world = 1
+    build = build_ours if args.impl == "ours" else build_torch
+    stoke, step, device = build(cfg, args, world)
+    is_cuda = device.type == "cuda"
+    B = args.batch_size or cfg["batch"]
+    accum = cfg["accum"]
+    if is_cuda and args.impl == "ours":
+        from pytorch_distributedtraining_b200.ops import require_library
+        require_library()            # a GPU run without the kernel library is an error, never a silent fallback
+
+    # ---- synthetic data of the named shape (random-init weights, no datasets on the box)
+    g = torch.Generator().manual_seed(1234 + rank)
+    n_pool = 2
+    host = [(torch.randn((B, *cfg["shape"]), generator=g), torch.randint(0, cfg["classes"], (B,), generator=g))
+            for _ in range(n_pool)]
+    cl = is_cuda and cfg["model"].startswith("resnet")
+    if is_cuda:
+        from pytorch_distributedtraining_b200.data import pin_channels_last
+        # pinned host batches; for the CNNs stored NHWC on the host (decoded-image order), so the H2D copy
+        # lands in the channels-last layout directly
+        host = [((pin_channels_last(x) if cl else x.pin_memory()), y.pin_memory()) for x, y in host]
+
+    def to_dev(x, y):
+        x = x.to(device, non_blocking=True)
+        if cl:
+            x = x.contiguous(memory_format=torch.channels_last)
+        return x, y.to(device, non_blocking=True)
+
+    dev_pool = [to_dev(x, y) for x, y in host]
+    standin_graphed = False
+    if args.impl == "torch" and is_cuda and world == 1 and not args.no_graph and accum == 1:
+        step = graph_torch_step(step, *dev_pool[0], device)
+        standin_graphed = True
+
+    res = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, not args.no_e2e, args.impl == "ours")
+    native = stoke.native_status if stoke is not None else None
+
+    # ---- same session, same box: the torch-native stand-in (NOT the reference, which cannot be installed)
+    standin = None
+    if args.impl == "ours" and is_cuda and not args.no_standin:
+        try:
+            _, t_step, _ = build_torch(cfg, args, world)
+            graphed = world == 1 and accum == 1 and not args.no_graph
+            if graphed:
+                t_step = graph_torch_step(t_step, *dev_pool[0], device)
+            t = measure(t_step, args, cfg, device, world, rank, host, dev_pool, cl, not args.no_e2e, False)
+            standin = {"what": "torch DDP/ZeRO/FSDP + torchvision + torch.amp + cuDNN/cuBLAS/NCCL, same process group; "
+                               "a stand-in, not the reference", "cuda_graph": graphed, "value": t["value"],
+                       "ms_per_step": t["ms_per_step"], "e2e_value": t["e2e"]["value"] if t["e2e"] else None,
+                       "ratio": res["value"] / t["value"],
+                       "e2e_ratio": (res["e2e"]["value"] / t["e2e"]["value"]) if (t["e2e"] and res["e2e"]) else None}
+            del t_step
+        except Exception as e:  # the stand-in must never take the product's number down with it
+            standin = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
+
+    # ---- exposed communication: the same captured step with every peer-memory collective muted.  Run last:
+    #      with the collectives off the replicas drift apart, so nothing may be measured after this.
+    exposed = None
+    if args.impl == "ours" and is_cuda and world > 1 and not args.no_exposed:
+        from pytorch_distributedtraining_b200.ops import collectives as C
+        stoke.reset_graphs()
+        C.MUTE = True
+        try:
+            muted = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, False, False)
+            exposed = {"exposed_comm_ms": res["ms_per_step"] - muted["ms_per_step"], "ms_per_step_comm_muted": muted["ms_per_step"],
+                       "how": "same whole-step CUDA graph re-captured with all peer-memory collective launches skipped"}
+        finally:
+            C.MUTE = False
 
     if rank == 0:
+        gflop = MODEL_GFLOP_PER_IMAGE.get(cfg["model"])
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
         out = {
-            "metric": "images/sec", "value": value, "unit": "images/sec", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "metric": "images/sec", "value": res["value"], "unit": "images/sec", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": res["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": cfg["dtype"] if is_cuda else "fp32",
             "data": "synthetic (random images of the named shape, random-init weights)",
             "impl": {"ours": "ours", "torch": "torch-native stand-in (not the reference)"}[args.impl],
@@ -299,26 +390,46 @@ def main() -> None:
                        "parallelism": f"{cfg['par']}{world}", "optimizer": "AdamW",
                        "l2": "per-step working set (inputs + activations, several GB) exceeds the 126 MB L2; "
                              "no explicit flush"},
-            "gpu_launches": launches,
-            "e2e": e2e,
+            "gpu_launches": res["launches"],
+            "e2e": res["e2e"],
+            "final_loss": res["final_loss"],
+            "native": native,
+            "standin": standin,
         }
-        if clocks is not None:
-            out["clocks"] = clocks
+        if args.impl == "torch":
+            out["cuda_graph"] = standin_graphed
+        if exposed is not None:
+            out.update(exposed)
+        if gflop is not None and is_cuda:
+            tflops = res["value"] * gflop / 1e3 / world
+            out["roofline"] = {"model_tflops_per_gpu": tflops,
+                               "frac_of_bf16_sustained": tflops / peaks["bf16_tflops_sustained"] if peaks.get("bf16_tflops_sustained") else None,
+                               "peaks": "MEASURED_PEAKS.json" if peaks else "absent"}
+        if res["clocks"] is not None:
+            out["clocks"] = res["clocks"]
         if is_cuda:
             out["peak_mem_gb"] = round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)
         print(json.dumps(out))
-    # teardown: CUDA graphs first (they may hold collective kernels), then the process group; a
-    # watchdog makes sure a stuck teardown can never hold the GPUs after the result is printed
+
+    def sync():
+        if is_cuda:
+            torch.cuda.synchronize()
+
+    # teardown: CUDA graphs first (they may hold collective kernels), then the process group, then a NORMAL
+    # interpreter exit so exit hooks run.  The daemon timer only fires if teardown is stuck for minutes.
     sys.stdout.flush()
     import threading
-    threading.Timer(20.0, lambda: os._exit(0)).start()
+    guard = threading.Timer(180.0, lambda: (sys.stderr.write("[bench] teardown stuck for 180 s; forcing exit\n"),
+                                            sys.stderr.flush(), os._exit(3)))
+    guard.daemon = True
+    guard.start()
     if stoke is not None:
         stoke.reset_graphs()
     sync()
     if world > 1 and dist.is_initialized():
-        barrier()
+        dist.barrier(device_ids=[device.index]) if is_cuda else dist.barrier()
         dist.destroy_process_group()
-    os._exit(0)
+    guard.cancel()
 
 
 if __name__ == "__main__":

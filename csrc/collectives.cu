@@ -286,7 +286,20 @@ __global__ void __launch_bounds__(kCommThreads) peer_allreduce_kernel(
                     else *reinterpret_cast<uint4*>(mine + off[u]) = r;      // slice r of my own bucket
                 }
         }
+        // NVLS: only the owner of a slice sees its reduced values, but the non-finite flag has to come up on
+        // EVERY rank (all ranks must skip the same optimizer step).  The owner posts the epoch of the barrier
+        // below into its slot of the inf row of this CTA on every rank; the barrier's release / acquire pair
+        // publishes it, and each rank then compares the slots with that epoch (no reset ever needed).
+        uint32_t inf_epoch = 0;
+        if (kMC && found_inf.p[me.rank] != nullptr) {
+            inf_epoch = c.epochs[me.rank][blockIdx.x] + 1u;       // written by thread 0 inside the barrier only
+            const bool cta_bad = __syncthreads_or(bad);
+            if (cta_bad && (int)threadIdx.x < me.world)
+                st_release_sys(c.flags[threadIdx.x] + ((size_t)c.max_blocks + blockIdx.x) * B200DP_MAX_RANKS + me.rank, inf_epoch);
+        }
         cta_barrier_all_ranks(c, me);  // every slice is reduced (and, with NVLS, already delivered)
+        if (kMC && found_inf.p[me.rank] != nullptr && (int)threadIdx.x < me.world)
+            bad |= ld_acquire_sys(c.flags[me.rank] + ((size_t)c.max_blocks + blockIdx.x) * B200DP_MAX_RANKS + threadIdx.x) == inf_epoch;
         if (!kMC) {
             // phase 2: gather the other slices from their owners, 4 loads in flight per thread
             for (int p = 1; p < me.world; ++p) {

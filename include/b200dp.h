@@ -261,7 +261,8 @@ typedef struct {
     int world;           /* number of ranks, <= B200DP_MAX_RANKS                                  */
     int emulate;         /* 1: single-GPU emulation, grid.y = world, cooperative launch           */
     int max_blocks;      /* rows in each flag array                                               */
-    uint32_t* flags[B200DP_MAX_RANKS];   /* [max_blocks][B200DP_MAX_RANKS] words per rank, zeroed once    */
+    uint32_t* flags[B200DP_MAX_RANKS];   /* [2*max_blocks][B200DP_MAX_RANKS] words per rank, zeroed once: barrier rows, then the
+                                            non-finite notice rows of the NVLS all-reduce */
     uint32_t* epochs[B200DP_MAX_RANKS];  /* [max_blocks] per-CTA barrier counters (local entry used)      */
     uint32_t* status[B200DP_MAX_RANKS];  /* one word per rank: non-zero after a barrier timed out         */
     uint64_t timeout_ns; /* spin limit per barrier; 0 = wait forever                              */

@@ -201,6 +201,9 @@ class B200Config:
                       loss / norm when the tensors live on a CUDA device.
     peer_collectives  use symmetric-memory (peer / NVLS multicast) fused collectives
                       instead of NCCL for the hot paths.
+    strict            a GPU run must really be on the native path: a missing kernel library or a
+                      failed peer-memory attachment raises instead of falling back to stock ops /
+                      NCCL (benchmarks and CI set this, so a fallback can never print a number).
     cuda_graph        capture the steady-state micro-step in a CUDA graph.
     channels_last     run convolutional models in NHWC.
     loss_sync_every   how often ``detach_and_sync_loss`` drains to the host
@@ -214,6 +217,7 @@ class B200Config:
 
     fused_kernels: bool = True
     peer_collectives: bool = True
+    strict: bool = False
     cuda_graph: bool = False
     channels_last: bool = True
     loss_sync_every: int = 1

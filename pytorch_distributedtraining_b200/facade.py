@@ -161,7 +161,9 @@ class Stoke:
     def _fused_ok(self) -> bool:
         if not (self._status.gpu and self._b200.fused_kernels):
             return False
-        from .ops import library_available
+        from .ops import library_available, require_library
+        if self._b200.strict:
+            require_library()
         return library_available()
 
     def _optimizer_class(self, cls: type) -> type:
@@ -233,6 +235,8 @@ class Stoke:
             self._peer = peer.attach(engine, optim, self._status, scaler_cfg=self._amp_cfg, ddp_cfg=self._ddp_cfg,
                                      oss_cfg=self._oss_cfg, timeout_s=self._b200.watchdog_timeout_s)
         except Exception as e:  # pragma: no cover - depends on the box
+            if self._b200.strict:
+                raise RuntimeError(f"peer-memory collectives could not be attached (B200Config.strict): {e}") from e
             if self._verbose:
                 self.print(f"[b200] peer-memory collectives unavailable ({type(e).__name__}: {e}); using NCCL")
             self._peer = None
@@ -436,6 +440,16 @@ class Stoke:
                 self._optimizer._sync_param_groups(self._optimizer.param_groups, opt.param_groups)
             opt.sync_lr()
 
+    @property
+    def native_status(self) -> Dict[str, Any]:
+        """What is really serving this run: kernel library, peer-memory engines, CUDA graph."""
+        from .ops import _lib
+        peer = getattr(self, "_peer", None)
+        return {"fused_kernels": self._fused_ok(), "kernel_library": _lib.lib_path() if self._fused_ok() else None,
+                "peer_collectives": sorted(k for k in peer if k not in ("arena", "small")) if peer else [],
+                "nvls_multicast": bool(peer and peer["arena"].mc_base),
+                "cuda_graph": bool(self._b200.cuda_graph and any(e.get("graph") is not None for e in self._graphs.values()))}
+
     def _graphed_step(self, args: Any, targets: Any) -> Any:
         flat = [a for a in args if isinstance(a, torch.Tensor)] + ([targets] if isinstance(targets, torch.Tensor) else [])
         key = (self._grad_accum_counter, tuple((tuple(t.shape), t.dtype, t.stride()) for t in flat))
@@ -462,6 +476,8 @@ class Stoke:
                 self._graphs.clear()
                 torch.cuda.synchronize(self._device)
                 self.reset()
+                if self._b200.strict:
+                    raise
                 self.print(f"[b200] CUDA-graph capture failed ({type(e).__name__}: {str(e)[:160]}); continuing eagerly")
                 return self._eager_step(args, targets)
             ent["launches"] = _lib.LAUNCHES - launches0    # b200dp kernels inside one replay

@@ -17,6 +17,9 @@ from ._lib import check, require_library
 from .fused import DT, AdamHParams
 
 MAX_RANKS = 8
+# measurement only (bench.py "exposed_comm_ms"): when True every collective launch below is skipped, so the same
+# step can be timed with its communication removed.  Results are garbage while it is set.
+MUTE = False
 VoidPtrTable = ctypes.c_void_p * MAX_RANKS
 
 
@@ -89,6 +92,8 @@ class PeerContext:
     def allreduce(self, bufs: VoidPtrTable, mc: int, n: int, dtype: torch.dtype, pre_mult: float = 1.0,
                   mult_dev: Optional[VoidPtrTable] = None, found_inf: Optional[VoidPtrTable] = None, algo: int = 1,
                   blocks: int = 32, stream=None) -> None:
+        if MUTE:
+            return
         check(self.lib.b200dp_peer_allreduce(ctypes.byref(self.c), bufs, ctypes.c_void_p(mc or None), ctypes.c_int64(n),
                                              DT[dtype], ctypes.c_float(pre_mult), mult_dev, found_inf, algo, blocks,
                                              self._s(stream)), "peer_allreduce")
@@ -97,6 +102,8 @@ class PeerContext:
                        pre_mult: float = 1.0, mult_dev: Optional[VoidPtrTable] = None,
                        found_inf: Optional[VoidPtrTable] = None, accumulate: bool = False, blocks: int = 32,
                        stream=None) -> None:
+        if MUTE:
+            return
         check(self.lib.b200dp_peer_reduce_scatter(ctypes.byref(self.c), in_bufs, ctypes.c_void_p(mc or None),
                                                   ctypes.c_int64(n_per_rank), DT[dtype], outs, ctypes.c_float(pre_mult),
                                                   mult_dev, found_inf, int(accumulate), blocks, self._s(stream)),
@@ -104,6 +111,8 @@ class PeerContext:
 
     def all_gather(self, outs: VoidPtrTable, mc: int, shards: VoidPtrTable, n_per_rank: int, shard_dtype: torch.dtype,
                    out_dtype: torch.dtype, blocks: int = 32, stream=None) -> None:
+        if MUTE:
+            return
         check(self.lib.b200dp_peer_all_gather(ctypes.byref(self.c), outs, ctypes.c_void_p(mc or None), shards,
                                               ctypes.c_int64(n_per_rank), DT[shard_dtype], DT[out_dtype], blocks,
                                               self._s(stream)), "peer_all_gather")
@@ -113,6 +122,8 @@ class PeerContext:
                   hp: AdamHParams, step: VoidPtrTable, pre_mult: float = 1.0, mult_dev: Optional[VoidPtrTable] = None,
                   found_inf: Optional[VoidPtrTable] = None, prereduced: bool = False,
                   local_grad: Optional[VoidPtrTable] = None, blocks: int = 32, stream=None) -> None:
+        if MUTE:
+            return
         seg_arr = (ctypes.c_int64 * (MAX_RANKS + 1))(*list(seg) + [seg[-1]] * (MAX_RANKS + 1 - len(seg)))
         check(self.lib.b200dp_peer_zero_adam(ctypes.byref(self.c), grad_bufs, ctypes.c_void_p(grad_mc or None), param_bufs,
                                              ctypes.c_void_p(param_mc or None), seg_arr, DT[wire_dtype], master, m, v, hp,
@@ -122,17 +133,23 @@ class PeerContext:
     def reduce_to_owner(self, grad_bufs: VoidPtrTable, seg: Sequence[int], local_out: VoidPtrTable,
                         pre_mult: float, mult_dev: Optional[VoidPtrTable], norm_out: VoidPtrTable,
                         partials: VoidPtrTable, counters: VoidPtrTable, blocks: int = 32, stream=None) -> None:
+        if MUTE:
+            return
         seg_arr = (ctypes.c_int64 * (MAX_RANKS + 1))(*list(seg) + [seg[-1]] * (MAX_RANKS + 1 - len(seg)))
         check(self.lib.b200dp_peer_reduce_to_owner(ctypes.byref(self.c), grad_bufs, seg_arr, local_out,
                                                    ctypes.c_float(pre_mult), mult_dev, norm_out, partials, counters,
                                                    blocks, self._s(stream)), "peer_reduce_to_owner")
 
     def broadcast(self, bufs: VoidPtrTable, mc: int, nbytes: int, root: int = 0, blocks: int = 8, stream=None) -> None:
+        if MUTE:
+            return
         check(self.lib.b200dp_peer_broadcast(ctypes.byref(self.c), bufs, ctypes.c_void_p(mc or None), ctypes.c_int64(nbytes),
                                              root, blocks, self._s(stream)), "peer_broadcast")
 
     def small_allreduce(self, staging: VoidPtrTable, io: VoidPtrTable, n: int, slot_floats: int,
                         call_counter: VoidPtrTable, stream=None) -> None:
+        if MUTE:
+            return
         check(self.lib.b200dp_peer_small_allreduce(ctypes.byref(self.c), staging, io, n, slot_floats, call_counter,
                                                    self._s(stream)), "peer_small_allreduce")
 
@@ -144,7 +161,8 @@ class EmulatedPeers:
     def __init__(self, world: int, max_blocks: int = 16, device: Optional[torch.device] = None, timeout_s: float = 10.0):
         device = device or torch.device("cuda", torch.cuda.current_device())
         self.world, self.device = world, device
-        self.flags = [torch.zeros(max_blocks * MAX_RANKS, dtype=torch.int32, device=device) for _ in range(world)]
+        # rows [0, max_blocks): barrier flags; rows [max_blocks, 2*max_blocks): non-finite notices of the NVLS all-reduce
+        self.flags = [torch.zeros(2 * max_blocks * MAX_RANKS, dtype=torch.int32, device=device) for _ in range(world)]
         self.epochs = [torch.zeros(max_blocks, dtype=torch.int32, device=device) for _ in range(world)]
         self.status = [torch.zeros(1, dtype=torch.int32, device=device) for _ in range(world)]
         self.ctx = PeerContext(0, world, [f.data_ptr() for f in self.flags], self.epochs[0], self.status[0], max_blocks,

@@ -53,7 +53,9 @@ class GradScaler:
         if self._scale is None:
             self._device = device
             self._scale = torch.full((), self._init_scale, dtype=torch.float32, device=device)
-            self._growth_tracker = torch.zeros((), dtype=torch.int32, device=device)
+            self._growth_tracker = torch.full((), int(getattr(self, "_pending_tracker", 0) or 0), dtype=torch.int32,
+                                              device=device)      # a checkpoint loaded before the first step
+            self._pending_tracker = 0
             self._found_inf = torch.zeros((), dtype=torch.float32, device=device)
 
     def is_enabled(self) -> bool:
@@ -171,6 +173,7 @@ class GradScaler:
             return
         if new_scale is not None:
             self._scale.fill_(float(new_scale))
+            self._found_inf.zero_()          # the fused update kernel clears it on the other path
         else:
             if self._scale.is_cuda:
                 from ..ops import fused

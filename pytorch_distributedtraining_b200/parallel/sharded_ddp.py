@@ -47,6 +47,7 @@ class _Bucket:
         self.fill = 0
         self.pending = 0
         self.sent = False
+        self.fired: set = set()      # ids of the members whose hook ran in this backward pass
 
     def can_add(self, p: torch.Tensor) -> bool:
         return self.fill + p.numel() <= self.buffer.numel()
@@ -59,6 +60,7 @@ class _Bucket:
     def reset(self) -> None:
         self.pending = len(self.params)
         self.sent = False
+        self.fired.clear()
 
 
 class ShardedDataParallel(nn.Module):
@@ -237,8 +239,9 @@ class ShardedDataParallel(nn.Module):
             if entry is not None:
                 bucket, off = entry
                 view = bucket.buffer[off: off + param.numel()]
-                view.copy_(grad.reshape(-1))
-                view.mul_(inv_world)
+                # scale in the gradient's own precision first: a 16-bit bucket must not see the unscaled value
+                view.copy_(grad.reshape(-1) * inv_world)
+                bucket.fired.add(id(param))
                 bucket.pending -= 1
                 if bucket.pending == 0:
                     self._send_bucket(bucket)
@@ -285,9 +288,8 @@ class ShardedDataParallel(nn.Module):
             for b in self._buckets.values():
                 if not b.sent and b.pending != len(b.params):
                     # some members never produced a gradient this pass: send zeros for them
-                    fired = {id(p) for p in b.params if p.grad is not None}
                     for p, off in zip(b.params, b.offsets):
-                        if id(p) not in fired:
+                        if id(p) not in b.fired:
                             b.buffer[off: off + p.numel()].zero_()
                     self._send_bucket(b)
         for h, done in self._work:

@@ -85,7 +85,7 @@ class PeerArena:
         """Flag set for one stream's worth of collectives."""
         ctx = self._contexts.get(name)
         if ctx is None:
-            flags = self.alloc(self.max_blocks * C.MAX_RANKS, torch.int32)
+            flags = self.alloc(2 * self.max_blocks * C.MAX_RANKS, torch.int32)   # barrier rows + inf-notice rows
             epochs = torch.zeros(self.max_blocks, dtype=torch.int32, device=self.device)
             status = torch.zeros(1, dtype=torch.int32, device=self.device)
             ctx = self._contexts[name] = C.PeerContext(self.rank, self.world, flags.ptrs, epochs, status,
@@ -274,6 +274,8 @@ class ZeroPeerEngine:
             for r in range(self.world):
                 off = seg[-1]
                 for p in part[r][gi]["params"]:
+                    if not p.requires_grad:
+                        continue        # frozen: never updated, never decayed (torch skips params without a gradient)
                     if p.dtype != torch.float32:
                         raise RuntimeError("fused ZeRO engine expects fp32 parameters")
                     entries.append((p, off, r))
@@ -401,8 +403,9 @@ class ZeroPeerEngine:
         return loss
 
     def _is_adamw(self) -> bool:
-        name = self.oss._optim_cls.__name__.lower()
-        return "adamw" in name
+        from ..ops.optim import FusedAdamW, FusedAdam
+        cls = self.oss._optim_cls
+        return cls is torch.optim.AdamW or (issubclass(cls, FusedAdamW) and not issubclass(cls, FusedAdam))
 
     # state dict plumbing (torch layout, per original parameter) ---------------------
     def local_state_dict(self) -> Dict[str, Any]:
@@ -466,6 +469,18 @@ def _arena_bytes(engine: Any, optim: Any, status: Any) -> int:
     return n_params * 4 + len(list(engine.parameters())) * 64 + (16 << 20)
 
 
+def _zero_engine_serves(oss: Any) -> bool:
+    """The fused ZeRO-2 step is Adam / AdamW (decoupled or L2 decay, no amsgrad, minimising).  Match the
+    optimizer CLASS, not its name: Adamax / NAdam / RAdam / SparseAdam are different update rules."""
+    from ..ops.optim import FusedAdam, FusedAdamW
+    if oss._optim_cls not in (torch.optim.Adam, torch.optim.AdamW, FusedAdam, FusedAdamW):
+        return False
+    for g in oss.param_groups:
+        if g.get("maximize", False) or g.get("amsgrad", False):
+            return False
+    return True
+
+
 def attach(engine: Any, optim: Any, status: Any, timeout_s: float = 30.0, **cfg: Any) -> Optional[Any]:
     """Create the arena for the default group and attach the engine that matches the run."""
     from .ddp import DistributedDataParallel
@@ -487,8 +502,8 @@ def attach(engine: Any, optim: Any, status: Any, timeout_s: float = 30.0, **cfg:
     if isinstance(engine, FullyShardedDataParallel):
         out["fsdp"] = FSDPPeerEngine(arena, engine)
     elif isinstance(engine, ShardedDataParallel) and isinstance(optim, OSS):
-        if "adam" not in optim._optim_cls.__name__.lower():
-            return out  # the fused ZeRO step implements Adam/AdamW; other optimizers keep the NCCL path
+        if not _zero_engine_serves(optim):
+            return out  # the fused ZeRO step implements exactly Adam / AdamW; anything else keeps the NCCL path
         oss_cfg = cfg.get("oss_cfg")
         wire = torch.float16 if (oss_cfg is not None and oss_cfg.broadcast_fp16) else None
         out["zero"] = ZeroPeerEngine(arena, optim, engine, wire_dtype=wire)

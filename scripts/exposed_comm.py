@@ -32,4 +32,9 @@ def fwd_bwd():
 r = exposed_comm_ms(stoke.wrapped_model, fwd_bwd, iters=a.iters)
 if int(os.environ.get("RANK", "0")) == 0:
     print(json.dumps({"config": a.config, "world": world, **r}), flush=True)
-os._exit(0)
+stoke.reset_graphs()
+torch.cuda.synchronize() if torch.cuda.is_available() else None
+if world > 1:
+    import torch.distributed as dist
+    dist.barrier()
+    dist.destroy_process_group()

@@ -212,6 +212,31 @@ def _w_real(rank, world):
                 torch.cuda.synchronize()
                 torch.testing.assert_close(sb.tensor.float(), ref, rtol=tol, atol=tol * 4)
                 assert flag.item() == 0
+    # a non-finite value on ONE rank must raise the flag on EVERY rank, also when the slice holding it is reduced
+    # in the switch and only its owner sees the result (NVLS)
+    n = 1 << 20
+    sb = arena.alloc(n, torch.float32)
+    for use_mc, algo in ((False, 0), (False, 1), (True, 1)):
+        if use_mc and not arena.mc_base:
+            continue
+        for bad_rank, pos in ((0, n - 5), (world - 1, 3)):
+            sb.tensor.fill_(1.0)
+            if rank == bad_rank:
+                sb.tensor[pos] = float("inf")
+            flag = torch.zeros((), device=dev)
+            torch.cuda.synchronize(); dist.barrier()
+            ctx.allreduce(sb.table, sb.mc if use_mc else 0, n, torch.float32, pre_mult=1.0,
+                          found_inf=C.local_table(rank, flag), algo=algo, blocks=32)
+            torch.cuda.synchronize()
+            assert flag.item() == 1.0, (use_mc, algo, bad_rank, rank)
+            # and the next clean call leaves a fresh flag untouched (the notice rows are epoch-tagged)
+            sb.tensor.fill_(1.0)
+            flag.zero_()
+            torch.cuda.synchronize(); dist.barrier()
+            ctx.allreduce(sb.table, sb.mc if use_mc else 0, n, torch.float32, pre_mult=1.0,
+                          found_inf=C.local_table(rank, flag), algo=algo, blocks=32)
+            torch.cuda.synchronize()
+            assert flag.item() == 0.0 and torch.all(sb.tensor == world)
     # reduce-scatter / all-gather
     n_per = 1 << 18
     sb = arena.alloc(n_per * world, torch.bfloat16)
