@@ -102,7 +102,7 @@ def build_ours(cfg: dict, args, world: int):
     return stoke, step, stoke.device
 
 
-def build_torch(cfg: dict, args, world: int):
+def build_torch(cfg: dict, args, world: int, capturable: bool = False):
     """Torch-native stand-in: torchvision model, torch DDP / ZeRO / FSDP,
     torch.amp autocast + GradScaler, channels_last."""
     import torch
@@ -138,7 +138,7 @@ def build_torch(cfg: dict, args, world: int):
             from torch.distributed.optim import ZeroRedundancyOptimizer
             opt = ZeroRedundancyOptimizer(model.parameters(), optimizer_class=torch.optim.AdamW, **ADAMW)
         else:
-            opt = torch.optim.AdamW(model.parameters(), fused=gpu, **ADAMW)
+            opt = torch.optim.AdamW(model.parameters(), fused=gpu, capturable=capturable and gpu, **ADAMW)
     scaler = torch.amp.GradScaler("cuda", init_scale=2.0 ** 14, enabled=amp_dtype == torch.float16)
     model.train()
     state = {"i": 0}
@@ -304,8 +304,11 @@ def main() -> None:
     rank = int(os.environ.get("RANK", "0"))
     if args.cpu and world == 1 and args.gpus > 1:
         world = 1
-    build = build_ours if args.impl == "ours" else build_torch
-    stoke, step, device = build(cfg, args, world)
+    graph_standin = args.impl == "torch" and not args.cpu and world == 1 and not args.no_graph and cfg["accum"] == 1
+    if args.impl == "ours":
+        stoke, step, device = build_ours(cfg, args, world)
+    else:
+        stoke, step, device = build_torch(cfg, args, world, capturable=graph_standin)
     is_cuda = device.type == "cuda"
     B = args.batch_size or cfg["batch"]
     accum = cfg["accum"]
@@ -333,7 +336,7 @@ def main() -> None:
 
     dev_pool = [to_dev(x, y) for x, y in host]
     standin_graphed = False
-    if args.impl == "torch" and is_cuda and world == 1 and not args.no_graph and accum == 1:
+    if graph_standin:
         step = graph_torch_step(step, *dev_pool[0], device)
         standin_graphed = True
 
@@ -344,8 +347,8 @@ def main() -> None:
     standin = None
     if args.impl == "ours" and is_cuda and not args.no_standin:
         try:
-            _, t_step, _ = build_torch(cfg, args, world)
             graphed = world == 1 and accum == 1 and not args.no_graph
+            _, t_step, _ = build_torch(cfg, args, world, capturable=graphed)
             if graphed:
                 t_step = graph_torch_step(t_step, *dev_pool[0], device)
             t = measure(t_step, args, cfg, device, world, rank, host, dev_pool, cl, not args.no_e2e, False)
