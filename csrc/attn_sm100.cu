@@ -1,0 +1,634 @@
+// Attention core on the 5th-generation tensor cores (K17): softmax(Q K^T * scale + bias) V, forward and backward,
+// for the two shapes the transformer models use — ViT (197 tokens, head dim 64) and Swin / SwinIR windows
+// (<= 64 tokens, small head dims, additive relative-position bias + shift mask).
+//
+// Everything is read from / written to the PACKED token-major projection tensors, so no per-head copies exist:
+//     qkv  [B][S][3][H][d]     (output of the qkv linear)         out [B][S][H][d]   (input of the out projection)
+//     dqkv [B][S][3][H][d]     (gradient of the qkv linear)       dout[B][S][H][d]
+//
+// One 128-row tile of queries per step (TMEM has 128 lanes).  Sequences of at most 64 tokens are stacked two
+// problems to a tile (same head, consecutive batch / window index): the score matrix is then block diagonal
+// and the off-diagonal blocks are written as exact zeros, so the second product needs no special casing.
+//
+// Forward (one CTA per query tile, two CTAs per SM):
+//     S = Q K^T                 tcgen05.mma, M = 128, N = keys (<= 256), fp32 in TMEM
+//     P = softmax rows          4 warps, one TMEM lane (row) per thread: tcgen05.ld, two passes (max, then exp / sum),
+//                               P written as 16-bit into 128B-swizzled shared memory over the dead Q / K tiles
+//     O = P V                   tcgen05.mma, A = P (K-major), B = V as loaded ([key][d], i.e. MN-major), into the
+//                               TMEM columns S no longer needs; rows scaled by 1 / sum on the way out
+// Backward (one CTA per (batch, head), 128 x 128 blocks of the score matrix, everything accumulated in TMEM):
+//     S = Q K^T, dP = dO V^T                        recomputed per block
+//     P = exp(S * scale + bias - lse), dS = P o (dP - delta) * scale       delta = rowsum(dO o O)
+//     dV += P^T dO,  dK += dS^T Q,  dQ += dS K      A operands P / dS are the SAME shared-memory tiles read
+//                                                   K-major (dQ) or MN-major (dV, dK): no transposes anywhere
+//   TMEM columns: S 0-127 | dP 128-255 | dQ tile0 256-319 | dQ tile1 320-383 | dK 384-447 | dV 448-511
+// Operand staging: TMA (3-D tensor maps over the packed tensors, out-of-range tokens zero-filled) when the head
+// dimension is 64; otherwise the threads copy the rows into the same swizzled layout, zero-padded to 64.
+//
+// Reference: the attention inside nn.MultiheadAttention / WindowAttention of the transformer models
+// (SwinIR built at Stoke-DDP.py:206-208; ViT-B/16 is BASELINE config 4); the library path there is
+// F.scaled_dot_product_attention (flash / efficient kernels).
+#include <string.h>
+
+#include "tc_common.cuh"
+
+namespace b200dp {
+namespace attn {
+
+using namespace b200dp::tc;
+
+constexpr int kTile = 128;
+constexpr int kTileBytes = kTile * 128;      // 128 rows x 64 x 2 B
+constexpr float kLog2e = 1.4426950408889634f;
+
+struct Geom {
+    int B, H, S, d;    // B x H problems of S tokens, head dimension d (even, <= 64)
+    int G;             // problems stacked per tile: 2 when S <= 64, else 1
+    int spad;          // tile rows per stacked problem (128 / G)
+    int nq;            // 128-row tiles per problem (1 or 2)
+    int nk;            // forward: keys staged per tile (multiple of 16, <= 256)
+    int manual;        // 1: threads stage the operands (head dim != 64 or stacked problems); 0: TMA
+    int nW;            // number of mask windows (mask index = batch % nW); 0: no mask
+    float scale;
+};
+
+__device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tm), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+// Copy `rows` token rows of one projection (q, k or v of head h; or dout) into a 128B-swizzled K-major tile,
+// zero-padding the head dimension to 64 and rows that do not exist.  src points at element [0][0][which][h][0].
+template <typename T>
+__device__ __forceinline__ void stage_rows(uint8_t* dst, const T* __restrict__ src, int64_t pitch /* elements between tokens */,
+                                           const Geom& g, int b0, int s0, int rows) {
+    const int sp_rows = g.G == 1 ? (1 << 20) : g.spad;      // one problem: every row is a token of it
+    for (int row = threadIdx.x; row < rows; row += blockDim.x) {
+        const int gi = row / sp_rows, lr = row - gi * sp_rows;
+        const int b = b0 + gi, s = s0 + lr;
+        uint8_t* rp = dst + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(rp + j * 16) = make_uint4(0, 0, 0, 0);
+        if (b < g.B && s < g.S && gi < g.G) {
+            const T* sp = src + ((int64_t)b * g.S + s) * pitch;
+            for (int e = 0; e < g.d; e += 2) {
+                const uint32_t w = *reinterpret_cast<const uint32_t*>(sp + e);
+                *reinterpret_cast<uint32_t*>(rp + (((e >> 3) ^ (row & 7)) << 4) + (e & 7) * 2) = w;
+            }
+        }
+    }
+}
+
+// Which (batch, token) a tile row / block column stands for.
+struct RowId { int b, s, gi; bool ok; };
+__device__ __forceinline__ RowId row_id(const Geom& g, int b0, int tile, int r) {
+    RowId o;
+    o.gi = r / g.spad;
+    o.b = b0 + o.gi;
+    o.s = tile * kTile + (r - o.gi * g.spad);
+    o.ok = o.b < g.B && o.s < g.S && o.gi < g.G;
+    return o;
+}
+
+template <typename T>
+__device__ __forceinline__ void store_row(T* dst, const float* v, int d) {
+    if ((d & 7) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        for (int e = 0; e < d; e += 8) {
+            float t[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t[k] = v[e + k];
+            store8<T>(dst + e, t);
+        }
+    } else {
+        for (int e = 0; e < d; e += 2) {
+            T pr[2] = {Cvt<T>::from_f(v[e]), Cvt<T>::from_f(v[e + 1])};
+            *reinterpret_cast<uint32_t*>(dst + e) = *reinterpret_cast<const uint32_t*>(pr);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- forward
+constexpr int kFwdSmem = 65536 + 32768 + 1024 /*align*/ + 128 /*barriers*/;
+
+template <typename T>
+__global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ,
+                                                          const __grid_constant__ CUtensorMap tmKV,
+                                                          const T* __restrict__ qkv, T* __restrict__ out,
+                                                          float* __restrict__ lse, const float* __restrict__ bias,
+                                                          const float* __restrict__ mask, const Geom g, int is_bf16) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;                     // 16 KB
+    uint8_t* sK = smem + kTileBytes;        // up to 256 keys: 32 KB
+    uint8_t* sP = smem;                     // 4 chunks of 64 keys x 128 rows: 64 KB, overlays Q and K once S exists
+    uint8_t* sV = smem + 65536;             // up to 256 keys: 32 KB
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 65536 + 32768);
+    uint64_t* bar_ld = bars;
+    uint64_t* bar_s = bars + 1;
+    uint64_t* bar_o = bars + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qt = blockIdx.x, h = blockIdx.y, b0 = blockIdx.z * g.G;
+    const int64_t pitch = (int64_t)3 * g.H * g.d;
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar_ld, 1); mbar_init(bar_s, 1); mbar_init(bar_o, 1);
+        fence_barrier_init();
+        if (!g.manual) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); }
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 256);
+    if (g.manual) {
+        stage_rows<T>(sQ, qkv + (int64_t)h * g.d, pitch, g, b0, qt * kTile, kTile);
+        stage_rows<T>(sK, qkv + (int64_t)(g.H + h) * g.d, pitch, g, b0, 0, g.nk);
+        stage_rows<T>(sV, qkv + (int64_t)(2 * g.H + h) * g.d, pitch, g, b0, 0, g.nk);
+        fence_async_smem();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const int ksteps = (g.d + 15) >> 4;
+
+    if (warp == 1 && lane == 0) {
+        if (!g.manual) {
+            mbar_expect_tx(bar_ld, kTileBytes + 2 * g.nk * 128);
+            tma_load_3d(sQ, &tmQ, bar_ld, h * 64, qt * kTile, b0);
+            tma_load_3d(sK, &tmKV, bar_ld, (g.H + h) * 64, 0, b0);
+            tma_load_3d(sV, &tmKV, bar_ld, (2 * g.H + h) * 64, 0, b0);
+            mbar_wait(bar_ld, 0);
+            tc_fence_after();
+        }
+        const uint32_t idesc = make_idesc(is_bf16, 0, 0, kTile, g.nk);
+        const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK);
+        for (int k = 0; k < ksteps; ++k)
+            umma_f16(tmem_base, make_desc(qa + k * 32, 16, 1024), make_desc(ka + k * 32, 16, 1024), idesc, k ? 1u : 0u);
+        umma_commit(bar_s);
+    }
+
+    float inv_sum = 0.f, row_lse = 0.f;
+    RowId me{0, 0, 0, false};
+    const int r = (warp - 4) * 32 + lane;                 // tile row == TMEM lane (warps 4..7)
+    if (warp >= 4) {
+        me = row_id(g, b0, qt, r);
+        // keys this row may attend to, as columns of the tile
+        const int klo = g.G == 1 ? 0 : me.gi * g.spad;
+        const int khi = klo + g.S;
+        const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S - klo : nullptr;
+        const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S - klo : nullptr;
+        const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
+        const int nch = (g.nk + 31) >> 5;
+        mbar_wait(bar_s, 0);
+        tc_fence_after();
+        float mx = -INFINITY;
+        for (int ch = 0; ch < nch; ++ch) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(taddr + ch * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const int c = ch * 32 + j;
+                if (me.ok && c >= klo && c < khi) {
+                    float x = __uint_as_float(v[j]) * g.scale;
+                    if (brow) x += __ldg(brow + c);
+                    if (mrow) x += __ldg(mrow + c);
+                    mx = fmaxf(mx, x);
+                }
+            }
+        }
+        if (mx == -INFINITY) mx = 0.f;
+        float sum = 0.f;
+        for (int ch = 0; ch < nch; ++ch) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(taddr + ch * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int q8 = 0; q8 < 4; ++q8) {
+                float t[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int c = ch * 32 + q8 * 8 + e;
+                    float p = 0.f;
+                    if (me.ok && c >= klo && c < khi) {
+                        float x = __uint_as_float(v[q8 * 8 + e]) * g.scale;
+                        if (brow) x += __ldg(brow + c);
+                        if (mrow) x += __ldg(mrow + c);
+                        p = exp2f((x - mx) * kLog2e);
+                    }
+                    // the second product sees the ROUNDED probabilities: sum the same values so rows still add up to 1
+                    p = Cvt<T>::to_f(Cvt<T>::from_f(p));
+                    sum += p;
+                    t[e] = p;
+                }
+                const int c0 = ch * 32 + q8 * 8;
+                store8<T>(reinterpret_cast<T*>(sP + (c0 >> 6) * kTileBytes + r * 128 + ((((c0 >> 3) & 7) ^ (r & 7)) << 4)), t);
+            }
+        }
+        inv_sum = sum > 0.f ? 1.f / sum : 0.f;
+        row_lse = mx + logf(fmaxf(sum, 1e-30f));
+        fence_async_smem();
+        tc_fence_before();
+    }
+    __syncthreads();                                      // P is complete; every thread is done with the S columns
+    if (warp == 1 && lane == 0) {
+        tc_fence_after();
+        const uint32_t idesc = make_idesc(is_bf16, 0, 1, kTile, 64);
+        const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
+        const int steps = g.nk >> 4;
+        for (int k = 0; k < steps; ++k)
+            umma_f16(tmem_base, make_desc(pa + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                     make_desc(va + k * 2048, 8192, 1024), idesc, k ? 1u : 0u);
+        umma_commit(bar_o);
+    }
+    if (warp >= 4) {
+        const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
+        mbar_wait(bar_o, 0);
+        tc_fence_after();
+        T* orow = out + (((int64_t)(me.ok ? me.b : 0) * g.S + (me.ok ? me.s : 0)) * g.H + h) * g.d;
+#pragma unroll 1
+        for (int l = 0; l < 2; ++l) {
+            uint32_t v[32];
+            tmem_ld_32x32b_x32(taddr + l * 32, v);
+            tmem_ld_wait();
+            float o[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(v[j]) * inv_sum;
+            if (me.ok && g.d > l * 32) store_row<T>(orow + l * 32, o, min(32, g.d - l * 32));
+        }
+        if (me.ok) lse[((int64_t)me.b * g.H + h) * g.S + me.s] = row_lse;
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 256);
+}
+
+// ---------------------------------------------------------------- backward
+constexpr int kDbStride = 65;    // floats per row of the per-CTA bias-gradient accumulator (bank spread)
+constexpr int kBwdSmemBase = 10 * kTileBytes;                      // Q0 Q1 dO0 dO1 K V P(2) dS(2)
+constexpr int kBwdSmem = kBwdSmemBase + 2 * 64 * kDbStride * 4 + 1024 + 128;
+
+template <typename T>
+__device__ __forceinline__ float row_dot(const T* __restrict__ a, const T* __restrict__ b, int d) {
+    float s = 0.f;
+    if ((d & 7) == 0 && ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0) {
+        for (int e = 0; e < d; e += 8) {
+            float x[8], y[8];
+            load8<T>(a + e, x);
+            load8<T>(b + e, y);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s = fmaf(x[k], y[k], s);
+        }
+    } else {
+        for (int e = 0; e < d; e += 2) {
+            const float2 x = unpack2<T>(*reinterpret_cast<const uint32_t*>(a + e));
+            const float2 y = unpack2<T>(*reinterpret_cast<const uint32_t*>(b + e));
+            s = fmaf(x.x, y.x, fmaf(x.y, y.y, s));
+        }
+    }
+    return s;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV,
+                                                          const __grid_constant__ CUtensorMap tmDO,
+                                                          const T* __restrict__ qkv, const T* __restrict__ out,
+                                                          const T* __restrict__ dout, const float* __restrict__ lse,
+                                                          T* __restrict__ dqkv, const float* __restrict__ bias,
+                                                          const float* __restrict__ mask, float* __restrict__ dbias,
+                                                          const Geom g, int is_bf16) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sQ = smem;                          // 2 tiles
+    uint8_t* sDO = smem + 2 * kTileBytes;        // 2 tiles
+    uint8_t* sK = smem + 4 * kTileBytes;
+    uint8_t* sV = smem + 5 * kTileBytes;
+    uint8_t* sP = smem + 6 * kTileBytes;         // 2 chunks of 64 keys
+    uint8_t* sDS = smem + 8 * kTileBytes;        // 2 chunks of 64 keys
+    float* sDB = reinterpret_cast<float*>(smem + kBwdSmemBase);          // [2][64][kDbStride]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kBwdSmemBase + 2 * 64 * kDbStride * 4);
+    uint64_t* bar_ld = bars;
+    uint64_t* bar_s = bars + 1;
+    uint64_t* bar_m = bars + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int h = blockIdx.y;
+    const int64_t pitch = (int64_t)3 * g.H * g.d, opitch = (int64_t)g.H * g.d;
+    const int nunits = (g.B + g.G - 1) / g.G;
+    const int nkb = g.nq;                         // 128-key blocks per problem (== query tiles)
+    const int ksteps = (g.d + 15) >> 4;
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar_ld, 1); mbar_init(bar_s, 1); mbar_init(bar_m, 1);
+        fence_barrier_init();
+        if (!g.manual) { tma_prefetch_desc(&tmQKV); tma_prefetch_desc(&tmDO); }
+    }
+    if (warp == 2) tmem_alloc(tmem_slot, 512);
+    if (dbias != nullptr)
+        for (int i = threadIdx.x; i < 2 * 64 * kDbStride; i += blockDim.x) sDB[i] = 0.f;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDQ = tmem_base + 256, tDK = tmem_base + 384, tDV = tmem_base + 448;
+
+    uint32_t n_ld = 0, n_s = 0, n_m = 0;          // commits / transactions issued so far on each barrier (all threads count)
+    const int r = (warp - 4) * 32 + lane;
+    const uint32_t lane_sel = (uint32_t)(((warp - 4) & 3) * 32) << 16;
+
+    for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
+        const int b0 = unit * g.G;
+        float delta[2] = {0.f, 0.f}, row_lse[2] = {0.f, 0.f};
+        for (int j = 0; j < nkb; ++j) {
+            for (int i = 0; i < g.nq; ++i) {
+                const bool need_q = j == 0, need_kv = i == 0;
+                // ---- operands.  Tiles may be overwritten only once every MMA issued so far has retired.
+                if (g.manual && (need_q || need_kv)) {
+                    if (n_m > 0) mbar_wait(bar_m, (n_m - 1) & 1);
+                    if (need_q) {
+                        stage_rows<T>(sQ + i * kTileBytes, qkv + (int64_t)h * g.d, pitch, g, b0, i * kTile, kTile);
+                        stage_rows<T>(sDO + i * kTileBytes, dout + (int64_t)h * g.d, opitch, g, b0, i * kTile, kTile);
+                    }
+                    if (need_kv) {
+                        stage_rows<T>(sK, qkv + (int64_t)(g.H + h) * g.d, pitch, g, b0, j * kTile, kTile);
+                        stage_rows<T>(sV, qkv + (int64_t)(2 * g.H + h) * g.d, pitch, g, b0, j * kTile, kTile);
+                    }
+                    fence_async_smem();
+                }
+                __syncthreads();
+                if (warp == 1 && lane == 0) {
+                    if (!g.manual && (need_q || need_kv)) {
+                        if (n_m > 0) mbar_wait(bar_m, (n_m - 1) & 1);
+                        mbar_expect_tx(bar_ld, (need_q ? 2 : 0) * kTileBytes + (need_kv ? 2 : 0) * kTileBytes);
+                        if (need_q) {
+                            tma_load_3d(sQ + i * kTileBytes, &tmQKV, bar_ld, h * 64, i * kTile, b0);
+                            tma_load_3d(sDO + i * kTileBytes, &tmDO, bar_ld, h * 64, i * kTile, b0);
+                        }
+                        if (need_kv) {
+                            tma_load_3d(sK, &tmQKV, bar_ld, (g.H + h) * 64, j * kTile, b0);
+                            tma_load_3d(sV, &tmQKV, bar_ld, (2 * g.H + h) * 64, j * kTile, b0);
+                        }
+                        mbar_wait(bar_ld, n_ld & 1);
+                    }
+                    tc_fence_after();
+                    const uint32_t idesc = make_idesc(is_bf16, 0, 0, kTile, kTile);
+                    const uint32_t qa = smem_u32(sQ + i * kTileBytes), doa = smem_u32(sDO + i * kTileBytes);
+                    const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
+                    for (int k = 0; k < ksteps; ++k)
+                        umma_f16(tS, make_desc(qa + k * 32, 16, 1024), make_desc(ka + k * 32, 16, 1024), idesc, k ? 1u : 0u);
+                    for (int k = 0; k < ksteps; ++k)
+                        umma_f16(tDP, make_desc(doa + k * 32, 16, 1024), make_desc(va + k * 32, 16, 1024), idesc, k ? 1u : 0u);
+                    umma_commit(bar_s);
+                }
+                if (!g.manual && (need_q || need_kv)) ++n_ld;
+                ++n_s;
+                if (warp >= 4) {
+                    const RowId me = row_id(g, b0, i, r);
+                    if (j == 0) {
+                        // per-row constants of this query tile, fetched while the tensor core works
+                        if (me.ok) {
+                            const int64_t o = (((int64_t)me.b * g.S + me.s) * g.H + h) * g.d;
+                            delta[i] = row_dot<T>(out + o, dout + o, g.d);
+                            row_lse[i] = lse[((int64_t)me.b * g.H + h) * g.S + me.s];
+                        } else {
+                            delta[i] = 0.f; row_lse[i] = 0.f;
+                        }
+                    }
+                    const int klo = g.G == 1 ? 0 : me.gi * g.spad;       // first tile column this row attends to
+                    const int kbase = j * kTile;                          // key index of column 0 (G == 1)
+                    const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+                    const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+                    float* dbrow = dbias ? sDB + (me.gi * 64 + (me.ok ? me.s : 0)) * kDbStride : nullptr;
+                    mbar_wait(bar_s, (n_s - 1) & 1);
+                    tc_fence_after();
+#pragma unroll 1
+                    for (int ch = 0; ch < 4; ++ch) {
+                        uint32_t sv[32], dv[32];
+                        tmem_ld_32x32b_x32(tS + lane_sel + ch * 32, sv);
+                        tmem_ld_32x32b_x32(tDP + lane_sel + ch * 32, dv);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int q8 = 0; q8 < 4; ++q8) {
+                            float tp[8], td[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                const int c = ch * 32 + q8 * 8 + e;
+                                const int key = g.G == 1 ? kbase + c : c - klo;     // key index within the problem
+                                float p = 0.f, ds = 0.f;
+                                if (me.ok && key >= 0 && key < g.S && (g.G == 1 || c < klo + g.spad)) {
+                                    float x = __uint_as_float(sv[q8 * 8 + e]) * g.scale;
+                                    if (brow) x += __ldg(brow + key);
+                                    if (mrow) x += __ldg(mrow + key);
+                                    p = exp2f((x - row_lse[i]) * kLog2e);
+                                    ds = p * (__uint_as_float(dv[q8 * 8 + e]) - delta[i]);
+                                    if (dbrow) dbrow[key] += ds;
+                                }
+                                tp[e] = p;
+                                td[e] = ds * g.scale;
+                            }
+                            const int c0 = ch * 32 + q8 * 8;
+                            const int off = (c0 >> 6) * kTileBytes + r * 128 + ((((c0 >> 3) & 7) ^ (r & 7)) << 4);
+                            store8<T>(reinterpret_cast<T*>(sP + off), tp);
+                            store8<T>(reinterpret_cast<T*>(sDS + off), td);
+                        }
+                    }
+                    fence_async_smem();
+                    tc_fence_before();
+                }
+                __syncthreads();
+                if (warp == 1 && lane == 0) {
+                    tc_fence_after();
+                    const uint32_t id_t = make_idesc(is_bf16, 1, 1, kTile, 64);     // A^T forms: dV, dK
+                    const uint32_t id_n = make_idesc(is_bf16, 0, 1, kTile, 64);     // dQ
+                    const uint32_t pa = smem_u32(sP), dsa = smem_u32(sDS), ka = smem_u32(sK);
+                    const uint32_t qa = smem_u32(sQ + i * kTileBytes), doa = smem_u32(sDO + i * kTileBytes);
+                    for (int k = 0; k < 8; ++k)         // dV[key][d] += sum_q P[q][key] dO[q][d]
+                        umma_f16(tDV, make_desc(pa + k * 2048, kTileBytes, 1024), make_desc(doa + k * 2048, 8192, 1024), id_t,
+                                 (i > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < 8; ++k)         // dK[key][d] += sum_q dS[q][key] Q[q][d]
+                        umma_f16(tDK, make_desc(dsa + k * 2048, kTileBytes, 1024), make_desc(qa + k * 2048, 8192, 1024), id_t,
+                                 (i > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < 8; ++k)         // dQ[q][d] += sum_key dS[q][key] K[key][d]
+                        umma_f16(tDQ + i * 64, make_desc(dsa + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                                 make_desc(ka + k * 2048, 8192, 1024), id_n, (j > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(bar_m);
+                }
+                ++n_m;
+            }
+            // ---- dK, dV of key block j are complete
+            if (warp >= 4) {
+                mbar_wait(bar_m, (n_m - 1) & 1);
+                tc_fence_after();
+                const RowId kr = row_id(g, b0, j, r);
+#pragma unroll 1
+                for (int w = 0; w < 2; ++w) {
+                    float o[64];
+#pragma unroll
+                    for (int l = 0; l < 2; ++l) {
+                        uint32_t v[32];
+                        tmem_ld_32x32b_x32((w == 0 ? tDK : tDV) + lane_sel + l * 32, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int q = 0; q < 32; ++q) o[l * 32 + q] = __uint_as_float(v[q]);
+                    }
+                    if (kr.ok)
+                        store_row<T>(dqkv + ((((int64_t)kr.b * g.S + kr.s) * 3 + (w + 1)) * g.H + h) * g.d, o, g.d);
+                }
+                tc_fence_before();
+            }
+        }
+        // ---- dQ of every query tile is complete (the last wait above covered the last commit)
+        if (warp >= 4) {
+            tc_fence_after();
+#pragma unroll 1
+            for (int i = 0; i < g.nq; ++i) {
+                const RowId qr = row_id(g, b0, i, r);
+                float o[64];
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+                    uint32_t v[32];
+                    tmem_ld_32x32b_x32(tDQ + i * 64 + lane_sel + l * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int q = 0; q < 32; ++q) o[l * 32 + q] = __uint_as_float(v[q]);
+                }
+                if (qr.ok) store_row<T>(dqkv + ((((int64_t)qr.b * g.S + qr.s) * 3 + 0) * g.H + h) * g.d, o, g.d);
+            }
+            tc_fence_before();
+        }
+    }
+    __syncthreads();
+    if (dbias != nullptr) {
+        // rows of the two stacked problems add into the same [H][S][S] gradient
+        for (int idx = threadIdx.x; idx < g.S * g.S; idx += blockDim.x) {
+            const int q = idx / g.S, k = idx - q * g.S;
+            const float v = sDB[q * kDbStride + k] + sDB[(64 + q) * kDbStride + k];
+            if (v != 0.f) atomicAdd(dbias + ((int64_t)h * g.S + q) * g.S + k, v);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+// ---------------------------------------------------------------- host
+static int make_tmap3(CUtensorMap* tm, const void* ptr, int is_bf16, int64_t cols, int64_t S, int64_t B, int box_rows) {
+    static PFN_cuTensorMapEncodeTiled_v12000 enc =
+        reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(driver_fn("cuTensorMapEncodeTiled"));
+    B200DP_REQUIRE(enc != nullptr, "attention: cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[3] = {(cuuint64_t)cols, (cuuint64_t)S, (cuuint64_t)B};
+    cuuint64_t strides[2] = {(cuuint64_t)cols * 2, (cuuint64_t)S * cols * 2};
+    cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    const CUtensorMapDataType dt = is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+    CUresult r = enc(tm, dt, 3, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    B200DP_REQUIRE(r == CUDA_SUCCESS, "attention: cuTensorMapEncodeTiled failed (%d) cols=%lld S=%lld B=%lld", (int)r,
+                   (long long)cols, (long long)S, (long long)B);
+    return 0;
+}
+
+static int make_geom(Geom* g, int B, int H, int S, int d, float scale, int nW, const void* p0, const void* p1) {
+    B200DP_REQUIRE(B > 0 && H > 0 && S > 0 && S <= 256 && d >= 2 && d <= 64 && (d & 1) == 0,
+                   "attention: unsupported shape B=%d H=%d S=%d d=%d (S <= 256, even d <= 64)", B, H, S, d);
+    g->B = B; g->H = H; g->S = S; g->d = d; g->scale = scale; g->nW = nW;
+    g->G = S <= 64 ? 2 : 1;
+    g->spad = kTile / g->G;
+    g->nq = (S + kTile - 1) / kTile;
+    g->nk = g->G == 2 ? kTile : ((S + 15) / 16) * 16;
+    g->manual = !(d == 64 && g->G == 1 && ((uintptr_t)p0 & 15) == 0 && ((uintptr_t)p1 & 15) == 0);
+    return 0;
+}
+
+}  // namespace attn
+}  // namespace b200dp
+
+using namespace b200dp;
+using namespace b200dp::attn;
+
+extern "C" int b200dp_attention_supported(int S, int d) { return S > 0 && S <= 256 && d >= 2 && d <= 64 && (d & 1) == 0; }
+
+// out[B][S][H][d] = softmax(q k^T * scale + bias[H][S][S] + mask[b % nW][S][S]) v over the packed qkv[B][S][3][H][d];
+// lse[B][H][S] (fp32) keeps the row log-sum-exp for the backward.  bias / mask may be NULL.
+extern "C" int b200dp_attention_fwd(const void* qkv, void* out, float* lse, const float* bias, const float* mask, int nW,
+                                    int B, int H, int S, int d, float scale, b200dp_dtype dtype, void* stream) {
+    B200DP_REQUIRE(qkv && out && lse, "attention_fwd: null pointer");
+    B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "attention_fwd: fp16 / bf16 only");
+    Geom g;
+    int rc = make_geom(&g, B, H, S, d, scale, mask ? nW : 0, qkv, out);
+    if (rc) return rc;
+    const int is_bf16 = dtype == B200DP_BF16;
+    CUtensorMap tq, tkv;
+    memset(&tq, 0, sizeof(tq)); memset(&tkv, 0, sizeof(tkv));
+    if (!g.manual) {
+        bind_context_once();
+        rc = make_tmap3(&tq, qkv, is_bf16, (int64_t)3 * H * d, S, B, kTile);
+        if (rc) return rc;
+        rc = make_tmap3(&tkv, qkv, is_bf16, (int64_t)3 * H * d, S, B, g.nk);
+        if (rc) return rc;
+    }
+    const dim3 grid(g.nq, H, (B + g.G - 1) / g.G);
+    cudaStream_t s = (cudaStream_t)stream;
+#define LAUNCH(TT)                                                                                                      \
+    {                                                                                                                   \
+        auto kern = attn_fwd_kernel<TT>;                                                                                \
+        static bool configured = false;                                                                                 \
+        if (!configured) {                                                                                              \
+            B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem));             \
+            configured = true;                                                                                          \
+        }                                                                                                               \
+        kern<<<grid, 256, kFwdSmem, s>>>(tq, tkv, (const TT*)qkv, (TT*)out, lse, bias, mask, g, is_bf16);               \
+    }
+    if (is_bf16) LAUNCH(__nv_bfloat16) else LAUNCH(__half)
+#undef LAUNCH
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+// dqkv[B][S][3][H][d] from dout / out [B][S][H][d], the packed qkv and lse.  dbias ([H][S][S] fp32, S <= 64 only)
+// is ACCUMULATED into (atomic adds; the caller zeroes it); pass NULL when the bias needs no gradient.
+extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                    const float* bias, const float* mask, int nW, float* dbias, int B, int H, int S, int d,
+                                    float scale, b200dp_dtype dtype, void* stream) {
+    B200DP_REQUIRE(qkv && out && dout && lse && dqkv, "attention_bwd: null pointer");
+    B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "attention_bwd: fp16 / bf16 only");
+    B200DP_REQUIRE(dbias == nullptr || S <= 64, "attention_bwd: the bias gradient is implemented for S <= 64 (windows)");
+    Geom g;
+    int rc = make_geom(&g, B, H, S, d, scale, mask ? nW : 0, qkv, dout);
+    if (rc) return rc;
+    if (((uintptr_t)dqkv & 15) != 0 || ((uintptr_t)out & 15) != 0) g.manual = 1;
+    const int is_bf16 = dtype == B200DP_BF16;
+    CUtensorMap tq, tdo;
+    memset(&tq, 0, sizeof(tq)); memset(&tdo, 0, sizeof(tdo));
+    if (!g.manual) {
+        bind_context_once();
+        rc = make_tmap3(&tq, qkv, is_bf16, (int64_t)3 * H * d, S, B, kTile);
+        if (rc) return rc;
+        rc = make_tmap3(&tdo, dout, is_bf16, (int64_t)H * d, S, B, kTile);
+        if (rc) return rc;
+    }
+    const int nunits = (B + g.G - 1) / g.G;
+    int gx = nunits;
+    if (dbias != nullptr) {            // fewer, longer-lived CTAs: each flushes its bias-gradient partial once
+        gx = (2 * B200DP_SMS + H - 1) / H;
+        if (gx > nunits) gx = nunits;
+    }
+    const dim3 grid(gx, H, 1);
+    cudaStream_t s = (cudaStream_t)stream;
+#define LAUNCH(TT)                                                                                                      \
+    {                                                                                                                   \
+        auto kern = attn_bwd_kernel<TT>;                                                                                \
+        static bool configured = false;                                                                                 \
+        if (!configured) {                                                                                              \
+            B200DP_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));             \
+            configured = true;                                                                                          \
+        }                                                                                                               \
+        kern<<<grid, 256, kBwdSmem, s>>>(tq, tdo, (const TT*)qkv, (const TT*)out, (const TT*)dout, lse, (TT*)dqkv, bias, \
+                                         mask, dbias, g, is_bf16);                                                      \
+    }
+    if (is_bf16) LAUNCH(__nv_bfloat16) else LAUNCH(__half)
+#undef LAUNCH
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}

@@ -321,6 +321,23 @@ int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* m
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
                                 int slot_floats, void* const* call_counter, void* stream);
 
+/* Attention core on the tcgen05 tensor cores: out = softmax(q k^T * scale + bias + mask) v, forward and backward,
+ * over the PACKED projections (no per-head copies):
+ *   qkv / dqkv [B][S][3][H][d],  out / dout [B][S][H][d],  lse [B][H][S] fp32 (row log-sum-exp, written by the forward),
+ *   bias [H][S][S] fp32 or NULL (window attention: relative-position bias),
+ *   mask [nW][S][S] fp32 or NULL, applied to batch entry b as mask[b % nW] (shifted windows),
+ *   dbias [H][S][S] fp32 or NULL: gradient of bias, ACCUMULATED with atomic adds (caller zeroes it); S <= 64 only.
+ * Envelope: S <= 256 tokens, even d <= 64 (b200dp_attention_supported).  Sequences of <= 64 tokens are stacked two
+ * to a 128-row tile.  Operands arrive by TMA when d == 64 and S > 64, else by a zero-padding copy in the kernel.
+ * Reference: the attention of the transformer models (SwinIR built at Stoke-DDP.py:206-208, window_size 8;
+ * ViT-B/16 of BASELINE config 4); the library path there is scaled_dot_product_attention. */
+int b200dp_attention_supported(int S, int d);
+int b200dp_attention_fwd(const void* qkv, void* out, float* lse, const float* bias, const float* mask, int nW, int B, int H,
+                         int S, int d, float scale, b200dp_dtype dtype, void* stream);
+int b200dp_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, const float* bias,
+                         const float* mask, int nW, float* dbias, int B, int H, int S, int d, float scale,
+                         b200dp_dtype dtype, void* stream);
+
 /* Attention layout moves (ViT / SwinIR): W per-head tensors [B][H][S][d] <-> one token-major tensor
  * [B][S][W][H][d] in one streaming pass (W = 3: packed q/k/v gradient; W = 1: merge heads).  Rows of
  * d elements must be multiples of 16 bytes.  Reference: the reshape / permute / stack chains around

@@ -22,7 +22,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from ..ops import gemm as _gemm
-from ..ops.attention import merge_heads, split_qkv
+from ..ops.attention import attention, attention_reference, attention_supported
 from ..ops.layers import LayerNorm, Linear
 
 __all__ = ["SwinIR"]
@@ -79,19 +79,15 @@ class WindowAttention(nn.Module):
 
     def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
         B_, N, C = x.shape
-        q, k, v = split_qkv(self.qkv(x), self.num_heads)      # strided per-head views; packed gradient in one pass
-        bias = self.relative_position_bias_table[self.relative_position_index.view(-1)].view(N, N, -1)
-        bias = bias.permute(2, 0, 1).unsqueeze(0).to(q.dtype)            # [1, heads, N, N]
-        if mask is not None:
-            nW = mask.shape[0]
-            m = mask.to(q.dtype).view(1, nW, 1, N, N).expand(B_ // nW, -1, -1, -1, -1).reshape(B_, 1, N, N)
-            bias = bias + m                                               # [B_, heads, N, N]
+        qkv = self.qkv(x)
+        bias = self.relative_position_bias_table[self.relative_position_index.view(-1)].view(N, N, -1).permute(2, 0, 1)
+        p_drop = self.attn_drop.p if self.training else 0.0
+        if p_drop == 0.0 and attention_supported(qkv, self.num_heads, bias):
+            # one tcgen05 kernel: softmax(q k^T * scale + relative-position bias + shift mask) v, two windows per tile
+            o = attention(qkv, self.num_heads, self.scale, bias, mask)
         else:
-            bias = bias.expand(B_, -1, -1, -1)
-        # one fused attention call: softmax(q k^T * scale + bias) v
-        o = F.scaled_dot_product_attention(q, k, v, attn_mask=bias,
-                                           dropout_p=self.attn_drop.p if self.training else 0.0, scale=self.scale)
-        return self.proj_drop(self.proj(merge_heads(o)))
+            o = attention_reference(qkv, self.num_heads, self.scale, bias, mask, dropout_p=p_drop)
+        return self.proj_drop(self.proj(o))
 
 
 class SwinTransformerBlock(nn.Module):

@@ -5,9 +5,9 @@ Shapes and parameter count match torchvision's ``vit_b_16`` (86,567,656 paramete
 (``fsdp_wrap_classes``): ≈7.1 M parameters → 14 MB in bf16, 1.8 MB per rank at 8 GPUs.
 
 B200-first: linears go through ``ops.layers.Linear`` (tcgen05 GEMM with fused bias /
-GELU epilogue on CUDA), LayerNorm through the fused kernel, attention through
-``F.scaled_dot_product_attention`` (library flash kernel: attention over 197 tokens is
-<4 % of the block's FLOPs and is not on the work list).
+GELU epilogue on CUDA), LayerNorm through the fused kernel, attention through the
+tcgen05 kernel pair of ``csrc/attn_sm100.cu`` (``ops.attention.attention``: q / k / v are read
+from the packed projection, the backward writes the packed gradient).
 """
 from __future__ import annotations
 
@@ -19,7 +19,7 @@ import torch.nn.functional as F
 
 from ..ops import dispatch
 from ..ops import gemm as _gemm
-from ..ops.attention import merge_heads, split_qkv
+from ..ops.attention import attention, attention_reference, attention_supported
 from ..ops.layers import LayerNorm, Linear
 
 __all__ = ["VisionTransformer", "vit_b_16", "vit_s_16", "vit_tiny"]
@@ -40,8 +40,10 @@ class Attention(nn.Module):
         self.out_proj = Linear(dim, dim)
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-        q, k, v = split_qkv(self.in_proj(x), self.heads)
-        return self.out_proj(merge_heads(F.scaled_dot_product_attention(q, k, v)), residual=residual)
+        qkv = self.in_proj(x)
+        # tcgen05 attention over the packed projection (csrc/attn_sm100.cu); library kernel outside its envelope
+        o = attention(qkv, self.heads) if attention_supported(qkv, self.heads) else attention_reference(qkv, self.heads)
+        return self.out_proj(o, residual=residual)
 
 
 class MLP(nn.Module):

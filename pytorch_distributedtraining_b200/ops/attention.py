@@ -1,8 +1,10 @@
-"""Layout glue around the attention core of the transformer models (ViT-B/16, SwinIR).
+"""Attention for the transformer models (ViT-B/16, SwinIR).
 
-The attention product itself is the library flash kernel (``F.scaled_dot_product_attention``; DESIGN.md
-lists it under "still on a library kernel").  What this module owns is everything between the packed
-``[B, S, 3*D]`` projection and that kernel, forward and backward:
+``attention(qkv, heads, ...)`` is the tcgen05 kernel pair of ``csrc/attn_sm100.cu``: it reads q / k / v straight
+out of the packed ``[B, S, 3*D]`` projection, writes the token-major ``[B, S, D]`` tensor the out projection
+consumes, and its backward writes the packed ``[B, S, 3*D]`` gradient — no per-head copies in either direction.
+Shapes outside its envelope (more than 256 tokens, head dimension above 64) use the library kernel
+(``F.scaled_dot_product_attention``) with the layout helpers below:
 
   * ``split_qkv``: q / k / v as strided per-head views of the projection output (no copy); the backward
     packs the three per-head gradients into the token-major ``[B, S, 3, H, d]`` gradient of the
@@ -16,7 +18,7 @@ transformer model (Stoke-DDP.py:206-208).
 from __future__ import annotations
 
 import ctypes
-from typing import Tuple
+from typing import Optional, Tuple
 
 import torch
 
@@ -104,6 +106,99 @@ class _MergeHeads(torch.autograd.Function):
         if ctx.mode == "kernel" and dy.is_contiguous():
             return _tokens_to_heads(dy, B, H, S, d, 1)[0]
         return dy.reshape(B, S, H, d).transpose(1, 2)
+
+
+def attention_supported(qkv: torch.Tensor, heads: int, bias: Optional[torch.Tensor] = None) -> bool:
+    """Envelope of the tcgen05 attention kernels: CUDA fp16 / bf16, packed ``[B, S, 3 * heads * d]`` projection,
+    at most 256 tokens, even head dimension <= 64; a learnable additive bias needs S <= 64 (window attention)."""
+    if not (qkv.is_cuda and qkv.dtype in _HALF and qkv.dim() == 3 and dispatch.enabled("attn") and dispatch._lib_ok()):
+        return False
+    B, S, D3 = qkv.shape
+    if D3 % (3 * heads) != 0:
+        return False
+    d = D3 // (3 * heads)
+    if not (0 < S <= 256 and 2 <= d <= 64 and d % 2 == 0):
+        return False
+    if bias is not None and bias.requires_grad and S > 64:
+        return False
+    return True
+
+
+class _AttentionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, heads, scale, bias, mask):  # type: ignore[override]
+        from .fused import DT
+        lib = require_library()
+        if not qkv.is_contiguous():
+            qkv = qkv.contiguous()
+        B, S, D3 = qkv.shape
+        d = D3 // (3 * heads)
+        out = torch.empty((B, S, heads * d), dtype=qkv.dtype, device=qkv.device)
+        lse = torch.empty((B, heads, S), dtype=torch.float32, device=qkv.device)
+        b32 = None if bias is None else bias.detach().float().contiguous()        # [H, S, S]
+        m32 = None if mask is None else mask.detach().float().contiguous()        # [nW, S, S]
+        nW = 0 if m32 is None else m32.shape[0]
+        check(lib.b200dp_attention_fwd(ptr(qkv), ptr(out), ptr(lse), ptr(b32), ptr(m32), nW, B, heads, S, d,
+                                       ctypes.c_float(scale), DT[qkv.dtype], stream_ptr(qkv.device)), "attention_fwd")
+        ctx.save_for_backward(qkv, out, lse, b32, m32)
+        ctx.geom = (B, heads, S, d, scale, nW)
+        ctx.bias_dtype = None if bias is None else bias.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):  # type: ignore[override]
+        from .fused import DT
+        lib = require_library()
+        qkv, out, lse, b32, m32 = ctx.saved_tensors
+        B, H, S, d, scale, nW = ctx.geom
+        if dout.dtype != qkv.dtype:
+            dout = dout.to(qkv.dtype)
+        if not dout.is_contiguous():
+            dout = dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        dbias = None
+        if b32 is not None and ctx.needs_input_grad[3]:
+            dbias = torch.zeros((H, S, S), dtype=torch.float32, device=qkv.device)
+        check(lib.b200dp_attention_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), ptr(b32), ptr(m32), nW,
+                                       ptr(dbias), B, H, S, d, ctypes.c_float(scale), DT[qkv.dtype],
+                                       stream_ptr(qkv.device)), "attention_bwd")
+        if dbias is not None and dbias.dtype != ctx.bias_dtype:
+            dbias = dbias.to(ctx.bias_dtype)
+        return dqkv, None, None, dbias, None
+
+
+def attention(qkv: torch.Tensor, heads: int, scale: Optional[float] = None, bias: Optional[torch.Tensor] = None,
+              mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``softmax(q k^T * scale + bias + mask) v`` over the packed projection ``qkv [B, S, 3 * heads * d]``
+    (memory order ``[B][S][3][heads][d]``); returns ``[B, S, heads * d]``.
+
+    ``bias``: ``[heads, S, S]`` (may require grad: the relative-position bias of window attention);
+    ``mask``: ``[nW, S, S]`` constant, applied to batch entry ``b`` as ``mask[b % nW]`` (shifted windows).
+    Call ``attention_supported`` first; outside the envelope use ``attention_reference``."""
+    d = qkv.shape[-1] // (3 * heads)
+    return _AttentionFn.apply(qkv, heads, float(scale if scale is not None else d ** -0.5), bias, mask)
+
+
+def attention_reference(qkv: torch.Tensor, heads: int, scale: Optional[float] = None, bias: Optional[torch.Tensor] = None,
+                        mask: Optional[torch.Tensor] = None, dropout_p: float = 0.0) -> torch.Tensor:
+    """Same contract on the library kernel (shapes outside the envelope, CPU, attention dropout)."""
+    import torch.nn.functional as F
+    B, S, _ = qkv.shape
+    q, k, v = split_qkv(qkv, heads)
+    attn_mask = None
+    if bias is not None:
+        attn_mask = bias.unsqueeze(0).to(q.dtype)
+        if mask is not None:
+            nW = mask.shape[0]
+            m = mask.to(q.dtype).view(1, nW, 1, S, S).expand(B // nW, -1, -1, -1, -1).reshape(B, 1, S, S)
+            attn_mask = attn_mask + m
+        else:
+            attn_mask = attn_mask.expand(B, -1, -1, -1)
+    elif mask is not None:
+        nW = mask.shape[0]
+        attn_mask = mask.to(q.dtype).view(1, nW, 1, S, S).expand(B // nW, -1, -1, -1, -1).reshape(B, 1, S, S)
+    o = F.scaled_dot_product_attention(q, k, v, attn_mask=attn_mask, dropout_p=dropout_p, scale=scale)
+    return merge_heads(o)
 
 
 def split_qkv(qkv: torch.Tensor, heads: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
