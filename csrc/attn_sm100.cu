@@ -91,21 +91,93 @@ __device__ __forceinline__ RowId row_id(const Geom& g, int b0, int tile, int r) 
     return o;
 }
 
-template <typename T>
-__device__ __forceinline__ void store_row(T* dst, const float* v, int d) {
+// First d of N fp32 values -> 16-bit row in global memory (fully unrolled with predicates: v stays in registers).
+template <typename T, int N>
+__device__ __forceinline__ void store_row(T* dst, const float (&v)[N], int d) {
     if ((d & 7) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-        for (int e = 0; e < d; e += 8) {
-            float t[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) t[k] = v[e + k];
-            store8<T>(dst + e, t);
+        for (int e = 0; e < N; e += 8) {
+            if (e < d) {
+                const float t[8] = {v[e], v[e + 1], v[e + 2], v[e + 3], v[e + 4], v[e + 5], v[e + 6], v[e + 7]};
+                store8<T>(dst + e, t);
+            }
         }
     } else {
-        for (int e = 0; e < d; e += 2) {
-            T pr[2] = {Cvt<T>::from_f(v[e]), Cvt<T>::from_f(v[e + 1])};
-            *reinterpret_cast<uint32_t*>(dst + e) = *reinterpret_cast<const uint32_t*>(pr);
+#pragma unroll
+        for (int e = 0; e < N; e += 2) {
+            if (e < d) {
+                T pr[2] = {Cvt<T>::from_f(v[e]), Cvt<T>::from_f(v[e + 1])};
+                *reinterpret_cast<uint32_t*>(dst + e) = *reinterpret_cast<const uint32_t*>(pr);
+            }
         }
     }
+}
+
+// 32 consecutive additive terms (bias + mask) of one score row, starting at key k0: every load is issued before the
+// first use (no branches around them), out-of-range keys read a clamped address and are masked by the caller.
+__device__ __forceinline__ void load_add32(float (&add)[32], const float* __restrict__ brow, const float* __restrict__ mrow,
+                                           int k0, int S) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) add[j] = 0.f;
+    const bool vec = (S & 3) == 0 && k0 >= 0 && k0 + 32 <= S;
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+        const float* row = w == 0 ? brow : mrow;
+        if (row == nullptr) continue;
+        if (vec) {
+            float4 t[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) t[j] = __ldg(reinterpret_cast<const float4*>(row + k0) + j);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { add[4 * j] += t[j].x; add[4 * j + 1] += t[j].y; add[4 * j + 2] += t[j].z; add[4 * j + 3] += t[j].w; }
+        } else {
+            float t[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) t[j] = __ldg(row + min(max(k0 + j, 0), S - 1));
+#pragma unroll
+            for (int j = 0; j < 32; ++j) add[j] += t[j];
+        }
+    }
+}
+
+// Row maximum over one 32-column chunk.  kAdd: scores carry an additive term (then the scaled score is compared);
+// otherwise the RAW accumulator is compared and the caller scales the result (scale > 0).  kFull: every column
+// of the chunk is a real key, so no per-element range test is needed.
+template <bool kAdd, bool kFull>
+__device__ __forceinline__ float chunk_max(const uint32_t (&v)[32], const float (&add)[32], float scale, int k0, int S, float m) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float x = kAdd ? fmaf(__uint_as_float(v[j]), scale, add[j]) : __uint_as_float(v[j]);
+        if (!kFull) x = (k0 + j >= 0 && k0 + j < S) ? x : -INFINITY;
+        m = fmaxf(m, x);
+    }
+    return m;
+}
+// p[j] = 2^(v[j] * sl + add[j] * log2e - off)   (exp of the shifted score; off = log2e * (row max | row lse))
+template <bool kAdd, bool kFull>
+__device__ __forceinline__ void chunk_exp(const uint32_t (&v)[32], const float (&add)[32], float sl, float off, int k0, int S,
+                                          float (&p)[32]) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        float x = exp2f(kAdd ? fmaf(__uint_as_float(v[j]), sl, fmaf(add[j], kLog2e, -off)) : fmaf(__uint_as_float(v[j]), sl, -off));
+        if (!kFull) x = (k0 + j >= 0 && k0 + j < S) ? x : 0.f;
+        p[j] = x;
+    }
+}
+#define ATTN_DISPATCH(has_add, full, CALL)                  \
+    do {                                                    \
+        if (has_add) { if (full) { CALL(true, true); } else { CALL(true, false); } }   \
+        else { if (full) { CALL(false, true); } else { CALL(false, false); } }         \
+    } while (0)
+
+// 8 values -> 16 bytes of shared memory (explicit shared-space store: the tile pointers are generic)
+template <typename T>
+__device__ __forceinline__ void sts8(uint32_t saddr, const float (&v)[8]) {
+    Vec8<T> r;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r.v[i] = Cvt<T>::from_f(v[i]);
+    const uint4 u = *reinterpret_cast<const uint4*>(&r);
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w) : "memory");
 }
 
 // ---------------------------------------------------------------- forward
@@ -173,56 +245,57 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     if (warp >= 4) {
         me = row_id(g, b0, qt, r);
         // keys this row may attend to, as columns of the tile
-        const int klo = g.G == 1 ? 0 : me.gi * g.spad;
-        const int khi = klo + g.S;
-        const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S - klo : nullptr;
-        const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S - klo : nullptr;
+        const int klo = g.G == 1 ? 0 : me.gi * g.spad;       // warp-uniform: a warp's 32 rows belong to one problem
+        const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+        const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
         const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
         const int nch = (g.nk + 31) >> 5;
+        const int ch_lo = klo >> 5, ch_hi = min(nch, (klo + g.S + 31) >> 5);      // chunks holding this problem's keys
+        const uint32_t p_row = smem_u32(sP) + r * 128;
         mbar_wait(bar_s, 0);
         tc_fence_after();
+        const bool has_add = brow != nullptr || mrow != nullptr || !(g.scale > 0.f);
         float mx = -INFINITY;
-        for (int ch = 0; ch < nch; ++ch) {
+        for (int ch = ch_lo; ch < ch_hi; ++ch) {
             uint32_t v[32];
+            float add[32];
+            const int k0 = ch * 32 - klo;
             tmem_ld_32x32b_x32(taddr + ch * 32, v);
+            if (has_add) load_add32(add, brow, mrow, k0, g.S);
             tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const int c = ch * 32 + j;
-                if (me.ok && c >= klo && c < khi) {
-                    float x = __uint_as_float(v[j]) * g.scale;
-                    if (brow) x += __ldg(brow + c);
-                    if (mrow) x += __ldg(mrow + c);
-                    mx = fmaxf(mx, x);
-                }
-            }
+            const bool full = k0 >= 0 && k0 + 32 <= g.S;
+#define CALL(A, F) mx = chunk_max<A, F>(v, add, g.scale, k0, g.S, mx)
+            ATTN_DISPATCH(has_add, full, CALL);
+#undef CALL
         }
-        if (mx == -INFINITY) mx = 0.f;
+        if (!has_add) mx *= g.scale;
+        if (!me.ok || mx == -INFINITY) mx = 0.f;
+        const float mxl = mx * kLog2e, sl = g.scale * kLog2e;
         float sum = 0.f;
         for (int ch = 0; ch < nch; ++ch) {
-            uint32_t v[32];
-            tmem_ld_32x32b_x32(taddr + ch * 32, v);
-            tmem_ld_wait();
+            float p[32];
+            if (ch >= ch_lo && ch < ch_hi) {                                      // warp-uniform
+                uint32_t v[32];
+                float add[32];
+                const int k0 = ch * 32 - klo;
+                tmem_ld_32x32b_x32(taddr + ch * 32, v);
+                if (has_add) load_add32(add, brow, mrow, k0, g.S);
+                tmem_ld_wait();
+                const bool full = k0 >= 0 && k0 + 32 <= g.S;
+#define CALL(A, F) chunk_exp<A, F>(v, add, sl, mxl, k0, g.S, p)
+                ATTN_DISPATCH(has_add, full, CALL);
+#undef CALL
+#pragma unroll
+                for (int j = 0; j < 32; ++j) sum += p[j];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) p[j] = 0.f;
+            }
 #pragma unroll
             for (int q8 = 0; q8 < 4; ++q8) {
-                float t[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const int c = ch * 32 + q8 * 8 + e;
-                    float p = 0.f;
-                    if (me.ok && c >= klo && c < khi) {
-                        float x = __uint_as_float(v[q8 * 8 + e]) * g.scale;
-                        if (brow) x += __ldg(brow + c);
-                        if (mrow) x += __ldg(mrow + c);
-                        p = exp2f((x - mx) * kLog2e);
-                    }
-                    // the second product sees the ROUNDED probabilities: sum the same values so rows still add up to 1
-                    p = Cvt<T>::to_f(Cvt<T>::from_f(p));
-                    sum += p;
-                    t[e] = p;
-                }
+                const float t[8] = {p[q8 * 8], p[q8 * 8 + 1], p[q8 * 8 + 2], p[q8 * 8 + 3], p[q8 * 8 + 4], p[q8 * 8 + 5], p[q8 * 8 + 6], p[q8 * 8 + 7]};
                 const int c0 = ch * 32 + q8 * 8;
-                store8<T>(reinterpret_cast<T*>(sP + (c0 >> 6) * kTileBytes + r * 128 + ((((c0 >> 3) & 7) ^ (r & 7)) << 4)), t);
+                sts8<T>(p_row + (c0 >> 6) * kTileBytes + ((((c0 >> 3) & 7) ^ (r & 7)) << 4), t);
             }
         }
         inv_sum = sum > 0.f ? 1.f / sum : 0.f;
@@ -254,7 +327,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
             float o[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(v[j]) * inv_sum;
-            if (me.ok && g.d > l * 32) store_row<T>(orow + l * 32, o, min(32, g.d - l * 32));
+            if (me.ok && g.d > l * 32) store_row<T, 32>(orow + l * 32, o, min(32, g.d - l * 32));
         }
         if (me.ok) lse[((int64_t)me.b * g.H + h) * g.S + me.s] = row_lse;
     }
@@ -395,42 +468,52 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                             delta[i] = 0.f; row_lse[i] = 0.f;
                         }
                     }
-                    const int klo = g.G == 1 ? 0 : me.gi * g.spad;       // first tile column this row attends to
-                    const int kbase = j * kTile;                          // key index of column 0 (G == 1)
+                    // key index of tile column c is c - koff (warp-uniform: a warp's rows belong to one problem)
+                    const int koff = g.G == 1 ? -j * kTile : me.gi * g.spad;
+                    const int ch_lo = g.G == 1 ? 0 : (koff >> 5), ch_hi = g.G == 1 ? 4 : min(4, (koff + g.S + 31) >> 5);
                     const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
                     const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
-                    float* dbrow = dbias ? sDB + (me.gi * 64 + (me.ok ? me.s : 0)) * kDbStride : nullptr;
+                    float* dbrow = (dbias && me.ok) ? sDB + (me.gi * 64 + me.s) * kDbStride : nullptr;     // rows are thread-private
+                    // rows that stand for no token get lse = +inf: their probabilities come out as exact zeros
+                    const float lsel = me.ok ? row_lse[i] * kLog2e : INFINITY, sl = g.scale * kLog2e, dl = delta[i];
+                    const bool has_add = brow != nullptr || mrow != nullptr;
+                    const uint32_t p_row = smem_u32(sP) + r * 128, ds_row = smem_u32(sDS) + r * 128;
                     mbar_wait(bar_s, (n_s - 1) & 1);
                     tc_fence_after();
 #pragma unroll 1
                     for (int ch = 0; ch < 4; ++ch) {
-                        uint32_t sv[32], dv[32];
-                        tmem_ld_32x32b_x32(tS + lane_sel + ch * 32, sv);
-                        tmem_ld_32x32b_x32(tDP + lane_sel + ch * 32, dv);
-                        tmem_ld_wait();
+                        float p[32], ds[32];
+                        if (ch >= ch_lo && ch < ch_hi) {                          // warp-uniform
+                            uint32_t sv[32], dv[32];
+                            float add[32];
+                            const int k0 = ch * 32 - koff;
+                            tmem_ld_32x32b_x32(tS + lane_sel + ch * 32, sv);
+                            tmem_ld_32x32b_x32(tDP + lane_sel + ch * 32, dv);
+                            if (has_add) load_add32(add, brow, mrow, k0, g.S);
+                            tmem_ld_wait();
+                            const bool full = k0 >= 0 && k0 + 32 <= g.S;
+#define CALL(A, F) chunk_exp<A, F>(sv, add, sl, lsel, k0, g.S, p)
+                            ATTN_DISPATCH(has_add, full, CALL);
+#undef CALL
+#pragma unroll
+                            for (int jj = 0; jj < 32; ++jj) ds[jj] = p[jj] * (__uint_as_float(dv[jj]) - dl);
+                            if (dbrow) {
+#pragma unroll
+                                for (int jj = 0; jj < 32; ++jj) dbrow[min(max(k0 + jj, 0), 63)] += ds[jj];   // ds == 0 where clamped
+                            }
+                        } else {
+#pragma unroll
+                            for (int jj = 0; jj < 32; ++jj) { p[jj] = 0.f; ds[jj] = 0.f; }
+                        }
 #pragma unroll
                         for (int q8 = 0; q8 < 4; ++q8) {
                             float tp[8], td[8];
 #pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                const int c = ch * 32 + q8 * 8 + e;
-                                const int key = g.G == 1 ? kbase + c : c - klo;     // key index within the problem
-                                float p = 0.f, ds = 0.f;
-                                if (me.ok && key >= 0 && key < g.S && (g.G == 1 || c < klo + g.spad)) {
-                                    float x = __uint_as_float(sv[q8 * 8 + e]) * g.scale;
-                                    if (brow) x += __ldg(brow + key);
-                                    if (mrow) x += __ldg(mrow + key);
-                                    p = exp2f((x - row_lse[i]) * kLog2e);
-                                    ds = p * (__uint_as_float(dv[q8 * 8 + e]) - delta[i]);
-                                    if (dbrow) dbrow[key] += ds;
-                                }
-                                tp[e] = p;
-                                td[e] = ds * g.scale;
-                            }
+                            for (int e = 0; e < 8; ++e) { tp[e] = p[q8 * 8 + e]; td[e] = ds[q8 * 8 + e] * g.scale; }
                             const int c0 = ch * 32 + q8 * 8;
-                            const int off = (c0 >> 6) * kTileBytes + r * 128 + ((((c0 >> 3) & 7) ^ (r & 7)) << 4);
-                            store8<T>(reinterpret_cast<T*>(sP + off), tp);
-                            store8<T>(reinterpret_cast<T*>(sDS + off), td);
+                            const uint32_t off = (c0 >> 6) * kTileBytes + ((((c0 >> 3) & 7) ^ (r & 7)) << 4);
+                            sts8<T>(p_row + off, tp);
+                            sts8<T>(ds_row + off, td);
                         }
                     }
                     fence_async_smem();
@@ -473,7 +556,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                         for (int q = 0; q < 32; ++q) o[l * 32 + q] = __uint_as_float(v[q]);
                     }
                     if (kr.ok)
-                        store_row<T>(dqkv + ((((int64_t)kr.b * g.S + kr.s) * 3 + (w + 1)) * g.H + h) * g.d, o, g.d);
+                        store_row<T, 64>(dqkv + ((((int64_t)kr.b * g.S + kr.s) * 3 + (w + 1)) * g.H + h) * g.d, o, g.d);
                 }
                 tc_fence_before();
             }
@@ -493,7 +576,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
 #pragma unroll
                     for (int q = 0; q < 32; ++q) o[l * 32 + q] = __uint_as_float(v[q]);
                 }
-                if (qr.ok) store_row<T>(dqkv + ((((int64_t)qr.b * g.S + qr.s) * 3 + 0) * g.H + h) * g.d, o, g.d);
+                if (qr.ok) store_row<T, 64>(dqkv + ((((int64_t)qr.b * g.S + qr.s) * 3 + 0) * g.H + h) * g.d, o, g.d);
             }
             tc_fence_before();
         }
