@@ -64,19 +64,21 @@ template <typename T>
 __device__ __forceinline__ void stage_rows(uint8_t* dst, const T* __restrict__ src, int64_t pitch /* elements between tokens */,
                                            const Geom& g, int b0, int s0, int rows) {
     const int sp_rows = g.G == 1 ? (1 << 20) : g.spad;      // one problem: every row is a token of it
+    const uint32_t sdst = smem_u32(dst);
     for (int row = threadIdx.x; row < rows; row += blockDim.x) {
         const int gi = row / sp_rows, lr = row - gi * sp_rows;
         const int b = b0 + gi, s = s0 + lr;
-        uint8_t* rp = dst + row * 128;
+        const bool ok = b < g.B && s < g.S && gi < g.G;
+        const uint32_t* sp = reinterpret_cast<const uint32_t*>(src + ((int64_t)(ok ? b : 0) * g.S + (ok ? s : 0)) * pitch);
+        const int nw = ok ? (g.d >> 1) : 0;                  // 32-bit words of this row that exist
+        // every load is issued before the first store; words past the head dimension stay zero
+        uint32_t w[32];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(rp + j * 16) = make_uint4(0, 0, 0, 0);
-        if (b < g.B && s < g.S && gi < g.G) {
-            const T* sp = src + ((int64_t)b * g.S + s) * pitch;
-            for (int e = 0; e < g.d; e += 2) {
-                const uint32_t w = *reinterpret_cast<const uint32_t*>(sp + e);
-                *reinterpret_cast<uint32_t*>(rp + (((e >> 3) ^ (row & 7)) << 4) + (e & 7) * 2) = w;
-            }
-        }
+        for (int e = 0; e < 32; ++e) w[e] = e < nw ? __ldg(sp + e) : 0u;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((j ^ (row & 7)) << 4)),
+                         "r"(w[4 * j]), "r"(w[4 * j + 1]), "r"(w[4 * j + 2]), "r"(w[4 * j + 3]) : "memory");
     }
 }
 
@@ -140,18 +142,66 @@ __device__ __forceinline__ void load_add32(float (&add)[32], const float* __rest
     }
 }
 
+// Window attention (two stacked problems of <= 64 tokens): bias[h] + mask[window] for both problems of the tile is
+// staged ONCE in shared memory with coalesced reads, as sAdd[gi][row][k ^ (row & 31)] — the XOR makes the row-wise
+// reads of the softmax threads (lane = row) hit 32 different banks.  Reading the [S][S] rows straight from global
+// memory costs one 128-byte line per lane per load.
+__device__ __forceinline__ void stage_add(float* sAdd, const float* __restrict__ bias, const float* __restrict__ mask,
+                                          const Geom& g, int h, int b0) {
+    const int S = g.S;
+    if (S == 64 && blockDim.x == 256) {
+        // the common window (8 x 8): 2 x 64 x 64 floats = 2048 float4, 8 per thread, every load issued before the first store
+        const bool has_m = mask != nullptr && g.nW > 0;
+        float4 bv[8], mv[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int idx4 = threadIdx.x + it * 256, gi = idx4 >> 10, row = (idx4 >> 4) & 63, k4 = (idx4 & 15) * 4;
+            const bool live = b0 + gi < g.B;
+            bv[it] = (bias && live) ? __ldg(reinterpret_cast<const float4*>(bias + ((int64_t)h * 64 + row) * 64 + k4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            mv[it] = (has_m && live) ? __ldg(reinterpret_cast<const float4*>(mask + ((int64_t)((b0 + gi) % g.nW) * 64 + row) * 64 + k4))
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int idx4 = threadIdx.x + it * 256, gi = idx4 >> 10, row = (idx4 >> 4) & 63, k4 = (idx4 & 15) * 4;
+            float* dst = sAdd + gi * 4096 + row * 64;
+            const int m = row & 31;
+            dst[(k4 + 0) ^ m] = bv[it].x + mv[it].x;
+            dst[(k4 + 1) ^ m] = bv[it].y + mv[it].y;
+            dst[(k4 + 2) ^ m] = bv[it].z + mv[it].z;
+            dst[(k4 + 3) ^ m] = bv[it].w + mv[it].w;
+        }
+        return;
+    }
+    for (int idx = threadIdx.x; idx < 2 * S * S; idx += blockDim.x) {
+        const int gi = idx / (S * S), rem = idx - gi * S * S;
+        const int row = rem / S, k = rem - row * S;
+        float v = 0.f;
+        if (b0 + gi < g.B) {
+            if (bias) v += __ldg(bias + ((int64_t)h * S + row) * S + k);
+            if (mask && g.nW > 0) v += __ldg(mask + ((int64_t)((b0 + gi) % g.nW) * S + row) * S + k);
+        }
+        sAdd[gi * 4096 + row * 64 + (k ^ (row & 31))] = v;
+    }
+}
+__device__ __forceinline__ void smem_add32(float (&add)[32], const float* sAddRow /* sAdd + gi*4096 + row*64 */, int row, int k0) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) add[j] = sAddRow[(k0 + j) ^ (row & 31)];
+}
+
 // Row maximum over one 32-column chunk.  kAdd: scores carry an additive term (then the scaled score is compared);
 // otherwise the RAW accumulator is compared and the caller scales the result (scale > 0).  kFull: every column
 // of the chunk is a real key, so no per-element range test is needed.
 template <bool kAdd, bool kFull>
 __device__ __forceinline__ float chunk_max(const uint32_t (&v)[32], const float (&add)[32], float scale, int k0, int S, float m) {
+    float m4[4] = {m, -INFINITY, -INFINITY, -INFINITY};        // four chains instead of one 32-long dependency
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
         float x = kAdd ? fmaf(__uint_as_float(v[j]), scale, add[j]) : __uint_as_float(v[j]);
         if (!kFull) x = (k0 + j >= 0 && k0 + j < S) ? x : -INFINITY;
-        m = fmaxf(m, x);
+        m4[j & 3] = fmaxf(m4[j & 3], x);
     }
-    return m;
+    return fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
 }
 // p[j] = 2^(v[j] * sl + add[j] * log2e - off)   (exp of the shifted score; off = log2e * (row max | row lse))
 template <bool kAdd, bool kFull>
@@ -181,7 +231,7 @@ __device__ __forceinline__ void sts8(uint32_t saddr, const float (&v)[8]) {
 }
 
 // ---------------------------------------------------------------- forward
-constexpr int kFwdSmem = 65536 + 32768 + 1024 /*align*/ + 128 /*barriers*/;
+constexpr int kFwdSmem = 65536 + 32768 + 1024 /*align*/ + 128 /*barriers*/ + 2048 /*row partials*/;
 
 template <typename T>
 __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ,
@@ -200,6 +250,8 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     uint64_t* bar_s = bars + 1;
     uint64_t* bar_o = bars + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+    float* s_max = reinterpret_cast<float*>(bars + 16);      // [2][128] partial row maxima of the two warp halves
+    float* s_sum = s_max + 2 * kTile;                        // [2][128] partial row sums
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qt = blockIdx.x, h = blockIdx.y, b0 = blockIdx.z * g.G;
@@ -211,6 +263,10 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
         if (!g.manual) { tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmKV); }
     }
     if (warp == 2) tmem_alloc(tmem_slot, 256);
+    // window attention: the additive tile lives in the upper half of the P region (nk = 128 uses only the lower half)
+    float* sAdd = reinterpret_cast<float*>(smem + 32768);
+    const bool use_sadd = g.G == 2 && (bias != nullptr || (mask != nullptr && g.nW > 0));
+    if (use_sadd) stage_add(sAdd, bias, mask, g, h, b0);
     if (g.manual) {
         stage_rows<T>(sQ, qkv + (int64_t)h * g.d, pitch, g, b0, qt * kTile, kTile);
         stage_rows<T>(sK, qkv + (int64_t)(g.H + h) * g.d, pitch, g, b0, 0, g.nk);
@@ -223,113 +279,173 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     const uint32_t tmem_base = *tmem_slot;
     const int ksteps = (g.d + 15) >> 4;
 
-    if (warp == 1 && lane == 0) {
-        if (!g.manual) {
-            mbar_expect_tx(bar_ld, kTileBytes + 2 * g.nk * 128);
-            tma_load_3d(sQ, &tmQ, bar_ld, h * 64, qt * kTile, b0);
-            tma_load_3d(sK, &tmKV, bar_ld, (g.H + h) * 64, 0, b0);
-            tma_load_3d(sV, &tmKV, bar_ld, (2 * g.H + h) * 64, 0, b0);
-            mbar_wait(bar_ld, 0);
-            tc_fence_after();
+    if (warp == 1) {
+        // lanes 1..31 park at the __syncwarp below instead of sleeping on an mbarrier: a suspended
+        // try_wait of the sibling lanes must never delay the one lane that issues the TMA / MMA work
+        if (lane == 0) {
+            if (!g.manual) {
+                mbar_expect_tx(bar_ld, kTileBytes + 2 * g.nk * 128);
+                tma_load_3d(sQ, &tmQ, bar_ld, h * 64, qt * kTile, b0);
+                tma_load_3d(sK, &tmKV, bar_ld, (g.H + h) * 64, 0, b0);
+                tma_load_3d(sV, &tmKV, bar_ld, (2 * g.H + h) * 64, 0, b0);
+                mbar_wait(bar_ld, 0);
+                tc_fence_after();
+            }
+            const uint32_t idesc = make_idesc(is_bf16, 0, 0, kTile, g.nk);
+            const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK);
+            for (int k = 0; k < ksteps; ++k)
+                umma_f16(tmem_base, make_desc(qa + k * 32, 16, 1024), make_desc(ka + k * 32, 16, 1024), idesc, k ? 1u : 0u);
+            umma_commit(bar_s);
         }
-        const uint32_t idesc = make_idesc(is_bf16, 0, 0, kTile, g.nk);
-        const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK);
-        for (int k = 0; k < ksteps; ++k)
-            umma_f16(tmem_base, make_desc(qa + k * 32, 16, 1024), make_desc(ka + k * 32, 16, 1024), idesc, k ? 1u : 0u);
-        umma_commit(bar_s);
+        __syncwarp();
     }
 
-    float inv_sum = 0.f, row_lse = 0.f;
-    RowId me{0, 0, 0, false};
-    const int r = (warp - 4) * 32 + lane;                 // tile row == TMEM lane (warps 4..7)
-    if (warp >= 4) {
-        me = row_id(g, b0, qt, r);
-        // keys this row may attend to, as columns of the tile
-        const int klo = g.G == 1 ? 0 : me.gi * g.spad;       // warp-uniform: a warp's 32 rows belong to one problem
-        const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
-        const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
-        const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
-        const int nch = (g.nk + 31) >> 5;
-        const int ch_lo = klo >> 5, ch_hi = min(nch, (klo + g.S + 31) >> 5);      // chunks holding this problem's keys
-        const uint32_t p_row = smem_u32(sP) + r * 128;
-        mbar_wait(bar_s, 0);
-        tc_fence_after();
-        const bool has_add = brow != nullptr || mrow != nullptr || !(g.scale > 0.f);
-        float mx = -INFINITY;
-        for (int ch = ch_lo; ch < ch_hi; ++ch) {
+    // ---- softmax: ALL eight warps.  Warps w and w + 4 reach the same TMEM lane quarter; they split a row's
+    //      32-column chunks by parity and combine their row maxima / sums through shared memory.
+    const int r = (warp & 3) * 32 + lane, half = warp >> 2;       // tile row == TMEM lane
+    const RowId me = row_id(g, b0, qt, r);
+    const int klo = g.G == 1 ? 0 : me.gi * g.spad;                // warp-uniform: a warp's 32 rows belong to one problem
+    const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+    const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+    const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    const int nch = (g.nk + 31) >> 5;
+    const int ch_lo = klo >> 5, ch_hi = min(nch, (klo + g.S + 31) >> 5);          // chunks holding this problem's keys
+    const uint32_t p_row = smem_u32(sP) + r * 128;
+    const bool has_add = brow != nullptr || mrow != nullptr || !(g.scale > 0.f);
+    const float* sadd_row = sAdd + me.gi * 4096 + (me.ok ? me.s : 0) * 64;
+    mbar_wait(bar_s, 0);
+    tc_fence_after();
+    float mx = -INFINITY;
+    const bool plain = !has_add && g.G == 1;          // ViT: no additive term, one problem per tile
+    if (plain) {
+        // two register buffers, the TMEM load of the next chunk in flight while this one is reduced
+        uint32_t va[32], vb[32];
+        float dummy[32];
+        int ch = ch_lo + ((ch_lo ^ half) & 1);
+        if (ch < ch_hi) tmem_ld_32x32b_x32(taddr + ch * 32, va);
+        while (ch < ch_hi) {
+            tmem_ld_wait();
+            if (ch + 2 < ch_hi) tmem_ld_32x32b_x32(taddr + (ch + 2) * 32, vb);
+            if (ch * 32 + 32 <= g.S) mx = chunk_max<false, true>(va, dummy, 1.f, ch * 32, g.S, mx);
+            else mx = chunk_max<false, false>(va, dummy, 1.f, ch * 32, g.S, mx);
+            ch += 2;
+            if (ch >= ch_hi) break;
+            tmem_ld_wait();
+            if (ch + 2 < ch_hi) tmem_ld_32x32b_x32(taddr + (ch + 2) * 32, va);
+            if (ch * 32 + 32 <= g.S) mx = chunk_max<false, true>(vb, dummy, 1.f, ch * 32, g.S, mx);
+            else mx = chunk_max<false, false>(vb, dummy, 1.f, ch * 32, g.S, mx);
+            ch += 2;
+        }
+    }
+    for (int ch = ch_lo + ((ch_lo ^ half) & 1); !plain && ch < ch_hi; ch += 2) {
+        uint32_t v[32];
+        float add[32];
+        const int k0 = ch * 32 - klo;
+        tmem_ld_32x32b_x32(taddr + ch * 32, v);
+        if (use_sadd) smem_add32(add, sadd_row, me.ok ? me.s : 0, k0);
+        else if (has_add) load_add32(add, brow, mrow, k0, g.S);
+        tmem_ld_wait();
+        const bool full = k0 >= 0 && k0 + 32 <= g.S;
+#define CALL(A, F) mx = chunk_max<A, F>(v, add, g.scale, k0, g.S, mx)
+        ATTN_DISPATCH(has_add, full, CALL);
+#undef CALL
+    }
+    if (!has_add) mx *= g.scale;
+    s_max[half * kTile + r] = mx;
+    __syncthreads();
+    mx = fmaxf(s_max[r], s_max[kTile + r]);
+    if (!me.ok || mx == -INFINITY) mx = 0.f;
+    const float mxl = mx * kLog2e, sl = g.scale * kLog2e;
+    float sum = 0.f;
+    auto put_p = [&](int ch, const float (&p)[32]) {
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s4[j & 3] += p[j];
+        sum += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+#pragma unroll
+        for (int q8 = 0; q8 < 4; ++q8) {
+            const float t[8] = {p[q8 * 8], p[q8 * 8 + 1], p[q8 * 8 + 2], p[q8 * 8 + 3], p[q8 * 8 + 4], p[q8 * 8 + 5], p[q8 * 8 + 6], p[q8 * 8 + 7]};
+            const int c0 = ch * 32 + q8 * 8;
+            sts8<T>(p_row + (c0 >> 6) * kTileBytes + ((((c0 >> 3) & 7) ^ (r & 7)) << 4), t);
+        }
+    };
+    if (plain) {
+        // every chunk of [0, nch) is live
+        uint32_t va[32], vb[32];
+        float dummy[32], p[32];
+        int ch = half;
+        const int end = nch;
+        if (ch < end) tmem_ld_32x32b_x32(taddr + ch * 32, va);
+        while (ch < end) {
+            tmem_ld_wait();
+            if (ch + 2 < end) tmem_ld_32x32b_x32(taddr + (ch + 2) * 32, vb);
+            if (ch * 32 + 32 <= g.S) chunk_exp<false, true>(va, dummy, sl, mxl, ch * 32, g.S, p);
+            else chunk_exp<false, false>(va, dummy, sl, mxl, ch * 32, g.S, p);
+            put_p(ch, p);
+            ch += 2;
+            if (ch >= end) break;
+            tmem_ld_wait();
+            if (ch + 2 < end) tmem_ld_32x32b_x32(taddr + (ch + 2) * 32, va);
+            if (ch * 32 + 32 <= g.S) chunk_exp<false, true>(vb, dummy, sl, mxl, ch * 32, g.S, p);
+            else chunk_exp<false, false>(vb, dummy, sl, mxl, ch * 32, g.S, p);
+            put_p(ch, p);
+            ch += 2;
+        }
+    }
+    for (int ch = half; !plain && ch < nch; ch += 2) {
+        float p[32];
+        if (ch >= ch_lo && ch < ch_hi) {                                          // warp-uniform
             uint32_t v[32];
             float add[32];
             const int k0 = ch * 32 - klo;
             tmem_ld_32x32b_x32(taddr + ch * 32, v);
-            if (has_add) load_add32(add, brow, mrow, k0, g.S);
+            if (use_sadd) smem_add32(add, sadd_row, me.ok ? me.s : 0, k0);
+            else if (has_add) load_add32(add, brow, mrow, k0, g.S);
             tmem_ld_wait();
             const bool full = k0 >= 0 && k0 + 32 <= g.S;
-#define CALL(A, F) mx = chunk_max<A, F>(v, add, g.scale, k0, g.S, mx)
+#define CALL(A, F) chunk_exp<A, F>(v, add, sl, mxl, k0, g.S, p)
             ATTN_DISPATCH(has_add, full, CALL);
 #undef CALL
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) p[j] = 0.f;
         }
-        if (!has_add) mx *= g.scale;
-        if (!me.ok || mx == -INFINITY) mx = 0.f;
-        const float mxl = mx * kLog2e, sl = g.scale * kLog2e;
-        float sum = 0.f;
-        for (int ch = 0; ch < nch; ++ch) {
-            float p[32];
-            if (ch >= ch_lo && ch < ch_hi) {                                      // warp-uniform
-                uint32_t v[32];
-                float add[32];
-                const int k0 = ch * 32 - klo;
-                tmem_ld_32x32b_x32(taddr + ch * 32, v);
-                if (has_add) load_add32(add, brow, mrow, k0, g.S);
-                tmem_ld_wait();
-                const bool full = k0 >= 0 && k0 + 32 <= g.S;
-#define CALL(A, F) chunk_exp<A, F>(v, add, sl, mxl, k0, g.S, p)
-                ATTN_DISPATCH(has_add, full, CALL);
-#undef CALL
-#pragma unroll
-                for (int j = 0; j < 32; ++j) sum += p[j];
-            } else {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) p[j] = 0.f;
-            }
-#pragma unroll
-            for (int q8 = 0; q8 < 4; ++q8) {
-                const float t[8] = {p[q8 * 8], p[q8 * 8 + 1], p[q8 * 8 + 2], p[q8 * 8 + 3], p[q8 * 8 + 4], p[q8 * 8 + 5], p[q8 * 8 + 6], p[q8 * 8 + 7]};
-                const int c0 = ch * 32 + q8 * 8;
-                sts8<T>(p_row + (c0 >> 6) * kTileBytes + ((((c0 >> 3) & 7) ^ (r & 7)) << 4), t);
-            }
-        }
-        inv_sum = sum > 0.f ? 1.f / sum : 0.f;
-        row_lse = mx + logf(fmaxf(sum, 1e-30f));
-        fence_async_smem();
-        tc_fence_before();
+        put_p(ch, p);
     }
+    s_sum[half * kTile + r] = sum;
+    fence_async_smem();
+    tc_fence_before();
     __syncthreads();                                      // P is complete; every thread is done with the S columns
-    if (warp == 1 && lane == 0) {
-        tc_fence_after();
-        const uint32_t idesc = make_idesc(is_bf16, 0, 1, kTile, 64);
-        const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
-        const int steps = g.nk >> 4;
-        for (int k = 0; k < steps; ++k)
-            umma_f16(tmem_base, make_desc(pa + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
-                     make_desc(va + k * 2048, 8192, 1024), idesc, k ? 1u : 0u);
-        umma_commit(bar_o);
-    }
-    if (warp >= 4) {
-        const uint32_t taddr = tmem_base + ((uint32_t)((warp - 4) * 32) << 16);
-        mbar_wait(bar_o, 0);
-        tc_fence_after();
-        T* orow = out + (((int64_t)(me.ok ? me.b : 0) * g.S + (me.ok ? me.s : 0)) * g.H + h) * g.d;
-#pragma unroll 1
-        for (int l = 0; l < 2; ++l) {
-            uint32_t v[32];
-            tmem_ld_32x32b_x32(taddr + l * 32, v);
-            tmem_ld_wait();
-            float o[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(v[j]) * inv_sum;
-            if (me.ok && g.d > l * 32) store_row<T, 32>(orow + l * 32, o, min(32, g.d - l * 32));
+    if (warp == 1) {
+        // lanes 1..31 park at the __syncwarp below instead of sleeping on an mbarrier: a suspended
+        // try_wait of the sibling lanes must never delay the one lane that issues the TMA / MMA work
+        if (lane == 0) {
+            tc_fence_after();
+            const uint32_t idesc = make_idesc(is_bf16, 0, 1, kTile, 64);
+            const uint32_t pa = smem_u32(sP), va = smem_u32(sV);
+            const int steps = g.nk >> 4;
+            for (int k = 0; k < steps; ++k)
+                umma_f16(tmem_base, make_desc(pa + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                         make_desc(va + k * 2048, 8192, 1024), idesc, k ? 1u : 0u);
+            umma_commit(bar_o);
         }
-        if (me.ok) lse[((int64_t)me.b * g.H + h) * g.S + me.s] = row_lse;
+        __syncwarp();
+    }
+    sum = s_sum[r] + s_sum[kTile + r];
+    const float inv_sum = sum > 0.f ? 1.f / sum : 0.f;
+    mbar_wait(bar_o, 0);
+    tc_fence_after();
+    {
+        // each half of the warps drains 32 of the 64 output columns of its rows
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(taddr + half * 32, v);
+        tmem_ld_wait();
+        float o[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(v[j]) * inv_sum;
+        if (me.ok && g.d > half * 32)
+            store_row<T, 32>(out + (((int64_t)me.b * g.S + me.s) * g.H + h) * g.d + half * 32, o, min(32, g.d - half * 32));
+        if (me.ok && half == 0) lse[((int64_t)me.b * g.H + h) * g.S + me.s] = mx + logf(fmaxf(sum, 1e-30f));
     }
     tc_fence_before();
     __syncthreads();
@@ -373,7 +489,9 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sQ = smem;                          // 2 tiles
-    uint8_t* sDO = smem + 2 * kTileBytes;        // 2 tiles
+    // stacked windows use one query tile: dO moves next to Q and the freed 32 KB hold the additive (bias + mask) tile
+    uint8_t* sDO = g.G == 2 ? smem + kTileBytes : smem + 2 * kTileBytes;        // 2 tiles (1 when G == 2)
+    float* sAdd = reinterpret_cast<float*>(smem + 2 * kTileBytes);
     uint8_t* sK = smem + 4 * kTileBytes;
     uint8_t* sV = smem + 5 * kTileBytes;
     uint8_t* sP = smem + 6 * kTileBytes;         // 2 chunks of 64 keys
@@ -407,11 +525,20 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
     const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDQ = tmem_base + 256, tDK = tmem_base + 384, tDV = tmem_base + 448;
 
     uint32_t n_ld = 0, n_s = 0, n_m = 0;          // commits / transactions issued so far on each barrier (all threads count)
-    const int r = (warp - 4) * 32 + lane;
-    const uint32_t lane_sel = (uint32_t)(((warp - 4) & 3) * 32) << 16;
+    // elementwise work and the TMEM drains use ALL eight warps: warps w and w + 4 share a lane quarter and split
+    // the 32-column chunks (resp. the 64 output columns) between them
+    const int r = (warp & 3) * 32 + lane, half = warp >> 2;
+    const uint32_t lane_sel = (uint32_t)((warp & 3) * 32) << 16;
 
+    const bool use_sadd = g.G == 2 && (bias != nullptr || (mask != nullptr && g.nW > 0));
+    bool sadd_valid = false;
     for (int unit = blockIdx.x; unit < nunits; unit += gridDim.x) {
         const int b0 = unit * g.G;
+        if (use_sadd && (!sadd_valid || (mask != nullptr && g.nW > 0))) {
+            // every thread is past its last read of the previous tile (the barrier before the second group of MMAs)
+            stage_add(sAdd, bias, mask, g, h, b0);
+            sadd_valid = true;
+        }
         float delta[2] = {0.f, 0.f}, row_lse[2] = {0.f, 0.f};
         for (int j = 0; j < nkb; ++j) {
             for (int i = 0; i < g.nq; ++i) {
@@ -430,33 +557,38 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                     fence_async_smem();
                 }
                 __syncthreads();
-                if (warp == 1 && lane == 0) {
-                    if (!g.manual && (need_q || need_kv)) {
-                        if (n_m > 0) mbar_wait(bar_m, (n_m - 1) & 1);
-                        mbar_expect_tx(bar_ld, (need_q ? 2 : 0) * kTileBytes + (need_kv ? 2 : 0) * kTileBytes);
-                        if (need_q) {
-                            tma_load_3d(sQ + i * kTileBytes, &tmQKV, bar_ld, h * 64, i * kTile, b0);
-                            tma_load_3d(sDO + i * kTileBytes, &tmDO, bar_ld, h * 64, i * kTile, b0);
+                if (warp == 1) {
+                    // lanes 1..31 park at the __syncwarp below instead of sleeping on an mbarrier: a suspended
+                    // try_wait of the sibling lanes must never delay the one lane that issues the TMA / MMA work
+                    if (lane == 0) {
+                        if (!g.manual && (need_q || need_kv)) {
+                            if (n_m > 0) mbar_wait(bar_m, (n_m - 1) & 1);
+                            mbar_expect_tx(bar_ld, (need_q ? 2 : 0) * kTileBytes + (need_kv ? 2 : 0) * kTileBytes);
+                            if (need_q) {
+                                tma_load_3d(sQ + i * kTileBytes, &tmQKV, bar_ld, h * 64, i * kTile, b0);
+                                tma_load_3d(sDO + i * kTileBytes, &tmDO, bar_ld, h * 64, i * kTile, b0);
+                            }
+                            if (need_kv) {
+                                tma_load_3d(sK, &tmQKV, bar_ld, (g.H + h) * 64, j * kTile, b0);
+                                tma_load_3d(sV, &tmQKV, bar_ld, (2 * g.H + h) * 64, j * kTile, b0);
+                            }
+                            mbar_wait(bar_ld, n_ld & 1);
                         }
-                        if (need_kv) {
-                            tma_load_3d(sK, &tmQKV, bar_ld, (g.H + h) * 64, j * kTile, b0);
-                            tma_load_3d(sV, &tmQKV, bar_ld, (2 * g.H + h) * 64, j * kTile, b0);
-                        }
-                        mbar_wait(bar_ld, n_ld & 1);
+                        tc_fence_after();
+                        const uint32_t idesc = make_idesc(is_bf16, 0, 0, kTile, kTile);
+                        const uint32_t qa = smem_u32(sQ + i * kTileBytes), doa = smem_u32(sDO + i * kTileBytes);
+                        const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
+                        for (int k = 0; k < ksteps; ++k)
+                            umma_f16(tS, make_desc(qa + k * 32, 16, 1024), make_desc(ka + k * 32, 16, 1024), idesc, k ? 1u : 0u);
+                        for (int k = 0; k < ksteps; ++k)
+                            umma_f16(tDP, make_desc(doa + k * 32, 16, 1024), make_desc(va + k * 32, 16, 1024), idesc, k ? 1u : 0u);
+                        umma_commit(bar_s);
                     }
-                    tc_fence_after();
-                    const uint32_t idesc = make_idesc(is_bf16, 0, 0, kTile, kTile);
-                    const uint32_t qa = smem_u32(sQ + i * kTileBytes), doa = smem_u32(sDO + i * kTileBytes);
-                    const uint32_t ka = smem_u32(sK), va = smem_u32(sV);
-                    for (int k = 0; k < ksteps; ++k)
-                        umma_f16(tS, make_desc(qa + k * 32, 16, 1024), make_desc(ka + k * 32, 16, 1024), idesc, k ? 1u : 0u);
-                    for (int k = 0; k < ksteps; ++k)
-                        umma_f16(tDP, make_desc(doa + k * 32, 16, 1024), make_desc(va + k * 32, 16, 1024), idesc, k ? 1u : 0u);
-                    umma_commit(bar_s);
+                    __syncwarp();
                 }
                 if (!g.manual && (need_q || need_kv)) ++n_ld;
                 ++n_s;
-                if (warp >= 4) {
+                {
                     const RowId me = row_id(g, b0, i, r);
                     if (j == 0) {
                         // per-row constants of this query tile, fetched while the tensor core works
@@ -481,7 +613,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                     mbar_wait(bar_s, (n_s - 1) & 1);
                     tc_fence_after();
 #pragma unroll 1
-                    for (int ch = 0; ch < 4; ++ch) {
+                    for (int ch = half; ch < 4; ch += 2) {
                         float p[32], ds[32];
                         if (ch >= ch_lo && ch < ch_hi) {                          // warp-uniform
                             uint32_t sv[32], dv[32];
@@ -489,7 +621,8 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                             const int k0 = ch * 32 - koff;
                             tmem_ld_32x32b_x32(tS + lane_sel + ch * 32, sv);
                             tmem_ld_32x32b_x32(tDP + lane_sel + ch * 32, dv);
-                            if (has_add) load_add32(add, brow, mrow, k0, g.S);
+                            if (use_sadd) smem_add32(add, sAdd + me.gi * 4096 + (me.ok ? me.s : 0) * 64, me.ok ? me.s : 0, k0);
+                            else if (has_add) load_add32(add, brow, mrow, k0, g.S);
                             tmem_ld_wait();
                             const bool full = k0 >= 0 && k0 + 32 <= g.S;
 #define CALL(A, F) chunk_exp<A, F>(sv, add, sl, lsel, k0, g.S, p)
@@ -497,9 +630,10 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
 #undef CALL
 #pragma unroll
                             for (int jj = 0; jj < 32; ++jj) ds[jj] = p[jj] * (__uint_as_float(dv[jj]) - dl);
-                            if (dbrow) {
+                            if (dbrow) {       // the two halves of a row own different chunks: no two threads share an entry
 #pragma unroll
-                                for (int jj = 0; jj < 32; ++jj) dbrow[min(max(k0 + jj, 0), 63)] += ds[jj];   // ds == 0 where clamped
+                                for (int jj = 0; jj < 32; ++jj)
+                                    if (full || (k0 + jj >= 0 && k0 + jj < g.S)) dbrow[k0 + jj] += ds[jj];
                             }
                         } else {
 #pragma unroll
@@ -520,63 +654,65 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                     tc_fence_before();
                 }
                 __syncthreads();
-                if (warp == 1 && lane == 0) {
-                    tc_fence_after();
-                    const uint32_t id_t = make_idesc(is_bf16, 1, 1, kTile, 64);     // A^T forms: dV, dK
-                    const uint32_t id_n = make_idesc(is_bf16, 0, 1, kTile, 64);     // dQ
-                    const uint32_t pa = smem_u32(sP), dsa = smem_u32(sDS), ka = smem_u32(sK);
-                    const uint32_t qa = smem_u32(sQ + i * kTileBytes), doa = smem_u32(sDO + i * kTileBytes);
-                    for (int k = 0; k < 8; ++k)         // dV[key][d] += sum_q P[q][key] dO[q][d]
-                        umma_f16(tDV, make_desc(pa + k * 2048, kTileBytes, 1024), make_desc(doa + k * 2048, 8192, 1024), id_t,
-                                 (i > 0 || k > 0) ? 1u : 0u);
-                    for (int k = 0; k < 8; ++k)         // dK[key][d] += sum_q dS[q][key] Q[q][d]
-                        umma_f16(tDK, make_desc(dsa + k * 2048, kTileBytes, 1024), make_desc(qa + k * 2048, 8192, 1024), id_t,
-                                 (i > 0 || k > 0) ? 1u : 0u);
-                    for (int k = 0; k < 8; ++k)         // dQ[q][d] += sum_key dS[q][key] K[key][d]
-                        umma_f16(tDQ + i * 64, make_desc(dsa + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
-                                 make_desc(ka + k * 2048, 8192, 1024), id_n, (j > 0 || k > 0) ? 1u : 0u);
-                    umma_commit(bar_m);
+                if (warp == 1) {
+                    // lanes 1..31 park at the __syncwarp below instead of sleeping on an mbarrier: a suspended
+                    // try_wait of the sibling lanes must never delay the one lane that issues the TMA / MMA work
+                    if (lane == 0) {
+                        tc_fence_after();
+                        const uint32_t id_t = make_idesc(is_bf16, 1, 1, kTile, 64);     // A^T forms: dV, dK
+                        const uint32_t id_n = make_idesc(is_bf16, 0, 1, kTile, 64);     // dQ
+                        const uint32_t pa = smem_u32(sP), dsa = smem_u32(sDS), ka = smem_u32(sK);
+                        const uint32_t qa = smem_u32(sQ + i * kTileBytes), doa = smem_u32(sDO + i * kTileBytes);
+                        for (int k = 0; k < 8; ++k)         // dV[key][d] += sum_q P[q][key] dO[q][d]
+                            umma_f16(tDV, make_desc(pa + k * 2048, kTileBytes, 1024), make_desc(doa + k * 2048, 8192, 1024), id_t,
+                                     (i > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < 8; ++k)         // dK[key][d] += sum_q dS[q][key] Q[q][d]
+                            umma_f16(tDK, make_desc(dsa + k * 2048, kTileBytes, 1024), make_desc(qa + k * 2048, 8192, 1024), id_t,
+                                     (i > 0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < 8; ++k)         // dQ[q][d] += sum_key dS[q][key] K[key][d]
+                            umma_f16(tDQ + i * 64, make_desc(dsa + (k >> 2) * kTileBytes + (k & 3) * 32, 16, 1024),
+                                     make_desc(ka + k * 2048, 8192, 1024), id_n, (j > 0 || k > 0) ? 1u : 0u);
+                        umma_commit(bar_m);
+                    }
+                    __syncwarp();
                 }
                 ++n_m;
             }
-            // ---- dK, dV of key block j are complete
-            if (warp >= 4) {
+            // ---- dK, dV of key block j are complete: each warp half drains 32 of the 64 columns
+            {
                 mbar_wait(bar_m, (n_m - 1) & 1);
                 tc_fence_after();
                 const RowId kr = row_id(g, b0, j, r);
 #pragma unroll 1
                 for (int w = 0; w < 2; ++w) {
-                    float o[64];
+                    uint32_t v[32];
+                    tmem_ld_32x32b_x32((w == 0 ? tDK : tDV) + lane_sel + half * 32, v);
+                    tmem_ld_wait();
+                    float o[32];
 #pragma unroll
-                    for (int l = 0; l < 2; ++l) {
-                        uint32_t v[32];
-                        tmem_ld_32x32b_x32((w == 0 ? tDK : tDV) + lane_sel + l * 32, v);
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int q = 0; q < 32; ++q) o[l * 32 + q] = __uint_as_float(v[q]);
-                    }
-                    if (kr.ok)
-                        store_row<T, 64>(dqkv + ((((int64_t)kr.b * g.S + kr.s) * 3 + (w + 1)) * g.H + h) * g.d, o, g.d);
+                    for (int q = 0; q < 32; ++q) o[q] = __uint_as_float(v[q]);
+                    if (kr.ok && g.d > half * 32)
+                        store_row<T, 32>(dqkv + ((((int64_t)kr.b * g.S + kr.s) * 3 + (w + 1)) * g.H + h) * g.d + half * 32, o,
+                                         min(32, g.d - half * 32));
                 }
                 tc_fence_before();
             }
         }
         // ---- dQ of every query tile is complete (the last wait above covered the last commit)
-        if (warp >= 4) {
+        {
             tc_fence_after();
 #pragma unroll 1
             for (int i = 0; i < g.nq; ++i) {
                 const RowId qr = row_id(g, b0, i, r);
-                float o[64];
+                uint32_t v[32];
+                tmem_ld_32x32b_x32(tDQ + i * 64 + lane_sel + half * 32, v);
+                tmem_ld_wait();
+                float o[32];
 #pragma unroll
-                for (int l = 0; l < 2; ++l) {
-                    uint32_t v[32];
-                    tmem_ld_32x32b_x32(tDQ + i * 64 + lane_sel + l * 32, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int q = 0; q < 32; ++q) o[l * 32 + q] = __uint_as_float(v[q]);
-                }
-                if (qr.ok) store_row<T, 64>(dqkv + ((((int64_t)qr.b * g.S + qr.s) * 3 + 0) * g.H + h) * g.d, o, g.d);
+                for (int q = 0; q < 32; ++q) o[q] = __uint_as_float(v[q]);
+                if (qr.ok && g.d > half * 32)
+                    store_row<T, 32>(dqkv + ((((int64_t)qr.b * g.S + qr.s) * 3 + 0) * g.H + h) * g.d + half * 32, o,
+                                     min(32, g.d - half * 32));
             }
             tc_fence_before();
         }
@@ -715,3 +851,4 @@ extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void
     B200DP_CHECK_LAUNCH();
     return 0;
 }
+
