@@ -77,6 +77,11 @@ class Stoke:
         verbose: bool = True,
         ema_weight: float = 0.1,
     ):
+        if gpu and not torch.cuda.is_available() and os.environ.get("B200DP_CPU_FALLBACK", "0") not in ("", "0"):
+            # scripts written for a GPU box (Stoke-DDP.py:246 hard-codes gpu=True) can be exercised on a CPU-only
+            # machine: everything runs through the portable engines over gloo
+            print("Stoke -- gpu=True but no CUDA device is visible; B200DP_CPU_FALLBACK is set: running on the CPU", flush=True)
+            gpu = False
         self._verbose = verbose
         self._info_rank = info_rank
         self._ema_weight = float(ema_weight)
