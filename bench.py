@@ -39,6 +39,12 @@ CONFIGS = {
                               oss=True, sddp=True, fsdp=False, accum=2, clip=0.1, par="zero2", dtype="fp16"),
     "vitb16_fsdp_bf16": dict(model="vit_b_16", batch=128, shape=(3, 224, 224), classes=1000, fp16="bf16",
                              oss=False, sddp=False, fsdp=True, accum=1, clip=None, par="fsdp", dtype="bf16"),
+    # the reference's own workload (Stoke-DDP.py:206-254): SwinIR-S x2 (embed_dim 60, 6 heads, window 8), 64x64 patches,
+    # batch 18 / GPU, OSS + ShardedDDP, accumulation 2, clip 0.1, fp16 owner broadcast, perceptual loss.  The reference
+    # leaves AMP off (fp32); here the compute dtype is bf16 (the B200 default), stated in `dtype`.
+    "swinir_s_oss_sddp": dict(model="swinir_s", batch=18, shape=(3, 64, 64), classes=0, fp16="bf16",
+                              oss=True, sddp=True, fsdp=False, accum=2, clip=0.1, par="zero2", dtype="bf16",
+                              loss="feat_loss", target_scale=2, broadcast_fp16=True),
     "resnet18_cifar": dict(model="resnet18", batch=128, shape=(3, 32, 32), classes=10, fp16=None,
                            oss=True, sddp=False, fsdp=False, accum=1, clip=None, par="zero1", dtype="fp32"),
 }
@@ -77,19 +83,27 @@ def build_ours(cfg: dict, args, world: int):
     from pytorch_distributedtraining_b200 import models
     from pytorch_distributedtraining_b200.ops.loss import cross_entropy
 
-    kw = {"num_classes": cfg["classes"]}
-    if cfg["model"] == "resnet18" and cfg["shape"][1] <= 64:
-        kw["small_input"] = True
-    model = getattr(models, cfg["model"])(**kw)
+    if cfg["model"] == "swinir_s":
+        model = models.SwinIR(upscale=2, in_chans=3, img_size=64, window_size=8, img_range=1., depths=[6, 6, 6, 6],
+                              embed_dim=60, num_heads=[6, 6, 6, 6], mlp_ratio=2, upsampler="pixelshuffledirect",
+                              resi_connection="1conv")
+    else:
+        kw = {"num_classes": cfg["classes"]}
+        if cfg["model"] == "resnet18" and cfg["shape"][1] <= 64:
+            kw["small_input"] = True
+        model = getattr(models, cfg["model"])(**kw)
+    loss_fn = cross_entropy
+    if cfg.get("loss") == "feat_loss":
+        from pytorch_distributedtraining_b200.models.perceptual import feat_loss as loss_fn
     gpu = not args.cpu
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     configs = [AMPConfig(init_scale=2.0 ** 14), DDPConfig(local_rank=local_rank, backend="nccl" if gpu else "gloo"),
-               FairscaleOSSConfig(broadcast_fp16=False), FairscaleFSDPConfig(mixed_precision=cfg["fp16"] is not None),
+               FairscaleOSSConfig(broadcast_fp16=bool(cfg.get("broadcast_fp16", False))), FairscaleFSDPConfig(mixed_precision=cfg["fp16"] is not None),
                B200Config(cuda_graph=gpu and not args.no_graph, strict=gpu)]
     stoke = Stoke(
         model=model, verbose=(int(os.environ.get("RANK", "0")) == 0),
         optimizer=StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs=dict(ADAMW)),
-        loss=cross_entropy, batch_size_per_device=args.batch_size or cfg["batch"], gpu=gpu,
+        loss=loss_fn, batch_size_per_device=args.batch_size or cfg["batch"], gpu=gpu,
         fp16=cfg["fp16"] if gpu else None, distributed="ddp" if (world > 1 or cfg["oss"] or cfg["fsdp"]) else None,
         fairscale_oss=cfg["oss"], fairscale_sddp=cfg["sddp"], fairscale_fsdp=cfg["fsdp"],
         grad_accum_steps=cfg["accum"], configs=configs,
@@ -117,7 +131,19 @@ def build_torch(cfg: dict, args, world: int, capturable: bool = False):
         torch.cuda.set_device(device)
     if world > 1 and not dist.is_initialized():
         dist.init_process_group("nccl" if gpu else "gloo", device_id=device if gpu else None)
-    model = getattr(torchvision.models, cfg["model"])(num_classes=cfg["classes"]).to(device)
+    if cfg["model"] == "swinir_s":
+        # no torch-native SwinIR exists: the stand-in runs THIS repository's module definition with every custom
+        # kernel switched off (stock cuBLAS / cuDNN / SDPA underneath), wrapped in torch DDP + ZeroRedundancyOptimizer
+        os.environ["B200DP_DISABLE"] = "conv,gemm,bn,ln,ce,pool,mse,convstats,attn_layout,mlp,dgrad_s2,attn,pad"
+        from pytorch_distributedtraining_b200.ops import dispatch
+        for f in os.environ["B200DP_DISABLE"].split(","):
+            dispatch.disable(f)
+        from pytorch_distributedtraining_b200 import models as our_models
+        model = our_models.SwinIR(upscale=2, in_chans=3, img_size=64, window_size=8, img_range=1., depths=[6, 6, 6, 6],
+                                  embed_dim=60, num_heads=[6, 6, 6, 6], mlp_ratio=2, upsampler="pixelshuffledirect",
+                                  resi_connection="1conv").to(device)
+    else:
+        model = getattr(torchvision.models, cfg["model"])(num_classes=cfg["classes"]).to(device)
     if cfg["model"].startswith("resnet") and gpu:
         model = model.to(memory_format=torch.channels_last)
     amp_dtype = {"amp": torch.float16, "bf16": torch.bfloat16, None: None}[cfg["fp16"] if gpu else None]
@@ -140,6 +166,9 @@ def build_torch(cfg: dict, args, world: int, capturable: bool = False):
         else:
             opt = torch.optim.AdamW(model.parameters(), fused=gpu, capturable=capturable and gpu, **ADAMW)
     scaler = torch.amp.GradScaler("cuda", init_scale=2.0 ** 14, enabled=amp_dtype == torch.float16)
+    t_loss = None
+    if cfg.get("loss") == "feat_loss":
+        from pytorch_distributedtraining_b200.models.perceptual import feat_loss as t_loss
     model.train()
     state = {"i": 0}
     import contextlib
@@ -150,7 +179,7 @@ def build_torch(cfg: dict, args, world: int, capturable: bool = False):
         ctx = contextlib.nullcontext() if (boundary or world == 1 or not hasattr(model, "no_sync")) else model.no_sync()
         with ctx:
             with torch.autocast("cuda", dtype=amp_dtype, enabled=amp_dtype is not None):
-                loss = F.cross_entropy(model(x), y) / accum
+                loss = (t_loss(model(x), y) if t_loss is not None else F.cross_entropy(model(x), y)) / accum
             scaler.scale(loss).backward()
         if boundary:
             if cfg["clip"] is not None:
@@ -319,8 +348,13 @@ def main() -> None:
     # ---- synthetic data of the named shape (random-init weights, no datasets on the box)
     g = torch.Generator().manual_seed(1234 + rank)
     n_pool = 2
-    host = [(torch.randn((B, *cfg["shape"]), generator=g), torch.randint(0, cfg["classes"], (B,), generator=g))
-            for _ in range(n_pool)]
+    if cfg.get("target_scale"):          # super-resolution: low-res input, high-res target
+        c, hh, ww = cfg["shape"]
+        sc = cfg["target_scale"]
+        host = [(torch.rand((B, c, hh, ww), generator=g), torch.rand((B, c, hh * sc, ww * sc), generator=g)) for _ in range(n_pool)]
+    else:
+        host = [(torch.randn((B, *cfg["shape"]), generator=g), torch.randint(0, cfg["classes"], (B,), generator=g))
+                for _ in range(n_pool)]
     cl = is_cuda and cfg["model"].startswith("resnet")
     if is_cuda:
         from pytorch_distributedtraining_b200.data import pin_channels_last

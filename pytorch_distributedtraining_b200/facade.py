@@ -350,6 +350,12 @@ class Stoke:
                     ddp_eng.inv_scale = torch.empty((), dtype=torch.float32, device=self._device)
                 torch.reciprocal(self._scaler.scale_tensor, out=ddp_eng.inv_scale)
                 ddp_eng.found_inf = self._scaler.found_inf_tensor
+            zero_eng = getattr(self._optimizer, "_flat_engine", None) if isinstance(self._optimizer, OSS) else None
+            if zero_eng is not None and sync_now:
+                # the bucket reduce-to-owner kernels of this backward apply 1/scale themselves (W2)
+                if zero_eng.inv_scale is None:
+                    zero_eng.inv_scale = torch.empty((), dtype=torch.float32, device=self._device)
+                torch.reciprocal(self._scaler.scale_tensor, out=zero_eng.inv_scale)
         ctx = contextlib.nullcontext()
         if not sync_now and self._ddp_cfg.no_sync and hasattr(self._model, "no_sync"):
             ctx = self._model.no_sync()

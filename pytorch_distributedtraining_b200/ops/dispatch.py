@@ -79,6 +79,39 @@ def linear_supported(mod: Any, x: torch.Tensor) -> bool:
     return mod.in_features % 8 == 0 and mod.out_features % 8 == 0
 
 
+def linear_padded_supported(mod: Any, x: torch.Tensor) -> bool:
+    """Widths that are not multiples of 8 (the reference's SwinIR-S: embed_dim 60, Stoke-DDP.py:206-208) still run on
+    the tcgen05 GEMM: ``ops.layers.Linear`` zero-pads the activation's K and the weight's K / N up to the next
+    multiple of 8 (16-byte TMA rows) and slices the result; 1-byte-per-element copies against keeping every linear of
+    that model on the library."""
+    if not (enabled("gemm") and enabled("pad") and _lib_ok()):
+        return False
+    from . import gemm
+    if not gemm.available():
+        return False
+    return _autocast_dtype(x) in _HALF and mod.in_features >= 8 and mod.out_features >= 8
+
+
+def conv_padded_supported(mod: Any, x: torch.Tensor) -> bool:
+    """Convolutions whose channel counts miss the implicit-GEMM envelope by padding only (e.g. 60 -> 64): input
+    channels are zero-padded to a multiple of 64, output channels to a multiple of 8 (64 when the input gradient is
+    needed).  First-layer convolutions (Cin < 32) are excluded: padding 3 channels to 64 would move 21x the bytes."""
+    if not (enabled("conv") and enabled("pad") and _lib_ok()):
+        return False
+    from . import conv
+    if not conv.available():
+        return False
+    dt = _autocast_dtype(x)
+    if dt not in _HALF or mod.groups != 1 or mod.dilation != (1, 1) or mod.padding_mode != "zeros":
+        return False
+    if x.dim() != 4 or mod.in_channels < 32 or mod.out_channels < 8:
+        return False
+    if mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.padding == (0, 0):
+        return False            # 1x1: handled as a (padded) linear
+    return (mod.stride[0] == mod.stride[1] and mod.stride[0] in (1, 2) and mod.padding[0] == mod.padding[1]
+            and isinstance(mod.padding[0], int) and x.shape[2] + 2 * mod.padding[0] >= mod.kernel_size[0])
+
+
 def conv_supported(mod: Any, x: torch.Tensor) -> bool:
     """Implicit-GEMM envelope: NHWC fp16/bf16, groups == 1, dilation == 1, Cin % 64 == 0, Cout % 16 == 0."""
     if not (enabled("conv") and _lib_ok()):

@@ -36,8 +36,27 @@ class Conv2d(nn.Conv2d):
                 and dispatch.enabled("convstats")
             return _conv.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups,
                                 emit_bn_stats=emit, carry=carry)
+        if x.is_cuda and not carry and dispatch.conv_padded_supported(self, x):
+            return self._forward_padded(x)
         y = super().forward(x)
         return (y, x) if carry else y
+
+    def _forward_padded(self, x: torch.Tensor) -> torch.Tensor:
+        """Channel counts just outside the kernel envelope (60 -> 64): zero-pad input channels and filters, run the
+        implicit-GEMM kernels, slice the output channels.  The pads / slice are ordinary autograd ops."""
+        from . import conv as _conv
+        cin, cout = self.in_channels, self.out_channels
+        cin_p = (cin + 63) // 64 * 64
+        cout_p = (cout + 63) // 64 * 64 if x.requires_grad else (cout + 7) // 8 * 8
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
+        xp = x.to(dt)
+        if cin_p != cin:
+            xp = torch.cat([xp, xp.new_zeros((x.shape[0], cin_p - cin, x.shape[2], x.shape[3]))], dim=1)
+        xp = xp.contiguous(memory_format=torch.channels_last)
+        w = F.pad(self.weight, (0, 0, 0, 0, 0, cin_p - cin, 0, cout_p - cout))
+        b = None if self.bias is None else F.pad(self.bias, (0, cout_p - cout))
+        y = _conv.conv2d(xp, w, b, self.stride, self.padding, self.dilation, self.groups)
+        return y[:, :cout] if cout_p != cout else y
 
     def forward_carry(self, x: torch.Tensor):
         """``(conv(x), x)``: use the second value for the branch that bypasses this layer (residual identity,
@@ -59,6 +78,19 @@ class Linear(nn.Linear):
         if x.is_cuda and dispatch.linear_supported(self, x):
             from . import gemm as _gemm
             return _gemm.linear(x, self.weight, self.bias, act=self.act, residual=residual)
+        if x.is_cuda and dispatch.linear_padded_supported(self, x):
+            # widths that are not multiples of 8 (SwinIR-S: 60 / 180 / 120): zero-pad K and N to the next multiple of 8,
+            # run the tcgen05 GEMM, slice — the pads and the slice are ordinary autograd ops
+            from . import gemm as _gemm
+            k, n = self.in_features, self.out_features
+            kp, np_ = (k + 7) // 8 * 8, (n + 7) // 8 * 8
+            xp = F.pad(x, (0, kp - k)) if kp != k else x
+            w = F.pad(self.weight, (0, kp - k, 0, np_ - n)) if (kp != k or np_ != n) else self.weight
+            b = None if self.bias is None else (F.pad(self.bias, (0, np_ - n)) if np_ != n else self.bias)
+            y = _gemm.linear(xp, w, b, act=self.act)
+            if np_ != n:
+                y = y[..., :n]
+            return y if residual is None else y + residual
         y = F.linear(x, self.weight, self.bias)
         if self.act == "gelu":
             y = F.gelu(y)

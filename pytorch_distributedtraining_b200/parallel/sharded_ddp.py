@@ -229,7 +229,13 @@ class ShardedDataParallel(nn.Module):
         inv_world = 1.0 / self.world_size
 
         def hook(param: torch.Tensor) -> None:
-            if self.should_accumulate_grads or self.world_size == 1 or self._fused_engine is not None:
+            if self.should_accumulate_grads or self.world_size == 1:
+                return
+            if self._fused_engine is not None:
+                # peer-memory path: the engine launches the bucket's reduce-to-owner on its comm stream as soon as
+                # the bucket is complete; the end-of-backward callback joins the streams
+                if self._fused_engine.grad_ready(param):
+                    self._queue_callback()
                 return
             grad = param.grad
             if grad is None:
@@ -284,6 +290,8 @@ class ShardedDataParallel(nn.Module):
         """End-of-backward: flush partially filled buckets (unused parameters count
         as zero gradients), wait for every reduce, then drop non-owned gradients."""
         self._callback_queued = False
+        if self._fused_engine is not None and not self.should_accumulate_grads:
+            self._fused_engine.finish_backward()
         if not self.should_accumulate_grads and self.world_size > 1 and self._fused_engine is None:
             for b in self._buckets.values():
                 if not b.sent and b.pending != len(b.params):

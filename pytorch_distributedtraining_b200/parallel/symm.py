@@ -255,43 +255,87 @@ class _FSDPUnitOps:
 
 # --------------------------------------------------------------------------- ZeRO-2 fused step
 class ZeroPeerEngine:
-    """OSS + ShardedDDP on owner-ordered flat buffers; see the module docstring."""
+    """OSS + ShardedDDP on the peer-memory kernels (W2 + W3; Fairscale-DDP.py:86-101, Stoke-DDP.py:249-251).
+
+    Gradients live in ONE symmetric buffer laid out as *units*: parameters of a group are cut, in reverse
+    registration order (the order backward produces them), into buckets of ~``BUCKET_BYTES``; inside a bucket the
+    members are ordered by owner rank, so rank r's share of the bucket is one contiguous segment.
+
+      backward   as soon as every member of a bucket has its gradient, ``peer_reduce_to_owner`` for that bucket is
+                 launched on the comm stream (own flag context): the owner pulls its segment from every rank,
+                 applies 1/world and the AMP unscale, writes the reduced slice into its OWNED gradient buffer and
+                 leaves sum(g^2) / the non-finite flag of the slice — fairscale's reduce-to-owner, overlapped with
+                 the rest of backward, and the clipping norm costs no extra pass
+      step()     one small all-reduce of the norm partials, the clip coefficient on the device, then per unit
+                 ``peer_zero_adam(prereduced)``: AdamW on the owner's fp32 master / m / v and the publish of the
+                 new values into every rank's parameter buffer (multicast or 16-bit wire)
+
+    What is sharded: optimizer state (master, m, v) and the REDUCED gradient (owned slices only).  The full-size
+    buffer is the storage backward writes its local gradients into (fairscale materialises those too, and frees the
+    non-owned ones after the reduce; a CUDA graph cannot free, so here the buffer is simply reused every step).
+    """
+
+    BUCKET_BYTES = 25 << 20
 
     def __init__(self, arena: PeerArena, oss: Any, sddp: Any, wire_dtype: Optional[torch.dtype] = None, blocks: int = 48):
         self.arena, self.oss, self.sddp, self.blocks = arena, oss, sddp, blocks
         self.ctx = arena.context("main")
+        self.cctx = arena.context("comm")
+        self.stream = torch.cuda.Stream(device=arena.device)
         self.rank, self.world = arena.rank, arena.world
         self.wire_dtype = wire_dtype or torch.float32
         self.small = SmallAllReduce(arena) if peer._STATE.get("small") is None else peer._STATE["small"]
         dev = arena.device
-        # ---- layout: for each param group, ranks in order, each rank's params in order, 8-aligned segments
-        self.groups: List[Dict[str, Any]] = []
-        total = 0
         part = oss.partition_parameters()
+        owner_of = {id(p): r for r in range(self.world) for g in part[r] for p in g["params"]}
+        # ---- layout
+        self.groups: List[Dict[str, Any]] = []
+        self.units: List[Dict[str, Any]] = []
+        total = 0
         for gi, group in enumerate(oss.param_groups):
-            seg = [total]
-            entries: List[Tuple[torch.Tensor, int, int]] = []  # (param, offset, owner)
-            for r in range(self.world):
-                off = seg[-1]
-                for p in part[r][gi]["params"]:
-                    if not p.requires_grad:
-                        continue        # frozen: never updated, never decayed (torch skips params without a gradient)
-                    if p.dtype != torch.float32:
-                        raise RuntimeError("fused ZeRO engine expects fp32 parameters")
-                    entries.append((p, off, r))
-                    off += p.numel()
-                seg.append((off + 7) // 8 * 8)
-            total = seg[-1]
-            self.groups.append({"seg": seg, "entries": entries})
+            params = [p for p in group["params"] if p.requires_grad]     # frozen: never updated, never decayed
+            for p in params:
+                if p.dtype != torch.float32:
+                    raise RuntimeError("fused ZeRO engine expects fp32 parameters")
+            buckets: List[List[torch.Tensor]] = [[]]
+            size = 0
+            for p in reversed(params):
+                if size + p.numel() * 4 > self.BUCKET_BYTES and buckets[-1]:
+                    buckets.append([])
+                    size = 0
+                buckets[-1].append(p)
+                size += p.numel() * 4
+            ginfo: Dict[str, Any] = {"units": [], "own_n": 0}
+            for members in buckets:
+                if not members:
+                    continue
+                seg = [total]
+                entries: List[Tuple[torch.Tensor, int, int]] = []       # (param, offset, owner)
+                for r in range(self.world):
+                    off = seg[-1]
+                    for p in members:
+                        if owner_of[id(p)] == r:
+                            entries.append((p, off, r))
+                            off += p.numel()
+                    seg.append((off + 7) // 8 * 8)
+                total = seg[-1]
+                own = seg[self.rank + 1] - seg[self.rank]
+                unit = {"gi": gi, "seg": seg, "entries": entries, "own_off": ginfo["own_n"], "own_n": own,
+                        "n_params": len(entries), "pending": len(entries), "launched": False, "index": len(self.units)}
+                ginfo["own_n"] += (own + 7) // 8 * 8
+                ginfo["units"].append(unit)
+                self.units.append(unit)
+            self.groups.append(ginfo)
         self.total = max(total, 8)
         self.G = arena.alloc(self.total, torch.float32)
         self.P = arena.alloc(self.total, torch.float32)
         self.P16 = arena.alloc(self.total, self.wire_dtype) if self.wire_dtype != torch.float32 else None
         self.G.tensor.zero_()
         self.P.tensor.zero_()
+        self._unit_of: Dict[int, Dict[str, Any]] = {}
         with torch.no_grad():
-            for g in self.groups:
-                for p, off, _r in g["entries"]:
+            for u in self.units:
+                for p, off, _r in u["entries"]:
                     view = self.P.tensor[off: off + p.numel()].view(p.shape)
                     view.copy_(p.detach())
                     p.data = view
@@ -299,22 +343,28 @@ class ZeroPeerEngine:
                     if p.grad is not None:
                         gview.copy_(p.grad)
                     p.grad = gview
-        # ---- owner-local state per group
+                    self._unit_of[id(p)] = u
+        # ---- owner-local state per group (sharded: only this rank's slices exist here)
         for g in self.groups:
-            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
-            n = max(s1 - s0, 8)
+            n = max(g["own_n"], 8)
             g["master"] = torch.zeros(n, dtype=torch.float32, device=dev)
-            g["master"][: s1 - s0].copy_(self.P.tensor[s0:s1])
             g["m"] = torch.zeros(n, dtype=torch.float32, device=dev)
             g["v"] = torch.zeros(n, dtype=torch.float32, device=dev)
+            g["reduced"] = torch.zeros(n, dtype=torch.float32, device=dev)
             g["step"] = torch.zeros((), dtype=torch.float32, device=dev)
-            g["reduced"] = None
+            for u in g["units"]:
+                s0 = u["seg"][self.rank]
+                g["master"][u["own_off"]: u["own_off"] + u["own_n"]].copy_(self.P.tensor[s0: s0 + u["own_n"]])
+        nu = max(len(self.units), 1)
+        self.unit_norms = torch.zeros(nu, 2, dtype=torch.float32, device=dev)      # per unit: sum(g^2), non-finite flag
         self.norm_buf = torch.zeros(2, dtype=torch.float32, device=dev)
         self.partials = torch.zeros(arena.max_blocks, dtype=torch.float32, device=dev)
         self.counter = torch.zeros(1, dtype=torch.int32, device=dev)
         self.grad_mult = torch.ones((), dtype=torch.float32, device=dev)
         self.total_norm = torch.zeros((), dtype=torch.float32, device=dev)
+        self.inv_scale: Optional[torch.Tensor] = None        # AMP: 1 / loss scale, refreshed by the facade before backward
         self._clip_pending = False
+        self._joined = True
         self.sync_buffers = PeerBufferSync(arena, sddp.module)
         torch.cuda.synchronize(dev)
         comm.barrier(arena.group)
@@ -327,44 +377,102 @@ class ZeroPeerEngine:
 
     def zero_grad(self) -> None:
         self.G.tensor.zero_()
-        for g in self.groups:
-            for p, off, _r in g["entries"]:
+        self.unit_norms.zero_()
+        for u in self.units:
+            u["pending"], u["launched"] = u["n_params"], False
+            for p, off, _r in u["entries"]:
                 if p.grad is None or p.grad.data_ptr() != self.G.tensor.data_ptr() + off * 4:
                     p.grad = self.G.tensor[off: off + p.numel()].view(p.shape)
 
     def _reattach_grads(self) -> None:
         """A foreign ``zero_grad(set_to_none=True)`` detaches the views; copy and re-alias."""
-        for g in self.groups:
-            for p, off, _r in g["entries"]:
+        for u in self.units:
+            for p, off, _r in u["entries"]:
                 want = self.G.tensor.data_ptr() + off * 4
                 if p.grad is not None and p.grad.data_ptr() != want:
                     v = self.G.tensor[off: off + p.numel()].view(p.shape)
                     v.copy_(p.grad)
                     p.grad = v
 
+    def grad_ready(self, param: torch.Tensor) -> bool:
+        """Post-accumulate hook of one parameter on a synchronising backward pass.  Returns True when an
+        end-of-backward ``finish_backward`` is needed."""
+        u = self._unit_of.get(id(param))
+        if u is None or u["launched"]:
+            return False
+        g = param.grad
+        if g is not None:
+            off = next(o for q, o, _ in u["entries"] if q is param)
+            if g.data_ptr() != self.G.tensor.data_ptr() + off * 4:
+                v = self.G.tensor[off: off + param.numel()].view(param.shape)
+                v.copy_(g)
+                param.grad = v
+        u["pending"] -= 1
+        # strictly in unit order: every rank must issue its collectives in the same sequence
+        launched = False
+        for nu in self.units:
+            if nu["launched"]:
+                continue
+            if nu["pending"] != 0:
+                break
+            self._reduce_unit(nu, self.stream)
+            launched = True
+        return launched or not self._joined
+
+    def _reduce_unit(self, u: Dict[str, Any], stream: Optional[torch.cuda.Stream]) -> None:
+        main = torch.cuda.current_stream(self.arena.device)
+        g = self.groups[u["gi"]]
+        ctx = self.cctx
+        if stream is not None:
+            stream.wait_stream(main)          # the unit's gradients are produced on the main stream
+            self._joined = False
+        else:
+            ctx = self.ctx
+        out = g["reduced"][u["own_off"]: u["own_off"] + max(u["own_n"], 8)]
+        n_own = u["own_n"]
+        ctx.reduce_to_owner(self.G.table, u["seg"], C.local_table(self.rank, out), 1.0 / self.world,
+                            C.local_table(self.rank, self.inv_scale),
+                            C.local_table(self.rank, self.unit_norms[u["index"]]), C.local_table(self.rank, self.partials),
+                            C.local_table(self.rank, self.counter), blocks=self._blocks(n_own), stream=stream)
+        u["launched"] = True
+
+    def finish_backward(self) -> None:
+        """End of backward: units whose members never all fired (unused parameters: their gradients are the zeros
+        ``zero_grad`` left) are reduced now, then the main stream joins the comm stream."""
+        for u in self.units:
+            if not u["launched"] and u["pending"] != u["n_params"]:
+                self._reduce_unit(u, self.stream)
+        if not self._joined:
+            torch.cuda.current_stream(self.arena.device).wait_stream(self.stream)
+            self._joined = True
+
+    def _ensure_reduced(self) -> None:
+        """``step()`` without a synchronising backward through the hooks (manual loops): reduce what is missing in line."""
+        self._reattach_grads()
+        if not self._joined:
+            torch.cuda.current_stream(self.arena.device).wait_stream(self.stream)
+            self._joined = True
+        for u in self.units:
+            if not u["launched"]:
+                self._reduce_unit(u, None)
+
     # OSS surface --------------------------------------------------------------------
     @torch.no_grad()
     def clip_grad_norm(self, max_norm: float, norm_type: float = 2.0, inv_scale: Optional[torch.Tensor] = None,
                        found_inf: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Total gradient norm from the per-unit partials the reduces left behind + ONE small all-reduce; the clip
+        coefficient stays on the device and rides into the update kernel.  ``inv_scale``: the reduce already applied
+        it when ``self.inv_scale`` was set before backward (the facade does); pass it only for the reported norm."""
         if float(norm_type) != 2.0:
             raise NotImplementedError("the fused ZeRO engine clips by the 2-norm only")
-        self._reattach_grads()
-        self.norm_buf.zero_()
-        tmp = torch.zeros(2, dtype=torch.float32, device=self.arena.device)
-        for g in self.groups:
-            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
-            if g["reduced"] is None:
-                g["reduced"] = torch.empty(max(s1 - s0, 8), dtype=torch.float32, device=self.arena.device)
-            tmp.zero_()
-            self.ctx.reduce_to_owner(self.G.table, g["seg"], C.local_table(self.rank, g["reduced"]), 1.0 / self.world,
-                                     None, C.local_table(self.rank, tmp), C.local_table(self.rank, self.partials),
-                                     C.local_table(self.rank, self.counter), blocks=self._blocks(s1 - s0))
-            self.norm_buf += tmp
+        self._ensure_reduced()
+        torch.sum(self.unit_norms, dim=0, out=self.norm_buf)
         if not self.small(self.norm_buf, self.arena.group):
             dist.all_reduce(self.norm_buf, group=self.arena.group)
         if found_inf is not None:
             torch.maximum(found_inf, (self.norm_buf[1] > 0).float(), out=found_inf)
-        fused.clip_coef(self.norm_buf[0:1], inv_scale, float(max_norm), self.grad_mult, self.total_norm)
+        already = self.inv_scale is not None
+        fused.clip_coef(self.norm_buf[0:1], None if already else inv_scale, float(max_norm), self.grad_mult, self.total_norm)
         self._clip_pending = True
         return self.total_norm
 
@@ -378,28 +486,29 @@ class ZeroPeerEngine:
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        self._reattach_grads()
+        self._ensure_reduced()
         oss = self.oss
-        prereduced = self._clip_pending
-        mult = grad_mult if grad_mult is not None else (self.grad_mult if prereduced else None)
+        mult = grad_mult if grad_mult is not None else (self.grad_mult if self._clip_pending else None)
+        pbuf = self.P16 if self.P16 is not None else self.P
         for gi, (g, pg) in enumerate(zip(self.groups, oss.param_groups)):
             b1, b2 = pg.get("betas", (0.9, 0.999))
             hp = fused.AdamHParams(float(pg["lr"]), float(b1), float(b2), float(pg.get("eps", 1e-8)),
                                    float(pg.get("weight_decay", 0.0)), 1 if self._is_adamw() else 0, 0, None)
             fused.step_advance(g["step"], found_inf)
-            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
-            pbuf = self.P16 if self.P16 is not None else self.P
-            self.ctx.zero_adam(None if prereduced else self.G.table, 0 if prereduced else self.G.mc, pbuf.table,
-                               pbuf.mc if self.P16 is None else 0, g["seg"], self.wire_dtype,
-                               C.local_table(self.rank, g["master"]), C.local_table(self.rank, g["m"]),
-                               C.local_table(self.rank, g["v"]), hp, C.local_table(self.rank, g["step"]),
-                               pre_mult=1.0 if prereduced else 1.0 / self.world,
-                               mult_dev=C.local_table(self.rank, mult), found_inf=C.local_table(self.rank, found_inf),
-                               prereduced=prereduced, local_grad=C.local_table(self.rank, g["reduced"]) if prereduced else None,
-                               blocks=self._blocks(max(g["seg"][r + 1] - g["seg"][r] for r in range(self.world))))
+            for u in g["units"]:
+                lo, n = u["own_off"], max(u["own_n"], 8)
+                self.ctx.zero_adam(None, 0, pbuf.table, pbuf.mc if self.P16 is None else 0, u["seg"], self.wire_dtype,
+                                   C.local_table(self.rank, g["master"][lo: lo + n]), C.local_table(self.rank, g["m"][lo: lo + n]),
+                                   C.local_table(self.rank, g["v"][lo: lo + n]), hp, C.local_table(self.rank, g["step"]),
+                                   pre_mult=1.0, mult_dev=C.local_table(self.rank, mult),
+                                   found_inf=C.local_table(self.rank, found_inf), prereduced=True,
+                                   local_grad=C.local_table(self.rank, g["reduced"][lo: lo + n]),
+                                   blocks=self._blocks(max(u["seg"][r + 1] - u["seg"][r] for r in range(self.world))))
         if self.P16 is not None:
             self.P.tensor.copy_(self.P16.tensor)     # local widen of the 16-bit wire copy
         self._clip_pending = False
+        for u in self.units:                         # the next backward starts a new round
+            u["pending"], u["launched"] = u["n_params"], False
         return loss
 
     def _is_adamw(self) -> bool:
@@ -408,51 +517,44 @@ class ZeroPeerEngine:
         return cls is torch.optim.AdamW or (issubclass(cls, FusedAdamW) and not issubclass(cls, FusedAdam))
 
     # state dict plumbing (torch layout, per original parameter) ---------------------
+    def _owned(self):
+        """(group, unit, param, offset into the group's owned arrays) for every parameter this rank owns."""
+        for g in self.groups:
+            for u in g["units"]:
+                s0 = u["seg"][self.rank]
+                for p, off, r in u["entries"]:
+                    if r == self.rank:
+                        yield g, u, p, u["own_off"] + (off - s0)
+
     def local_state_dict(self) -> Dict[str, Any]:
         state, gmap = {}, []
-        k = 0
-        for g in self.groups:
-            s0 = g["seg"][self.rank]
+        for k, (g, _u, p, lo) in enumerate(self._owned()):
+            gmap.append(self.oss.param_to_index[id(p)])
             if float(g["step"].item()) == 0.0:
-                for p, off, r in g["entries"]:
-                    if r == self.rank:
-                        gmap.append(self.oss.param_to_index[id(p)])
-                        k += 1
                 continue
-            for p, off, r in g["entries"]:
-                if r != self.rank:
-                    continue
-                lo = off - s0
-                state[k] = {"step": g["step"].detach().clone(),
-                            "exp_avg": g["m"][lo: lo + p.numel()].view(p.shape).clone(),
-                            "exp_avg_sq": g["v"][lo: lo + p.numel()].view(p.shape).clone()}
-                gmap.append(self.oss.param_to_index[id(p)])
-                k += 1
+            state[k] = {"step": g["step"].detach().clone(),
+                        "exp_avg": g["m"][lo: lo + p.numel()].view(p.shape).clone(),
+                        "exp_avg_sq": g["v"][lo: lo + p.numel()].view(p.shape).clone()}
         return {"state": state, "param_groups": [], "global_index": gmap}
 
     @torch.no_grad()
     def load_full_state(self, full_state: Dict[Any, Any]) -> None:
-        for g in self.groups:
-            s0 = g["seg"][self.rank]
-            for p, off, r in g["entries"]:
-                if r != self.rank:
-                    continue
-                gi = self.oss.param_to_index[id(p)]
-                st = full_state.get(gi, full_state.get(str(gi)))
-                lo = off - s0
-                if st is not None:
-                    g["m"][lo: lo + p.numel()].copy_(st["exp_avg"].reshape(-1))
-                    g["v"][lo: lo + p.numel()].copy_(st["exp_avg_sq"].reshape(-1))
-                    g["step"].fill_(float(st["step"]))
-            n = g["seg"][self.rank + 1] - s0
-            g["master"][:n].copy_(self.P.tensor[s0: s0 + n])
+        for g, _u, p, lo in self._owned():
+            gi = self.oss.param_to_index[id(p)]
+            st = full_state.get(gi, full_state.get(str(gi)))
+            if st is not None:
+                g["m"][lo: lo + p.numel()].copy_(st["exp_avg"].reshape(-1))
+                g["v"][lo: lo + p.numel()].copy_(st["exp_avg_sq"].reshape(-1))
+                g["step"].fill_(float(st["step"]))
+        self.refresh_master()
 
     @torch.no_grad()
     def refresh_master(self) -> None:
         """Parameters were overwritten from outside (checkpoint load): re-seed the masters."""
         for g in self.groups:
-            s0, s1 = g["seg"][self.rank], g["seg"][self.rank + 1]
-            g["master"][: s1 - s0].copy_(self.P.tensor[s0:s1])
+            for u in g["units"]:
+                s0 = u["seg"][self.rank]
+                g["master"][u["own_off"]: u["own_off"] + u["own_n"]].copy_(self.P.tensor[s0: s0 + u["own_n"]])
 
 
 # --------------------------------------------------------------------------- attachment

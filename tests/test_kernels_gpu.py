@@ -313,19 +313,22 @@ def test_attention_layout_kernels_and_autograd(dtype, B, S, H, d):
     torch.testing.assert_close(g1, x.grad, rtol=2e-2, atol=2e-2)
 
 
-def test_swinir_on_kernel_path_matches_stock_ops():
-    """SwinIR with kernel-friendly widths (multiples of 8): tcgen05 linears, fused LayerNorm, attention layout
-    kernels vs the same weights on stock torch ops."""
+@pytest.mark.parametrize("embed_dim", [96, 60])
+def test_swinir_on_kernel_path_matches_stock_ops(embed_dim):
+    """SwinIR on the kernel path (tcgen05 linears / convolutions, fused LayerNorm, tcgen05 window attention) vs the same
+    weights on stock torch ops.  embed_dim 96: widths inside the kernels' envelope; embed_dim 60: the reference's own
+    SwinIR-S (Stoke-DDP.py:206-208) — head dimension 10, every width padded to the next multiple of 8 / 64."""
     from pytorch_distributedtraining_b200.models.swinir import SwinIR
-    from pytorch_distributedtraining_b200.ops import dispatch
+    from pytorch_distributedtraining_b200.ops import _lib, dispatch
     torch.manual_seed(2)
-    net = SwinIR(upscale=2, in_chans=3, img_size=64, window_size=8, img_range=1., depths=[2, 2], embed_dim=96,
+    net = SwinIR(upscale=2, in_chans=3, img_size=64, window_size=8, img_range=1., depths=[2, 2], embed_dim=embed_dim,
                  num_heads=[6, 6], mlp_ratio=2, upsampler="pixelshuffledirect", resi_connection="1conv").cuda()
     x = torch.rand(4, 3, 64, 64, device="cuda")
     outs = []
     for stock in (False, True):
         net.zero_grad(set_to_none=True)
-        feats = ("gemm", "ln", "attn_layout", "mlp", "conv")
+        feats = ("gemm", "ln", "attn_layout", "mlp", "conv", "attn", "pad")
+        launches0 = _lib.LAUNCHES
         if stock:
             for f in feats:
                 dispatch.disable(f)
@@ -338,6 +341,9 @@ def test_swinir_on_kernel_path_matches_stock_ops():
                 dispatch.enable(f)
         g = torch.cat([p.grad.flatten().float() for p in net.parameters() if p.grad is not None])
         outs.append((y.float().detach(), g))
+        if not stock:
+            # 4 blocks x (qkv, proj, fc1, fc2 forward + 2 backward GEMMs each, attention fwd + bwd) + convolutions
+            assert _lib.LAUNCHES - launches0 >= 4 * (4 * 3 + 2), _lib.LAUNCHES - launches0
     assert torch.isfinite(outs[0][0]).all() and torch.isfinite(outs[0][1]).all()
     torch.testing.assert_close(outs[0][0], outs[1][0], rtol=5e-2, atol=5e-2)
     rel = (outs[0][1] - outs[1][1]).norm() / outs[1][1].norm()
