@@ -63,19 +63,23 @@ def _reduce_scatter_into(out: torch.Tensor, full: torch.Tensor, group: Any, worl
 
 
 class _Unshard(torch.autograd.Function):
-    """forward: shard -> gathered flat tensor; backward: full grad -> shard grad."""
+    """forward: shard -> per-parameter views of the gathered flat tensor; backward: the per-parameter gradients ->
+    shard gradient.  Returning the VIEWS (instead of the flat tensor, split afterwards) hands the backward the
+    individual gradient pieces: the peer-memory path copies them straight into its symmetric staging buffer and
+    reduce-scatters from there — one copy in total, where ``cat`` + stage would be two."""
 
     @staticmethod
-    def forward(ctx, flat_shard: torch.Tensor, unit: "FullyShardedDataParallel") -> torch.Tensor:  # type: ignore[override]
+    def forward(ctx, flat_shard: torch.Tensor, unit: "FullyShardedDataParallel"):  # type: ignore[override]
         ctx.unit = unit
+        ctx.set_materialize_grads(False)
         # a fresh alias each call: clean autograd history, same storage (so the
         # re-gather before backward refills what autograd saved)
-        return unit._gather_full().detach()
+        return unit._split(unit._gather_full().detach())
 
     @staticmethod
-    def backward(ctx, grad_full: torch.Tensor):  # type: ignore[override]
+    def backward(ctx, *grads: Optional[torch.Tensor]):  # type: ignore[override]
         unit: FullyShardedDataParallel = ctx.unit
-        return unit._reduce_grad(grad_full), None
+        return unit._reduce_grad(grads), None
 
 
 class FullyShardedDataParallel(nn.Module):
@@ -241,19 +245,46 @@ class FullyShardedDataParallel(nn.Module):
             self._full.untyped_storage().resize_(0)
         self._full_valid = False
 
-    def _install_views(self, full: torch.Tensor) -> None:
+    def _split(self, full: torch.Tensor) -> Tuple[torch.Tensor, ...]:
         pad = self._padded - self._total
-        views = full.split(self._numels + ([pad] if pad else []))  # backward is one cat, no slice copy
+        return tuple(full.split(self._numels + ([pad] if pad else [])))[: len(self._numels)]
+
+    def _install_views(self, full) -> None:
+        """``full``: the gathered flat tensor, or the tuple of per-parameter views of it."""
+        views = full if isinstance(full, tuple) else self._split(full)
         for (m, name, shape, _n, _fq), v in zip(self._infos, views):
             setattr(m, name, v.view(shape))
         for m, name, idx in self._shared:
             src_m, src_name = self._infos[idx][0], self._infos[idx][1]
             setattr(m, name, getattr(src_m, src_name))
 
+    def _cat_grads(self, grads) -> torch.Tensor:
+        """Per-parameter gradient pieces (``None``: no gradient) -> flat padded gradient in the compute dtype."""
+        ref = next((g for g in grads if g is not None), None)
+        dt = ref.dtype if ref is not None else self.compute_dtype
+        dev = ref.device if ref is not None else self.flat_param.device
+        pieces = [(g.reshape(-1) if g is not None else torch.zeros(n, dtype=dt, device=dev)) for g, n in zip(grads, self._numels)]
+        pad = self._padded - self._total
+        if pad:
+            pieces.append(torch.zeros(pad, dtype=dt, device=dev))
+        return torch.cat(pieces)
+
     @torch.no_grad()
-    def _reduce_grad(self, grad_full: torch.Tensor) -> Optional[torch.Tensor]:
+    def _reduce_grad(self, grads) -> Optional[torch.Tensor]:
         """Post-backward for this unit: (accumulate) → pre-divide → reduce-scatter →
-        post-divide → fp32 shard gradient."""
+        post-divide → fp32 shard gradient.  ``grads``: the per-parameter gradient pieces."""
+        if (self._peer_engine is not None and self._require_backward_grad_sync and self._grad_accum_full is None
+                and not self.fp32_reduce_scatter and hasattr(self._peer_engine, "reduce_scatter_pieces")):
+            # peer path: pieces -> symmetric staging (the only copy) -> reduce-scatter + scale + fp32 cast on the
+            # reduce stream, overlapped with the backward of the units below; the shard gradient is attached to
+            # flat_param.grad at the end of backward (nothing flows through autograd here)
+            if self._full is not None:
+                self._install_views(self._full.detach())
+            if self.reshard_after_forward:
+                self._free_full()
+            self._peer_engine.reduce_scatter_pieces(grads, 1.0 / self.world_size)
+            return None
+        grad_full = self._cat_grads(grads)
         # the module attributes still point at views of this iteration's autograd graph; swap them
         # for history-free views so the graph (and its AccumulateGrad nodes, which would otherwise be
         # re-used by the next iteration and break CUDA-graph capture) can be freed
@@ -329,7 +360,11 @@ class FullyShardedDataParallel(nn.Module):
         def hook(_grad: torch.Tensor) -> None:
             if not fired[0]:
                 fired[0] = True
-                self._gather_full()
+                self._bwd_gather = True          # tells a prefetching engine which way the pass is moving
+                try:
+                    self._gather_full()
+                finally:
+                    self._bwd_gather = False
 
         def visit(x: Any) -> Any:
             if isinstance(x, torch.Tensor) and x.requires_grad:

@@ -206,49 +206,197 @@ class DDPPeerEngine:
 
 # --------------------------------------------------------------------------- FSDP
 class FSDPPeerEngine:
-    def __init__(self, arena: PeerArena, root: Any, blocks: int = 32):
+    """ZeRO-3 on the peer-memory kernels: parameters stay SHARDED in memory.
+
+    Leaf units (the transformer blocks) share a ring of ``ring`` gathered-parameter buffers in symmetric memory;
+    a unit's parameters are gathered into slot ``i % ring`` right before it runs, in forward and again in backward
+    (fairscale's ``reshard_after_forward``), by the all-gather kernel with the fp32 -> compute-dtype cast fused
+    in.  The gather of the NEXT unit (forward: i + 1, backward: i - 1) is launched on the gather stream when unit i
+    starts, so it overlaps unit i's compute.  Units that contain other units (the root: embedding + head) span the
+    whole pass and keep a buffer of their own.
+
+    Gradients: the per-parameter pieces autograd hands to the unit's backward are copied into one of two symmetric
+    staging buffers (the only copy) and the reduce-scatter kernel (sum, 1/world, fp32 shard out) runs on the reduce
+    stream, overlapped with the backward of the units below.  The shard gradients are attached to ``flat_param.grad``
+    by the end-of-backward callback, after the main stream has joined the reduce stream.
+
+    The ring assumes the leaf units run one after the other in the same order every pass (true for layer stacks);
+    ``B200DP_FSDP_RESIDENT=1`` gives every unit its own buffer instead (no re-gather in backward, nothing sharded
+    but the optimizer state and the gradients)."""
+
+    def __init__(self, arena: PeerArena, root: Any, blocks: int = 32, ring: int = 3):
+        import os
         from .fsdp import FullyShardedDataParallel
         self.arena, self.blocks = arena, blocks
-        self.ctx = arena.context("main")
+        self.gctx, self.rctx = arena.context("gather"), arena.context("reduce")
+        self.gstream = torch.cuda.Stream(device=arena.device)
+        self.rstream = torch.cuda.Stream(device=arena.device)
         units = [u for u in root.modules() if isinstance(u, FullyShardedDataParallel) and u.flat_param is not None]
+        self.units = units
+        spanning = [any(isinstance(m, FullyShardedDataParallel) and m is not u and m.flat_param is not None
+                        for m in u.module.modules()) for u in units]
+        leaves = [u for u, sp in zip(units, spanning) if not sp]
+        ring = max(2, int(os.environ.get("B200DP_FSDP_RING", ring)))     # >= 2: the prefetch target is the slot of unit i - 1
+        resident = os.environ.get("B200DP_FSDP_RESIDENT", "0") not in ("", "0") or len(leaves) <= ring \
+            or not all(u.reshard_after_forward for u in leaves)
+        self.resident = resident
+        self.ring = ring
+        self._ops: Dict[int, _FSDPUnitOps] = {}
         biggest = max(u._padded for u in units)
-        self.grad_stage: Dict[torch.dtype, SymmBuffer] = {}
-        self._full: Dict[int, SymmBuffer] = {}
-        self._biggest = biggest
-        for u in units:
-            sb = arena.alloc(u._padded, u.compute_dtype)
+        slots: List[SymmBuffer] = []
+        if not resident:
+            big_leaf = max(u._padded for u in leaves)
+            dts = {u.compute_dtype for u in leaves}
+            if len(dts) != 1:
+                raise RuntimeError("FSDP peer ring: leaf units must share one compute dtype")
+            slots = [arena.alloc(big_leaf, leaves[0].compute_dtype) for _ in range(ring)]
+        self.slots = slots
+        self.slot_owner: List[Optional[int]] = [None] * len(slots)
+        leaf_i = 0
+        for u, sp in zip(units, spanning):
+            if sp or resident:
+                sb = arena.alloc(u._padded, u.compute_dtype)
+                slot = None
+                u.reshard_after_forward = False          # its buffer is its own: nothing to re-gather
+            else:
+                slot = leaf_i % ring
+                base = slots[slot]
+                sb = SymmBuffer(base.tensor[: u._padded], base.ptrs, base.mc)
+                u.reshard_after_forward = True
+                leaf_i += 1
             u._full = sb.tensor
             u._full_valid = False
-            u._full_persistent = True           # arena memory is never resized away
-            u.reshard_after_forward = False     # gathered params stay resident: no re-gather in backward
-            self._full[id(u)] = sb
-            u.attach_peer_engine(_FSDPUnitOps(self, u, sb))
+            u._full_persistent = True                    # arena memory is never resized away
+            ops = _FSDPUnitOps(self, u, sb, slot, len(self._ops))
+            self._ops[id(u)] = ops
+            u.attach_peer_engine(ops)
+        self.order: List[_FSDPUnitOps] = []              # leaf units in execution order (recorded on the first pass)
+        self._order_frozen = False
+        self._last = -1
+        self._inflight: Dict[int, bool] = {}             # unit index -> a gather for it is queued on the gather stream
+        self.stage: Dict[torch.dtype, SymmBuffer] = {}      # one symmetric staging buffer per gradient dtype
+        self._biggest = biggest
+        self._pending: List[Tuple[Any, torch.Tensor]] = []
+        self._callback_queued = False
+        self._rs_in_pass = False
 
-    def stage(self, dtype: torch.dtype) -> SymmBuffer:
-        sb = self.grad_stage.get(dtype)
-        if sb is None:
-            sb = self.grad_stage[dtype] = self.arena.alloc(self._biggest, dtype)
-        return sb
+    # ---- gather side
+    def _launch_gather(self, ops: "_FSDPUnitOps") -> None:
+        u, a = ops.unit, self.arena
+        main = torch.cuda.current_stream(a.device)
+        self.gstream.wait_stream(main)        # the slot's previous user (two units ago) is done on the main stream
+        src = u.flat_param.detach()
+        self.gctx.all_gather(ops.full.table, ops.full.mc, C.local_table(a.rank, src), u._shard_numel, src.dtype,
+                             u.compute_dtype, blocks=min(self.blocks, max(1, u._shard_numel // 4096)), stream=self.gstream)
+        if ops.slot is not None:
+            self.slot_owner[ops.slot] = ops.index
+        self._inflight[ops.index] = True
+
+    def gather(self, ops: "_FSDPUnitOps") -> None:
+        """Make unit ``ops``'s full parameters valid on the main stream; prefetch its successor."""
+        a = self.arena
+        main = torch.cuda.current_stream(a.device)
+        if ops.slot is not None and not self._order_frozen and ops not in self.order:
+            self.order.append(ops)
+        have = self._inflight.pop(ops.index, False) and (ops.slot is None or self.slot_owner[ops.slot] == ops.index)
+        if not have:
+            self._launch_gather(ops)
+            self._inflight.pop(ops.index, None)
+        main.wait_stream(self.gstream)
+        # ---- prefetch the neighbour in the direction the pass is moving
+        if ops.slot is None or ops not in self.order:
+            return
+        pos = self.order.index(ops)
+        step = -1 if getattr(ops.unit, "_bwd_gather", False) else 1
+        if pos == 0 and step == 1:
+            self._inflight.clear()             # a new pass: parameters may have changed since any old prefetch
+        self._last = pos
+        nxt = pos + step
+        if 0 <= nxt < len(self.order) and (self._order_frozen or step == -1):
+            self._launch_gather(self.order[nxt])
+
+    def _stage(self, dtype: torch.dtype) -> SymmBuffer:
+        st = self.stage.get(dtype)
+        if st is None:
+            st = self.stage[dtype] = self.arena.alloc(self._biggest, dtype)
+        return st
+
+    def end_of_forward_order(self) -> None:
+        self._order_frozen = len(self.order) > 0
+
+    # ---- gradient side
+    def reduce_scatter_pieces(self, ops: "_FSDPUnitOps", grads: Any, scale: float) -> None:
+        u, a = ops.unit, self.arena
+        main = torch.cuda.current_stream(a.device)
+        ref = next((g for g in grads if g is not None), None)
+        dt = ref.dtype if ref is not None else u.compute_dtype
+        st = self._stage(dt)
+        # the previous unit's reduce-scatter (launched one unit of backward ago) must have finished reading the buffer;
+        # its kernel ends with an all-rank barrier, so the peers are done with it too
+        if self._rs_in_pass:                  # (a side stream may only be waited on once it has joined this pass / capture)
+            main.wait_stream(self.rstream)
+        self._rs_in_pass = True
+        off = 0
+        for g, n in zip(grads, u._numels):
+            dst = st.tensor[off: off + n]
+            if g is None:
+                dst.zero_()
+            else:
+                dst.copy_(g.reshape(-1))
+            off += n
+        if u._padded > off:
+            st.tensor[off: u._padded].zero_()
+        out = torch.empty(u._shard_numel, dtype=torch.float32, device=a.device)
+        self.rstream.wait_stream(main)
+        self.rctx.reduce_scatter(st.table, st.mc, u._shard_numel, dt, C.local_table(a.rank, out), pre_mult=scale,
+                                 blocks=min(self.blocks, max(1, u._shard_numel // 4096)), stream=self.rstream)
+        # `out` is held in _pending until the main stream has joined the reduce stream: no record_stream needed (and
+        # under graph capture its deferred-free event would leave the side stream unjoined)
+        self._pending.append((u, out))
+        if not self._callback_queued:
+            self._callback_queued = True
+            from torch.autograd import Variable
+            Variable._execution_engine.queue_callback(self.finish_backward)
+
+    def finish_backward(self) -> None:
+        self._callback_queued = False
+        self.end_of_forward_order()
+        torch.cuda.current_stream(self.arena.device).wait_stream(self.rstream)
+        for u, out in self._pending:
+            g = out if out.dtype == u.flat_param.dtype else out.to(u.flat_param.dtype)
+            if u.flat_param.grad is None:
+                u.flat_param.grad = g
+            else:
+                u.flat_param.grad.add_(g)
+        self._pending.clear()
+        self._last = -1
+        self._rs_in_pass = False
 
 
 class _FSDPUnitOps:
-    def __init__(self, eng: FSDPPeerEngine, unit: Any, full: SymmBuffer):
-        self.eng, self.unit, self.full = eng, unit, full
+    def __init__(self, eng: FSDPPeerEngine, unit: Any, full: SymmBuffer, slot: Optional[int], index: int):
+        self.eng, self.unit, self.full, self.slot, self.index = eng, unit, full, slot, index
 
     def all_gather(self, full: torch.Tensor, shard_compute: torch.Tensor) -> None:
-        # gather straight from the fp32 shard: the cast to the compute dtype happens in the kernel
-        u, a = self.unit, self.eng.arena
-        src = u.flat_param.detach()
-        self.eng.ctx.all_gather(self.full.table, self.full.mc, C.local_table(a.rank, src), u._shard_numel, src.dtype,
-                                u.compute_dtype, blocks=min(self.eng.blocks, max(1, u._shard_numel // 4096)))
+        self.eng.gather(self)
+
+    def reduce_scatter_pieces(self, grads: Any, scale: float) -> None:
+        self.eng.reduce_scatter_pieces(self, grads, scale)
 
     def reduce_scatter(self, out: torch.Tensor, grad_full: torch.Tensor, scale: float) -> None:
-        u, a = self.unit, self.eng.arena
-        st = self.eng.stage(grad_full.dtype)
+        """Flat-gradient form (accumulated ``no_sync`` gradients, fp32 reduce-scatter): staged and reduced in line."""
+        u, a, eng = self.unit, self.eng.arena, self.eng
+        st = eng._stage(grad_full.dtype)
+        main = torch.cuda.current_stream(a.device)
+        if eng._rs_in_pass:
+            main.wait_stream(eng.rstream)
+        eng._rs_in_pass = True
         st.tensor[: grad_full.numel()].copy_(grad_full.reshape(-1))
         out32 = out if out.dtype == torch.float32 else torch.empty_like(out, dtype=torch.float32)
-        self.eng.ctx.reduce_scatter(st.table, st.mc, u._shard_numel, grad_full.dtype, C.local_table(a.rank, out32),
-                                    pre_mult=scale, blocks=min(self.eng.blocks, max(1, u._shard_numel // 4096)))
+        eng.rstream.wait_stream(main)
+        eng.rctx.reduce_scatter(st.table, st.mc, u._shard_numel, grad_full.dtype, C.local_table(a.rank, out32),
+                                pre_mult=scale, blocks=min(eng.blocks, max(1, u._shard_numel // 4096)), stream=eng.rstream)
+        main.wait_stream(eng.rstream)
         if out32 is not out:
             out.copy_(out32)
 
@@ -429,11 +577,13 @@ class ZeroPeerEngine:
         else:
             ctx = self.ctx
         out = g["reduced"][u["own_off"]: u["own_off"] + max(u["own_n"], 8)]
-        n_own = u["own_n"]
         ctx.reduce_to_owner(self.G.table, u["seg"], C.local_table(self.rank, out), 1.0 / self.world,
                             C.local_table(self.rank, self.inv_scale),
                             C.local_table(self.rank, self.unit_norms[u["index"]]), C.local_table(self.rank, self.partials),
-                            C.local_table(self.rank, self.counter), blocks=self._blocks(n_own), stream=stream)
+                            C.local_table(self.rank, self.counter),
+                            # the CTA count must be the SAME on every rank (CTA b of all ranks meet at barrier row b):
+                            # derive it from the largest segment of the unit, never from this rank's own share
+                            blocks=self._blocks(max(u["seg"][r + 1] - u["seg"][r] for r in range(self.world))), stream=stream)
         u["launched"] = True
 
     def finish_backward(self) -> None:
@@ -564,7 +714,8 @@ def _arena_bytes(engine: Any, optim: Any, status: Any) -> int:
     if status.fully_sharded:
         from .fsdp import FullyShardedDataParallel
         units = [u for u in engine.modules() if isinstance(u, FullyShardedDataParallel) and u.flat_param is not None]
-        total = sum(u._padded for u in units) * 2 + max(u._padded for u in units) * 4 * 2
+        # worst case (every unit resident) + two staging buffers (also as fp32) + flag contexts
+        total = sum(u._padded for u in units) * 2 + max(u._padded for u in units) * 4 * 4
         return total + (8 << 20)
     if status.sharded:
         return n_params * 4 * 3 + (16 << 20)

@@ -306,9 +306,21 @@ def _w_facade_peer(rank, world, mode):
     # epilogue accumulates with float atomics) so that what is compared is the collectives
     dispatch.disable("convstats")
 
+    ring = mode == "fsdp_ring"
+    if ring:
+        # four blocks over a ring of two gathered-parameter slots: parameters are re-gathered in backward, the next
+        # unit's gather is prefetched, gradients leave through the staged reduce-scatter on the side stream
+        import os
+        os.environ["B200DP_FSDP_RING"] = "2"
+        mode = "fsdp"
+
     def run(peer):
         torch.manual_seed(0)
-        model = vit_tiny() if mode == "fsdp" else resnet18(num_classes=10, small_input=True)
+        if mode == "fsdp":
+            from pytorch_distributedtraining_b200.models.vit import VisionTransformer
+            model = VisionTransformer(32, 8, 4, 2, 64, 128, 10) if ring else vit_tiny()
+        else:
+            model = resnet18(num_classes=10, small_input=True)
         kw = dict(fairscale_oss=mode == "sddp", fairscale_sddp=mode == "sddp", fairscale_fsdp=mode == "fsdp")
         s = Stoke(model=model, verbose=False,
                   optimizer=StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs={"lr": 1e-3, "betas": (0.9, 0.99),
@@ -319,6 +331,8 @@ def _w_facade_peer(rank, world, mode):
                   configs=[AMPConfig(init_scale=2.0 ** 10), DDPConfig(local_rank=rank),
                            FairscaleFSDPConfig(min_num_params=10 ** 9), B200Config(peer_collectives=peer)], **kw)
         assert (s._peer is not None) == peer
+        if peer and ring:
+            assert not s._peer["fsdp"].resident and len(s._peer["fsdp"].slots) == 2
         s.model_access.train()
         g = torch.Generator().manual_seed(77 + rank)
         losses = []
@@ -344,10 +358,19 @@ def _w_facade_peer(rank, world, mode):
 
 
 @needs2
-@pytest.mark.parametrize("mode", ["ddp", "sddp", "fsdp"])
+@pytest.mark.parametrize("mode", ["ddp", "sddp", "fsdp", "fsdp_ring"])
 def test_real_facade_peer_matches_nccl(mode):
     from pytorch_distributedtraining_b200.utils.testing import spawn
     spawn(_w_facade_peer, 2, (mode,), backend="nccl")
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs >= 4 GPUs")
+@pytest.mark.parametrize("mode", ["ddp", "sddp", "fsdp_ring"])
+def test_real_facade_peer_matches_nccl_on_every_gpu(mode):
+    """The same equivalence on all GPUs of the box (4 or 8 ranks): loss trajectories and final weights of the
+    peer-memory engines against the NCCL engines."""
+    from pytorch_distributedtraining_b200.utils.testing import spawn
+    spawn(_w_facade_peer, min(torch.cuda.device_count(), 8), (mode,), backend="nccl")
 
 
 @pytest.mark.parametrize("world", [2, 8])
