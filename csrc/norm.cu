@@ -129,6 +129,9 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
     if (!(rl < rpb && cg < tpr)) return;
     float sc[8], sh[8];
     const int c0 = cg * 8;
+    // count <= 0: the element count rides in sums[2C] (cross-rank statistics: the all-reduced TRUE count, so ranks with
+    // ragged last batches still normalise by what was really summed)
+    if (kTrain && !(count > 0.f)) count = sums[2 * C];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         float mean, invstd;
@@ -282,6 +285,7 @@ __global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_apply_kernel(
     const int c0 = cg * 8;
     // dx = ga*(dz - m1 - xhat*m2) with xhat = (x - mu)*is  ==  A*dz + B*x + K  (three constants per channel)
     float A[8], B[8], K[8];
+    if (!(count > 0.f)) count = dsums[2 * C];          // same convention: the true cross-rank count in slot 2C
     const float inv_n = 1.f / count;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {

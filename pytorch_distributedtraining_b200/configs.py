@@ -208,6 +208,8 @@ class B200Config:
     channels_last     run convolutional models in NHWC.
     loss_sync_every   how often ``detach_and_sync_loss`` drains to the host
                       (1 keeps the reference's per-batch ``.item()`` semantics).
+    loss_sync_lag     1: ``detach_and_sync_loss`` returns the previous call's value, so the host never waits
+                      for the step it has just enqueued (0: wait, the reference's semantics).
     watchdog_timeout_s  spin limit of the in-kernel cross-rank barriers (a stuck peer raises a
                       status word instead of hanging the GPU).
     step_watchdog_s   host-side hang guard: if no optimizer step finishes for this many seconds
@@ -221,6 +223,7 @@ class B200Config:
     cuda_graph: bool = False
     channels_last: bool = True
     loss_sync_every: int = 1
+    loss_sync_lag: int = 0
     watchdog_timeout_s: float = 120.0
     step_watchdog_s: float = 0.0
     step_watchdog_abort: bool = False

@@ -557,23 +557,57 @@ class Stoke:
     def detach_and_sync_loss(self, loss: LossT, device: Optional[torch.device] = None) -> Any:
         """Mean of a loss across ranks as a Python float (Stoke-DDP.py:86).
 
-        The reference pays one all-reduce and one host sync per batch here.  With
-        ``B200Config(loss_sync_every=k)`` the value is refreshed only every *k*-th call
-        and the last synced value is returned in between.
+        The reference pays one NCCL all-reduce and one blocking ``.item()`` per batch here.  On the GPU path the
+        cross-rank sum is the one-shot peer-memory kernel (W11: no NCCL launch), the scalar is copied into pinned
+        host memory asynchronously, and
+          * ``B200Config(loss_sync_lag=0)`` (default) waits for that copy: the reference's exact semantics;
+          * ``loss_sync_lag=1`` returns the value of the PREVIOUS call instead (first call: this one's), so the host
+            never waits for the step it has just enqueued — the loss curve is the same, one call late;
+          * ``loss_sync_every=k`` refreshes only every k-th call and returns the last value in between.
         """
         self._loss_sync_calls += 1
         k = max(1, self._b200.loss_sync_every)
         if k > 1 and (self._loss_sync_calls % k) != 0 and getattr(self, "_last_synced", None) is not None:
             return self._last_synced
+        dist_on = self._status.is_distributed and self.world_size > 1
 
-        def one(l: torch.Tensor) -> float:
+        def one_host(l: torch.Tensor) -> float:
             t = l.detach().float().clone()
-            if self._status.is_distributed and self.world_size > 1:
+            if dist_on:
                 dist.all_reduce(t)
                 t /= self.world_size
             return float(t.item())
 
-        self._last_synced = _map_loss(one, loss)
+        losses = list(loss) if isinstance(loss, (list, tuple)) else [loss]
+        on_gpu = self._status.gpu and all(isinstance(l, torch.Tensor) and l.is_cuda for l in losses)
+        if not on_gpu:
+            self._last_synced = _map_loss(one_host, loss)
+            return self._last_synced
+        # ---- device path: pack, one small all-reduce, async drain
+        n = len(losses)
+        st = getattr(self, "_loss_sync_state", None)
+        if st is None or st["dev"].numel() != n:
+            st = self._loss_sync_state = {
+                "dev": torch.zeros(n, dtype=torch.float32, device=self._device),
+                "host": [torch.zeros(n, dtype=torch.float32).pin_memory() for _ in range(2)],
+                "evt": [torch.cuda.Event(), torch.cuda.Event()], "slot": 0, "pending": None}
+        buf = st["dev"]
+        for i, l in enumerate(losses):
+            buf[i].copy_(l.detach().float().reshape(()))
+        if dist_on:
+            from .parallel import peer
+            if not peer.small_allreduce(buf, None):
+                dist.all_reduce(buf)
+            buf.div_(self.world_size)
+        slot = st["slot"]
+        st["host"][slot].copy_(buf, non_blocking=True)
+        st["evt"][slot].record()
+        lag = max(0, int(getattr(self._b200, "loss_sync_lag", 0)))
+        read = slot if (lag == 0 or st["pending"] is None) else st["pending"]
+        st["evt"][read].synchronize()
+        vals = [float(v) for v in st["host"][read]]
+        st["pending"], st["slot"] = slot, slot ^ 1
+        self._last_synced = type(loss)(vals) if isinstance(loss, (list, tuple)) else vals[0]
         return self._last_synced
 
     def _is_info_rank(self) -> bool:

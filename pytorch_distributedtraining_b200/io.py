@@ -83,6 +83,8 @@ def save(stoke, path: str, name: str = "", extension: str = "pt", create_directo
         optim_sd = _fsdp_optim_state(stoke)
         optim_layout = "fsdp_named"
     else:
+        if hasattr(model, "_flush_lazy_buffers"):
+            model._flush_lazy_buffers()      # BatchNorm statistics whose per-forward broadcast was elided (collective)
         model_sd = _strip_prefix(stoke._unwrapped.state_dict())
         if isinstance(optim, OSS):
             optim.consolidate_state_dict(recipient_rank=0)

@@ -113,7 +113,7 @@ def conv_padded_supported(mod: Any, x: torch.Tensor) -> bool:
 
 
 def conv_supported(mod: Any, x: torch.Tensor) -> bool:
-    """Implicit-GEMM envelope: NHWC fp16/bf16, groups == 1, dilation == 1, Cin % 64 == 0, Cout % 16 == 0."""
+    """Implicit-GEMM envelope: NHWC fp16/bf16, groups == 1, dilation == 1, Cin % 64 == 0 (any multiple of 8 for 1x1 / stride 1), Cout % 8 == 0 — `ops.conv.shape_supported` is the check."""
     if not (enabled("conv") and _lib_ok()):
         return False
     from . import conv

@@ -66,7 +66,9 @@ class _BatchNormActFn(torch.autograd.Function):
         if world > 1:
             sums[2 * C] = count
             _allreduce_stats(sums, group)
-            count = float(rows) * world  # equal per-rank batch (DistributedSampler pads); avoids a host sync
+            # the kernels read the TRUE element count from slot 2C of the reduced vector (count <= 0 selects that):
+            # no host sync, and a ragged last batch on one rank (validation, drop_last=False) does not skew the statistics
+            count = 0.0
         y = torch.empty_like(x)
         mean = torch.empty(C, dtype=torch.float32, device=dev)
         invstd = torch.empty(C, dtype=torch.float32, device=dev)
@@ -77,6 +79,7 @@ class _BatchNormActFn(torch.autograd.Function):
                                   ptr(invstd), ctypes.c_int(int(relu)), ptr(mask), st), "bn_apply")
         ctx.save_for_backward(x, mask, weight, mean, invstd)
         ctx.relu, ctx.group, ctx.world, ctx.count = relu, group, world, count
+        ctx.total = sums[2 * C: 2 * C + 1] if world > 1 else None      # device scalar: cross-rank element count
         ctx.has_res = residual is not None
         return y
 
@@ -91,7 +94,7 @@ class _BatchNormActFn(torch.autograd.Function):
         dev = x.device
         ws = Workspace.get(dev)
         scratch = ws.scratch(int(lib.b200dp_bn_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
-        dsums = torch.empty(2 * C, dtype=torch.float32, device=dev)
+        dsums = torch.empty(2 * C + 1, dtype=torch.float32, device=dev)     # [sum dz | sum dz*xhat | element count]
         st = stream_ptr(dev)
         relu = ctypes.c_int(int(ctx.relu))
         check(lib.b200dp_bn_bwd_reduce(ptr(dy), None, ptr(x), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(mean),
@@ -99,10 +102,11 @@ class _BatchNormActFn(torch.autograd.Function):
               "bn_bwd_reduce")
         # parameter gradients are the LOCAL sums (the data-parallel engine averages them); they only need
         # their own storage when the cross-rank exchange is about to overwrite dsums
-        dbias, dweight = dsums[:C], dsums[C:]
+        dbias, dweight = dsums[:C], dsums[C: 2 * C]
         if ctx.world > 1:
             dbias, dweight = dbias.clone(), dweight.clone()
-            _allreduce_stats(dsums, ctx.group)
+            _allreduce_stats(dsums[: 2 * C], ctx.group)
+            dsums[2 * C: 2 * C + 1].copy_(ctx.total)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if ctx.has_res else None
         check(lib.b200dp_bn_bwd_apply(ptr(dy), None, ptr(x), ptr(dx), ptr(dres), ctypes.c_int64(rows), ctypes.c_int(C),

@@ -209,6 +209,8 @@ class DistributedDataParallel(nn.Module):
                 bufs = [b.data for b in self.module.buffers()]
                 if bufs:
                     comm.broadcast_coalesced(bufs, src=0, group=self.process_group)
+        elif not self.training:
+            self._flush_lazy_buffers()           # first eval forward after training: the statistics are read now
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             for b in self.buckets:
                 b.reset()
@@ -296,7 +298,13 @@ class DistributedDataParallel(nn.Module):
                 self._post_reduce(b)
 
     # convenience -------------------------------------------------------------
+    def _flush_lazy_buffers(self) -> None:
+        sync = getattr(self._peer_allreduce, "sync_buffers", None)
+        if sync is not None and getattr(sync, "dirty", False) and self.world_size > 1:
+            sync.flush()
+
     def state_dict(self, *args: Any, **kwargs: Any):  # type: ignore[override]
+        self._flush_lazy_buffers()       # running statistics whose per-forward broadcast was elided (collective call)
         return self.module.state_dict(*args, **kwargs)
 
     def load_state_dict(self, *args: Any, **kwargs: Any):  # type: ignore[override]

@@ -20,9 +20,14 @@ Design (functional, not storage-swizzling of ``nn.Parameter``):
   * ``no_sync()`` accumulates the unsharded gradient locally and reduces once.
 
 On CUDA with the kernel library the all-gather / reduce-scatter are the
-peer-memory kernels (reduce-scatter fused with the scale and fp32 cast, W5; gather
-fused into the consuming GEMM's operand fetch for linears, W4); with gloo/NCCL the
-``dist`` collectives are used — that is the baseline and the CPU test path.
+peer-memory kernels (``parallel.symm.FSDPPeerEngine``): the gather casts fp32 shards to the
+compute dtype on the fly, writes into a small ring of gathered-parameter slots and is
+PREFETCHED one unit ahead on its own stream; the reduce-scatter is fused with the scale and
+the fp32 cast (W5), reads the gradient pieces from one symmetric staging buffer and runs on a
+third stream under the backward of the units below.  The gather-inside-the-GEMM kernel (W4,
+``ops.gemm.gemm_gather``) is NOT used here: with the gather prefetched a full unit ahead it
+measured no faster than gather + GEMM.  With gloo/NCCL the ``dist``
+collectives are used — that is the baseline and the CPU test path.
 """
 from __future__ import annotations
 

@@ -15,10 +15,10 @@ Mechanics
   * ``no_sync()`` suppresses communication for gradient accumulation;
   * forward re-broadcasts buffers from rank 0 (``broadcast_buffers``).
 
-On CUDA the facade swaps the per-parameter reduce for the fused
-reduce-to-owner + sharded-AdamW kernel over a flat owner-ordered gradient buffer
-(``parallel.fused_zero``); this module is the portable definition and the NCCL /
-gloo baseline.
+On CUDA the facade attaches ``parallel.symm.ZeroPeerEngine``: the same hooks then
+launch one peer-memory ``reduce_to_owner`` kernel per gradient bucket on a comm stream
+while backward is still running, and ``step()`` finishes with the sharded AdamW + publish
+kernel.  This module is the portable definition and the NCCL / gloo baseline.
 """
 from __future__ import annotations
 
@@ -181,6 +181,8 @@ class ShardedDataParallel(nn.Module):
                 peer_sync()                      # one peer-memory kernel, no NCCL on the hot path
             else:
                 self.sync_buffers()
+        elif not self.training:
+            self._flush_lazy_buffers()           # first eval forward after training: the statistics are read now
         if self._fused_engine is not None:
             self._fused_engine.pre_forward()
         for b in self._buckets.values():
@@ -308,7 +310,13 @@ class ShardedDataParallel(nn.Module):
         self.accumulate_grads_flipped = False
 
     # convenience -------------------------------------------------------------
+    def _flush_lazy_buffers(self) -> None:
+        sync = getattr(self._fused_engine, "sync_buffers", None)
+        if sync is not None and getattr(sync, "dirty", False) and self.world_size > 1:
+            sync.flush()
+
     def state_dict(self, *args: Any, **kwargs: Any):  # type: ignore[override]
+        self._flush_lazy_buffers()       # running statistics whose per-forward broadcast was elided (collective call)
         return self.module.state_dict(*args, **kwargs)
 
     def load_state_dict(self, *args: Any, **kwargs: Any):  # type: ignore[override]

@@ -136,6 +136,7 @@ class PeerBufferSync:
             off += (nbytes + 15) // 16 * 16
         self.nbytes = off
         self.flat: Optional[SymmBuffer] = None
+        self.lazy, self.dirty = False, False
         if off == 0:
             return
         self.flat = arena.alloc(off, torch.uint8)
@@ -148,10 +149,32 @@ class PeerBufferSync:
                 view.copy_(b)
                 b.data = view
 
+        # Buffers that are ONLY BatchNorm running statistics do not influence a training forward: the per-forward
+        # broadcast (a kernel with two all-rank barriers at the top of every step, which serialises rank skew into the
+        # step) is elided and replaced by one broadcast when the statistics are about to be READ — the first eval
+        # forward after training, and state_dict / checkpointing (K11: "elide when the buffers cannot differ in effect").
+        bn_bufs = set()
+        for m in module.modules():
+            if isinstance(m, torch.nn.modules.batchnorm._BatchNorm):
+                bn_bufs.update(id(b) for b in m.buffers(recurse=False))
+        self.lazy = bool(bufs) and all(id(b) in bn_bufs for b in bufs)
+        self.dirty = False
+
     def __call__(self) -> None:
-        if self.flat is not None:
+        """Training forward."""
+        if self.flat is None:
+            return
+        if self.lazy:
+            self.dirty = True
+            return
+        self.flush(force=True)
+
+    def flush(self, force: bool = False) -> None:
+        """Replicate rank 0's buffers now (every rank must call it at the same point)."""
+        if self.flat is not None and (force or self.dirty):
             self.ctx.broadcast(self.flat.table, self.flat.mc, self.nbytes, root=0,
                                blocks=int(min(8, max(1, self.nbytes // 65536))))
+            self.dirty = False
 
 
 # --------------------------------------------------------------------------- DDP

@@ -343,7 +343,7 @@ def _w_facade_peer(rank, world, mode):
             s.backward(loss)
             s.step()
             losses.append(s.detach_and_sync_loss(loss))
-        sd = s.wrapped_model.state_dict() if mode == "fsdp" else s.model_access.state_dict()
+        sd = s.wrapped_model.state_dict()      # through the engine: flushes the lazily synchronised BatchNorm statistics
         return losses, {k: v.detach().float().clone() for k, v in sd.items()}
 
     l_peer, sd_peer = run(True)
