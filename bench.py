@@ -222,7 +222,7 @@ def graph_torch_step(step, x, y, device):
     return replay
 
 
-def measure(step, args, cfg, device, world, rank, host, dev_pool, cl, want_e2e, count_launches):
+def measure(step, args, cfg, device, world, rank, host, dev_pool, cl, want_e2e, count_launches, graphs_pending=None):
     """Device-timed steps (CUDA events, barrier + synchronize on both sides, max over ranks), then the same
     through the host path: pinned batch -> H2D every step, loss -> D2H every step."""
     import torch
@@ -250,6 +250,12 @@ def measure(step, args, cfg, device, world, rank, host, dev_pool, cl, want_e2e, 
         return loss
 
     run_device_steps(max(args.warmup, 3))
+    extra = 0
+    while graphs_pending is not None and graphs_pending() and extra < 8:
+        # every accumulation phase needs three eager calls before its graph is captured: keep warming up (untimed)
+        # until all of them replay, so no capture lands inside the timed region
+        run_device_steps(1)
+        extra += 1
     sync(); barrier(); sync()
     sampler = ClockSampler(gpu_index=device.index or 0).start() if (is_cuda and rank == 0) else None
     launches0 = _lib.LAUNCHES
@@ -270,6 +276,7 @@ def measure(step, args, cfg, device, world, rank, host, dev_pool, cl, want_e2e, 
     ms = max_over_ranks(ms, device if is_cuda else None)
     images = B * accum * world * args.steps
     res = {"value": images / (ms / 1e3), "ms_per_step": ms / args.steps, "launches": launches, "clocks": clocks,
+           "warmup_done": max(args.warmup, 3) + extra,
            "final_loss": float(last.detach().float()) if last is not None else None, "e2e": None}
 
     # ---- end to end: pinned host batch -> H2D every step (prefetched one step ahead on a
@@ -374,7 +381,12 @@ def main() -> None:
         step = graph_torch_step(step, *dev_pool[0], device)
         standin_graphed = True
 
-    res = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, not args.no_e2e, args.impl == "ours")
+    pending = None
+    if stoke is not None and is_cuda and not args.no_graph:
+        def pending():
+            g = stoke._graphs
+            return len(g) < accum or any(e.get("graph") is None for e in g.values())
+    res = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, not args.no_e2e, args.impl == "ours", pending)
     native = stoke.native_status if stoke is not None else None
 
     # ---- same session, same box: the torch-native stand-in (NOT the reference, which cannot be installed)
@@ -403,7 +415,7 @@ def main() -> None:
         stoke.reset_graphs()
         C.MUTE = True
         try:
-            muted = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, False, False)
+            muted = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, False, False, pending)
             exposed = {"exposed_comm_ms": res["ms_per_step"] - muted["ms_per_step"], "ms_per_step_comm_muted": muted["ms_per_step"],
                        "how": "same whole-step CUDA graph re-captured with all peer-memory collective launches skipped"}
         finally:
@@ -418,7 +430,7 @@ def main() -> None:
             pass
         out = {
             "metric": "images/sec", "value": res["value"], "unit": "images/sec", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": res["ms_per_step"], "higher_is_better": True,
+            "warmup": res["warmup_done"], "ms_per_step": res["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": cfg["dtype"] if is_cuda else "fp32",
             "data": "synthetic (random images of the named shape, random-init weights)",
             "impl": {"ours": "ours", "torch": "torch-native stand-in (not the reference)"}[args.impl],

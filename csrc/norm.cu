@@ -20,13 +20,13 @@ struct BNGeom {
     int gy;    // row slices
 };
 
-static inline BNGeom bn_geom(int64_t rows, int C) {
+static inline BNGeom bn_geom(int64_t rows, int C, int per_sm = 4) {
     BNGeom g;
     g.tpr = C / 8;
     g.cgb = g.tpr < 32 ? g.tpr : 32;
     g.rpb = kBNThreads / g.cgb;
     g.gx = (g.tpr + g.cgb - 1) / g.cgb;
-    int64_t want = (B200DP_SMS * 4 + g.gx - 1) / g.gx;        // ~4 CTAs per SM in total
+    int64_t want = (B200DP_SMS * per_sm + g.gx - 1) / g.gx;   // ~per_sm CTAs per SM in total
     int64_t maxy = (rows + (int64_t)g.rpb * 4 - 1) / ((int64_t)g.rpb * 4);  // >= 4 rows per thread
     if (maxy < 1) maxy = 1;
     g.gy = (int)(want < maxy ? want : maxy);
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(kBNThreads, 4) bn_reduce_kernel(const T* __res
 }
 
 template <typename T, bool kTrain>
-__global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
+__global__ void __launch_bounds__(kBNThreads, 3) bn_apply_kernel(
     const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t rows, int C, int tpr, int cgb,
     int rpb, const float* __restrict__ sums, float count, const float* __restrict__ gamma,
     const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
@@ -173,7 +173,27 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
     // convolution, so its tail is what is still resident in the 126 MB L2 when this kernel starts.
     const int64_t last = rows - 1;
     int64_t r = (int64_t)blockIdx.y * rpb + rl;
-    // two rows per iteration: four independent 16-byte loads in flight per thread
+    // four rows per iteration while they last: up to eight independent 16-byte loads in flight per thread
+    for (; r + 3 * rstep < rows; r += 4 * rstep) {
+        Vec8<T> xr[4], rr[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int64_t o = (last - (r + u * rstep)) * C + c0;
+            xr[u] = *reinterpret_cast<const Vec8<T>*>(x + o);
+            if (res != nullptr) rr[u] = *reinterpret_cast<const Vec8<T>*>(res + o);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = Cvt<T>::to_f(xr[u].v[k]) * sc[k] + sh[k];
+            if (res != nullptr) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] += Cvt<T>::to_f(rr[u].v[k]);
+            }
+            finish(v, last - (r + u * rstep));
+        }
+    }
     for (; r + rstep < rows; r += 2 * rstep) {
         const int64_t p0 = last - r, p1 = last - (r + rstep);
         float v0[8], v1[8];
@@ -210,7 +230,7 @@ __global__ void __launch_bounds__(kBNThreads) bn_apply_kernel(
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_reduce_kernel(
+__global__ void __launch_bounds__(kBNThreads, 3) bn_bwd_reduce_kernel(
     const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, int64_t rows, int C, int tpr,
     int cgb, int rpb, const float* __restrict__ mean, const float* __restrict__ invstd, int relu,
     float* __restrict__ scratch, unsigned int* __restrict__ counters, float* __restrict__ dsums,
@@ -245,6 +265,30 @@ __global__ void __launch_bounds__(kBNThreads, 4) bn_bwd_reduce_kernel(
         const int64_t rs = rstep * C;
         int64_t left = rows - ((int64_t)blockIdx.y * rpb + rl);          // rows still ahead of this thread (incl. its current one)
         int64_t off = (rows - 1 - ((int64_t)blockIdx.y * rpb + rl)) * C + c0;
+        // four rows per iteration while they last: eight independent 16-byte loads (plus the mask bytes) in flight per
+        // thread, held as raw vectors until used — a read-only kernel needs more bytes in flight than a copy does
+        for (; left > 3 * rstep; left -= 4 * rstep, off -= 4 * rs) {
+            Vec8<T> dr[4], xr[4];
+            unsigned mk[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                dr[u] = *reinterpret_cast<const Vec8<T>*>(dy + off - u * rs);
+                xr[u] = *reinterpret_cast<const Vec8<T>*>(x + off - u * rs);
+                mk[u] = (relu && mask != nullptr) ? mask[(off - u * rs) >> 3] : 0xffu;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    float d = Cvt<T>::to_f(dr[u].v[k]);
+                    const float xv = Cvt<T>::to_f(xr[u].v[k]);
+                    if (relu && mask == nullptr) d = Cvt<T>::to_f(y[off - u * rs + k]) > 0.f ? d : 0.f;
+                    d = ((mk[u] >> k) & 1u) ? d : 0.f;
+                    a[k] += d;
+                    b[k] = fmaf(d, xv, b[k]);
+                }
+            }
+        }
         for (; left > rstep; left -= 2 * rstep, off -= 2 * rs) {
             float d0[8], x0[8], d1[8], x1[8];
             load8<T>(dy + off, d0);
@@ -545,7 +589,7 @@ int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, 
     B200DP_REQUIRE(x && y && sums && gamma && beta && mean_out && invstd_out, "bn_apply: null argument");
     BN_COMMON_CHECKS("bn_apply")
     B200DP_DISPATCH_HALF(dtype, T, {
-        bn_apply_kernel<T, true><<<grid, kBNThreads, 0, s>>>((const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr,
+        bn_apply_kernel<T, true><<<dim3(bn_geom(rows, C, 3).gx, bn_geom(rows, C, 3).gy), kBNThreads, 0, s>>>((const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr,
                                                              g.cgb, g.rpb, sums, count, gamma, beta, eps, momentum,
                                                              running_mean, running_var, mean_out, invstd_out, relu, relu_mask);
     });
@@ -573,10 +617,14 @@ int b200dp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t r
     B200DP_REQUIRE(dy && x && mean && invstd && scratch && counter && dsums, "bn_bwd_reduce: null argument");
     B200DP_REQUIRE(!relu || y || relu_mask, "bn_bwd_reduce: relu needs the forward output y or the relu mask");
     BN_COMMON_CHECKS("bn_bwd_reduce")
+    // three CTAs per SM with eight 16-byte loads in flight per thread (the kernel is register-heavier than its siblings);
+    // fewer row slices than b200dp_bn_scratch_floats provides for, never more
+    const BNGeom g3 = bn_geom(rows, C, 3);
+    const dim3 grid3(g3.gx, g3.gy);
     B200DP_DISPATCH_HALF(dtype, T, {
-        bn_bwd_reduce_kernel<T><<<grid, kBNThreads, 0, s>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, g.tpr,
-                                                            g.cgb, g.rpb, mean, invstd, relu, scratch, counter,
-                                                            dsums, relu_mask);
+        bn_bwd_reduce_kernel<T><<<grid3, kBNThreads, 0, s>>>((const T*)dy, (const T*)y, (const T*)x, rows, C, g3.tpr,
+                                                             g3.cgb, g3.rpb, mean, invstd, relu, scratch, counter,
+                                                             dsums, relu_mask);
     });
     B200DP_CHECK_LAUNCH();
     return 0;
