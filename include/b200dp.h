@@ -321,6 +321,20 @@ int b200dp_peer_broadcast(const b200dp_peer_ctx* ctx, void* const* bufs, void* m
 int b200dp_peer_small_allreduce(const b200dp_peer_ctx* ctx, void* const* staging, void* const* io, int n,
                                 int slot_floats, void* const* call_counter, void* stream);
 
+/* First-layer convolutions (Cin <= 4: RGB stems) on the tcgen05 tensor cores, without im2col: the input rows of a tile are
+ * staged in shared memory with channels padded so that consecutive output pixels start 16 bytes apart, and the un-swizzled
+ * UMMA layout (LBO 16, SBO 128) reads the overlapping windows straight out of them.
+ *   fwd    y[N][P][Q][Cout] = conv(x[N][H][W][Cin], w[Cout][R][S][Cin]) (+ bias[Cout]), 16-bit NHWC
+ *   wgrad  dw[Cout][R][S][Cin] (fp32) += dy^T im2col(x); ATOMIC accumulation, the caller zeroes dw
+ * Envelope: Cin <= 4, stride 1 or 2, R <= 7, Cout a multiple of 8 up to 64 (b200dp_conv2d_smallc_supported).
+ * Reference: the first convolution of the CNN models (ResNet stem 7x7/2; the SR net of Fairscale-DDP.py:74;
+ * SwinIR conv_first and the VGG layer of feat_loss, Stoke-DDP.py:206-224) — cuDNN first_layer kernels there. */
+int b200dp_conv2d_smallc_supported(int Cin, int Cout, int R, int S, int stride);
+int b200dp_conv2d_smallc_fwd(const void* x, const void* w, void* y, const float* bias, int N, int H, int W, int Cin, int Cout,
+                             int R, int S, int stride, int pad, b200dp_dtype dtype, void* stream);
+int b200dp_conv2d_smallc_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
+                               int stride, int pad, b200dp_dtype dtype, void* stream);
+
 /* Attention core on the tcgen05 tensor cores: out = softmax(q k^T * scale + bias + mask) v, forward and backward,
  * over the PACKED projections (no per-head copies):
  *   qkv / dqkv [B][S][3][H][d],  out / dout [B][S][H][d],  lse [B][H][S] fp32 (row log-sum-exp, written by the forward),

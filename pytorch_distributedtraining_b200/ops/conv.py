@@ -36,8 +36,26 @@ def _is_1x1_s1(mod) -> bool:
     return mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.padding == (0, 0)
 
 
+def smallc_supported(mod) -> bool:
+    """First-layer envelope of ``csrc/conv_smallc_sm100.cu``: Cin <= 4 (RGB), stride 1 or 2, filters up to 7 x 7,
+    Cout a multiple of 8 up to 64."""
+    r, s = mod.kernel_size
+    st = mod.stride[0]
+    if not (mod.in_channels <= 4 and st in (1, 2) and mod.stride[0] == mod.stride[1] and r <= 7):
+        return False
+    kr = (s * (8 // st) + 15) // 16 * 16
+    return (kr <= 64 and r * kr <= 512 and 8 <= mod.out_channels <= 64 and mod.out_channels % 8 == 0
+            and mod.padding[0] == mod.padding[1] and isinstance(mod.padding[0], int))
+
+
 def shape_supported(mod, x) -> bool:
-    if x.dim() != 4 or not x.is_contiguous(memory_format=torch.channels_last):
+    if x.dim() != 4:
+        return False
+    from . import dispatch
+    if smallc_supported(mod) and dispatch.enabled("conv_first"):
+        # a 3-channel NCHW image has no channels-last "contiguity" to speak of: the front end lays it out itself
+        return x.shape[2] + 2 * mod.padding[0] >= mod.kernel_size[0] and x.shape[3] + 2 * mod.padding[0] >= mod.kernel_size[1]
+    if not x.is_contiguous(memory_format=torch.channels_last):
         return False
     if mod.out_channels % 8 != 0:
         return False
@@ -69,6 +87,26 @@ def conv2d_raw(mode: int, x: torch.Tensor, w: torch.Tensor, bias: Optional[torch
     return out.permute(0, 3, 1, 2)
 
 
+def conv2d_smallc_raw(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], n: int, h: int, wd: int, cin: int, cout: int,
+                      r: int, s: int, stride: int, pad: int) -> torch.Tensor:
+    """First-layer forward (Cin <= 4) on ``b200dp_conv2d_smallc_fwd``; NHWC 16-bit in, NCHW-shaped channels-last out."""
+    lib = require_library()
+    p, q = (h + 2 * pad - r) // stride + 1, (wd + 2 * pad - s) // stride + 1
+    out = torch.empty((n, p, q, cout), dtype=x.dtype, device=x.device)
+    check(lib.b200dp_conv2d_smallc_fwd(ptr(x), ptr(w), ptr(out), ptr(bias), n, h, wd, cin, cout, r, s, stride, pad, DT[x.dtype],
+                                       stream_ptr(x.device)), "conv2d_smallc_fwd")
+    return out.permute(0, 3, 1, 2)
+
+
+def conv2d_smallc_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, n: int, h: int, wd: int, cin: int, cout: int, r: int, s: int,
+                            stride: int, pad: int) -> torch.Tensor:
+    lib = require_library()
+    dw = torch.zeros((cout, r, s, cin), dtype=torch.float32, device=x.device)       # the kernel accumulates atomically
+    check(lib.b200dp_conv2d_smallc_wgrad(ptr(x), ptr(dy), ptr(dw), n, h, wd, cin, cout, r, s, stride, pad, DT[x.dtype],
+                                         stream_ptr(x.device)), "conv2d_smallc_wgrad")
+    return dw.permute(0, 3, 1, 2)
+
+
 def conv2d_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, n: int, h: int, wd: int, cin: int, cout: int, r: int, s: int,
                      stride: int, pad: int) -> torch.Tensor:
     """fp32 weight gradient in the channels-last weight layout ([Cout][R][S][Cin] memory)."""
@@ -94,7 +132,11 @@ class _ConvFn(torch.autograd.Function):
             w16 = w16.contiguous(memory_format=torch.channels_last)       # memory = [Cout][R][S][Cin]
         b32 = None if bias is None else bias.float()
         one = r == 1 and s == 1 and stride == 1 and pad == 0
-        if one:
+        small = cin <= 4
+        if small:
+            colstats = None
+            y = conv2d_smallc_raw(x, w16, b32, n, h, w, cin, cout, r, s, stride, pad)
+        elif one:
             x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)
             if colstats is not None and b32 is None:
                 y = gemm(x2, w16.reshape(cout, cin), x2.shape[0], cout, cin, colstats=colstats)
@@ -107,6 +149,7 @@ class _ConvFn(torch.autograd.Function):
         ctx.emitted_stats = colstats is not None
         ctx.save_for_backward(x, w16)
         ctx.geom = (n, cin, h, w, cout, r, s, stride, pad, one)
+        ctx.small = small
         ctx.w_dtype, ctx.has_bias = weight.dtype, bias is not None
         if carry:
             # second output: the input itself, for the branch that bypasses this convolution (residual
@@ -125,7 +168,20 @@ class _ConvFn(torch.autograd.Function):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = dw = db = None
         need_dx, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        if one:
+        if ctx.small:
+            if need_dw:
+                dw = conv2d_smallc_wgrad_raw(x, dy, n, h, w, cin, cout, r, s, stride, pad)
+            if need_dx:
+                from . import dispatch
+                if cout % 64 == 0 and (stride == 1 or (stride == 2 and dispatch.enabled("dgrad_s2"))):
+                    # rare (perceptual loss on an RGB output): pad Cin to 8 and use the regular input-gradient kernel
+                    w8 = torch.zeros((cout, 8, r, s), dtype=w16.dtype, device=w16.device).contiguous(memory_format=torch.channels_last)
+                    w8[:, :cin] = w16
+                    dx = conv2d_raw(1, dy, w8, None, n, h, w, 8, cout, r, s, stride, pad)[:, :cin]
+                else:
+                    dx = torch.ops.aten.convolution_backward(dy, x, w16, None, (stride, stride), (pad, pad), (1, 1), False,
+                                                             (0, 0), 1, (True, False, False))[0]
+        elif one:
             x2 = x.permute(0, 2, 3, 1).reshape(-1, cin)
             dy2 = dy.permute(0, 2, 3, 1).reshape(-1, cout)
             rows = x2.shape[0]

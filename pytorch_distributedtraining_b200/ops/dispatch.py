@@ -104,7 +104,14 @@ def conv_padded_supported(mod: Any, x: torch.Tensor) -> bool:
     dt = _autocast_dtype(x)
     if dt not in _HALF or mod.groups != 1 or mod.dilation != (1, 1) or mod.padding_mode != "zeros":
         return False
-    if x.dim() != 4 or mod.in_channels < 32 or mod.out_channels < 8:
+    if x.dim() != 4 or mod.out_channels < 8:
+        return False
+    if mod.in_channels <= 4:
+        # first layers whose Cout is not a multiple of 8 (SwinIR conv_first: 3 -> 60): pad the filters' Cout only
+        return (enabled("conv_first") and mod.kernel_size[0] <= 7 and mod.kernel_size[1] <= 7 and mod.out_channels <= 64
+                and mod.stride[0] == mod.stride[1] and mod.stride[0] in (1, 2)
+                and mod.padding[0] == mod.padding[1] and isinstance(mod.padding[0], int))
+    if mod.in_channels < 32:
         return False
     if mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.padding == (0, 0):
         return False            # 1x1: handled as a (padded) linear

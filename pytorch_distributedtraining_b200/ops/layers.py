@@ -46,8 +46,9 @@ class Conv2d(nn.Conv2d):
         implicit-GEMM kernels, slice the output channels.  The pads / slice are ordinary autograd ops."""
         from . import conv as _conv
         cin, cout = self.in_channels, self.out_channels
-        cin_p = (cin + 63) // 64 * 64
-        cout_p = (cout + 63) // 64 * 64 if x.requires_grad else (cout + 7) // 8 * 8
+        first_layer = cin <= 4                       # RGB stems keep their channels: only Cout is padded (to 8)
+        cin_p = cin if first_layer else (cin + 63) // 64 * 64
+        cout_p = (cout + 63) // 64 * 64 if (x.requires_grad and not first_layer) else (cout + 7) // 8 * 8
         dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
         xp = x.to(dt)
         if cin_p != cin:

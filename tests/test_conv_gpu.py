@@ -261,3 +261,46 @@ def test_conv_strided_dgrad_by_parity_classes(dtype, N, H, W, Cin, Cout, R, pad)
     torch.cuda.synchronize()
     tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
     torch.testing.assert_close(got.float(), want, rtol=tol, atol=tol * (Cout * R * R) ** 0.5 * 0.05)
+
+
+FIRST_LAYERS = [
+    # N, H, W, Cin, Cout, R, stride, pad, bias
+    (4, 224, 224, 3, 64, 7, 2, 3, False),      # ResNet stem
+    (3, 32, 32, 3, 64, 3, 1, 1, False),        # CIFAR stem / VGG conv1_1 of the perceptual loss
+    (2, 40, 36, 3, 64, 5, 1, 2, True),         # the SR net's first layer (Fairscale-DDP.py:74)
+    (2, 64, 64, 3, 60, 3, 1, 1, True),         # SwinIR conv_first (Stoke-DDP.py:206): Cout padded to 64
+    (2, 19, 23, 4, 24, 3, 2, 1, True),         # four channels, ragged sizes, stride 2
+    (1, 16, 16, 1, 8, 3, 1, 0, False),         # one channel, no padding
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,Cin,Cout,R,stride,pad,bias", FIRST_LAYERS)
+def test_first_layer_convolution_matches_reference(dtype, N, H, W, Cin, Cout, R, stride, pad, bias):
+    """tcgen05 first-layer kernels (im2col tile built in shared memory): forward, weight gradient, bias gradient and —
+    through the padded-Cin route — the input gradient, against fp32 torch on the same rounded data."""
+    from pytorch_distributedtraining_b200.ops import _lib
+    from pytorch_distributedtraining_b200.ops.layers import Conv2d
+    torch.manual_seed(N * 100 + H)
+    conv = Conv2d(Cin, Cout, R, stride, pad, bias=bias).to(cuda)
+    x = torch.randn(N, Cin, H, W, device=cuda).to(dtype).float().requires_grad_(True)       # values exactly representable
+    before = _lib.LAUNCHES
+    with torch.autocast("cuda", dtype=dtype):
+        y = conv(x)
+    assert _lib.LAUNCHES > before, "the first layer did not run on the kernel library"
+    dy = torch.randn_like(y.float())
+    y.float().backward(dy)
+    gw, gb, gx = conv.weight.grad.clone(), (conv.bias.grad.clone() if bias else None), x.grad.clone()
+    conv.zero_grad(); x.grad = None
+    w32 = conv.weight.detach().to(dtype).float().requires_grad_(True)
+    b32 = conv.bias.detach().clone().requires_grad_(True) if bias else None
+    ref = F.conv2d(x, w32, b32, stride=stride, padding=pad)
+    ref.backward(dy.to(dtype).float())
+    tol = 3e-2 if dtype == torch.bfloat16 else 5e-3
+    k = Cin * R * R
+    torch.testing.assert_close(y.float(), ref, rtol=tol, atol=tol * k ** 0.5 * 0.1)
+    scale_w = max(1.0, float(w32.grad.abs().max()))
+    torch.testing.assert_close(gw.float(), w32.grad, rtol=tol, atol=tol * scale_w)
+    if bias:
+        torch.testing.assert_close(gb.float(), b32.grad, rtol=tol, atol=tol * max(1.0, float(b32.grad.abs().max())))
+    torch.testing.assert_close(gx, x.grad, rtol=tol, atol=tol * max(1.0, float(x.grad.abs().max())))
