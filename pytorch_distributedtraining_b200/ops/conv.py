@@ -201,10 +201,17 @@ class _ConvFn(torch.autograd.Function):
                     dx = gemm(dy2, w16.reshape(cout, cin), rows, cin, cout, a_mn=False, b_mn=True).view(n, h, w, cin).permute(0, 3, 1, 2)
         else:
             from . import dispatch
-            ours_dx = need_dx and (stride == 1 or (stride == 2 and dispatch.enabled("dgrad_s2"))) and cout % 64 == 0 and cin % 8 == 0
+            ours_dx = need_dx and (stride == 1 or (stride == 2 and dispatch.enabled("dgrad_s2"))) and cin % 8 == 0
             if need_dw:
                 dw = conv2d_wgrad_raw(x, dy, n, h, w, cin, cout, r, s, stride, pad)
-            if ours_dx:
+            if ours_dx and cout % 64 != 0:
+                # the input-gradient kernel reduces over Cout in 64-channel chunks: zero-pad dY and the filters to the next
+                # multiple of 64 (zeros add nothing) instead of handing the layer to the library
+                cp = (cout + 63) // 64 * 64
+                dyp = torch.cat([dy, dy.new_zeros((n, cp - cout, dy.shape[2], dy.shape[3]))], dim=1).contiguous(memory_format=torch.channels_last)
+                wp = torch.cat([w16, w16.new_zeros((cp - cout, cin, r, s))], dim=0).contiguous(memory_format=torch.channels_last)
+                dx = conv2d_raw(1, dyp, wp, None, n, h, w, cin, cp, r, s, stride, pad)
+            elif ours_dx:
                 dx = conv2d_raw(1, dy, w16, None, n, h, w, cin, cout, r, s, stride, pad)
             if need_dx and not ours_dx:
                 # library path for what the implicit-GEMM kernels do not cover: input gradients

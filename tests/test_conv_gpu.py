@@ -304,3 +304,36 @@ def test_first_layer_convolution_matches_reference(dtype, N, H, W, Cin, Cout, R,
     if bias:
         torch.testing.assert_close(gb.float(), b32.grad, rtol=tol, atol=tol * max(1.0, float(b32.grad.abs().max())))
     torch.testing.assert_close(gx, x.grad, rtol=tol, atol=tol * max(1.0, float(x.grad.abs().max())))
+
+
+@pytest.mark.parametrize("cin,cout,k,stride", [(64, 32, 3, 1), (32, 12, 3, 1), (64, 40, 3, 2), (128, 72, 3, 1)])
+def test_convolutions_outside_the_64_channel_grid_stay_on_the_kernel_library(cin, cout, k, stride):
+    """Layers of the SR net (Fairscale-DDP.py:74: 64 -> 32 -> 12 channels) and other widths that miss the kernels'
+    64-channel granularity: forward, weight gradient and INPUT gradient all run on the tcgen05 kernels (channels
+    zero-padded where needed) and match fp32 torch; the profiler sees no cuDNN kernel."""
+    from torch.profiler import ProfilerActivity, profile
+    from pytorch_distributedtraining_b200.ops.layers import Conv2d
+    torch.manual_seed(cin + cout)
+    conv = Conv2d(cin, cout, k, stride, k // 2).to(cuda).to(memory_format=torch.channels_last)
+    x = torch.randn(4, cin, 24, 24, device=cuda).half().float().contiguous(memory_format=torch.channels_last).requires_grad_(True)
+
+    def run():
+        with torch.autocast("cuda", dtype=torch.float16):
+            y = conv(x)
+        y.float().square().mean().backward()
+        return y
+
+    run(); conv.zero_grad(); x.grad = None
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        y = run()
+        torch.cuda.synchronize()
+    names = [e.key for e in prof.key_averages()]
+    assert not [n for n in names if "cudnn" in n.lower() or "cutlass" in n.lower()], names
+    gw, gx = conv.weight.grad.clone(), x.grad.clone()
+    conv.zero_grad(); x.grad = None
+    w32 = conv.weight.detach().half().float().requires_grad_(True)
+    ref = F.conv2d(x, w32, conv.bias.detach(), stride=stride, padding=k // 2)
+    ref.square().mean().backward()
+    torch.testing.assert_close(y.float(), ref, rtol=5e-3, atol=5e-3 * (cin * k * k) ** 0.5 * 0.1)
+    torch.testing.assert_close(gw.float(), w32.grad, rtol=2e-2, atol=2e-2 * max(1e-3, float(w32.grad.abs().max())))
+    torch.testing.assert_close(gx, x.grad, rtol=2e-2, atol=2e-2 * max(1e-4, float(x.grad.abs().max())))
