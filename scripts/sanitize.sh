@@ -7,7 +7,8 @@ TOOL=${1:-memcheck}
 mkdir -p gpurun_out
 # small shapes only: the sanitizer slows kernels 10-100x
 timeout 800 compute-sanitizer --tool "$TOOL" --error-exitcode 3 --log-file gpurun_out/sanitizer_${TOOL}.log \
-    python -m pytest tests/test_kernels_gpu.py -m gpu -q -x -k "adamw or sgd or cross_entropy or mse or layer_norm or unscale or sumsq" \
+    python -m pytest tests/test_kernels_gpu.py tests/test_attention_gpu.py tests/test_conv_gpu.py -m gpu -q -x \
+    -k "adamw or sgd or cross_entropy or mse or layer_norm or unscale or sumsq or 5-2-17-32 or 16-6-64-10 or 16-16-1-8 or 19-23-4-24" \
     > gpurun_out/sanitizer_${TOOL}_pytest.log 2>&1
 rc=$?
 tail -3 gpurun_out/sanitizer_${TOOL}_pytest.log
