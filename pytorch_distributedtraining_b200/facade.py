@@ -137,6 +137,13 @@ class Stoke:
         # 3/4. optimizer + engine
         self._optimizer_spec = optimizer
         self._model, self._optimizer = self._build_engine(model, optimizer)
+        # 16-bit weight shadows: the fused update kernel also writes the compute-dtype copy of every matrix-shaped
+        # parameter, so convolutions / linears stop casting their fp32 weights each forward
+        if self._fused_ok() and self._status.fp16 is not None and not self._status.fully_sharded:
+            inner = self._optimizer.optim if isinstance(self._optimizer, OSS) else self._optimizer
+            if getattr(inner, "writes_shadows", False) and getattr(self._optimizer, "_flat_engine", None) is None:
+                inner.lp_dtype = torch.bfloat16 if self._status.is_bf16 else torch.float16
+                inner.make_shadows()
         # 5. scaler
         self._scaler = self._build_scaler()
         if self._verbose:

@@ -127,7 +127,8 @@ class _ConvFn(torch.autograd.Function):
             x = x.to(dtype)
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
-        w16 = weight.to(dtype) if weight.dtype != dtype else weight
+        from .fused import lp_weight
+        w16 = lp_weight(weight, dtype)        # the optimizer's 16-bit shadow when it has one: no cast kernel
         if not w16.is_contiguous(memory_format=torch.channels_last):
             w16 = w16.contiguous(memory_format=torch.channels_last)       # memory = [Cout][R][S][Cin]
         b32 = None if bias is None else bias.float()

@@ -215,3 +215,27 @@ def multi_sgd(tl: TensorList, grad_dtype: torch.dtype, lp_dtype: torch.dtype, hp
     check(lib.b200dp_multi_sgd(ptr(tl.desc), ptr(tl.chunks), ctypes.c_int(tl.n_chunks), ctypes.c_int(DT[grad_dtype]),
                                ctypes.c_int(DT.get(lp_dtype, 1)), hp, ctypes.c_int(int(first_step)), ptr(grad_mult),
                                ptr(found_inf), stream_ptr(tl.device)), "multi_sgd")
+
+
+# --------------------------------------------------------------------------- 16-bit weight shadows
+LP_ATTR, LP_VER = "_b200dp_lp", "_b200dp_lp_version"
+
+
+def lp_weight(weight: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """The 16-bit copy of an fp32 weight for a tensor-core kernel.  When the optimizer keeps a shadow of the parameter in
+    ``dtype`` (written by the SAME kernel that updates the fp32 master, or the 16-bit wire copy a ZeRO owner published)
+    and the parameter has not been touched since, that shadow is the operand — no per-forward cast kernel; otherwise
+    one ``.to(dtype)``."""
+    if weight.dtype == dtype:
+        return weight
+    lp = getattr(weight, LP_ATTR, None)
+    if (lp is not None and lp.dtype == dtype and lp.shape == weight.shape
+            and getattr(weight, LP_VER, -1) == weight._version):
+        return lp
+    return weight.to(dtype)
+
+
+def stamp_lp(params) -> None:
+    for p in params:
+        if getattr(p, LP_ATTR, None) is not None:
+            setattr(p, LP_VER, p._version)

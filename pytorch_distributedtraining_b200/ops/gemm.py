@@ -81,7 +81,8 @@ def _as_rows(t: torch.Tensor, cols: int, dtype: torch.dtype) -> torch.Tensor:
 
 
 def _w16(w: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
-    w = w if w.dtype == dtype else w.to(dtype)
+    from .fused import lp_weight
+    w = lp_weight(w, dtype)                 # the optimizer's 16-bit shadow when it has one: no cast kernel
     return w if w.is_contiguous() else w.contiguous()
 
 

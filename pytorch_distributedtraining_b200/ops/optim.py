@@ -44,6 +44,33 @@ class _FusedBase(Optimizer):
         self._total_norm: Optional[torch.Tensor] = None
         self._norm_table: Optional[fused.TensorList] = None
 
+    # 16-bit shadows of the matrix-shaped parameters, written by the update kernel itself (``desc.p_lp``): the
+    # convolution / linear kernels read them instead of casting the fp32 weights every forward.  Set by the facade to
+    # the autocast dtype; None keeps the optimizer shadow-free.
+    lp_dtype: Optional[torch.dtype] = None
+
+    def _shadows(self, params: List[torch.Tensor]) -> Optional[List[Optional[torch.Tensor]]]:
+        if self.lp_dtype is None:
+            return None
+        out: List[Optional[torch.Tensor]] = []
+        for p in params:
+            if p.dim() < 2:
+                out.append(None)
+                continue
+            lp = getattr(p, fused.LP_ATTR, None)
+            if lp is None or lp.dtype != self.lp_dtype or lp.shape != p.shape or not fused.same_layout(lp, p):
+                lp = torch.empty_like(p, dtype=self.lp_dtype)
+                lp.copy_(p.detach())
+                setattr(p, fused.LP_ATTR, lp)
+                setattr(p, fused.LP_VER, p._version)
+            out.append(lp)
+        return out
+
+    def make_shadows(self) -> None:
+        """Create the shadows up front (before the first step), so the very first forward already uses them."""
+        for g in self.param_groups:
+            self._shadows([p for p in g["params"] if p.requires_grad])
+
     # -- helpers ---------------------------------------------------------------
     def _params_with_grad(self, group) -> List[torch.Tensor]:
         out = []
@@ -146,6 +173,7 @@ class _FusedBase(Optimizer):
 
 class FusedAdamW(_FusedBase):
     _adamw = 1
+    writes_shadows = True        # its update kernel also emits the 16-bit copy of each parameter (desc.p_lp)
 
     def __init__(self, params, lr: float = 1e-3, betas: Tuple[float, float] = (0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 1e-2, amsgrad: bool = False, maximize: bool = False, **_ignored: Any):
@@ -200,14 +228,15 @@ class FusedAdamW(_FusedBase):
             if tl is None or tl.key != key:
                 tl = self._tables[gi] = fused.TensorList(
                     params, grads, [self.state[p]["exp_avg"] for p in params],
-                    [self.state[p]["exp_avg_sq"] for p in params])
+                    [self.state[p]["exp_avg_sq"] for p in params], self._shadows(params))
             b1, b2 = group["betas"]
             hp = fused.AdamHParams(float(group["lr"]), float(b1), float(b2), float(group["eps"]),
                                    float(group["weight_decay"]), self._adamw, int(bool(group.get("maximize", False))),
                                    self._lr_tensor(gi, group, params[0].device))
             fused.step_advance(step_t, found_inf)
-            fused.multi_adam(tl, grads[0].dtype, torch.float16, hp, step_t, grad_mult, found_inf)
+            fused.multi_adam(tl, grads[0].dtype, self.lp_dtype or torch.float16, hp, step_t, grad_mult, found_inf)
             self._bump_versions(params)
+            fused.stamp_lp(params)
         return loss
 
     def load_state_dict(self, state_dict: Dict[str, Any]) -> None:

@@ -50,3 +50,35 @@ def test_graphed_train_step_matches_eager(accum, clip):
     # rounding noise of near-zero gradients into +-lr moves, so two runs agree to ~1e-2, not bitwise
     assert (num / den).sqrt().item() < 2e-2, (num, den)
     assert float(s.ema_loss) == float(s.ema_loss) and s.ema_loss is not None
+
+
+def test_optimizer_keeps_16bit_weight_shadows_the_layers_read():
+    """The fused AdamW kernel writes the compute-dtype copy of every matrix-shaped parameter; convolutions and linears
+    use it instead of casting fp32 weights each forward.  The shadow must equal ``p.to(dtype)`` after every step
+    (including a step skipped on overflow), and a parameter modified behind the optimizer's back must NOT use it."""
+    from pytorch_distributedtraining_b200 import AMPConfig, Stoke, StokeOptimizer
+    from pytorch_distributedtraining_b200.models import resnet18
+    from pytorch_distributedtraining_b200.ops import fused
+    from pytorch_distributedtraining_b200.ops.loss import cross_entropy
+    torch.manual_seed(0)
+    s = Stoke(model=resnet18(num_classes=10, small_input=True), verbose=False,
+              optimizer=StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs={"lr": 1e-3}), loss=cross_entropy,
+              batch_size_per_device=8, gpu=True, fp16="amp", configs=[AMPConfig(init_scale=2.0 ** 10)])
+    s.model_access.train()
+    mats = [p for p in s.model_access.parameters() if p.dim() >= 2]
+    assert all(getattr(p, fused.LP_ATTR, None) is not None for p in mats)
+    x, y = torch.randn(8, 3, 32, 32, device="cuda"), torch.randint(0, 10, (8,), device="cuda")
+    for it in range(4):
+        loss = s.loss(s.model(x), y)
+        s.backward(loss)
+        if it == 2:
+            mats[0].grad[(0,) * mats[0].dim()] = float("inf")        # this step is skipped on the device
+        s.step()
+        for p in mats:
+            assert torch.equal(getattr(p, fused.LP_ATTR), p.detach().half())
+            assert fused.lp_weight(p, torch.float16) is getattr(p, fused.LP_ATTR)
+    with torch.no_grad():
+        mats[0].mul_(2.0)                                    # e.g. a checkpoint load
+    assert fused.lp_weight(mats[0], torch.float16) is not getattr(mats[0], fused.LP_ATTR)
+    loss = s.loss(s.model(x), y); s.backward(loss); s.step()
+    assert fused.lp_weight(mats[0], torch.float16) is getattr(mats[0], fused.LP_ATTR)
