@@ -62,6 +62,7 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="disable CUDA-graph capture of the train step")
     ap.add_argument("--cpu", action="store_true", help="CPU/gloo plumbing run (config 1)")
+    ap.add_argument("--sync-bn", action="store_true", help="convert BatchNorm to SyncBatchNorm (Stoke-DDP.py:192) in both arms")
     ap.add_argument("--no-standin", action="store_true", help="skip the same-session torch stand-in arm")
     ap.add_argument("--no-exposed", action="store_true", help="skip the exposed-communication measurement (N > 1)")
     return ap.parse_args()
@@ -97,7 +98,8 @@ def build_ours(cfg: dict, args, world: int):
         from pytorch_distributedtraining_b200.models.perceptual import feat_loss as loss_fn
     gpu = not args.cpu
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    configs = [AMPConfig(init_scale=2.0 ** 14), DDPConfig(local_rank=local_rank, backend="nccl" if gpu else "gloo"),
+    configs = [AMPConfig(init_scale=2.0 ** 14),
+               DDPConfig(local_rank=local_rank, backend="nccl" if gpu else "gloo", convert_to_sync_batch_norm=args.sync_bn),
                FairscaleOSSConfig(broadcast_fp16=bool(cfg.get("broadcast_fp16", False))), FairscaleFSDPConfig(mixed_precision=cfg["fp16"] is not None),
                B200Config(cuda_graph=gpu and not args.no_graph, strict=gpu)]
     stoke = Stoke(
@@ -146,6 +148,8 @@ def build_torch(cfg: dict, args, world: int, capturable: bool = False):
         model = getattr(torchvision.models, cfg["model"])(num_classes=cfg["classes"]).to(device)
     if cfg["model"].startswith("resnet") and gpu:
         model = model.to(memory_format=torch.channels_last)
+    if getattr(args, "sync_bn", False) and world > 1:
+        model = torch.nn.SyncBatchNorm.convert_sync_batchnorm(model)
     amp_dtype = {"amp": torch.float16, "bf16": torch.bfloat16, None: None}[cfg["fp16"] if gpu else None]
     accum = cfg["accum"]
     if cfg["fsdp"] and world > 1:
@@ -416,7 +420,10 @@ def main() -> None:
         C.MUTE = True
         try:
             muted = measure(step, args, cfg, device, world, rank, host, dev_pool, cl, False, False, pending)
-            exposed = {"exposed_comm_ms": res["ms_per_step"] - muted["ms_per_step"], "ms_per_step_comm_muted": muted["ms_per_step"],
+            diff = res["ms_per_step"] - muted["ms_per_step"]
+            # a muted step that comes out SLOWER is not a measurement (with the collectives off, replicas diverge and the
+            # optimizer state goes stale): report nothing rather than a negative number
+            exposed = {"exposed_comm_ms": diff if diff > -0.05 * res["ms_per_step"] else None, "ms_per_step_comm_muted": muted["ms_per_step"],
                        "how": "same whole-step CUDA graph re-captured with all peer-memory collective launches skipped"}
         finally:
             C.MUTE = False
@@ -436,7 +443,7 @@ def main() -> None:
             "impl": {"ours": "ours", "torch": "torch-native stand-in (not the reference)"}[args.impl],
             "config": {"model": cfg["model"], "global_batch": B * accum * world, "per_gpu_batch": B,
                        "grad_accum": accum, "input": list(cfg["shape"]), "name": args.config,
-                       "parallelism": f"{cfg['par']}{world}", "optimizer": "AdamW",
+                       "parallelism": f"{cfg['par']}{world}", "optimizer": "AdamW", "sync_bn": bool(args.sync_bn),
                        "l2": "per-step working set (inputs + activations, several GB) exceeds the 126 MB L2; "
                              "no explicit flush"},
             "gpu_launches": res["launches"],

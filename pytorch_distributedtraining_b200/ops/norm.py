@@ -64,7 +64,7 @@ class _BatchNormActFn(torch.autograd.Function):
                                        ptr(sums), st), "bn_reduce")
         count = float(rows)
         if world > 1:
-            sums[2 * C] = count
+            sums[2 * C: 2 * C + 1].fill_(count)          # (a fill kernel: indexed assignment would be a host copy, illegal under capture)
             _allreduce_stats(sums, group)
             # the kernels read the TRUE element count from slot 2C of the reduced vector (count <= 0 selects that):
             # no host sync, and a ragged last batch on one rank (validation, drop_last=False) does not skew the statistics
