@@ -138,11 +138,20 @@ def unscale_check_(grads: List[torch.Tensor], inv_scale: torch.Tensor, found_inf
     for g in grads:
         by_dtype.setdefault(g.dtype, []).append(g)
     for dtype, gs in by_dtype.items():
-        tl = TensorList([None] * len(gs), gs)
+        # tables are cached by the gradient addresses: steady-state training (and a CUDA-graph capture after the warm-up
+        # steps) never rebuilds them
+        key = (dtype,) + tuple(g.data_ptr() for g in gs)
+        tl = _UNSCALE_TABLES.get(key)
+        if tl is None:
+            if len(_UNSCALE_TABLES) > 16:
+                _UNSCALE_TABLES.clear()
+            tl = _UNSCALE_TABLES[key] = TensorList([None] * len(gs), gs)
         check(lib.b200dp_multi_unscale_check(ptr(tl.desc), ptr(tl.chunks), ctypes.c_int(tl.n_chunks),
                                              ctypes.c_int(DT[dtype]), ptr(inv_scale), ptr(found_inf),
                                              stream_ptr(tl.device)), "multi_unscale_check")
-        _keep(tl)
+
+
+_UNSCALE_TABLES: Dict[tuple, "TensorList"] = {}
 
 
 _KEEP: List[object] = []
