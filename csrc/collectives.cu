@@ -453,7 +453,8 @@ __global__ void __launch_bounds__(kCommThreads) peer_zero_adam_kernel(
     const float bc1 = 1.f - powf(hp.beta1, step), bc2 = 1.f - powf(hp.beta2, step);
     const float lr = hp.lr_dev ? *hp.lr_dev : hp.lr;
     const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
-    const float decay = hp.adamw ? 1.f - lr * hp.weight_decay : 1.f, l2 = hp.adamw ? 0.f : hp.weight_decay;
+    const bool sgd = hp.adamw == 2;                      // the same fused step for SGD (momentum / Nesterov / L2): see below
+    const float decay = hp.adamw == 1 ? 1.f - lr * hp.weight_decay : 1.f, l2 = hp.adamw == 1 ? 0.f : hp.weight_decay;
     if (!prereduced) cta_barrier_all_ranks(c, me);   // all ranks' gradients are complete
     int64_t b, e;
     slice_range(n_vec, gridDim.x, blockIdx.x, b, e);
@@ -483,19 +484,33 @@ __global__ void __launch_bounds__(kCommThreads) peer_zero_adam_kernel(
                 if (!ok[u]) continue;
                 const int64_t li = off[u] - s0;     // element index inside the owned segment
                 float4 p4 = *reinterpret_cast<float4*>(pm + li), m4 = *reinterpret_cast<float4*>(mm + li),
-                       v4 = *reinterpret_cast<float4*>(vm + li);
+                       v4 = sgd ? make_float4(0.f, 0.f, 0.f, 0.f) : *reinterpret_cast<float4*>(vm + li);
                 float pv[V] = {p4.x, p4.y, p4.z, p4.w}, mv[V] = {m4.x, m4.y, m4.z, m4.w}, vv[V] = {v4.x, v4.y, v4.z, v4.w};
+                if (sgd) {
+                    // hp: beta1 = momentum, beta2 = dampening, eps != 0 selects Nesterov, weight_decay is L2; the first
+                    // step seeds the momentum buffer with the gradient (torch.optim.SGD)
 #pragma unroll
-                for (int k = 0; k < V; ++k) {
-                    const float gv = g[u][k] * mult + l2 * pv[k];
-                    pv[k] *= decay;
-                    mv[k] = hp.beta1 * mv[k] + (1.f - hp.beta1) * gv;
-                    vv[k] = hp.beta2 * vv[k] + (1.f - hp.beta2) * gv * gv;
-                    pv[k] -= step_size * (mv[k] / (sqrtf(vv[k]) * inv_sqrt_bc2 + hp.eps));
+                    for (int k = 0; k < V; ++k) {
+                        float gv = g[u][k] * mult + hp.weight_decay * pv[k];
+                        if (hp.beta1 != 0.f) {
+                            mv[k] = step <= 1.f ? gv : hp.beta1 * mv[k] + (1.f - hp.beta2) * gv;
+                            gv = hp.eps != 0.f ? gv + hp.beta1 * mv[k] : mv[k];
+                        }
+                        pv[k] -= lr * gv;
+                    }
+                } else {
+#pragma unroll
+                    for (int k = 0; k < V; ++k) {
+                        const float gv = g[u][k] * mult + l2 * pv[k];
+                        pv[k] *= decay;
+                        mv[k] = hp.beta1 * mv[k] + (1.f - hp.beta1) * gv;
+                        vv[k] = hp.beta2 * vv[k] + (1.f - hp.beta2) * gv * gv;
+                        pv[k] -= step_size * (mv[k] / (sqrtf(vv[k]) * inv_sqrt_bc2 + hp.eps));
+                    }
+                    *reinterpret_cast<float4*>(vm + li) = make_float4(vv[0], vv[1], vv[2], vv[3]);
                 }
                 *reinterpret_cast<float4*>(pm + li) = make_float4(pv[0], pv[1], pv[2], pv[3]);
                 *reinterpret_cast<float4*>(mm + li) = make_float4(mv[0], mv[1], mv[2], mv[3]);
-                *reinterpret_cast<float4*>(vm + li) = make_float4(vv[0], vv[1], vv[2], vv[3]);
                 // publish (W3): fp32 wire = one 16-byte store per 4 values; 16-bit wire = 8 bytes
                 if (sizeof(TW) == 4) {
                     const uint4 r = Pack<float>::pack(pv);

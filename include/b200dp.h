@@ -297,6 +297,8 @@ int b200dp_peer_all_gather(const b200dp_peer_ctx* ctx, void* const* outs, void* 
  * (multiples of 8).  Reduce the owned gradient segment across ranks (or read it pre-reduced
  * from local_grad), apply AdamW to the rank-local fp32 master/m/v, and publish the new
  * parameter values into every rank's parameter buffer (fp32 or 16-bit wire). */
+/* hp.adamw selects the update rule: 1 = AdamW, 0 = Adam with L2, 2 = SGD — then beta1 is the momentum, beta2 the
+ * dampening, eps != 0 selects Nesterov, weight_decay is L2, `m` is the momentum buffer and `v` is not touched. */
 int b200dp_peer_zero_adam(const b200dp_peer_ctx* ctx, void* const* grad_bufs, void* grad_mc, void* const* param_bufs,
                           void* param_mc, const int64_t* seg, b200dp_dtype wire_dtype, void* const* master,
                           void* const* m, void* const* v, b200dp_adam_hparams hp, const void* const* step,

@@ -664,9 +664,13 @@ class ZeroPeerEngine:
         mult = grad_mult if grad_mult is not None else (self.grad_mult if self._clip_pending else None)
         pbuf = self.P16 if self.P16 is not None else self.P
         for gi, (g, pg) in enumerate(zip(self.groups, oss.param_groups)):
-            b1, b2 = pg.get("betas", (0.9, 0.999))
-            hp = fused.AdamHParams(float(pg["lr"]), float(b1), float(b2), float(pg.get("eps", 1e-8)),
-                                   float(pg.get("weight_decay", 0.0)), 1 if self._is_adamw() else 0, 0, None)
+            if self._is_sgd():
+                hp = fused.AdamHParams(float(pg["lr"]), float(pg.get("momentum", 0.0)), float(pg.get("dampening", 0.0)),
+                                       1.0 if pg.get("nesterov", False) else 0.0, float(pg.get("weight_decay", 0.0)), 2, 0, None)
+            else:
+                b1, b2 = pg.get("betas", (0.9, 0.999))
+                hp = fused.AdamHParams(float(pg["lr"]), float(b1), float(b2), float(pg.get("eps", 1e-8)),
+                                       float(pg.get("weight_decay", 0.0)), 1 if self._is_adamw() else 0, 0, None)
             fused.step_advance(g["step"], found_inf)
             for u in g["units"]:
                 lo, n = u["own_off"], max(u["own_n"], 8)
@@ -683,6 +687,10 @@ class ZeroPeerEngine:
         for u in self.units:                         # the next backward starts a new round
             u["pending"], u["launched"] = u["n_params"], False
         return loss
+
+    def _is_sgd(self) -> bool:
+        from ..ops.optim import FusedSGD
+        return self.oss._optim_cls is torch.optim.SGD or issubclass(self.oss._optim_cls, FusedSGD)
 
     def _is_adamw(self) -> bool:
         from ..ops.optim import FusedAdamW, FusedAdam
@@ -705,9 +713,12 @@ class ZeroPeerEngine:
             gmap.append(self.oss.param_to_index[id(p)])
             if float(g["step"].item()) == 0.0:
                 continue
-            state[k] = {"step": g["step"].detach().clone(),
-                        "exp_avg": g["m"][lo: lo + p.numel()].view(p.shape).clone(),
-                        "exp_avg_sq": g["v"][lo: lo + p.numel()].view(p.shape).clone()}
+            if self._is_sgd():
+                state[k] = {"momentum_buffer": g["m"][lo: lo + p.numel()].view(p.shape).clone()}
+            else:
+                state[k] = {"step": g["step"].detach().clone(),
+                            "exp_avg": g["m"][lo: lo + p.numel()].view(p.shape).clone(),
+                            "exp_avg_sq": g["v"][lo: lo + p.numel()].view(p.shape).clone()}
         return {"state": state, "param_groups": [], "global_index": gmap}
 
     @torch.no_grad()
@@ -715,7 +726,11 @@ class ZeroPeerEngine:
         for g, _u, p, lo in self._owned():
             gi = self.oss.param_to_index[id(p)]
             st = full_state.get(gi, full_state.get(str(gi)))
-            if st is not None:
+            if st is not None and "momentum_buffer" in st:
+                if st["momentum_buffer"] is not None:
+                    g["m"][lo: lo + p.numel()].copy_(st["momentum_buffer"].reshape(-1))
+                    g["step"].fill_(2.0)             # past the step that seeds the buffer
+            elif st is not None:
                 g["m"][lo: lo + p.numel()].copy_(st["exp_avg"].reshape(-1))
                 g["v"][lo: lo + p.numel()].copy_(st["exp_avg_sq"].reshape(-1))
                 g["step"].fill_(float(st["step"]))
@@ -746,10 +761,10 @@ def _arena_bytes(engine: Any, optim: Any, status: Any) -> int:
 
 
 def _zero_engine_serves(oss: Any) -> bool:
-    """The fused ZeRO-2 step is Adam / AdamW (decoupled or L2 decay, no amsgrad, minimising).  Match the
-    optimizer CLASS, not its name: Adamax / NAdam / RAdam / SparseAdam are different update rules."""
-    from ..ops.optim import FusedAdam, FusedAdamW
-    if oss._optim_cls not in (torch.optim.Adam, torch.optim.AdamW, FusedAdam, FusedAdamW):
+    """The fused ZeRO-2 step is Adam / AdamW (decoupled or L2 decay, no amsgrad) or SGD (momentum, dampening, Nesterov,
+    L2), minimising.  Match the optimizer CLASS, not its name: Adamax / NAdam / RAdam / SparseAdam are different rules."""
+    from ..ops.optim import FusedAdam, FusedAdamW, FusedSGD
+    if oss._optim_cls not in (torch.optim.Adam, torch.optim.AdamW, FusedAdam, FusedAdamW, torch.optim.SGD, FusedSGD):
         return False
     for g in oss.param_groups:
         if g.get("maximize", False) or g.get("amsgrad", False):

@@ -306,6 +306,9 @@ def _w_facade_peer(rank, world, mode):
     # epilogue accumulates with float atomics) so that what is compared is the collectives
     dispatch.disable("convstats")
 
+    sgd = mode == "sddp_sgd"             # the fused ZeRO-2 step with SGD (momentum + Nesterov + L2) instead of AdamW
+    if sgd:
+        mode = "sddp"
     ring = mode == "fsdp_ring"
     if ring:
         # four blocks over a ring of two gathered-parameter slots: parameters are re-gathered in backward, the next
@@ -323,14 +326,18 @@ def _w_facade_peer(rank, world, mode):
             model = resnet18(num_classes=10, small_input=True)
         kw = dict(fairscale_oss=mode == "sddp", fairscale_sddp=mode == "sddp", fairscale_fsdp=mode == "fsdp")
         s = Stoke(model=model, verbose=False,
-                  optimizer=StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs={"lr": 1e-3, "betas": (0.9, 0.99),
-                                                                                         "eps": 1e-8, "weight_decay": 1e-4}),
+                  optimizer=(StokeOptimizer(optimizer=torch.optim.SGD, optimizer_kwargs={"lr": 0.05, "momentum": 0.9, "nesterov": True,
+                                                                                         "weight_decay": 1e-4}) if sgd else
+                             StokeOptimizer(optimizer=torch.optim.AdamW, optimizer_kwargs={"lr": 1e-3, "betas": (0.9, 0.99),
+                                                                                           "eps": 1e-8, "weight_decay": 1e-4})),
                   loss=cross_entropy, batch_size_per_device=16, gpu=True, fp16="bf16" if mode == "fsdp" else "amp",
                   distributed="ddp", grad_accum_steps=2 if mode == "sddp" else 1,
                   grad_clip=ClipGradNormConfig(max_norm=1.0, norm_type=2.0) if mode != "ddp" else None,
                   configs=[AMPConfig(init_scale=2.0 ** 10), DDPConfig(local_rank=rank),
                            FairscaleFSDPConfig(min_num_params=10 ** 9), B200Config(peer_collectives=peer)], **kw)
         assert (s._peer is not None) == peer
+        if peer and mode == "sddp":
+            assert "zero" in s._peer, "the fused ZeRO-2 engine did not attach"
         if peer and ring:
             assert not s._peer["fsdp"].resident and len(s._peer["fsdp"].slots) == 2
         s.model_access.train()
@@ -358,7 +365,7 @@ def _w_facade_peer(rank, world, mode):
 
 
 @needs2
-@pytest.mark.parametrize("mode", ["ddp", "sddp", "fsdp", "fsdp_ring"])
+@pytest.mark.parametrize("mode", ["ddp", "sddp", "sddp_sgd", "fsdp", "fsdp_ring"])
 def test_real_facade_peer_matches_nccl(mode):
     from pytorch_distributedtraining_b200.utils.testing import spawn
     spawn(_w_facade_peer, 2, (mode,), backend="nccl")
