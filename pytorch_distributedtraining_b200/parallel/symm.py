@@ -183,8 +183,14 @@ class DDPPeerEngine:
 
     ONE_SHOT_BYTES = 512 * 1024
 
-    def __init__(self, arena: PeerArena, ddp: Any, blocks: int = 32):
+    def __init__(self, arena: PeerArena, ddp: Any, blocks: int = 32, wire_dtype: Optional[torch.dtype] = None):
         self.arena, self.ddp, self.blocks = arena, ddp, blocks
+        # 16-bit wire (K1 "and the cast", DDPConfig.comm_dtype): every bucket gets a bf16 / fp16 twin in symmetric
+        # memory; the bucket is cast into it, the peers exchange 2-byte values (sums still accumulate in fp32 inside the
+        # kernel, 1/world and 1/scale are applied before the result is rounded), and the result is widened back into
+        # the fp32 bucket the optimizer reads.  Halves the NVLink bytes for two local passes over the bucket.
+        self.wire_dtype = wire_dtype if wire_dtype in (torch.float16, torch.bfloat16) else None
+        self._wire: Dict[int, SymmBuffer] = {}
         self.ctx = arena.context("comm")
         self.stream = torch.cuda.Stream(device=arena.device)
         self._bufs: Dict[int, SymmBuffer] = {}
@@ -196,6 +202,10 @@ class DDPPeerEngine:
             sb = arena.alloc(numel, dtype)
             sb.tensor.zero_()
             self._bufs[sb.tensor.data_ptr()] = sb
+            if self.wire_dtype is not None and dtype == torch.float32:
+                w = arena.alloc(numel, self.wire_dtype)
+                w.tensor.zero_()
+                self._wire[sb.tensor.data_ptr()] = w
             return sb.tensor
 
         ddp.rebuild_buckets(allocator)
@@ -213,13 +223,24 @@ class DDPPeerEngine:
         n = bucket.buffer.numel()
         main = torch.cuda.current_stream(self.arena.device)
         self.stream.wait_stream(main)          # the bucket's gradients are produced on the main stream
-        nbytes = n * bucket.buffer.element_size()
-        algo = 0 if nbytes <= self.ONE_SHOT_BYTES else 1
-        mc = sb.mc if algo == 1 else 0
+        wire = self._wire.get(bucket.buffer.data_ptr())
         rank = self.arena.rank
-        self.ctx.allreduce(sb.table, mc, n, bucket.buffer.dtype, pre_mult=1.0 / self.arena.world,
-                           mult_dev=C.local_table(rank, self.inv_scale), found_inf=C.local_table(rank, self.found_inf),
-                           algo=algo, blocks=min(self.blocks, max(1, n // 4096)), stream=self.stream)
+        if wire is not None:
+            with torch.cuda.stream(self.stream):
+                wire.tensor.copy_(bucket.buffer)                      # fp32 -> 16-bit, on the comm stream
+                nbytes = n * wire.tensor.element_size()
+                algo = 0 if nbytes <= self.ONE_SHOT_BYTES else 1
+                self.ctx.allreduce(wire.table, wire.mc if algo == 1 else 0, n, wire.tensor.dtype, pre_mult=1.0 / self.arena.world,
+                                   mult_dev=C.local_table(rank, self.inv_scale), found_inf=C.local_table(rank, self.found_inf),
+                                   algo=algo, blocks=min(self.blocks, max(1, n // 4096)), stream=self.stream)
+                bucket.buffer.copy_(wire.tensor)                      # widen back into the bucket the optimizer reads
+        else:
+            nbytes = n * bucket.buffer.element_size()
+            algo = 0 if nbytes <= self.ONE_SHOT_BYTES else 1
+            mc = sb.mc if algo == 1 else 0
+            self.ctx.allreduce(sb.table, mc, n, bucket.buffer.dtype, pre_mult=1.0 / self.arena.world,
+                               mult_dev=C.local_table(rank, self.inv_scale), found_inf=C.local_table(rank, self.found_inf),
+                               algo=algo, blocks=min(self.blocks, max(1, n // 4096)), stream=self.stream)
 
         def finish() -> None:
             torch.cuda.current_stream(self.arena.device).wait_stream(self.stream)
@@ -757,7 +778,7 @@ def _arena_bytes(engine: Any, optim: Any, status: Any) -> int:
         return total + (8 << 20)
     if status.sharded:
         return n_params * 4 * 3 + (16 << 20)
-    return n_params * 4 + len(list(engine.parameters())) * 64 + (16 << 20)
+    return n_params * 6 + len(list(engine.parameters())) * 64 + (16 << 20)      # fp32 buckets + optional 16-bit wire twins
 
 
 def _zero_engine_serves(oss: Any) -> bool:
@@ -799,5 +820,6 @@ def attach(engine: Any, optim: Any, status: Any, timeout_s: float = 30.0, **cfg:
         wire = torch.float16 if (oss_cfg is not None and oss_cfg.broadcast_fp16) else None
         out["zero"] = ZeroPeerEngine(arena, optim, engine, wire_dtype=wire)
     elif isinstance(engine, DistributedDataParallel):
-        out["ddp"] = DDPPeerEngine(arena, engine)
+        ddp_cfg = cfg.get("ddp_cfg")
+        out["ddp"] = DDPPeerEngine(arena, engine, wire_dtype=getattr(ddp_cfg, "comm_dtype", None))
     return out

@@ -306,6 +306,9 @@ def _w_facade_peer(rank, world, mode):
     # epilogue accumulates with float atomics) so that what is compared is the collectives
     dispatch.disable("convstats")
 
+    wire16 = mode == "ddp_bf16wire"      # DDP bucket all-reduce with a 16-bit wire (DDPConfig.comm_dtype)
+    if wire16:
+        mode = "ddp"
     sgd = mode == "sddp_sgd"             # the fused ZeRO-2 step with SGD (momentum + Nesterov + L2) instead of AdamW
     if sgd:
         mode = "sddp"
@@ -333,9 +336,12 @@ def _w_facade_peer(rank, world, mode):
                   loss=cross_entropy, batch_size_per_device=16, gpu=True, fp16="bf16" if mode == "fsdp" else "amp",
                   distributed="ddp", grad_accum_steps=2 if mode == "sddp" else 1,
                   grad_clip=ClipGradNormConfig(max_norm=1.0, norm_type=2.0) if mode != "ddp" else None,
-                  configs=[AMPConfig(init_scale=2.0 ** 10), DDPConfig(local_rank=rank),
+                  configs=[AMPConfig(init_scale=2.0 ** 10),
+                           DDPConfig(local_rank=rank, comm_dtype=torch.bfloat16 if (wire16 and peer) else None),
                            FairscaleFSDPConfig(min_num_params=10 ** 9), B200Config(peer_collectives=peer)], **kw)
         assert (s._peer is not None) == peer
+        if peer and wire16:
+            assert s._peer["ddp"]._wire, "no 16-bit wire buffers were created"
         if peer and mode == "sddp":
             assert "zero" in s._peer, "the fused ZeRO-2 engine did not attach"
         if peer and ring:
@@ -365,7 +371,7 @@ def _w_facade_peer(rank, world, mode):
 
 
 @needs2
-@pytest.mark.parametrize("mode", ["ddp", "sddp", "sddp_sgd", "fsdp", "fsdp_ring"])
+@pytest.mark.parametrize("mode", ["ddp", "ddp_bf16wire", "sddp", "sddp_sgd", "fsdp", "fsdp_ring"])
 def test_real_facade_peer_matches_nccl(mode):
     from pytorch_distributedtraining_b200.utils.testing import spawn
     spawn(_w_facade_peer, 2, (mode,), backend="nccl")
