@@ -524,6 +524,134 @@ __global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd_fused_kernel(
     for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) mine[i] = red[i];
 }
 
+// ---- narrow rows (D % 4 == 0, D <= 256, e.g. SwinIR-S: 60): the same two kernels on 4-element vectors (8-byte accesses
+//      for 16-bit data — rows of such widths are not 16-byte aligned)
+template <typename T> struct alignas(sizeof(T) * 4) Vec4 { T v[4]; };
+
+template <typename T, int NCH>
+__global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwd4_kernel(
+    const T* __restrict__ x, T* __restrict__ y, int64_t rows, int D, const float* __restrict__ gamma,
+    const float* __restrict__ beta, float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * kLNWarps + (threadIdx.x >> 5);
+    if (row >= rows) return;
+    const int nchunk = D / 4;
+    float v[NCH][4];
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+            const Vec4<T> r = *reinterpret_cast<const Vec4<T>*>(x + row * D + ch * 4);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { v[j][k] = Cvt<T>::to_f(r.v[k]); s += v[j][k]; }
+        }
+    }
+    const float mu = warp_sum(s) / D;
+    float q = 0.f;
+#pragma unroll
+    for (int j = 0; j < NCH; ++j)
+        if (lane + j * 32 < nchunk) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { const float d = v[j][k] - mu; q += d * d; }
+        }
+    const float rs = rsqrtf(warp_sum(q) / D + eps);
+    if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+        const int ch = lane + j * 32;
+        if (ch < nchunk) {
+            const float4 g = *reinterpret_cast<const float4*>(gamma + ch * 4), b = *reinterpret_cast<const float4*>(beta + ch * 4);
+            const float ga[4] = {g.x, g.y, g.z, g.w}, be[4] = {b.x, b.y, b.z, b.w};
+            Vec4<T> o;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o.v[k] = Cvt<T>::from_f((v[j][k] - mu) * rs * ga[k] + be[k]);
+            *reinterpret_cast<Vec4<T>*>(y + row * D + ch * 4) = o;
+        }
+    }
+}
+
+template <typename T, int NCH>
+__global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd4_kernel(
+    const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t rows, int D,
+    const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
+    float* __restrict__ scratch, const T* __restrict__ add_in) {
+    __shared__ float red[2 * NCH * 128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nchunk = D / 4;
+    float pa[NCH][4], pb[NCH][4], ga[NCH][4];
+#pragma unroll
+    for (int j = 0; j < NCH; ++j) {
+        const int ch = lane + j * 32;
+        const float4 g = ch < nchunk ? *reinterpret_cast<const float4*>(gamma + ch * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        ga[j][0] = g.x; ga[j][1] = g.y; ga[j][2] = g.z; ga[j][3] = g.w;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { pa[j][k] = 0.f; pb[j][k] = 0.f; }
+    }
+    for (int64_t row = (int64_t)blockIdx.x * kLNWarps + warp; row < rows; row += (int64_t)gridDim.x * kLNWarps) {
+        const float mu = mean[row], rs = rstd[row];
+        Vec4<T> dv[NCH], xv[NCH], av[NCH];
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int ch = lane + j * 32;
+            if (ch < nchunk) {
+                dv[j] = *reinterpret_cast<const Vec4<T>*>(dy + row * D + ch * 4);
+                xv[j] = *reinterpret_cast<const Vec4<T>*>(x + row * D + ch * 4);
+                if (add_in != nullptr) av[j] = *reinterpret_cast<const Vec4<T>*>(add_in + row * D + ch * 4);
+            }
+        }
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NCH; ++j)
+            if (lane + j * 32 < nchunk) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float d = Cvt<T>::to_f(dv[j].v[k]);
+                    const float xh = (Cvt<T>::to_f(xv[j].v[k]) - mu) * rs;
+                    const float g = d * ga[j][k];
+                    c1 += g * xh; c2 += g;
+                    pa[j][k] += d; pb[j][k] += d * xh;
+                }
+            }
+        c1 = warp_sum(c1) / D;
+        c2 = warp_sum(c2) / D;
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) {
+            const int ch = lane + j * 32;
+            if (ch < nchunk) {
+                Vec4<T> o;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float xh = (Cvt<T>::to_f(xv[j].v[k]) - mu) * rs;
+                    float r = rs * (Cvt<T>::to_f(dv[j].v[k]) * ga[j][k] - c2 - xh * c1);
+                    if (add_in != nullptr) r += Cvt<T>::to_f(av[j].v[k]);
+                    o.v[k] = Cvt<T>::from_f(r);
+                }
+                *reinterpret_cast<Vec4<T>*>(dx + row * D + ch * 4) = o;
+            }
+        }
+    }
+    for (int w = 0; w < kLNWarps; ++w) {      // combine the CTA's warps in a fixed order
+        if (warp == w) {
+#pragma unroll
+            for (int j = 0; j < NCH; ++j) {
+                const int ch = lane + j * 32;
+                if (ch < nchunk) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int c = ch * 4 + k;
+                        red[c] = (w == 0 ? 0.f : red[c]) + pa[j][k];
+                        red[D + c] = (w == 0 ? 0.f : red[D + c]) + pb[j][k];
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    float* mine = scratch + (size_t)blockIdx.x * 2 * D;
+    for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) mine[i] = red[i];
+}
+
 // out[c] = sum over the CTA partials of column c, in a fixed order: 32 columns x 8 partial slices per CTA
 __global__ void __launch_bounds__(256) ln_partials_reduce_kernel(const float* __restrict__ scratch, int parts, int cols,
                                                                  float* __restrict__ out) {
@@ -660,9 +788,20 @@ int64_t b200dp_ln_scratch_floats(int64_t rows, int D) { return rows <= 0 || D <=
 int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dtype dtype, const float* gamma,
                          const float* beta, float eps, float* mean, float* rstd, void* stream) {
     B200DP_REQUIRE(x && y && gamma && beta && mean && rstd, "layernorm_fwd: null argument");
-    B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_fwd: D must be a multiple of 8, <= %d",
-                   kLNMaxChunks * 256);
     const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
+    if (rows > 0 && D % 8 != 0 && D % 4 == 0 && D <= 256) {      // narrow rows: 4-element vectors
+        if (D <= 128) {
+            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 1><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
+                (const T*)x, (T*)y, rows, D, gamma, beta, eps, mean, rstd); });
+        } else {
+            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 2><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
+                (const T*)x, (T*)y, rows, D, gamma, beta, eps, mean, rstd); });
+        }
+        B200DP_CHECK_LAUNCH();
+        return 0;
+    }
+    B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_fwd: D must be a multiple of 8 (or of 4 up to 256), <= %d",
+                   kLNMaxChunks * 256);
     B200DP_DISPATCH_DTYPE(dtype, T, {
         layernorm_fwd_kernel<T><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, rows, D, gamma,
                                                                                     beta, eps, mean, rstd);
@@ -677,10 +816,22 @@ static int layernorm_bwd_impl(const void* dy, const void* x, void* dx, int64_t r
     B200DP_REQUIRE(dy && x && dx && gamma && mean && rstd && scratch && counter && dgamma && dbeta,
                    "layernorm_bwd: null argument");
     B200DP_REQUIRE(dgamma == dbeta + D, "layernorm_bwd: dbeta and dgamma must be one buffer [dbeta(D) | dgamma(D)]");
-    B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_bwd: D must be a multiple of 8, <= %d",
-                   kLNMaxChunks * 256);
     cudaStream_t s = (cudaStream_t)stream;
     const unsigned grid = ln_bwd_grid(rows);
+    if (rows > 0 && D % 8 != 0 && D % 4 == 0 && D <= 256) {      // narrow rows: 4-element vectors
+        if (D <= 128) {
+            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_bwd4_kernel<T, 1><<<grid, kLNWarps * 32, 0, s>>>(
+                (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in); });
+        } else {
+            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_bwd4_kernel<T, 2><<<grid, kLNWarps * 32, 0, s>>>(
+                (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in); });
+        }
+        ln_partials_reduce_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(scratch, (int)grid, 2 * D, dbeta);
+        B200DP_CHECK_LAUNCH();
+        return 0;
+    }
+    B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_bwd: D must be a multiple of 8 (or of 4 up to 256), <= %d",
+                   kLNMaxChunks * 256);
     const int nch = (D + 255) / 256;
 #define LNB(N_)                                                                                                     \
     B200DP_DISPATCH_DTYPE(dtype, T, {                                                                               \

@@ -13,7 +13,7 @@ ap.add_argument("--config", default="resnet50_ddp_amp")
 ap.add_argument("--iters", type=int, default=10)
 a = ap.parse_args()
 world = int(os.environ.get("WORLD_SIZE", "1"))
-args = argparse.Namespace(cpu=not torch.cuda.is_available(), batch_size=0, impl="ours", no_graph=True)
+args = argparse.Namespace(cpu=not torch.cuda.is_available(), batch_size=0, impl="ours", no_graph=True, sync_bn=False)
 cfg = dict(bench.CONFIGS[a.config])
 stoke, step, device = bench.build_ours(cfg, args, world)
 B = cfg["batch"]

@@ -208,7 +208,7 @@ def test_batchnorm_act_matches_torch(dtype, shape, res, act):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("rows,D", [(197 * 4, 768), (33, 64), (5, 2048), (1000, 384)])
+@pytest.mark.parametrize("rows,D", [(197 * 4, 768), (33, 64), (5, 2048), (1000, 384), (4099, 60), (77, 180), (9, 4)])
 def test_layernorm_matches_torch(dtype, rows, D):
     from pytorch_distributedtraining_b200.ops.layers import LayerNorm
     torch.manual_seed(2)
