@@ -50,7 +50,23 @@ struct Geom {
     int manual;        // 1: threads stage the operands (head dim != 64 or stacked problems); 0: TMA
     int nW;            // number of mask windows (mask index = batch % nW); 0: no mask
     float scale;
+    int qp, op, dop;   // elements between consecutive tokens of qkv / out / dout (>= 3 H d, H d, H d)
+    // window mode (win != 0): problem b is window (b % wpi) of image b / wpi, an ws x ws patch of an Hi x Wi token grid
+    // cyclically shifted by `shift`; token rows are then addressed in IMAGE order, so no partition / roll copy exists
+    int win, ws, nWx, wpi, Hi, Wi, shift;
 };
+
+// Row index (in units of the token pitch) of token s of problem b.
+__device__ __forceinline__ int64_t tok(const Geom& g, int b, int s) {
+    if (g.win == 0) return (int64_t)b * g.S + s;
+    const int img = b / g.wpi, w = b - img * g.wpi;
+    const int wy = w / g.nWx, wx = w - wy * g.nWx;
+    const int ty = s / g.ws, tx = s - ty * g.ws;
+    int y = wy * g.ws + ty + g.shift, x = wx * g.ws + tx + g.shift;
+    if (y >= g.Hi) y -= g.Hi;
+    if (x >= g.Wi) x -= g.Wi;
+    return ((int64_t)img * g.Hi + y) * g.Wi + x;
+}
 
 __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* tm, uint64_t* bar, int c0, int c1, int c2) {
     asm volatile(
@@ -69,7 +85,7 @@ __device__ __forceinline__ void stage_rows(uint8_t* dst, const T* __restrict__ s
         const int gi = row / sp_rows, lr = row - gi * sp_rows;
         const int b = b0 + gi, s = s0 + lr;
         const bool ok = b < g.B && s < g.S && gi < g.G;
-        const uint32_t* sp = reinterpret_cast<const uint32_t*>(src + ((int64_t)(ok ? b : 0) * g.S + (ok ? s : 0)) * pitch);
+        const uint32_t* sp = reinterpret_cast<const uint32_t*>(src + tok(g, ok ? b : 0, ok ? s : 0) * pitch);
         const int nw = ok ? (g.d >> 1) : 0;                  // 32-bit words of this row that exist
         // every load is issued before the first store; words past the head dimension stay zero
         uint32_t w[32];
@@ -79,6 +95,45 @@ __device__ __forceinline__ void stage_rows(uint8_t* dst, const T* __restrict__ s
         for (int j = 0; j < 8; ++j)
             asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((j ^ (row & 7)) << 4)),
                          "r"(w[4 * j]), "r"(w[4 * j + 1]), "r"(w[4 * j + 2]), "r"(w[4 * j + 3]) : "memory");
+    }
+}
+
+// Up to four tiles staged in ONE round: every thread first issues the loads of all its rows (of all tiles), then stores.
+// The staging of a tile is a pure latency chain (global load -> shared store); doing the tiles one after the other pays
+// that latency once per tile.
+template <typename T>
+struct StageJob { uint8_t* dst; const T* src; int64_t pitch; int s0; int rows; };
+
+template <typename T, int NJ>
+__device__ __forceinline__ void stage_many(const StageJob<T> (&jobs)[NJ], const Geom& g, int b0) {
+    const int sp_rows = g.G == 1 ? (1 << 20) : g.spad;
+    // 128-row tiles, 256 threads: thread t serves row (t & 127) of jobs {t >> 7, (t >> 7) + 2}
+    const int row = threadIdx.x & 127, jsel = threadIdx.x >> 7;
+    constexpr int kPer = (NJ + 1) / 2;
+    uint32_t w[kPer][32];
+    bool live[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+        const int j = jsel + 2 * k;
+        live[k] = j < NJ && row < jobs[j < NJ ? j : 0].rows;
+        const StageJob<T>& jb = jobs[j < NJ ? j : 0];
+        const int gi = row / sp_rows, lr = row - gi * sp_rows;
+        const int b = b0 + gi, sidx = jb.s0 + lr;
+        const bool ok = live[k] && b < g.B && sidx < g.S && gi < g.G;
+        const uint32_t* sp = reinterpret_cast<const uint32_t*>(jb.src + tok(g, ok ? b : 0, ok ? sidx : 0) * jb.pitch);
+        const int nw = ok ? (g.d >> 1) : 0;
+#pragma unroll
+        for (int e = 0; e < 32; ++e) w[k][e] = e < nw ? __ldg(sp + e) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+        if (!live[k]) continue;
+        const int j = jsel + 2 * k;
+        const uint32_t sdst = smem_u32(jobs[j].dst);
+#pragma unroll
+        for (int p = 0; p < 8; ++p)
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((p ^ (row & 7)) << 4)),
+                         "r"(w[k][4 * p]), "r"(w[k][4 * p + 1]), "r"(w[k][4 * p + 2]), "r"(w[k][4 * p + 3]) : "memory");
     }
 }
 
@@ -255,7 +310,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qt = blockIdx.x, h = blockIdx.y, b0 = blockIdx.z * g.G;
-    const int64_t pitch = (int64_t)3 * g.H * g.d;
+    const int64_t pitch = g.qp;
 
     if (threadIdx.x == 0) {
         mbar_init(bar_ld, 1); mbar_init(bar_s, 1); mbar_init(bar_o, 1);
@@ -444,7 +499,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
 #pragma unroll
         for (int j = 0; j < 32; ++j) o[j] = __uint_as_float(v[j]) * inv_sum;
         if (me.ok && g.d > half * 32)
-            store_row<T, 32>(out + (((int64_t)me.b * g.S + me.s) * g.H + h) * g.d + half * 32, o, min(32, g.d - half * 32));
+            store_row<T, 32>(out + tok(g, me.b, me.s) * g.op + h * g.d + half * 32, o, min(32, g.d - half * 32));
         if (me.ok && half == 0) lse[((int64_t)me.b * g.H + h) * g.S + me.s] = mx + logf(fmaxf(sum, 1e-30f));
     }
     tc_fence_before();
@@ -505,7 +560,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.y;
-    const int64_t pitch = (int64_t)3 * g.H * g.d, opitch = (int64_t)g.H * g.d;
+    const int64_t pitch = g.qp, opitch = g.dop;
     const int nunits = (g.B + g.G - 1) / g.G;
     const int nkb = g.nq;                         // 128-key blocks per problem (== query tiles)
     const int ksteps = (g.d + 15) >> 4;
@@ -546,13 +601,21 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                 // ---- operands.  Tiles may be overwritten only once every MMA issued so far has retired.
                 if (g.manual && (need_q || need_kv)) {
                     if (n_m > 0) mbar_wait(bar_m, (n_m - 1) & 1);
-                    if (need_q) {
-                        stage_rows<T>(sQ + i * kTileBytes, qkv + (int64_t)h * g.d, pitch, g, b0, i * kTile, kTile);
-                        stage_rows<T>(sDO + i * kTileBytes, dout + (int64_t)h * g.d, opitch, g, b0, i * kTile, kTile);
-                    }
-                    if (need_kv) {
-                        stage_rows<T>(sK, qkv + (int64_t)(g.H + h) * g.d, pitch, g, b0, j * kTile, kTile);
-                        stage_rows<T>(sV, qkv + (int64_t)(2 * g.H + h) * g.d, pitch, g, b0, j * kTile, kTile);
+                    if (need_q && need_kv) {
+                        const StageJob<T> jobs[4] = {
+                            {sQ + i * kTileBytes, qkv + (int64_t)h * g.d, pitch, i * kTile, kTile},
+                            {sDO + i * kTileBytes, dout + (int64_t)h * g.d, opitch, i * kTile, kTile},
+                            {sK, qkv + (int64_t)(g.H + h) * g.d, pitch, j * kTile, kTile},
+                            {sV, qkv + (int64_t)(2 * g.H + h) * g.d, pitch, j * kTile, kTile}};
+                        stage_many<T, 4>(jobs, g, b0);
+                    } else if (need_q) {
+                        const StageJob<T> jobs[2] = {{sQ + i * kTileBytes, qkv + (int64_t)h * g.d, pitch, i * kTile, kTile},
+                                                     {sDO + i * kTileBytes, dout + (int64_t)h * g.d, opitch, i * kTile, kTile}};
+                        stage_many<T, 2>(jobs, g, b0);
+                    } else {
+                        const StageJob<T> jobs[2] = {{sK, qkv + (int64_t)(g.H + h) * g.d, pitch, j * kTile, kTile},
+                                                     {sV, qkv + (int64_t)(2 * g.H + h) * g.d, pitch, j * kTile, kTile}};
+                        stage_many<T, 2>(jobs, g, b0);
                     }
                     fence_async_smem();
                 }
@@ -593,8 +656,8 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                     if (j == 0) {
                         // per-row constants of this query tile, fetched while the tensor core works
                         if (me.ok) {
-                            const int64_t o = (((int64_t)me.b * g.S + me.s) * g.H + h) * g.d;
-                            delta[i] = row_dot<T>(out + o, dout + o, g.d);
+                            const int64_t t = tok(g, me.b, me.s);
+                            delta[i] = row_dot<T>(out + t * g.op + h * g.d, dout + t * g.dop + h * g.d, g.d);
                             row_lse[i] = lse[((int64_t)me.b * g.H + h) * g.S + me.s];
                         } else {
                             delta[i] = 0.f; row_lse[i] = 0.f;
@@ -692,7 +755,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
 #pragma unroll
                     for (int q = 0; q < 32; ++q) o[q] = __uint_as_float(v[q]);
                     if (kr.ok && g.d > half * 32)
-                        store_row<T, 32>(dqkv + ((((int64_t)kr.b * g.S + kr.s) * 3 + (w + 1)) * g.H + h) * g.d + half * 32, o,
+                        store_row<T, 32>(dqkv + tok(g, kr.b, kr.s) * g.qp + ((w + 1) * g.H + h) * g.d + half * 32, o,
                                          min(32, g.d - half * 32));
                 }
                 tc_fence_before();
@@ -711,7 +774,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
 #pragma unroll
                 for (int q = 0; q < 32; ++q) o[q] = __uint_as_float(v[q]);
                 if (qr.ok && g.d > half * 32)
-                    store_row<T, 32>(dqkv + ((((int64_t)qr.b * g.S + qr.s) * 3 + 0) * g.H + h) * g.d + half * 32, o,
+                    store_row<T, 32>(dqkv + tok(g, qr.b, qr.s) * g.qp + h * g.d + half * 32, o,
                                      min(32, g.d - half * 32));
             }
             tc_fence_before();
@@ -757,6 +820,22 @@ static int make_geom(Geom* g, int B, int H, int S, int d, float scale, int nW, c
     g->nq = (S + kTile - 1) / kTile;
     g->nk = g->G == 2 ? kTile : ((S + 15) / 16) * 16;
     g->manual = !(d == 64 && g->G == 1 && ((uintptr_t)p0 & 15) == 0 && ((uintptr_t)p1 & 15) == 0);
+    g->qp = 3 * H * d; g->op = H * d; g->dop = H * d;
+    g->win = 0; g->ws = g->nWx = g->wpi = g->Hi = g->Wi = g->shift = 0;
+    return 0;
+}
+
+// Window mode on top of make_geom: images of Hi x Wi tokens cut into ws x ws windows after a cyclic shift; pitches in elements.
+static int set_windows(Geom* g, int Hi, int Wi, int ws, int shift, int qp, int op, int dop) {
+    B200DP_REQUIRE(ws > 0 && ws * ws == g->S && Hi % ws == 0 && Wi % ws == 0 && shift >= 0 && shift < ws,
+                   "window attention: %d x %d tokens do not tile into %d x %d windows (S=%d, shift %d)", Hi, Wi, ws, ws, g->S, shift);
+    const int wpi = (Hi / ws) * (Wi / ws);
+    B200DP_REQUIRE(g->B % wpi == 0, "window attention: %d windows are not whole images of %d", g->B, wpi);
+    B200DP_REQUIRE(qp >= 3 * g->H * g->d && op >= g->H * g->d && dop >= g->H * g->d && ((qp | op | dop) & 1) == 0,
+                   "window attention: pitches %d / %d / %d too small or odd", qp, op, dop);
+    g->win = 1; g->ws = ws; g->nWx = Wi / ws; g->wpi = wpi; g->Hi = Hi; g->Wi = Wi; g->shift = shift;
+    g->qp = qp; g->op = op; g->dop = dop;
+    g->manual = 1;
     return 0;
 }
 
@@ -770,13 +849,16 @@ extern "C" int b200dp_attention_supported(int S, int d) { return S > 0 && S <= 2
 
 // out[B][S][H][d] = softmax(q k^T * scale + bias[H][S][S] + mask[b % nW][S][S]) v over the packed qkv[B][S][3][H][d];
 // lse[B][H][S] (fp32) keeps the row log-sum-exp for the backward.  bias / mask may be NULL.
-extern "C" int b200dp_attention_fwd(const void* qkv, void* out, float* lse, const float* bias, const float* mask, int nW,
-                                    int B, int H, int S, int d, float scale, b200dp_dtype dtype, void* stream) {
+struct WinArgs { int Hi, Wi, ws, shift, qp, op, dop; };
+
+static int attention_fwd_impl(const void* qkv, void* out, float* lse, const float* bias, const float* mask, int nW,
+                              int B, int H, int S, int d, float scale, b200dp_dtype dtype, void* stream, const WinArgs* win) {
     B200DP_REQUIRE(qkv && out && lse, "attention_fwd: null pointer");
     B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "attention_fwd: fp16 / bf16 only");
     Geom g;
     int rc = make_geom(&g, B, H, S, d, scale, mask ? nW : 0, qkv, out);
     if (rc) return rc;
+    if (win) { rc = set_windows(&g, win->Hi, win->Wi, win->ws, win->shift, win->qp, win->op, win->op); if (rc) return rc; }
     const int is_bf16 = dtype == B200DP_BF16;
     CUtensorMap tq, tkv;
     memset(&tq, 0, sizeof(tq)); memset(&tkv, 0, sizeof(tkv));
@@ -805,11 +887,29 @@ extern "C" int b200dp_attention_fwd(const void* qkv, void* out, float* lse, cons
     return 0;
 }
 
+extern "C" int b200dp_attention_fwd(const void* qkv, void* out, float* lse, const float* bias, const float* mask, int nW,
+                                    int B, int H, int S, int d, float scale, b200dp_dtype dtype, void* stream) {
+    return attention_fwd_impl(qkv, out, lse, bias, mask, nW, B, H, S, d, scale, dtype, stream, nullptr);
+}
+
+// Window attention straight on the image-ordered token grid: qkv is [images][Hi][Wi][qkv_pitch] (first 3*H*d elements of
+// a row are q|k|v), out [images][Hi][Wi][out_pitch]; the cyclic shift and the cut into ws x ws windows happen in the
+// kernel's addressing.  lse / bias / mask / dbias keep the window-major layouts of the plain entry points
+// (B = images * windows-per-image problems of S = ws * ws tokens; mask index = window index inside its image).
+extern "C" int b200dp_window_attention_fwd(const void* qkv, void* out, float* lse, const float* bias, const float* mask,
+                                           int images, int Hi, int Wi, int ws, int shift, int H, int d, int qkv_pitch,
+                                           int out_pitch, float scale, b200dp_dtype dtype, void* stream) {
+    B200DP_REQUIRE(ws > 0 && Hi > 0 && Wi > 0 && Hi % ws == 0 && Wi % ws == 0, "window_attention_fwd: bad window geometry");
+    const int wpi = (Hi / ws) * (Wi / ws);
+    const WinArgs w{Hi, Wi, ws, shift, qkv_pitch, out_pitch, out_pitch};
+    return attention_fwd_impl(qkv, out, lse, bias, mask, wpi, images * wpi, H, ws * ws, d, scale, dtype, stream, &w);
+}
+
 // dqkv[B][S][3][H][d] from dout / out [B][S][H][d], the packed qkv and lse.  dbias ([H][S][S] fp32, S <= 64 only)
 // is ACCUMULATED into (atomic adds; the caller zeroes it); pass NULL when the bias needs no gradient.
-extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
-                                    const float* bias, const float* mask, int nW, float* dbias, int B, int H, int S, int d,
-                                    float scale, b200dp_dtype dtype, void* stream) {
+static int attention_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                              const float* bias, const float* mask, int nW, float* dbias, int B, int H, int S, int d,
+                              float scale, b200dp_dtype dtype, void* stream, const WinArgs* win) {
     B200DP_REQUIRE(qkv && out && dout && lse && dqkv, "attention_bwd: null pointer");
     B200DP_REQUIRE(dtype == B200DP_F16 || dtype == B200DP_BF16, "attention_bwd: fp16 / bf16 only");
     B200DP_REQUIRE(dbias == nullptr || S <= 64, "attention_bwd: the bias gradient is implemented for S <= 64 (windows)");
@@ -817,6 +917,7 @@ extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void
     int rc = make_geom(&g, B, H, S, d, scale, mask ? nW : 0, qkv, dout);
     if (rc) return rc;
     if (((uintptr_t)dqkv & 15) != 0 || ((uintptr_t)out & 15) != 0) g.manual = 1;
+    if (win) { rc = set_windows(&g, win->Hi, win->Wi, win->ws, win->shift, win->qp, win->op, win->dop); if (rc) return rc; }
     const int is_bf16 = dtype == B200DP_BF16;
     CUtensorMap tq, tdo;
     memset(&tq, 0, sizeof(tq)); memset(&tdo, 0, sizeof(tdo));
@@ -829,8 +930,11 @@ extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void
     }
     const int nunits = (B + g.G - 1) / g.G;
     int gx = nunits;
-    if (dbias != nullptr) {            // fewer, longer-lived CTAs: each flushes its bias-gradient partial once
-        gx = (2 * B200DP_SMS + H - 1) / H;
+    if (dbias != nullptr) {
+        // persistent CTAs, exactly one wave (one CTA per SM: the kernel owns all 512 TMEM columns): each walks its share
+        // of the windows of one head and flushes its bias-gradient partial once
+        gx = B200DP_SMS / H;
+        if (gx < 1) gx = 1;
         if (gx > nunits) gx = nunits;
     }
     const dim3 grid(gx, H, 1);
@@ -851,4 +955,24 @@ extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void
     B200DP_CHECK_LAUNCH();
     return 0;
 }
+
+extern "C" int b200dp_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                    const float* bias, const float* mask, int nW, float* dbias, int B, int H, int S, int d,
+                                    float scale, b200dp_dtype dtype, void* stream) {
+    return attention_bwd_impl(qkv, out, dout, lse, dqkv, bias, mask, nW, dbias, B, H, S, d, scale, dtype, stream, nullptr);
+}
+
+// Backward of b200dp_window_attention_fwd.  dqkv has the layout (and pitch) of qkv; only its first 3*H*d elements per
+// token are written, so the caller zeroes any padding columns.  dout may have its own pitch.
+extern "C" int b200dp_window_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                           const float* bias, const float* mask, float* dbias, int images, int Hi, int Wi,
+                                           int ws, int shift, int H, int d, int qkv_pitch, int out_pitch, int dout_pitch,
+                                           float scale, b200dp_dtype dtype, void* stream) {
+    B200DP_REQUIRE(ws > 0 && Hi > 0 && Wi > 0 && Hi % ws == 0 && Wi % ws == 0, "window_attention_bwd: bad window geometry");
+    const int wpi = (Hi / ws) * (Wi / ws);
+    const WinArgs w{Hi, Wi, ws, shift, qkv_pitch, out_pitch, dout_pitch};
+    return attention_bwd_impl(qkv, out, dout, lse, dqkv, bias, mask, wpi, dbias, images * wpi, H, ws * ws, d, scale, dtype,
+                              stream, &w);
+}
+
 

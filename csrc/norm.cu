@@ -531,11 +531,14 @@ template <typename T> struct alignas(sizeof(T) * 4) Vec4 { T v[4]; };
 template <typename T, int NCH>
 __global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwd4_kernel(
     const T* __restrict__ x, T* __restrict__ y, int64_t rows, int D, const float* __restrict__ gamma,
-    const float* __restrict__ beta, float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+    const float* __restrict__ beta, float eps, float* __restrict__ mean, float* __restrict__ rstd, int pitch) {
+    // pitch: elements between rows (>= D, multiple of 4); columns D .. pitch of y are written as zeros, so a row padded
+    // to a tensor-core friendly width (60 -> 64) stays padded with zeros through the layer
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * kLNWarps + (threadIdx.x >> 5);
     if (row >= rows) return;
-    const int nchunk = D / 4;
+    const int nchunk = D / 4, pchunk = pitch / 4;
+    x += row * (pitch - D); y += row * (pitch - D);          // the row * D indexing below then lands on row * pitch
     float v[NCH][4];
     float s = 0.f;
 #pragma unroll
@@ -567,6 +570,11 @@ __global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwd4_kernel(
 #pragma unroll
             for (int k = 0; k < 4; ++k) o.v[k] = Cvt<T>::from_f((v[j][k] - mu) * rs * ga[k] + be[k]);
             *reinterpret_cast<Vec4<T>*>(y + row * D + ch * 4) = o;
+        } else if (ch < pchunk) {
+            Vec4<T> o;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) o.v[k] = Cvt<T>::from_f(0.f);
+            *reinterpret_cast<Vec4<T>*>(y + row * D + ch * 4) = o;
         }
     }
 }
@@ -575,10 +583,11 @@ template <typename T, int NCH>
 __global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd4_kernel(
     const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t rows, int D,
     const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
-    float* __restrict__ scratch, const T* __restrict__ add_in) {
+    float* __restrict__ scratch, const T* __restrict__ add_in, int pitch) {
     __shared__ float red[2 * NCH * 128];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int nchunk = D / 4;
+    const int nchunk = D / 4, pchunk = pitch / 4;
+    const int64_t P = pitch;             // rows of dy / x / dx / add_in are `pitch` elements apart; padding of dx is zeroed
     float pa[NCH][4], pb[NCH][4], ga[NCH][4];
 #pragma unroll
     for (int j = 0; j < NCH; ++j) {
@@ -595,9 +604,9 @@ __global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd4_kernel(
         for (int j = 0; j < NCH; ++j) {
             const int ch = lane + j * 32;
             if (ch < nchunk) {
-                dv[j] = *reinterpret_cast<const Vec4<T>*>(dy + row * D + ch * 4);
-                xv[j] = *reinterpret_cast<const Vec4<T>*>(x + row * D + ch * 4);
-                if (add_in != nullptr) av[j] = *reinterpret_cast<const Vec4<T>*>(add_in + row * D + ch * 4);
+                dv[j] = *reinterpret_cast<const Vec4<T>*>(dy + row * P + ch * 4);
+                xv[j] = *reinterpret_cast<const Vec4<T>*>(x + row * P + ch * 4);
+                if (add_in != nullptr) av[j] = *reinterpret_cast<const Vec4<T>*>(add_in + row * P + ch * 4);
             }
         }
         float c1 = 0.f, c2 = 0.f;
@@ -627,7 +636,12 @@ __global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd4_kernel(
                     if (add_in != nullptr) r += Cvt<T>::to_f(av[j].v[k]);
                     o.v[k] = Cvt<T>::from_f(r);
                 }
-                *reinterpret_cast<Vec4<T>*>(dx + row * D + ch * 4) = o;
+                *reinterpret_cast<Vec4<T>*>(dx + row * P + ch * 4) = o;
+            } else if (ch < pchunk) {
+                Vec4<T> o;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) o.v[k] = Cvt<T>::from_f(0.f);
+                *reinterpret_cast<Vec4<T>*>(dx + row * P + ch * 4) = o;
             }
         }
     }
@@ -785,21 +799,36 @@ static unsigned ln_bwd_grid(int64_t rows) {
 // one [dbeta | dgamma] partial per CTA of the fused backward
 int64_t b200dp_ln_scratch_floats(int64_t rows, int D) { return rows <= 0 || D <= 0 ? 0 : (int64_t)ln_bwd_grid(rows) * 2 * D; }
 
+static int layernorm_fwd4(const void* x, void* y, int64_t rows, int D, int pitch, b200dp_dtype dtype, const float* gamma,
+                          const float* beta, float eps, float* mean, float* rstd, void* stream) {
+    const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
+    if (pitch <= 128) {
+        B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 1><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
+            (const T*)x, (T*)y, rows, D, gamma, beta, eps, mean, rstd, pitch); });
+    } else {
+        B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 2><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
+            (const T*)x, (T*)y, rows, D, gamma, beta, eps, mean, rstd, pitch); });
+    }
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
+
+// LayerNorm over the first D elements of rows that are `pitch` elements apart (D % 4 == 0, D <= pitch <= 256,
+// pitch % 4 == 0); y has the same pitch and its columns D .. pitch come out as zeros.
+int b200dp_layernorm_fwd_pitched(const void* x, void* y, int64_t rows, int D, int pitch, b200dp_dtype dtype,
+                                 const float* gamma, const float* beta, float eps, float* mean, float* rstd, void* stream) {
+    B200DP_REQUIRE(x && y && gamma && beta && mean && rstd, "layernorm_fwd_pitched: null argument");
+    B200DP_REQUIRE(rows > 0 && D > 0 && D % 4 == 0 && pitch % 4 == 0 && pitch >= D && pitch <= 256,
+                   "layernorm_fwd_pitched: D=%d pitch=%d (multiples of 4, D <= pitch <= 256)", D, pitch);
+    return layernorm_fwd4(x, y, rows, D, pitch, dtype, gamma, beta, eps, mean, rstd, stream);
+}
+
 int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dtype dtype, const float* gamma,
                          const float* beta, float eps, float* mean, float* rstd, void* stream) {
     B200DP_REQUIRE(x && y && gamma && beta && mean && rstd, "layernorm_fwd: null argument");
     const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
-    if (rows > 0 && D % 8 != 0 && D % 4 == 0 && D <= 256) {      // narrow rows: 4-element vectors
-        if (D <= 128) {
-            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 1><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
-                (const T*)x, (T*)y, rows, D, gamma, beta, eps, mean, rstd); });
-        } else {
-            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 2><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
-                (const T*)x, (T*)y, rows, D, gamma, beta, eps, mean, rstd); });
-        }
-        B200DP_CHECK_LAUNCH();
-        return 0;
-    }
+    if (rows > 0 && D % 8 != 0 && D % 4 == 0 && D <= 256)        // narrow rows: 4-element vectors
+        return layernorm_fwd4(x, y, rows, D, D, dtype, gamma, beta, eps, mean, rstd, stream);
     B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_fwd: D must be a multiple of 8 (or of 4 up to 256), <= %d",
                    kLNMaxChunks * 256);
     B200DP_DISPATCH_DTYPE(dtype, T, {
@@ -812,19 +841,21 @@ int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dty
 
 static int layernorm_bwd_impl(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
                               const float* gamma, const float* mean, const float* rstd, float* scratch,
-                              unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream) {
+                              unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream,
+                              int pitch = 0) {
     B200DP_REQUIRE(dy && x && dx && gamma && mean && rstd && scratch && counter && dgamma && dbeta,
                    "layernorm_bwd: null argument");
     B200DP_REQUIRE(dgamma == dbeta + D, "layernorm_bwd: dbeta and dgamma must be one buffer [dbeta(D) | dgamma(D)]");
     cudaStream_t s = (cudaStream_t)stream;
     const unsigned grid = ln_bwd_grid(rows);
-    if (rows > 0 && D % 8 != 0 && D % 4 == 0 && D <= 256) {      // narrow rows: 4-element vectors
-        if (D <= 128) {
+    if (rows > 0 && (pitch > 0 || (D % 8 != 0 && D % 4 == 0 && D <= 256))) {      // narrow rows: 4-element vectors
+        if (pitch <= 0) pitch = D;
+        if (pitch <= 128) {
             B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_bwd4_kernel<T, 1><<<grid, kLNWarps * 32, 0, s>>>(
-                (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in); });
+                (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in, pitch); });
         } else {
             B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_bwd4_kernel<T, 2><<<grid, kLNWarps * 32, 0, s>>>(
-                (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in); });
+                (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in, pitch); });
         }
         ln_partials_reduce_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(scratch, (int)grid, 2 * D, dbeta);
         B200DP_CHECK_LAUNCH();
@@ -858,6 +889,16 @@ int b200dp_layernorm_bwd_add(const void* dy, const void* x, void* dx, int64_t ro
                              const float* gamma, const float* mean, const float* rstd, float* scratch,
                              unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream) {
     return layernorm_bwd_impl(dy, x, dx, rows, D, dtype, gamma, mean, rstd, scratch, counter, dgamma, dbeta, add_in, stream);
+}
+
+// Backward of b200dp_layernorm_fwd_pitched: dy / x / dx (/ add_in, may be NULL) all have rows `pitch` elements apart;
+// columns D .. pitch of dx are written as zeros.
+int b200dp_layernorm_bwd_pitched(const void* dy, const void* x, void* dx, int64_t rows, int D, int pitch, b200dp_dtype dtype,
+                                 const float* gamma, const float* mean, const float* rstd, float* scratch,
+                                 unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream) {
+    B200DP_REQUIRE(rows > 0 && D > 0 && D % 4 == 0 && pitch % 4 == 0 && pitch >= D && pitch <= 256,
+                   "layernorm_bwd_pitched: D=%d pitch=%d (multiples of 4, D <= pitch <= 256)", D, pitch);
+    return layernorm_bwd_impl(dy, x, dx, rows, D, dtype, gamma, mean, rstd, scratch, counter, dgamma, dbeta, add_in, stream, pitch);
 }
 
 }  // extern "C"

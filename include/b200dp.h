@@ -208,6 +208,14 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
 int b200dp_layernorm_bwd_add(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
                              const float* gamma, const float* mean, const float* rstd, float* scratch,
                              unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream);
+/* Zero-padded rows: x / y (dy / dx / add_in) have rows `pitch` elements apart, the first D of which are normalised;
+ * columns D .. pitch of y and dx are written as zeros, so a width padded for the tensor cores (SwinIR-S: 60 -> 64)
+ * stays padded with zeros through the layer.  D % 4 == 0, pitch % 4 == 0, D <= pitch <= 256.  add_in may be NULL. */
+int b200dp_layernorm_fwd_pitched(const void* x, void* y, int64_t rows, int D, int pitch, b200dp_dtype dtype,
+                                 const float* gamma, const float* beta, float eps, float* mean, float* rstd, void* stream);
+int b200dp_layernorm_bwd_pitched(const void* dy, const void* x, void* dx, int64_t rows, int D, int pitch, b200dp_dtype dtype,
+                                 const float* gamma, const float* mean, const float* rstd, float* scratch,
+                                 unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream);
 
 /* ------------------------------------------------------------------ tensor-core GEMM (tcgen05 / TMEM / TMA)
  * C[M,N] (+)= A(MxK) * B(NxK)^T (+ bias[N]), 16-bit inputs, fp32 accumulation in TMEM.
@@ -353,6 +361,22 @@ int b200dp_attention_fwd(const void* qkv, void* out, float* lse, const float* bi
 int b200dp_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, const float* bias,
                          const float* mask, int nW, float* dbias, int B, int H, int S, int d, float scale,
                          b200dp_dtype dtype, void* stream);
+
+/* (Shifted-)window attention addressed on the IMAGE-ordered token grid: qkv [images][Hi][Wi][qkv_pitch] (the first 3*H*d
+ * elements of a token row are q|k|v in [3][H][d] order), out [images][Hi][Wi][out_pitch].  The cyclic shift by `shift`
+ * tokens and the cut into ws x ws windows are part of the kernels' addressing, so the roll / window_partition /
+ * window_reverse copies of a Swin block do not exist.  lse [windows][H][ws*ws], bias [H][S][S], mask
+ * [windows per image][S][S] and dbias keep the layouts of the plain entry points.  Padding columns (past 3*H*d / H*d)
+ * are never read; the backward writes only the first 3*H*d elements of each dqkv row (the caller zeroes the padding).
+ * Envelope: ws*ws <= 64, Hi % ws == Wi % ws == 0, even d <= 64, even pitches.
+ * Reference: SwinIR's SwinTransformerBlock (built at Stoke-DDP.py:206-208, window_size 8). */
+int b200dp_window_attention_fwd(const void* qkv, void* out, float* lse, const float* bias, const float* mask, int images,
+                                int Hi, int Wi, int ws, int shift, int H, int d, int qkv_pitch, int out_pitch, float scale,
+                                b200dp_dtype dtype, void* stream);
+int b200dp_window_attention_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv,
+                                const float* bias, const float* mask, float* dbias, int images, int Hi, int Wi, int ws,
+                                int shift, int H, int d, int qkv_pitch, int out_pitch, int dout_pitch, float scale,
+                                b200dp_dtype dtype, void* stream);
 
 /* Attention layout moves (ViT / SwinIR): W per-head tensors [B][H][S][d] <-> one token-major tensor
  * [B][S][W][H][d] in one streaming pass (W = 3: packed q/k/v gradient; W = 1: merge heads).  Rows of

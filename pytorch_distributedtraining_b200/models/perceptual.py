@@ -15,6 +15,8 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops.layers import Conv2d
+
 __all__ = ["VGGFeatures", "PerceptualLoss", "feat_loss"]
 
 _CFG = [64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512]
@@ -30,7 +32,7 @@ class VGGFeatures(nn.Module):
             if v == "M":
                 layers.append(nn.MaxPool2d(2, 2))
             else:
-                layers += [nn.Conv2d(c, int(v), 3, padding=1), nn.ReLU(inplace=False)]
+                layers += [Conv2d(c, int(v), 3, padding=1), nn.ReLU(inplace=False)]
                 c = int(v)
         self.features = nn.Sequential(*layers[: max(taps) + 1])
         self.taps = tuple(taps)

@@ -22,8 +22,9 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from ..ops import gemm as _gemm
-from ..ops.attention import attention, attention_reference, attention_supported
-from ..ops.layers import LayerNorm, Linear
+from ..ops.attention import (attention, attention_reference, attention_supported, window_attention,
+                             window_attention_reference, window_attention_supported)
+from ..ops.layers import Conv2d, LayerNorm, Linear
 
 __all__ = ["SwinIR"]
 
@@ -51,10 +52,17 @@ class Mlp(nn.Module):
         self.fc2 = Linear(hidden, dim)
         self.drop = nn.Dropout(drop)
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if (self.drop.p == 0.0 or not self.training) and _gemm.mlp_supported(x, self.fc1.weight, self.fc2.weight):
-            return _gemm.mlp(x, self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias)
-        return self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+    def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``fc2(gelu(fc1(x))) (+ residual)``; the residual add rides in the last GEMM's epilogue when there is no dropout."""
+        no_drop = self.drop.p == 0.0 or not self.training
+        if no_drop:
+            w1, b1 = self.fc1.padded_params()
+            w2, b2 = self.fc2.padded_params()
+            if _gemm.mlp_supported(x, w1, w2):
+                return _gemm.mlp(x, w1, b1, w2, b2, residual)
+            return self.fc2(self.act(self.fc1(x)), residual=residual)
+        y = self.drop(self.fc2(self.drop(self.act(self.fc1(x)))))
+        return y if residual is None else y + residual
 
 
 class WindowAttention(nn.Module):
@@ -89,6 +97,33 @@ class WindowAttention(nn.Module):
             o = attention_reference(qkv, self.num_heads, self.scale, bias, mask, dropout_p=p_drop)
         return self.proj_drop(self.proj(o))
 
+    def rel_bias(self) -> torch.Tensor:
+        n = self.window_size[0] * self.window_size[1]
+        return self.relative_position_bias_table[self.relative_position_index.view(-1)].view(n, n, -1).permute(2, 0, 1)
+
+    def forward_grid(self, h: torch.Tensor, x_size: Tuple[int, int], shift: int, mask: Optional[torch.Tensor],
+                     residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Attention of one Swin block on the IMAGE-ordered tokens ``h [B, L, C]``: the per-token projections run on the
+        whole grid and the (shifted) windows exist only in the attention kernel's addressing — no roll, partition or
+        reverse copies.  ``residual`` is added in the output projection's epilogue.  Rows may be zero-padded
+        (``phys_*`` widths of the projections); the result has the width of ``proj``'s output."""
+        B, L, _ = h.shape
+        H, W = x_size
+        ws = self.window_size[0]
+        heads, d = self.num_heads, self.dim // self.num_heads
+        qkv = self.qkv(h).view(B, H, W, -1)
+        p_drop = self.attn_drop.p if self.training else 0.0
+        out_pitch = self.proj.phys_in or self.dim
+        if p_drop == 0.0 and window_attention_supported(qkv, heads, d, ws):
+            o = window_attention(qkv, heads, d, ws, shift, self.scale, self.rel_bias(), mask, out_pitch)
+        else:
+            o = window_attention_reference(qkv, heads, d, ws, shift, self.scale, self.rel_bias(), mask, out_pitch, p_drop)
+        o = o.reshape(B, L, -1)
+        if self.proj_drop.p == 0.0 or not self.training:
+            return self.proj(o, residual=residual)
+        y = self.proj_drop(self.proj(o))
+        return y if residual is None else y + residual
+
 
 class SwinTransformerBlock(nn.Module):
     def __init__(self, dim: int, input_resolution: Tuple[int, int], num_heads: int, window_size: int = 7,
@@ -106,6 +141,7 @@ class SwinTransformerBlock(nn.Module):
         self.norm2 = norm_layer(dim)
         self.mlp = Mlp(dim, int(dim * mlp_ratio), drop)
         self.register_buffer("attn_mask", self.calculate_mask(input_resolution) if self.shift_size > 0 else None)
+        self.legacy_block = False        # True: the classic roll -> window_partition -> attention -> window_reverse -> roll chain
 
     def calculate_mask(self, x_size: Tuple[int, int]) -> torch.Tensor:
         H, W = x_size
@@ -127,9 +163,29 @@ class SwinTransformerBlock(nn.Module):
         mask = x.new_empty((x.shape[0],) + (1,) * (x.dim() - 1)).bernoulli_(keep)
         return x * mask / keep
 
+    def _add_dropped(self, x: torch.Tensor, branch: torch.Tensor) -> torch.Tensor:
+        """``x + drop_path(branch)`` as one elementwise pass (per-sample keep mask / keep probability, broadcast)."""
+        keep = 1 - self.drop_path_p
+        mask = x.new_empty((x.shape[0],) + (1,) * (x.dim() - 1)).bernoulli_(keep).div_(keep)
+        return torch.addcmul(x, branch, mask)
+
     def forward(self, x: torch.Tensor, x_size: Tuple[int, int]) -> torch.Tensor:
         H, W = x_size
         B, L, C = x.shape
+        ws = self.window_size
+        no_path_drop = self.drop_path_p == 0.0 or not self.training
+        if H % ws == 0 and W % ws == 0 and self.attn.window_size == (ws, ws) and not self.legacy_block:
+            # image-ordered block: LN -> qkv on the grid -> window attention by addressing -> proj (+ shortcut) -> MLP (+ x)
+            if self.shift_size > 0:
+                mask = (self.attn_mask if tuple(self.input_resolution) == tuple(x_size)
+                        else self.calculate_mask(x_size).to(x.device))
+            else:
+                mask = None
+            if no_path_drop:
+                x = self.attn.forward_grid(self.norm1(x), x_size, self.shift_size, mask, residual=x)
+                return self.mlp(self.norm2(x), residual=x)
+            x = self._add_dropped(x, self.attn.forward_grid(self.norm1(x), x_size, self.shift_size, mask))
+            return self._add_dropped(x, self.mlp(self.norm2(x)))
         shortcut = x
         x = self.norm1(x).view(B, H, W, C)
         if self.shift_size > 0:
@@ -186,7 +242,7 @@ class PatchUnEmbed(nn.Module):
 
     def forward(self, x: torch.Tensor, x_size: Tuple[int, int]) -> torch.Tensor:
         B = x.shape[0]
-        return x.transpose(1, 2).reshape(B, self.embed_dim, x_size[0], x_size[1])
+        return x.transpose(1, 2).reshape(B, x.shape[2], x_size[0], x_size[1])     # width may be physical (zero-padded)
 
 
 class RSTB(nn.Module):
@@ -199,11 +255,11 @@ class RSTB(nn.Module):
         self.residual_group = BasicLayer(dim, input_resolution, depth, num_heads, window_size, mlp_ratio, qkv_bias,
                                          qk_scale, drop, attn_drop, drop_path, norm_layer, use_checkpoint)
         if resi_connection == "1conv":
-            self.conv: nn.Module = nn.Conv2d(dim, dim, 3, 1, 1)
+            self.conv: nn.Module = Conv2d(dim, dim, 3, 1, 1)
         elif resi_connection == "3conv":
-            self.conv = nn.Sequential(nn.Conv2d(dim, dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, True),
-                                      nn.Conv2d(dim // 4, dim // 4, 1, 1, 0), nn.LeakyReLU(0.2, True),
-                                      nn.Conv2d(dim // 4, dim, 3, 1, 1))
+            self.conv = nn.Sequential(Conv2d(dim, dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, True),
+                                      Conv2d(dim // 4, dim // 4, 1, 1, 0), nn.LeakyReLU(0.2, True),
+                                      Conv2d(dim // 4, dim, 3, 1, 1))
         else:
             raise ValueError(resi_connection)
         self.patch_embed = PatchEmbed(dim)
@@ -218,9 +274,9 @@ class Upsample(nn.Sequential):
         m: List[nn.Module] = []
         if (scale & (scale - 1)) == 0:
             for _ in range(int(math.log2(scale))):
-                m += [nn.Conv2d(num_feat, 4 * num_feat, 3, 1, 1), nn.PixelShuffle(2)]
+                m += [Conv2d(num_feat, 4 * num_feat, 3, 1, 1), nn.PixelShuffle(2)]
         elif scale == 3:
-            m += [nn.Conv2d(num_feat, 9 * num_feat, 3, 1, 1), nn.PixelShuffle(3)]
+            m += [Conv2d(num_feat, 9 * num_feat, 3, 1, 1), nn.PixelShuffle(3)]
         else:
             raise ValueError(f"scale {scale} is not supported (2^n and 3 are)")
         super().__init__(*m)
@@ -230,7 +286,12 @@ class UpsampleOneStep(nn.Sequential):
     """conv + pixel-shuffle in one step (``pixelshuffledirect``, the lightweight variant)."""
 
     def __init__(self, scale: int, num_feat: int, num_out_ch: int):
-        super().__init__(nn.Conv2d(num_feat, (scale ** 2) * num_out_ch, 3, 1, 1), nn.PixelShuffle(scale))
+        super().__init__(Conv2d(num_feat, (scale ** 2) * num_out_ch, 3, 1, 1), nn.PixelShuffle(scale))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:  # type: ignore[override]
+        y = self[0](x)
+        cout = self[0].out_channels
+        return self[1](y[:, :cout] if y.shape[1] != cout else y)         # the conv may emit zero-padded channels
 
 
 class SwinIR(nn.Module):
@@ -247,7 +308,7 @@ class SwinIR(nn.Module):
         self.img_range, self.upscale, self.upsampler, self.window_size = img_range, upscale, upsampler, window_size
         mean = torch.tensor((0.4488, 0.4371, 0.4040)).view(1, 3, 1, 1) if in_chans == 3 else torch.zeros(1, 1, 1, 1)
         self.register_buffer("mean", mean, persistent=False)
-        self.conv_first = nn.Conv2d(in_chans, embed_dim, 3, 1, 1)
+        self.conv_first = Conv2d(in_chans, embed_dim, 3, 1, 1)
         self.num_layers, self.embed_dim, self.ape, self.patch_norm = len(depths), embed_dim, ape, patch_norm
         self.patch_embed = PatchEmbed(embed_dim, norm_layer if patch_norm else None)
         self.patch_unembed = PatchUnEmbed(embed_dim)
@@ -263,28 +324,78 @@ class SwinIR(nn.Module):
             for i in range(self.num_layers)])
         self.norm = norm_layer(embed_dim)
         if resi_connection == "1conv":
-            self.conv_after_body: nn.Module = nn.Conv2d(embed_dim, embed_dim, 3, 1, 1)
+            self.conv_after_body: nn.Module = Conv2d(embed_dim, embed_dim, 3, 1, 1)
         else:
-            self.conv_after_body = nn.Sequential(nn.Conv2d(embed_dim, embed_dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, True),
-                                                 nn.Conv2d(embed_dim // 4, embed_dim // 4, 1, 1, 0),
-                                                 nn.LeakyReLU(0.2, True), nn.Conv2d(embed_dim // 4, embed_dim, 3, 1, 1))
+            self.conv_after_body = nn.Sequential(Conv2d(embed_dim, embed_dim // 4, 3, 1, 1), nn.LeakyReLU(0.2, True),
+                                                 Conv2d(embed_dim // 4, embed_dim // 4, 1, 1, 0),
+                                                 nn.LeakyReLU(0.2, True), Conv2d(embed_dim // 4, embed_dim, 3, 1, 1))
         if upsampler == "pixelshuffle":
-            self.conv_before_upsample = nn.Sequential(nn.Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
+            self.conv_before_upsample = nn.Sequential(Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
             self.upsample: nn.Module = Upsample(upscale, num_feat)
-            self.conv_last = nn.Conv2d(num_feat, in_chans, 3, 1, 1)
+            self.conv_last = Conv2d(num_feat, in_chans, 3, 1, 1)
         elif upsampler == "pixelshuffledirect":
             self.upsample = UpsampleOneStep(upscale, embed_dim, in_chans)
         elif upsampler == "nearest+conv":
-            self.conv_before_upsample = nn.Sequential(nn.Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
-            self.conv_up1 = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_before_upsample = nn.Sequential(Conv2d(embed_dim, num_feat, 3, 1, 1), nn.LeakyReLU(inplace=True))
+            self.conv_up1 = Conv2d(num_feat, num_feat, 3, 1, 1)
             if upscale == 4:
-                self.conv_up2 = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
-            self.conv_hr = nn.Conv2d(num_feat, num_feat, 3, 1, 1)
-            self.conv_last = nn.Conv2d(num_feat, in_chans, 3, 1, 1)
+                self.conv_up2 = Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_hr = Conv2d(num_feat, num_feat, 3, 1, 1)
+            self.conv_last = Conv2d(num_feat, in_chans, 3, 1, 1)
             self.lrelu = nn.LeakyReLU(0.2, inplace=True)
         else:
-            self.conv_last = nn.Conv2d(embed_dim, in_chans, 3, 1, 1)
+            self.conv_last = Conv2d(embed_dim, in_chans, 3, 1, 1)
         self.apply(self._init_weights)
+        self.resi_connection = resi_connection
+        self.phys_mode: Optional[bool] = None      # None: decide per call (CUDA 16-bit kernel path); True / False: force
+        self._phys: Optional[int] = None
+
+    # ---- physical width: an embed_dim that is not a multiple of 64 (the reference's 60, Stoke-DDP.py:206-208) runs with
+    # activations zero-padded to the next multiple of 64 from conv_first to the upsampler.  Only the (small) weights are
+    # padded — every activation is PRODUCED padded by the layer before it, so no pad / slice copy of an activation exists
+    # and every linear / convolution is inside the tcgen05 kernels' envelope (16-byte TMA rows, 64-channel K chunks).
+    def _phys_width(self, x: torch.Tensor) -> Optional[int]:
+        c = self.embed_dim
+        cp = (c + 63) // 64 * 64
+        ok = (c % 64 != 0 and c % 4 == 0 and (cp - c) * 8 <= c and not self.ape and self.resi_connection == "1conv"
+              and self.upsampler in ("pixelshuffle", "pixelshuffledirect", "nearest+conv"))
+        if not ok or self.phys_mode is False:
+            return None
+        if self.phys_mode:
+            return cp
+        from ..ops import dispatch
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled() else x.dtype
+        on = x.is_cuda and dt in (torch.float16, torch.bfloat16) and dispatch.enabled("pad") and dispatch.enabled("gemm") \
+            and dispatch.enabled("conv") and dispatch._lib_ok()
+        return cp if on else None
+
+    def _set_phys(self, cp: Optional[int]) -> None:
+        if cp == self._phys:
+            return
+        self._phys = cp
+        c = self.embed_dim
+        r8 = lambda v: (v + 7) // 8 * 8     # noqa: E731
+        self.conv_first.phys_out = cp
+        if self.patch_embed.norm is not None:
+            self.patch_embed.norm.phys = cp
+        self.norm.phys = cp
+        for rstb in self.layers:
+            rstb.conv.phys_in = rstb.conv.phys_out = cp
+            if rstb.patch_embed.norm is not None:
+                rstb.patch_embed.norm.phys = cp
+            for blk in rstb.residual_group.blocks:
+                hid = blk.mlp.fc1.out_features
+                blk.norm1.phys = blk.norm2.phys = cp
+                blk.attn.qkv.phys_in, blk.attn.qkv.phys_out = cp, (r8(3 * c) if cp else None)
+                blk.attn.proj.phys_in = blk.attn.proj.phys_out = cp
+                blk.mlp.fc1.phys_in, blk.mlp.fc1.phys_out = cp, (r8(hid) if cp else None)
+                blk.mlp.fc2.phys_in, blk.mlp.fc2.phys_out = (r8(hid) if cp else None), cp
+        self.conv_after_body.phys_in = self.conv_after_body.phys_out = cp
+        if self.upsampler == "pixelshuffledirect":
+            self.upsample[0].phys_in = cp
+            self.upsample[0].phys_out = r8(self.upsample[0].out_channels) if cp else None
+        else:
+            self.conv_before_upsample[0].phys_in = cp
 
     @staticmethod
     def _init_weights(m: nn.Module) -> None:
@@ -314,6 +425,7 @@ class SwinIR(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         H, W = x.shape[2:]
+        self._set_phys(self._phys_width(x))
         x = self.check_image_size(x)
         mean = self.mean.to(x.dtype)
         x = (x - mean) * self.img_range

@@ -179,6 +179,102 @@ def attention(qkv: torch.Tensor, heads: int, scale: Optional[float] = None, bias
     return _AttentionFn.apply(qkv, heads, float(scale if scale is not None else d ** -0.5), bias, mask)
 
 
+def window_attention_supported(qkv: torch.Tensor, heads: int, d: int, ws: int) -> bool:
+    """``window_attention`` on the tcgen05 kernels: CUDA fp16 / bf16 ``[B, Hi, Wi, P]`` projection (P >= 3 * heads * d,
+    even), windows of at most 64 tokens that tile the token grid, even head dimension <= 64."""
+    if not (qkv.is_cuda and qkv.dtype in _HALF and qkv.dim() == 4 and dispatch.enabled("attn") and dispatch._lib_ok()):
+        return False
+    _, Hi, Wi, P = qkv.shape
+    return (qkv.is_contiguous() and P >= 3 * heads * d and P % 2 == 0 and 0 < ws * ws <= 64 and Hi % ws == 0
+            and Wi % ws == 0 and 2 <= d <= 64 and d % 2 == 0)
+
+
+class _WindowAttentionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, heads, d, ws, shift, scale, bias, mask, out_pitch):  # type: ignore[override]
+        from .fused import DT
+        lib = require_library()
+        B, Hi, Wi, P = qkv.shape
+        S = ws * ws
+        nwin = B * (Hi // ws) * (Wi // ws)
+        # columns past heads * d of a padded output row stay zero
+        out = (torch.empty if out_pitch == heads * d else torch.zeros)((B, Hi, Wi, out_pitch), dtype=qkv.dtype, device=qkv.device)
+        lse = torch.empty((nwin, heads, S), dtype=torch.float32, device=qkv.device)
+        b32 = None if bias is None else bias.detach().float().contiguous()        # [H, S, S]
+        m32 = None if (mask is None or shift == 0) else mask.detach().float().contiguous()   # [windows per image, S, S]
+        check(lib.b200dp_window_attention_fwd(ptr(qkv), ptr(out), ptr(lse), ptr(b32), ptr(m32), B, Hi, Wi, ws, shift, heads, d,
+                                              P, out_pitch, ctypes.c_float(scale), DT[qkv.dtype], stream_ptr(qkv.device)),
+              "window_attention_fwd")
+        ctx.save_for_backward(qkv, out, lse, b32, m32)
+        ctx.geom = (B, Hi, Wi, P, heads, d, ws, shift, scale, out_pitch)
+        ctx.bias_dtype = None if bias is None else bias.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):  # type: ignore[override]
+        from .fused import DT
+        lib = require_library()
+        qkv, out, lse, b32, m32 = ctx.saved_tensors
+        B, Hi, Wi, P, H, d, ws, shift, scale, out_pitch = ctx.geom
+        S = ws * ws
+        if dout.dtype != qkv.dtype:
+            dout = dout.to(qkv.dtype)
+        if not dout.is_contiguous():
+            dout = dout.contiguous()
+        dqkv = (torch.empty_like if P == 3 * H * d else torch.zeros_like)(qkv)
+        dbias = None
+        if b32 is not None and ctx.needs_input_grad[6]:
+            dbias = torch.zeros((H, S, S), dtype=torch.float32, device=qkv.device)
+        check(lib.b200dp_window_attention_bwd(ptr(qkv), ptr(out), ptr(dout), ptr(lse), ptr(dqkv), ptr(b32), ptr(m32), ptr(dbias),
+                                              B, Hi, Wi, ws, shift, H, d, P, out_pitch, dout.shape[-1],
+                                              ctypes.c_float(scale), DT[qkv.dtype], stream_ptr(qkv.device)),
+              "window_attention_bwd")
+        if dbias is not None and dbias.dtype != ctx.bias_dtype:
+            dbias = dbias.to(ctx.bias_dtype)
+        return dqkv, None, None, None, None, None, dbias, None, None
+
+
+def window_attention(qkv: torch.Tensor, heads: int, d: int, ws: int, shift: int, scale: float,
+                     bias: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None,
+                     out_pitch: Optional[int] = None) -> torch.Tensor:
+    """(Shifted-)window attention on the image-ordered token grid, no partition / roll copies.
+
+    ``qkv [B, Hi, Wi, P]``: per token the packed projection (first ``3 * heads * d`` of its ``P`` elements, memory order
+    ``[3][heads][d]``; ``P`` may be padded).  The grid is cyclically shifted by ``-shift`` in both directions, cut into
+    ``ws x ws`` windows, ``softmax(q k^T * scale + bias + mask[window]) v`` runs per window and head, and the result goes
+    back to each token's own position: ``[B, Hi, Wi, out_pitch]`` (first ``heads * d`` elements; the rest zeros).
+    ``bias [heads, S, S]`` may require grad; ``mask [windows per image, S, S]`` is the shift mask (ignored when
+    ``shift == 0``).  Equivalent to the roll -> window_partition -> attention -> window_reverse -> roll chain of a Swin
+    block (Stoke-DDP.py:206-208 builds SwinIR with window_size 8).  Call ``window_attention_supported`` first."""
+    return _WindowAttentionFn.apply(qkv, heads, d, ws, shift, float(scale), bias, mask,
+                                    int(out_pitch) if out_pitch else heads * d)
+
+
+def window_attention_reference(qkv: torch.Tensor, heads: int, d: int, ws: int, shift: int, scale: float,
+                               bias: Optional[torch.Tensor] = None, mask: Optional[torch.Tensor] = None,
+                               out_pitch: Optional[int] = None, dropout_p: float = 0.0) -> torch.Tensor:
+    """Same contract with torch ops (CPU, shapes outside the envelope, attention dropout)."""
+    import torch.nn.functional as F
+    B, Hi, Wi, _ = qkv.shape
+    C3 = 3 * heads * d
+    x = qkv[..., :C3]
+    if shift > 0:
+        x = torch.roll(x, shifts=(-shift, -shift), dims=(1, 2))
+    xw = x.reshape(B, Hi // ws, ws, Wi // ws, ws, C3).permute(0, 1, 3, 2, 4, 5).reshape(-1, ws * ws, C3)
+    m = mask if shift > 0 else None
+    if attention_supported(xw, heads, bias) and dropout_p == 0.0:
+        o = attention(xw.contiguous(), heads, scale, bias, m)
+    else:
+        o = attention_reference(xw, heads, scale, bias, m, dropout_p=dropout_p)
+    C = heads * d
+    o = o.reshape(B, Hi // ws, Wi // ws, ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B, Hi, Wi, C)
+    if shift > 0:
+        o = torch.roll(o, shifts=(shift, shift), dims=(1, 2))
+    if out_pitch and out_pitch != C:
+        o = F.pad(o, (0, out_pitch - C))
+    return o
+
+
 def attention_reference(qkv: torch.Tensor, heads: int, scale: Optional[float] = None, bias: Optional[torch.Tensor] = None,
                         mask: Optional[torch.Tensor] = None, dropout_p: float = 0.0) -> torch.Tensor:
     """Same contract on the library kernel (shapes outside the envelope, CPU, attention dropout)."""

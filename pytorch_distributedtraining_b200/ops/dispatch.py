@@ -66,6 +66,48 @@ def ln_supported(mod: Any, x: torch.Tensor) -> bool:
     return x.dtype in _HALF + (torch.float32,) and ((d % 8 == 0 and d <= 8192) or (d % 4 == 0 and d <= 256)) and x.is_contiguous()
 
 
+def ln_phys_supported(mod: Any, x: torch.Tensor) -> bool:
+    """LayerNorm over the first d elements of zero-padded rows (``ops.layers.LayerNorm.phys``)."""
+    if not (enabled("ln") and _lib_ok()):
+        return False
+    if len(mod.normalized_shape) != 1 or mod.weight is None or mod.bias is None:
+        return False
+    d, p = mod.normalized_shape[0], x.shape[-1]
+    return (x.dtype in _HALF + (torch.float32,) and d % 4 == 0 and p % 4 == 0 and d <= p <= 256 and x.is_contiguous())
+
+
+def linear_phys_supported(w: torch.Tensor, x: torch.Tensor) -> bool:
+    """A linear whose (already zero-padded) weight is inside the tcgen05 GEMM envelope."""
+    if not (enabled("gemm") and _lib_ok()):
+        return False
+    from . import gemm
+    if not gemm.available():
+        return False
+    return _autocast_dtype(x) in _HALF and w.shape[0] % 8 == 0 and w.shape[1] % 8 == 0 and x.shape[-1] == w.shape[1]
+
+
+def conv_phys_supported(mod: Any, x: torch.Tensor, cin: int, cout: int) -> bool:
+    """A convolution with zero-padded filters (``ops.layers.Conv2d.phys_in`` / ``phys_out``) inside the implicit-GEMM
+    envelope: NHWC 16-bit compute, Cin % 64 == 0 (first layers: Cin <= 4), Cout % 8 == 0."""
+    if not (enabled("conv") and _lib_ok()):
+        return False
+    from . import conv
+    if not conv.available():
+        return False
+    dt = _autocast_dtype(x)
+    if dt not in _HALF or mod.groups != 1 or mod.dilation != (1, 1) or mod.padding_mode != "zeros" or x.dim() != 4:
+        return False
+    if x.shape[1] != cin or cout % 8 != 0:
+        return False
+    sq = (mod.stride[0] == mod.stride[1] and mod.stride[0] in (1, 2) and mod.padding[0] == mod.padding[1]
+          and isinstance(mod.padding[0], int) and x.shape[2] + 2 * mod.padding[0] >= mod.kernel_size[0])
+    if cin <= 4:
+        return (enabled("conv_first") and sq and mod.kernel_size[0] <= 7 and mod.kernel_size[1] <= 7 and cout <= 64)
+    if mod.kernel_size == (1, 1) and mod.stride == (1, 1) and mod.padding == (0, 0):
+        return cin % 8 == 0
+    return sq and cin % 64 == 0 and x.is_contiguous(memory_format=torch.channels_last)
+
+
 def linear_supported(mod: Any, x: torch.Tensor) -> bool:
     """tcgen05 GEMM envelope: fp16/bf16 compute (directly or under autocast), in/out features % 8 == 0
     (16-byte TMA row pitches); ragged M/N/K tile edges are handled in the kernel."""

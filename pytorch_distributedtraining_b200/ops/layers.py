@@ -28,8 +28,25 @@ class Conv2d(nn.Conv2d):
     # set by ``pair_conv_bn``: a BatchNormAct2d consumes this layer's output directly, so in training
     # the convolution's epilogue also emits the batch statistics that layer needs
     emit_bn_stats: bool = False
+    # "physical" channel counts (set by a model that keeps its activations zero-padded to a tensor-core friendly width,
+    # e.g. SwinIR-S 60 -> 64): the input then HAS phys_in channels (extras are zeros) and the output is produced with
+    # phys_out channels (extras are zeros) — only the small filters are padded, never an activation
+    phys_in: Optional[int] = None
+    phys_out: Optional[int] = None
+
+    def _forward_phys(self, x: torch.Tensor) -> torch.Tensor:
+        cin, cout = self.in_channels, self.out_channels
+        pi, po = self.phys_in or cin, self.phys_out or cout
+        w = F.pad(self.weight, (0, 0, 0, 0, 0, pi - cin, 0, po - cout)) if (pi != cin or po != cout) else self.weight
+        b = None if self.bias is None else (F.pad(self.bias, (0, po - cout)) if po != cout else self.bias)
+        if x.is_cuda and dispatch.conv_phys_supported(self, x, pi, po):
+            from . import conv as _conv
+            return _conv.conv2d(x, w, b, self.stride, self.padding, self.dilation, self.groups)
+        return F.conv2d(x, w, b, self.stride, self.padding, self.dilation, self.groups)
 
     def forward(self, x: torch.Tensor, carry: bool = False):
+        if (self.phys_in or self.phys_out) and not carry:
+            return self._forward_phys(x)
         if x.is_cuda and dispatch.conv_supported(self, x):
             from . import conv as _conv
             emit = self.emit_bn_stats and self.training and torch.is_grad_enabled() and dispatch.enabled("bn") \
@@ -73,9 +90,32 @@ class Linear(nn.Linear):
                  device=None, dtype=None):
         super().__init__(in_features, out_features, bias, device=device, dtype=dtype)
         self.act = act
+        # physical widths, as for Conv2d: the input has phys_in features (extras are zeros), the output phys_out
+        self.phys_in: Optional[int] = None
+        self.phys_out: Optional[int] = None
+
+    def padded_params(self):
+        """Weight / bias zero-padded to the physical widths (autograd slices the gradients back)."""
+        k, n = self.in_features, self.out_features
+        kp, np_ = self.phys_in or k, self.phys_out or n
+        w = F.pad(self.weight, (0, kp - k, 0, np_ - n)) if (kp != k or np_ != n) else self.weight
+        b = None if self.bias is None else (F.pad(self.bias, (0, np_ - n)) if np_ != n else self.bias)
+        return w, b
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
         """``act(x W^T + b) (+ residual)``; on the kernel path the residual add is part of the GEMM epilogue."""
+        if self.phys_in or self.phys_out:
+            w, b = self.padded_params()
+            if x.is_cuda and dispatch.linear_phys_supported(w, x):
+                from . import gemm as _gemm
+                return _gemm.linear(x, w, b, act=self.act, residual=residual)
+            y = F.linear(x, w.to(x.dtype) if w.dtype != x.dtype and not torch.is_autocast_enabled() else w,
+                         None if b is None else (b.to(x.dtype) if b.dtype != x.dtype and not torch.is_autocast_enabled() else b))
+            if self.act == "gelu":
+                y = F.gelu(y)
+            elif self.act == "relu":
+                y = F.relu(y)
+            return y if residual is None else y + residual
         if x.is_cuda and dispatch.linear_supported(self, x):
             from . import gemm as _gemm
             return _gemm.linear(x, self.weight, self.bias, act=self.act, residual=residual)
@@ -145,7 +185,20 @@ def pair_conv_bn(model: nn.Module) -> int:
 
 
 class LayerNorm(nn.LayerNorm):
+    # physical row width (see Conv2d.phys_in): rows of the input are `phys` wide, the first normalized_shape[0] elements
+    # are normalised and the rest of the output row is zeros
+    phys: Optional[int] = None
+
+    def _forward_phys(self, x: torch.Tensor) -> torch.Tensor:
+        d = self.normalized_shape[0]
+        if x.is_cuda and dispatch.ln_phys_supported(self, x):
+            from . import norm as _norm
+            return _norm.layer_norm(x, self.weight, self.bias, self.eps, logical=d)
+        return F.pad(F.layer_norm(x[..., :d], (d,), self.weight, self.bias, self.eps), (0, x.shape[-1] - d))
+
     def forward(self, x: torch.Tensor, carry: bool = False):
+        if self.phys and self.phys != self.normalized_shape[0] and not carry:
+            return self._forward_phys(x)
         if x.is_cuda and dispatch.ln_supported(self, x):
             from . import norm as _norm
             return _norm.layer_norm(x, self.weight, self.bias, self.eps, carry=carry)

@@ -147,7 +147,9 @@ def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) 
 
 class _LayerNormFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, eps, carry=False):  # type: ignore[override]
+    def forward(ctx, x, weight, bias, eps, carry=False, logical=0):  # type: ignore[override]
+        """``logical``: when non-zero, rows of ``x`` are ``x.shape[-1]`` elements apart but only the first
+        ``logical`` of them are normalised (zero-padded rows, e.g. 60 -> 64); the padding of ``y`` / ``dx`` is zeros."""
         lib = require_library()
         # parameters arrive in their own dtype (bf16 under FSDP mixed precision); the kernels read fp32.  Casting
         # here instead of in the caller keeps autograd from adding one cast-backward kernel per parameter.
@@ -162,9 +164,16 @@ class _LayerNormFn(torch.autograd.Function):
         y = torch.empty_like(x2)
         mean = torch.empty(rows, dtype=torch.float32, device=x.device)
         rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
-        check(lib.b200dp_layernorm_fwd(ptr(x2), ptr(y), ctypes.c_int64(rows), ctypes.c_int(D), ctypes.c_int(DT[x.dtype]),
-                                       ptr(weight), ptr(bias), ctypes.c_float(eps), ptr(mean), ptr(rstd),
-                                       stream_ptr(x.device)), "layernorm_fwd")
+        ctx.logical = int(logical) if logical and int(logical) != D else 0
+        if ctx.logical:
+            check(lib.b200dp_layernorm_fwd_pitched(ptr(x2), ptr(y), ctypes.c_int64(rows), ctypes.c_int(ctx.logical),
+                                                   ctypes.c_int(D), ctypes.c_int(DT[x.dtype]), ptr(weight), ptr(bias),
+                                                   ctypes.c_float(eps), ptr(mean), ptr(rstd), stream_ptr(x.device)),
+                  "layernorm_fwd_pitched")
+        else:
+            check(lib.b200dp_layernorm_fwd(ptr(x2), ptr(y), ctypes.c_int64(rows), ctypes.c_int(D), ctypes.c_int(DT[x.dtype]),
+                                           ptr(weight), ptr(bias), ctypes.c_float(eps), ptr(mean), ptr(rstd),
+                                           stream_ptr(x.device)), "layernorm_fwd")
         ctx.save_for_backward(x2, weight, mean, rstd)
         ctx.shape = shape
         if carry:
@@ -192,6 +201,18 @@ class _LayerNormFn(torch.autograd.Function):
                 add_in = add_in.contiguous()
         dx = torch.empty_like(x2)
         ws = Workspace.get(x2.device)
+        if ctx.logical:
+            P, D = D, ctx.logical
+            scratch = ws.scratch(int(lib.b200dp_ln_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(D))))
+            dparams = torch.empty(2 * D, dtype=torch.float32, device=x2.device)  # [dbeta | dgamma]
+            check(lib.b200dp_layernorm_bwd_pitched(ptr(dy2), ptr(x2), ptr(dx), ctypes.c_int64(rows), ctypes.c_int(D),
+                                                   ctypes.c_int(P), ctypes.c_int(DT[x2.dtype]), ptr(weight), ptr(mean),
+                                                   ptr(rstd), ptr(scratch), ptr(ws.counters), ptr(dparams[D:]),
+                                                   ptr(dparams[:D]), ptr(add_in), stream_ptr(x2.device)),
+                  "layernorm_bwd_pitched", launches=2)
+            if dparams.dtype != ctx.p_dtype:
+                dparams = dparams.to(ctx.p_dtype)
+            return dx.view(ctx.shape), dparams[D:], dparams[:D], None, None, None
         scratch = ws.scratch(int(lib.b200dp_ln_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(D))))
         dparams = torch.empty(2 * D, dtype=torch.float32, device=x2.device)  # [dbeta | dgamma]
         check(lib.b200dp_layernorm_bwd_add(ptr(dy2), ptr(x2), ptr(dx), ctypes.c_int64(rows), ctypes.c_int(D),
@@ -201,9 +222,11 @@ class _LayerNormFn(torch.autograd.Function):
               "layernorm_bwd", launches=2)
         if dparams.dtype != ctx.p_dtype:
             dparams = dparams.to(ctx.p_dtype)           # one cast for both parameter gradients
-        return dx.view(ctx.shape), dparams[D:], dparams[:D], None, None
+        return dx.view(ctx.shape), dparams[D:], dparams[:D], None, None, None
 
 
-def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float, carry: bool = False):
-    """``carry=True`` returns ``(LN(x), x)``: use the second value as the residual that bypasses the block."""
-    return _LayerNormFn.apply(x, weight, bias, eps, carry)
+def layer_norm(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor, eps: float, carry: bool = False,
+               logical: int = 0):
+    """``carry=True`` returns ``(LN(x), x)``: use the second value as the residual that bypasses the block.
+    ``logical``: normalise only the first ``logical`` elements of zero-padded rows (see ``_LayerNormFn.forward``)."""
+    return _LayerNormFn.apply(x, weight, bias, eps, carry, logical)

@@ -66,6 +66,62 @@ def test_attention_matches_fp32_reference(B, H, S, d, with_bias, nW, dtype):
         assert err <= gtol * max(1.0, b32.grad.abs().max().item()), err
 
 
+WIN_CASES = [
+    # images, Hi, Wi, ws, shift, heads, d, qkv pitch pad, out pitch pad, dtype
+    (3, 16, 24, 8, 0, 6, 10, 0, 0, torch.bfloat16),        # SwinIR-S block, plain windows
+    (3, 16, 24, 8, 4, 6, 10, 4, 4, torch.bfloat16),        # shifted windows + mask, rows zero-padded 180 -> 184 / 60 -> 64
+    (2, 64, 64, 8, 4, 6, 10, 4, 4, torch.bfloat16),        # the bench geometry
+    (1, 14, 21, 7, 3, 4, 32, 0, 0, torch.float16),         # 7 x 7 windows, odd window count
+    (5, 8, 8, 8, 0, 2, 16, 8, 0, torch.float16),           # one window per image
+]
+
+
+@pytest.mark.parametrize("B,Hi,Wi,ws,shift,H,d,qpad,opad,dtype", WIN_CASES)
+def test_window_attention_matches_roll_partition_reference(B, Hi, Wi, ws, shift, H, d, qpad, opad, dtype):
+    """Window attention addressed on the image grid (no roll / partition copies) against the fp32 chain
+    roll -> window_partition -> softmax(q k^T * scale + bias + mask) v -> window_reverse -> roll."""
+    from pytorch_distributedtraining_b200.ops.attention import window_attention, window_attention_supported
+    g = torch.Generator(device="cpu").manual_seed(Hi * 100 + Wi + d)
+    C, S = H * d, ws * ws
+    P, OP = 3 * C + qpad, C + opad
+    qkv = torch.randn(B, Hi, Wi, P, generator=g).to(cuda).to(dtype).requires_grad_(True)
+    bias = (torch.randn(H, S, S, generator=g) * 0.5).to(cuda).requires_grad_(True)
+    nW = (Hi // ws) * (Wi // ws)
+    mask = None
+    if shift:
+        mask = torch.where(torch.rand(nW, S, S, generator=g) < 0.2, -100.0, 0.0).to(cuda)
+        mask[:, torch.arange(S), torch.arange(S)] = 0.0
+    scale = d ** -0.5
+    assert window_attention_supported(qkv, H, d, ws)
+    out = window_attention(qkv, H, d, ws, shift, scale, bias, mask, OP)
+    assert out.shape == (B, Hi, Wi, OP)
+    if opad:
+        assert (out[..., C:] == 0).all()
+    dout = torch.randn(B, Hi, Wi, OP, generator=g).to(cuda).to(dtype)
+    out.backward(dout)
+    dq, db = qkv.grad.clone(), bias.grad.clone()
+    if qpad:
+        assert (dq[..., 3 * C:] == 0).all()
+
+    q32 = qkv.detach().float().requires_grad_(True)
+    b32 = bias.detach().float().clone().requires_grad_(True)
+    x = q32[..., :3 * C]
+    if shift:
+        x = torch.roll(x, shifts=(-shift, -shift), dims=(1, 2))
+    xw = x.reshape(B, Hi // ws, ws, Wi // ws, ws, 3 * C).permute(0, 1, 3, 2, 4, 5).reshape(-1, S, 3 * C)
+    o = _reference(xw, H, scale, b32, mask)
+    o = o.reshape(B, Hi // ws, Wi // ws, ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B, Hi, Wi, C)
+    if shift:
+        o = torch.roll(o, shifts=(shift, shift), dims=(1, 2))
+    o.backward(dout.float()[..., :C])
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+    torch.testing.assert_close(out.float()[..., :C], o, rtol=tol, atol=tol)
+    gtol = 4e-2 if dtype == torch.bfloat16 else 8e-3
+    torch.testing.assert_close(dq.float(), q32.grad, rtol=gtol, atol=gtol * max(1.0, float(q32.grad.abs().max())) * 0.25)
+    err = (db.float() - b32.grad).abs().max().item()
+    assert err <= gtol * max(1.0, b32.grad.abs().max().item()), err
+
+
 def test_attention_twice_is_bit_identical_and_graph_capturable():
     from pytorch_distributedtraining_b200.ops.attention import attention
     qkv = torch.randn(8, 197, 3 * 12 * 64, device=cuda).bfloat16()

@@ -229,6 +229,35 @@ def test_layernorm_matches_torch(dtype, rows, D):
     torch.testing.assert_close(ln.bias.grad, ref.bias.grad, rtol=tol * 10, atol=tol * 4 * math.sqrt(rows))
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("rows,D,P", [(4099, 60, 64), (77, 180, 192), (9, 4, 8), (300, 60, 60)])
+def test_layernorm_on_zero_padded_rows(dtype, rows, D, P):
+    """LayerNorm over the first D elements of rows that are P wide (``LayerNorm.phys``): statistics over D only, padding
+    of the output and of the input gradient comes out as zeros."""
+    from pytorch_distributedtraining_b200.ops.layers import LayerNorm
+    torch.manual_seed(3)
+    ln = LayerNorm(D, eps=1e-5).to(cuda)
+    ln.phys = P
+    with torch.no_grad():
+        ln.weight.uniform_(0.5, 1.5); ln.bias.uniform_(-0.5, 0.5)
+    ref = copy.deepcopy(ln)
+    x = torch.randn(rows, P, device=cuda).to(dtype)
+    x[:, D:] = 0
+    x.requires_grad_(True)
+    xr = x.detach().float()[:, :D].clone().requires_grad_(True)
+    y = ln(x)
+    yr = F.layer_norm(xr, (D,), ref.weight, ref.bias, 1e-5)
+    tol = {torch.float32: 1e-5, torch.bfloat16: 3e-2}[dtype]
+    torch.testing.assert_close(y.float()[:, :D], yr, rtol=tol, atol=tol)
+    assert (y[:, D:] == 0).all()
+    g = torch.randn(rows, P, device=cuda).to(dtype)
+    y.backward(g); yr.backward(g.float()[:, :D])
+    torch.testing.assert_close(x.grad.float()[:, :D], xr.grad, rtol=tol * 4, atol=tol * 4)
+    assert (x.grad[:, D:] == 0).all()
+    torch.testing.assert_close(ln.weight.grad, ref.weight.grad, rtol=tol * 10, atol=tol * 4 * math.sqrt(rows))
+    torch.testing.assert_close(ln.bias.grad, ref.bias.grad, rtol=tol * 10, atol=tol * 4 * math.sqrt(rows))
+
+
 def test_resnet18_fused_path_matches_stock_ops():
     """Whole-model check: the fused BN/ReLU/CE path must be as close to an fp32 reference as
     the same model on stock torch fp16 ops is (both carry fp16 rounding; neither is exact)."""

@@ -226,3 +226,37 @@ def test_facade_starts_the_step_watchdog_on_request():
     s2 = Stoke(model=nn.Linear(4, 2), verbose=False, optimizer=StokeOptimizer(optimizer=torch.optim.SGD, optimizer_kwargs={"lr": 0.1}),
                loss=nn.MSELoss(), batch_size_per_device=2, gpu=False)
     assert s2.watchdog is None
+
+
+def test_swinir_grid_attention_and_physical_widths_match_the_roll_partition_blocks():
+    """SwinIR's image-ordered blocks (window attention by addressing, projections on the whole grid) with activations
+    zero-padded 60 -> 64 ("physical" widths) against the classic roll -> window_partition -> attention ->
+    window_reverse -> roll blocks on the logical widths: same output, same gradients (fp64, CPU)."""
+    import copy
+    from pytorch_distributedtraining_b200 import models
+    torch.manual_seed(0)
+    m = models.SwinIR(upscale=2, in_chans=3, img_size=16, window_size=8, img_range=1., depths=[2, 2], embed_dim=60,
+                      num_heads=[6, 6], mlp_ratio=2, upsampler="pixelshuffledirect", resi_connection="1conv",
+                      drop_path_rate=0.0).double()
+    for p in m.parameters():
+        if p.dim() == 2 and p.shape[1] == 6:
+            torch.nn.init.normal_(p, std=0.5)           # relative-position bias tables: make them matter
+    legacy = copy.deepcopy(m)
+    for mod in legacy.modules():
+        if hasattr(mod, "legacy_block"):
+            mod.legacy_block = True
+    m.train(); legacy.train()
+    m.phys_mode, legacy.phys_mode = True, False
+    x = torch.rand(2, 3, 16, 24, dtype=torch.double)
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    y1, y2 = m(x1), legacy(x2)
+    assert m._phys == 64 and legacy._phys is None
+    torch.testing.assert_close(y1, y2, rtol=1e-10, atol=1e-12)
+    y1.square().sum().backward(); y2.square().sum().backward()
+    torch.testing.assert_close(x1.grad, x2.grad, rtol=1e-9, atol=1e-11)
+    for (n, p), (_, q) in zip(m.named_parameters(), legacy.named_parameters()):
+        torch.testing.assert_close(p.grad, q.grad, rtol=1e-8, atol=1e-10, msg=n)
+    # switching the mode off again restores the logical widths everywhere
+    m.phys_mode = False
+    torch.testing.assert_close(m(x), y2.detach(), rtol=1e-10, atol=1e-12)
+    assert m.conv_first.phys_out is None and m.layers[0].residual_group.blocks[0].attn.qkv.phys_out is None
