@@ -117,6 +117,50 @@ __global__ void __launch_bounds__(kBNThreads, 4) bn_reduce_kernel(const T* __res
     bn_reduce_tail(s, q, C, cgb, rpb, rl, cgl, cg, active, scratch, counters, sums);
 }
 
+// Column sums only (bias gradients of linear layers): per-CTA partials [gridDim.y][C]; ln_partials_reduce_kernel sums
+// them.  A transformer's bias gradients are many SMALL reductions (tens of MB): the single-CTA tail of the moment
+// kernel above (one CTA walking ~600 partials) costs more than streaming the data, so this pair keeps the partial count
+// low (>= 16 rows per thread) and spreads the second stage over several CTAs.
+template <typename T>
+__global__ void __launch_bounds__(kBNThreads, 4) colsum_kernel(const T* __restrict__ x, int64_t rows, int C, int tpr,
+                                                            int cgb, int rpb, float* __restrict__ scratch) {
+    __shared__ float sm[kBNThreads * 8];
+    const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
+    const int cg = blockIdx.x * cgb + cgl;
+    const bool active = rl < rpb && cg < tpr;
+    const int nch = cgb * 8;
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (active) {
+        const int64_t rstep = (int64_t)gridDim.y * rpb;
+        const T* xp = x + (int64_t)cg * 8;
+        int64_t r = (int64_t)blockIdx.y * rpb + rl;
+        for (; r + 3 * rstep < rows; r += 4 * rstep) {
+            float v0[8], v1[8], v2[8], v3[8];
+            load8<T>(xp + r * C, v0);
+            load8<T>(xp + (r + rstep) * C, v1);
+            load8<T>(xp + (r + 2 * rstep) * C, v2);
+            load8<T>(xp + (r + 3 * rstep) * C, v3);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s[k] += (v0[k] + v1[k]) + (v2[k] + v3[k]);
+        }
+        for (; r < rows; r += rstep) {
+            float v[8];
+            load8<T>(xp + r * C, v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s[k] += v[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) sm[rl * nch + cgl * 8 + k] = s[k];
+    }
+    __syncthreads();
+    const int c0 = blockIdx.x * nch;
+    if ((int)threadIdx.x < nch && c0 + (int)threadIdx.x < C) {
+        float t = 0.f;
+        for (int r = 0; r < rpb; ++r) t += sm[r * nch + threadIdx.x];
+        scratch[(int64_t)blockIdx.y * C + c0 + threadIdx.x] = t;
+    }
+}
+
 template <typename T, bool kTrain>
 __global__ void __launch_bounds__(kBNThreads, 3) bn_apply_kernel(
     const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, int64_t rows, int C, int tpr, int cgb,
@@ -666,6 +710,118 @@ __global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwd4_kernel(
     for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) mine[i] = red[i];
 }
 
+// ---- short rows (pitch % 8 == 0, pitch <= 256; D <= pitch, any D): LPR = 8 / 16 / 32 lanes per row, 32 / LPR rows per
+//      warp, every lane owns ONE 8-element chunk (a 16-byte access for 16-bit data).  A 60- or 64-wide row keeps all
+//      32 lanes of a warp busy on four rows instead of 8 - 15 lanes on one.  Columns D .. pitch are written as zeros.
+template <int LPR>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <typename T, int LPR>
+__global__ void __launch_bounds__(kLNWarps * 32) layernorm_fwdR_kernel(
+    const T* __restrict__ x, T* __restrict__ y, int64_t rows, int D, int pitch, const float* __restrict__ gamma,
+    const float* __restrict__ beta, float eps, float* __restrict__ mean, float* __restrict__ rstd) {
+    constexpr int RPW = 32 / LPR;
+    const int lane = threadIdx.x & 31, sub = lane / LPR, li = lane % LPR;
+    const int64_t row = ((int64_t)blockIdx.x * kLNWarps + (threadIdx.x >> 5)) * RPW + sub;
+    const int c0 = li * 8;
+    const bool live = row < rows && c0 < pitch;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (live) load8<T>(x + row * pitch + c0, v);
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { if (c0 + k >= D) v[k] = 0.f; s += v[k]; }
+    const float mu = group_sum<LPR>(s) / D;
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { const float d = c0 + k < D ? v[k] - mu : 0.f; q += d * d; }
+    const float rs = rsqrtf(group_sum<LPR>(q) / D + eps);
+    if (li == 0 && row < rows) { mean[row] = mu; rstd[row] = rs; }
+    if (live) {
+        float o[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) o[k] = c0 + k < D ? (v[k] - mu) * rs * __ldg(gamma + c0 + k) + __ldg(beta + c0 + k) : 0.f;
+        store8<T>(y + row * pitch + c0, o);
+    }
+}
+
+template <typename T, int LPR>
+__global__ void __launch_bounds__(kLNWarps * 32, 3) layernorm_bwdR_kernel(
+    const T* __restrict__ dy, const T* __restrict__ x, T* __restrict__ dx, int64_t rows, int D, int pitch,
+    const float* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
+    float* __restrict__ scratch, const T* __restrict__ add_in) {
+    constexpr int RPW = 32 / LPR;
+    __shared__ float red[2 * 256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane / LPR, li = lane % LPR;
+    const int c0 = li * 8;
+    const bool col_live = c0 < pitch;
+    float ga[8], pa[8], pb[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { ga[k] = c0 + k < D ? __ldg(gamma + c0 + k) : 0.f; pa[k] = 0.f; pb[k] = 0.f; }
+    const int64_t groups = (rows + RPW - 1) / RPW;
+    for (int64_t grp = (int64_t)blockIdx.x * kLNWarps + warp; grp < groups; grp += (int64_t)gridDim.x * kLNWarps) {
+        const int64_t row = grp * RPW + sub;
+        const bool live = row < rows && col_live;
+        float d[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, xv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, av[8];
+        float mu = 0.f, rs = 0.f;
+        if (live) {
+            load8<T>(dy + row * pitch + c0, d);
+            load8<T>(x + row * pitch + c0, xv);
+            if (add_in != nullptr) load8<T>(add_in + row * pitch + c0, av);
+        }
+        if (row < rows) { mu = mean[row]; rs = rstd[row]; }
+        float c1 = 0.f, c2 = 0.f, xh[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const bool in = live && c0 + k < D;
+            if (!in) d[k] = 0.f;
+            xh[k] = in ? (xv[k] - mu) * rs : 0.f;
+            const float g = d[k] * ga[k];
+            c1 += g * xh[k]; c2 += g;
+            pa[k] += d[k]; pb[k] += d[k] * xh[k];
+        }
+        c1 = group_sum<LPR>(c1) / D;
+        c2 = group_sum<LPR>(c2) / D;
+        if (live) {
+            float o[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                float r = c0 + k < D ? rs * (d[k] * ga[k] - c2 - xh[k] * c1) : 0.f;
+                if (add_in != nullptr && c0 + k < D) r += av[k];
+                o[k] = r;
+            }
+            store8<T>(dx + row * pitch + c0, o);
+        }
+    }
+    // lanes that own the same columns (the warp's RPW rows), then the CTA's warps in a fixed order
+#pragma unroll
+    for (int o = LPR; o < 32; o <<= 1) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            pa[k] += __shfl_xor_sync(0xffffffffu, pa[k], o);
+            pb[k] += __shfl_xor_sync(0xffffffffu, pb[k], o);
+        }
+    }
+    for (int w = 0; w < kLNWarps; ++w) {
+        if (warp == w && sub == 0) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const int c = c0 + k;
+                if (c < D) {
+                    red[c] = (w == 0 ? 0.f : red[c]) + pa[k];
+                    red[D + c] = (w == 0 ? 0.f : red[D + c]) + pb[k];
+                }
+            }
+        }
+        __syncthreads();
+    }
+    float* mine = scratch + (size_t)blockIdx.x * 2 * D;
+    for (int i = threadIdx.x; i < 2 * D; i += blockDim.x) mine[i] = red[i];
+}
+
 // out[c] = sum over the CTA partials of column c, in a fixed order: 32 columns x 8 partial slices per CTA
 __global__ void __launch_bounds__(256) ln_partials_reduce_kernel(const float* __restrict__ scratch, int parts, int cols,
                                                                  float* __restrict__ out) {
@@ -704,7 +860,34 @@ using namespace b200dp;
     const dim3 grid(g.gx, g.gy);                                                                     \
     cudaStream_t s = (cudaStream_t)stream;
 
+static inline BNGeom colsum_geom(int64_t rows, int C) {
+    BNGeom g = bn_geom(rows, C, 2);
+    int64_t maxy = rows / ((int64_t)g.rpb * 16);          // >= 16 rows per thread: few partials
+    if (maxy < 1) maxy = 1;
+    if (g.gy > maxy) g.gy = (int)maxy;
+    return g;
+}
+
 extern "C" {
+
+int64_t b200dp_column_sums_scratch_floats(int64_t rows, int C) {
+    if (rows <= 0 || C <= 0 || C % 8) return 0;
+    return (int64_t)colsum_geom(rows, C).gy * C;
+}
+
+// out[C] (fp32) = column sums of the 16-bit / fp32 matrix x[rows][C] (C % 8 == 0); scratch: b200dp_column_sums_scratch_floats.
+int b200dp_column_sums(const void* x, int64_t rows, int C, b200dp_dtype dtype, float* scratch, float* out, void* stream) {
+    B200DP_REQUIRE(x && scratch && out, "column_sums: null argument");
+    B200DP_REQUIRE(rows > 0 && C > 0 && C % 8 == 0, "column_sums: C must be a positive multiple of 8");
+    const BNGeom g = colsum_geom(rows, C);
+    cudaStream_t s = (cudaStream_t)stream;
+    B200DP_DISPATCH_DTYPE(dtype, T, {
+        colsum_kernel<T><<<dim3(g.gx, g.gy), kBNThreads, 0, s>>>((const T*)x, rows, C, g.tpr, g.cgb, g.rpb, scratch);
+    });
+    ln_partials_reduce_kernel<<<(C + 31) / 32, 256, 0, s>>>(scratch, g.gy, C, out);
+    B200DP_CHECK_LAUNCH();
+    return 0;
+}
 
 int64_t b200dp_bn_scratch_floats(int64_t rows, int C) {
     if (rows <= 0 || C <= 0 || C % 8) return 0;
@@ -801,6 +984,18 @@ int64_t b200dp_ln_scratch_floats(int64_t rows, int D) { return rows <= 0 || D <=
 
 static int layernorm_fwd4(const void* x, void* y, int64_t rows, int D, int pitch, b200dp_dtype dtype, const float* gamma,
                           const float* beta, float eps, float* mean, float* rstd, void* stream) {
+    if (pitch % 8 == 0) {                // several rows per warp, 16-byte accesses
+#define LNR(LPR_)                                                                                                      \
+        {                                                                                                              \
+            const unsigned nb = (unsigned)((rows + kLNWarps * (32 / LPR_) - 1) / (kLNWarps * (32 / LPR_)));            \
+            B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwdR_kernel<T, LPR_><<<nb, kLNWarps * 32, 0, (cudaStream_t)stream>>>( \
+                (const T*)x, (T*)y, rows, D, pitch, gamma, beta, eps, mean, rstd); });                                 \
+        }
+        if (pitch <= 64) LNR(8) else if (pitch <= 128) LNR(16) else LNR(32)
+#undef LNR
+        B200DP_CHECK_LAUNCH();
+        return 0;
+    }
     const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
     if (pitch <= 128) {
         B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_fwd4_kernel<T, 1><<<blocks, kLNWarps * 32, 0, (cudaStream_t)stream>>>(
@@ -827,7 +1022,7 @@ int b200dp_layernorm_fwd(const void* x, void* y, int64_t rows, int D, b200dp_dty
                          const float* beta, float eps, float* mean, float* rstd, void* stream) {
     B200DP_REQUIRE(x && y && gamma && beta && mean && rstd, "layernorm_fwd: null argument");
     const unsigned blocks = (unsigned)((rows + kLNWarps - 1) / kLNWarps);
-    if (rows > 0 && D % 8 != 0 && D % 4 == 0 && D <= 256)        // narrow rows: 4-element vectors
+    if (rows > 0 && D % 4 == 0 && D <= 256)                      // short rows: several per warp / 4-element vectors
         return layernorm_fwd4(x, y, rows, D, D, dtype, gamma, beta, eps, mean, rstd, stream);
     B200DP_REQUIRE(rows > 0 && D % 8 == 0 && D <= kLNMaxChunks * 256, "layernorm_fwd: D must be a multiple of 8 (or of 4 up to 256), <= %d",
                    kLNMaxChunks * 256);
@@ -848,8 +1043,22 @@ static int layernorm_bwd_impl(const void* dy, const void* x, void* dx, int64_t r
     B200DP_REQUIRE(dgamma == dbeta + D, "layernorm_bwd: dbeta and dgamma must be one buffer [dbeta(D) | dgamma(D)]");
     cudaStream_t s = (cudaStream_t)stream;
     const unsigned grid = ln_bwd_grid(rows);
-    if (rows > 0 && (pitch > 0 || (D % 8 != 0 && D % 4 == 0 && D <= 256))) {      // narrow rows: 4-element vectors
+    if (rows > 0 && (pitch > 0 || (D % 4 == 0 && D <= 256))) {      // short rows: several per warp / 4-element vectors
         if (pitch <= 0) pitch = D;
+        if (pitch % 8 == 0) {
+#define LNR(LPR_)                                                                                                      \
+            {                                                                                                          \
+                const int64_t want = ((rows + (32 / LPR_) - 1) / (32 / LPR_) + kLNWarps - 1) / kLNWarps;               \
+                const unsigned gr = (unsigned)(want < (int64_t)grid ? want : (int64_t)grid);                           \
+                B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_bwdR_kernel<T, LPR_><<<gr, kLNWarps * 32, 0, s>>>(         \
+                    (const T*)dy, (const T*)x, (T*)dx, rows, D, pitch, gamma, mean, rstd, scratch, (const T*)add_in); }); \
+                ln_partials_reduce_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(scratch, (int)gr, 2 * D, dbeta);           \
+            }
+            if (pitch <= 64) LNR(8) else if (pitch <= 128) LNR(16) else LNR(32)
+#undef LNR
+            B200DP_CHECK_LAUNCH();
+            return 0;
+        }
         if (pitch <= 128) {
             B200DP_DISPATCH_DTYPE(dtype, T, { layernorm_bwd4_kernel<T, 1><<<grid, kLNWarps * 32, 0, s>>>(
                 (const T*)dy, (const T*)x, (T*)dx, rows, D, gamma, mean, rstd, scratch, (const T*)add_in, pitch); });

@@ -208,6 +208,11 @@ int b200dp_layernorm_bwd(const void* dy, const void* x, void* dx, int64_t rows, 
 int b200dp_layernorm_bwd_add(const void* dy, const void* x, void* dx, int64_t rows, int D, b200dp_dtype dtype,
                              const float* gamma, const float* mean, const float* rstd, float* scratch,
                              unsigned int* counter, float* dgamma, float* dbeta, const void* add_in, void* stream);
+/* out[C] (fp32) = column sums of x[rows][C] (C % 8 == 0): the bias gradient of a linear layer.  Two small launches
+ * (per-CTA partials, then a multi-CTA second stage); scratch holds b200dp_column_sums_scratch_floats(rows, C) floats. */
+int64_t b200dp_column_sums_scratch_floats(int64_t rows, int C);
+int b200dp_column_sums(const void* x, int64_t rows, int C, b200dp_dtype dtype, float* scratch, float* out, void* stream);
+
 /* Zero-padded rows: x / y (dy / dx / add_in) have rows `pitch` elements apart, the first D of which are normalised;
  * columns D .. pitch of y and dx are written as zeros, so a width padded for the tensor cores (SwinIR-S: 60 -> 64)
  * stays padded with zeros through the layer.  D % 4 == 0, pitch % 4 == 0, D <= pitch <= 256.  add_in may be NULL. */

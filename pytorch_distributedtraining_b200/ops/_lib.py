@@ -108,7 +108,8 @@ def _try_load() -> Optional[ctypes.CDLL]:
         lib = ctypes.CDLL(_SO, mode=ctypes.RTLD_GLOBAL)
         lib.b200dp_last_error.restype = ctypes.c_char_p
         lib.b200dp_version.restype = ctypes.c_int
-        for name in ("b200dp_sumsq_scratch_floats", "b200dp_bn_scratch_floats", "b200dp_ln_scratch_floats"):
+        for name in ("b200dp_sumsq_scratch_floats", "b200dp_bn_scratch_floats", "b200dp_ln_scratch_floats",
+                     "b200dp_column_sums_scratch_floats"):
             getattr(lib, name).restype = ctypes.c_int64
         _lib = lib
     except OSError as e:  # e.g. no libcuda on a CPU-only box

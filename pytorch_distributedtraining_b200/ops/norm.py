@@ -33,16 +33,16 @@ def _allreduce_stats(buf: torch.Tensor, group: Any) -> None:
 
 
 def column_sums(x2: torch.Tensor) -> torch.Tensor:
-    """fp32 column sums of a contiguous 16-bit ``[rows, C]`` matrix with the BatchNorm moment kernel
-    (one streaming read; used for bias gradients).  ``C % 8 == 0`` and ``C <= 16384``."""
+    """fp32 column sums of a contiguous 16-bit ``[rows, C]`` matrix (one streaming read plus a small second stage;
+    used for bias gradients).  ``C % 8 == 0`` and ``C <= 16384``."""
     lib = require_library()
     rows, C = x2.shape
     ws = Workspace.get(x2.device)
-    scratch = ws.scratch(int(lib.b200dp_bn_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
-    sums = torch.empty(2 * C + 1, dtype=torch.float32, device=x2.device)
-    check(lib.b200dp_bn_reduce(ptr(x2), ctypes.c_int64(rows), ctypes.c_int(C), ctypes.c_int(DT[x2.dtype]), ptr(scratch),
-                               ptr(ws.counters), ptr(sums), stream_ptr(x2.device)), "bn_reduce")
-    return sums[:C]
+    scratch = ws.scratch(int(lib.b200dp_column_sums_scratch_floats(ctypes.c_int64(rows), ctypes.c_int(C))))
+    sums = torch.empty(C, dtype=torch.float32, device=x2.device)
+    check(lib.b200dp_column_sums(ptr(x2), ctypes.c_int64(rows), ctypes.c_int(C), ctypes.c_int(DT[x2.dtype]), ptr(scratch),
+                                 ptr(sums), stream_ptr(x2.device)), "column_sums", launches=2)
+    return sums
 
 
 class _BatchNormActFn(torch.autograd.Function):
