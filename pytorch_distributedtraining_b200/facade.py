@@ -418,6 +418,8 @@ class Stoke:
         self._grad_accum_counter = 0
         self._agg_fresh = True          # the next training loss restarts the accumulation window
         self._optimizer_steps += 1
+        from .ops.fused import bump_param_epoch
+        bump_param_epoch()              # value caches of parameters (zero-padded copies) are stale now
         if self._watchdog is not None:
             self._watchdog.beat()
 
@@ -518,6 +520,9 @@ class Stoke:
         self._backward_steps += d[0]
         self._optimizer_steps += d[1]
         self._grad_accum_counter, self._agg_fresh = d[2], d[3]
+        if d[1]:
+            from .ops.fused import bump_param_epoch
+            bump_param_epoch()          # the replay updated the parameters without running any Python
         return self._last_step_loss
 
     def _clip(self) -> None:

@@ -65,6 +65,29 @@ class Mlp(nn.Module):
         return y if residual is None else y + residual
 
 
+class _RelBias(torch.autograd.Function):
+    """``table[index] -> [heads, N, N]``.  The stock backward of the gather is a sort-based ``index_put`` (a chain of small
+    kernels, ~40 us per block); one ``index_add_`` does the same scatter-sum (atomic adds; the sorted form is kept for
+    ``torch.use_deterministic_algorithms``)."""
+
+    @staticmethod
+    def forward(ctx, table, index, n):  # type: ignore[override]
+        ctx.save_for_backward(index)
+        ctx.rows = table.shape[0]
+        return table[index].view(n, n, -1).permute(2, 0, 1)
+
+    @staticmethod
+    def backward(ctx, g):  # type: ignore[override]
+        (index,) = ctx.saved_tensors
+        gt = g.permute(1, 2, 0).reshape(index.numel(), -1)
+        out = torch.zeros((ctx.rows, gt.shape[1]), dtype=gt.dtype, device=gt.device)
+        if torch.are_deterministic_algorithms_enabled():
+            out.index_put_((index,), gt, accumulate=True)
+        else:
+            out.index_add_(0, index, gt)
+        return out, None, None
+
+
 class WindowAttention(nn.Module):
     def __init__(self, dim: int, window_size: Tuple[int, int], num_heads: int, qkv_bias: bool = True,
                  qk_scale: Optional[float] = None, attn_drop: float = 0.0, proj_drop: float = 0.0):
@@ -99,7 +122,7 @@ class WindowAttention(nn.Module):
 
     def rel_bias(self) -> torch.Tensor:
         n = self.window_size[0] * self.window_size[1]
-        return self.relative_position_bias_table[self.relative_position_index.view(-1)].view(n, n, -1).permute(2, 0, 1)
+        return _RelBias.apply(self.relative_position_bias_table, self.relative_position_index.view(-1), n)
 
     def forward_grid(self, h: torch.Tensor, x_size: Tuple[int, int], shift: int, mask: Optional[torch.Tensor],
                      residual: Optional[torch.Tensor] = None) -> torch.Tensor:

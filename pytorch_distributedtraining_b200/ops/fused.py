@@ -244,6 +244,68 @@ def lp_weight(weight: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     return weight.to(dtype)
 
 
+# Bumped whenever parameters are updated by a path that does not touch their version counters: the fused optimizer
+# kernels write through raw pointers, and a CUDA-graph replay runs no Python at all.  Caches derived from parameter
+# VALUES (``padded_param``) key on (parameter version, this epoch).
+PARAM_EPOCH = 0
+
+
+def bump_param_epoch() -> None:
+    global PARAM_EPOCH
+    PARAM_EPOCH += 1
+
+
+class _PaddedParam(torch.autograd.Function):
+    """A parameter zero-padded to ``shape`` in a persistent buffer, refreshed only when the parameter changed (once per
+    optimizer step — not once per micro-batch and not once per use), together with its 16-bit twin for the tensor-core
+    kernels (hung on the result the way ``lp_weight`` expects, so the consumer runs no cast kernel).  Backward: the slice
+    of the incoming gradient that belongs to the parameter."""
+
+    @staticmethod
+    def forward(ctx, p, shape, holder, lp_dtype):  # type: ignore[override]
+        ctx.core = tuple(slice(0, n) for n in p.shape)
+        buf = holder.get("buf")
+        if buf is None or buf.shape != torch.Size(shape) or buf.device != p.device or buf.dtype != p.dtype:
+            buf = holder["buf"] = torch.zeros(shape, dtype=p.dtype, device=p.device)
+            holder["key"], holder["lp"] = None, None
+        key = (p._version, PARAM_EPOCH, p.data_ptr())
+        fresh = holder.get("key") != key
+        if fresh:
+            buf[ctx.core].copy_(p.detach())
+            holder["key"] = key
+        out = buf.view(shape)               # a new tensor object per call (the buffer itself never gets a grad_fn)
+        if lp_dtype is not None and lp_dtype != p.dtype:
+            lp = holder.get("lp")
+            if lp is None or lp.dtype != lp_dtype or lp.shape != buf.shape:
+                # convolution filters: the kernels want the 16-bit copy channels-last ([Cout][R][S][Cin] memory)
+                mf = torch.channels_last if buf.dim() == 4 else torch.contiguous_format
+                lp = holder["lp"] = torch.empty_like(buf, dtype=lp_dtype, memory_format=mf)
+                fresh = True
+            if fresh:
+                lp.copy_(buf)
+            setattr(out, LP_ATTR, lp)
+            setattr(out, LP_VER, out._version)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):  # type: ignore[override]
+        return g[ctx.core], None, None, None
+
+
+def padded_param(p: torch.Tensor, shape, holder: dict, lp_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """``p`` zero-padded to ``shape`` (see ``_PaddedParam``); ``holder`` is the caller's cache slot (one dict per
+    parameter, e.g. on the owning module).  Parameters that are re-materialised every forward (FSDP views) skip the
+    cache: their identity, not just their value, changes."""
+    if tuple(shape) == tuple(p.shape):
+        return p
+    if not isinstance(p, torch.nn.Parameter):
+        pad = []
+        for have, want in zip(reversed(p.shape), reversed(tuple(shape))):
+            pad += [0, want - have]
+        return torch.nn.functional.pad(p, pad)
+    return _PaddedParam.apply(p, tuple(shape), holder, lp_dtype)
+
+
 def stamp_lp(params) -> None:
     for p in params:
         if getattr(p, LP_ATTR, None) is not None:

@@ -35,10 +35,13 @@ class Conv2d(nn.Conv2d):
     phys_out: Optional[int] = None
 
     def _forward_phys(self, x: torch.Tensor) -> torch.Tensor:
+        from .fused import padded_param
         cin, cout = self.in_channels, self.out_channels
         pi, po = self.phys_in or cin, self.phys_out or cout
-        w = F.pad(self.weight, (0, 0, 0, 0, 0, pi - cin, 0, po - cout)) if (pi != cin or po != cout) else self.weight
-        b = None if self.bias is None else (F.pad(self.bias, (0, po - cout)) if po != cout else self.bias)
+        cache = self.__dict__.setdefault("_phys_cache", {"w": {}, "b": {}})
+        lp = torch.get_autocast_dtype("cuda") if (x.is_cuda and torch.is_autocast_enabled()) else None
+        w = padded_param(self.weight, (po, pi) + tuple(self.weight.shape[2:]), cache["w"], lp)
+        b = None if self.bias is None else padded_param(self.bias, (po,), cache["b"])
         if x.is_cuda and dispatch.conv_phys_supported(self, x, pi, po):
             from . import conv as _conv
             return _conv.conv2d(x, w, b, self.stride, self.padding, self.dilation, self.groups)
@@ -96,10 +99,15 @@ class Linear(nn.Linear):
 
     def padded_params(self):
         """Weight / bias zero-padded to the physical widths (autograd slices the gradients back)."""
+        from .fused import padded_param
         k, n = self.in_features, self.out_features
         kp, np_ = self.phys_in or k, self.phys_out or n
-        w = F.pad(self.weight, (0, kp - k, 0, np_ - n)) if (kp != k or np_ != n) else self.weight
-        b = None if self.bias is None else (F.pad(self.bias, (0, np_ - n)) if np_ != n else self.bias)
+        if kp == k and np_ == n:
+            return self.weight, self.bias
+        cache = self.__dict__.setdefault("_phys_cache", {"w": {}, "b": {}})
+        lp = torch.get_autocast_dtype("cuda") if (self.weight.is_cuda and torch.is_autocast_enabled()) else None
+        w = padded_param(self.weight, (np_, kp), cache["w"], lp)
+        b = None if self.bias is None else padded_param(self.bias, (np_,), cache["b"])
         return w, b
 
     def forward(self, x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:

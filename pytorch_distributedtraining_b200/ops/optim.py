@@ -132,7 +132,8 @@ class _FusedBase(Optimizer):
 
     @staticmethod
     def _bump_versions(params: List[torch.Tensor]) -> None:
-        """The kernels write parameters through raw pointers; tell autograd they changed."""
+        """The kernels write parameters through raw pointers; tell autograd (and value caches) they changed."""
+        fused.bump_param_epoch()
         try:
             torch.autograd.graph.increment_version(params)
         except Exception:  # pragma: no cover - older torch: per-tensor signature

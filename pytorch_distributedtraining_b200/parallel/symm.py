@@ -707,6 +707,7 @@ class ZeroPeerEngine:
         self._clip_pending = False
         for u in self.units:                         # the next backward starts a new round
             u["pending"], u["launched"] = u["n_params"], False
+        fused.bump_param_epoch()                     # parameters changed through raw pointers
         return loss
 
     def _is_sgd(self) -> bool:

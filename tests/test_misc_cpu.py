@@ -256,7 +256,20 @@ def test_swinir_grid_attention_and_physical_widths_match_the_roll_partition_bloc
     torch.testing.assert_close(x1.grad, x2.grad, rtol=1e-9, atol=1e-11)
     for (n, p), (_, q) in zip(m.named_parameters(), legacy.named_parameters()):
         torch.testing.assert_close(p.grad, q.grad, rtol=1e-8, atol=1e-10, msg=n)
+    # the zero-padded parameter copies are cached per parameter version: an optimizer step must invalidate them
+    for net in (m, legacy):
+        torch.optim.SGD(net.parameters(), lr=1e-6).step()
+        net.zero_grad()
+    torch.testing.assert_close(m(x), legacy(x), rtol=1e-10, atol=1e-12)
+    # ... and so must an update that bypasses the version counters (fused kernels, graph replays) once the epoch is bumped
+    from pytorch_distributedtraining_b200.ops import fused
+    with torch.no_grad():
+        for net in (m, legacy):
+            w = net.layers[0].residual_group.blocks[0].attn.qkv.weight
+            w.data.view(-1)[:7] += 0.25          # .data: no version bump
+    fused.bump_param_epoch()
+    torch.testing.assert_close(m(x), legacy(x), rtol=1e-10, atol=1e-12)
     # switching the mode off again restores the logical widths everywhere
     m.phys_mode = False
-    torch.testing.assert_close(m(x), y2.detach(), rtol=1e-10, atol=1e-12)
+    torch.testing.assert_close(m(x), legacy(x), rtol=1e-10, atol=1e-12)
     assert m.conv_first.phys_out is None and m.layers[0].residual_group.blocks[0].attn.qkv.phys_out is None
