@@ -54,14 +54,30 @@ struct Geom {
     // window mode (win != 0): problem b is window (b % wpi) of image b / wpi, an ws x ws patch of an Hi x Wi token grid
     // cyclically shifted by `shift`; token rows are then addressed in IMAGE order, so no partition / roll copy exists
     int win, ws, nWx, wpi, Hi, Wi, shift;
+    // shifts for the index arithmetic (the kernels are issue-bound on these shapes: no runtime divisions on the hot path)
+    int sp_sh;         // log2(spad)
+    int p2;            // window geometry is all powers of two: ws, nWx, wpi (then *_sh are their logs)
+    int ws_sh, nwx_sh, wpi_sh;
+    int nw_mask;       // nW - 1 when nW is a power of two, else -1
 };
+
+__device__ __forceinline__ int mask_index(const Geom& g, int b) { return g.nw_mask >= 0 ? (b & g.nw_mask) : (b % g.nW); }
 
 // Row index (in units of the token pitch) of token s of problem b.
 __device__ __forceinline__ int64_t tok(const Geom& g, int b, int s) {
     if (g.win == 0) return (int64_t)b * g.S + s;
-    const int img = b / g.wpi, w = b - img * g.wpi;
-    const int wy = w / g.nWx, wx = w - wy * g.nWx;
-    const int ty = s / g.ws, tx = s - ty * g.ws;
+    int img, wy, wx, ty, tx;
+    if (g.p2) {
+        img = b >> g.wpi_sh;
+        const int w = b & (g.wpi - 1);
+        wy = w >> g.nwx_sh; wx = w & (g.nWx - 1);
+        ty = s >> g.ws_sh; tx = s & (g.ws - 1);
+    } else {
+        img = b / g.wpi;
+        const int w = b - img * g.wpi;
+        wy = w / g.nWx; wx = w - wy * g.nWx;
+        ty = s / g.ws; tx = s - ty * g.ws;
+    }
     int y = wy * g.ws + ty + g.shift, x = wx * g.ws + tx + g.shift;
     if (y >= g.Hi) y -= g.Hi;
     if (x >= g.Wi) x -= g.Wi;
@@ -79,15 +95,26 @@ __device__ __forceinline__ void tma_load_3d(void* smem_dst, const CUtensorMap* t
 template <typename T>
 __device__ __forceinline__ void stage_rows(uint8_t* dst, const T* __restrict__ src, int64_t pitch /* elements between tokens */,
                                            const Geom& g, int b0, int s0, int rows) {
-    const int sp_rows = g.G == 1 ? (1 << 20) : g.spad;      // one problem: every row is a token of it
+    const int sp_sh = g.G == 1 ? 20 : g.sp_sh;              // one problem: every row is a token of it
     const uint32_t sdst = smem_u32(dst);
     for (int row = threadIdx.x; row < rows; row += blockDim.x) {
-        const int gi = row / sp_rows, lr = row - gi * sp_rows;
+        const int gi = row >> sp_sh, lr = row - (gi << sp_sh);
         const int b = b0 + gi, s = s0 + lr;
         const bool ok = b < g.B && s < g.S && gi < g.G;
         const uint32_t* sp = reinterpret_cast<const uint32_t*>(src + tok(g, ok ? b : 0, ok ? s : 0) * pitch);
         const int nw = ok ? (g.d >> 1) : 0;                  // 32-bit words of this row that exist
         // every load is issued before the first store; words past the head dimension stay zero
+        if (g.d <= 16) {                                     // small heads: 8 words instead of 32 predicated loads
+            uint32_t w[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) w[e] = e < nw ? __ldg(sp + e) : 0u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((j ^ (row & 7)) << 4)),
+                             "r"(j < 2 ? w[4 * (j & 1)] : 0u), "r"(j < 2 ? w[4 * (j & 1) + 1] : 0u),
+                             "r"(j < 2 ? w[4 * (j & 1) + 2] : 0u), "r"(j < 2 ? w[4 * (j & 1) + 3] : 0u) : "memory");
+            continue;
+        }
         uint32_t w[32];
 #pragma unroll
         for (int e = 0; e < 32; ++e) w[e] = e < nw ? __ldg(sp + e) : 0u;
@@ -106,34 +133,54 @@ struct StageJob { uint8_t* dst; const T* src; int64_t pitch; int s0; int rows; }
 
 template <typename T, int NJ>
 __device__ __forceinline__ void stage_many(const StageJob<T> (&jobs)[NJ], const Geom& g, int b0) {
-    const int sp_rows = g.G == 1 ? (1 << 20) : g.spad;
+    const int sp_sh = g.G == 1 ? 20 : g.sp_sh;
     // 128-row tiles, 256 threads: thread t serves row (t & 127) of jobs {t >> 7, (t >> 7) + 2}
     const int row = threadIdx.x & 127, jsel = threadIdx.x >> 7;
     constexpr int kPer = (NJ + 1) / 2;
+    const int gi = row >> sp_sh, lr = row - (gi << sp_sh);
+    const int b = b0 + gi;
+    const bool small = g.d <= 16;
     uint32_t w[kPer][32];
     bool live[kPer];
+    int64_t t_prev = 0;
+    int s_prev = -1;
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
         const int j = jsel + 2 * k;
         live[k] = j < NJ && row < jobs[j < NJ ? j : 0].rows;
         const StageJob<T>& jb = jobs[j < NJ ? j : 0];
-        const int gi = row / sp_rows, lr = row - gi * sp_rows;
-        const int b = b0 + gi, sidx = jb.s0 + lr;
-        const bool ok = live[k] && b < g.B && sidx < g.S && gi < g.G;
-        const uint32_t* sp = reinterpret_cast<const uint32_t*>(jb.src + tok(g, ok ? b : 0, ok ? sidx : 0) * jb.pitch);
+        const int sidx = jb.s0 + lr;
+        const bool okp = b < g.B && sidx < g.S && gi < g.G;
+        const bool ok = live[k] && okp;
+        // the jobs of one call usually start at the same token: one index computation serves them all
+        if (sidx != s_prev) { t_prev = tok(g, okp ? b : 0, okp ? sidx : 0); s_prev = sidx; }
+        const uint32_t* sp = reinterpret_cast<const uint32_t*>(jb.src + t_prev * jb.pitch);
         const int nw = ok ? (g.d >> 1) : 0;
+        if (small) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e) w[k][e] = e < nw ? __ldg(sp + e) : 0u;
+            for (int e = 0; e < 8; ++e) w[k][e] = e < nw ? __ldg(sp + e) : 0u;
+        } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) w[k][e] = e < nw ? __ldg(sp + e) : 0u;
+        }
     }
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
         if (!live[k]) continue;
         const int j = jsel + 2 * k;
         const uint32_t sdst = smem_u32(jobs[j].dst);
+        if (small) {
 #pragma unroll
-        for (int p = 0; p < 8; ++p)
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((p ^ (row & 7)) << 4)),
-                         "r"(w[k][4 * p]), "r"(w[k][4 * p + 1]), "r"(w[k][4 * p + 2]), "r"(w[k][4 * p + 3]) : "memory");
+            for (int p = 0; p < 8; ++p)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((p ^ (row & 7)) << 4)),
+                             "r"(p < 2 ? w[k][4 * (p & 1)] : 0u), "r"(p < 2 ? w[k][4 * (p & 1) + 1] : 0u),
+                             "r"(p < 2 ? w[k][4 * (p & 1) + 2] : 0u), "r"(p < 2 ? w[k][4 * (p & 1) + 3] : 0u) : "memory");
+        } else {
+#pragma unroll
+            for (int p = 0; p < 8; ++p)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sdst + row * 128 + ((p ^ (row & 7)) << 4)),
+                             "r"(w[k][4 * p]), "r"(w[k][4 * p + 1]), "r"(w[k][4 * p + 2]), "r"(w[k][4 * p + 3]) : "memory");
+        }
     }
 }
 
@@ -141,9 +188,9 @@ __device__ __forceinline__ void stage_many(const StageJob<T> (&jobs)[NJ], const 
 struct RowId { int b, s, gi; bool ok; };
 __device__ __forceinline__ RowId row_id(const Geom& g, int b0, int tile, int r) {
     RowId o;
-    o.gi = r / g.spad;
+    o.gi = r >> g.sp_sh;
     o.b = b0 + o.gi;
-    o.s = tile * kTile + (r - o.gi * g.spad);
+    o.s = tile * kTile + (r - (o.gi << g.sp_sh));
     o.ok = o.b < g.B && o.s < g.S && o.gi < g.G;
     return o;
 }
@@ -213,7 +260,7 @@ __device__ __forceinline__ void stage_add(float* sAdd, const float* __restrict__
             const int idx4 = threadIdx.x + it * 256, gi = idx4 >> 10, row = (idx4 >> 4) & 63, k4 = (idx4 & 15) * 4;
             const bool live = b0 + gi < g.B;
             bv[it] = (bias && live) ? __ldg(reinterpret_cast<const float4*>(bias + ((int64_t)h * 64 + row) * 64 + k4)) : make_float4(0.f, 0.f, 0.f, 0.f);
-            mv[it] = (has_m && live) ? __ldg(reinterpret_cast<const float4*>(mask + ((int64_t)((b0 + gi) % g.nW) * 64 + row) * 64 + k4))
+            mv[it] = (has_m && live) ? __ldg(reinterpret_cast<const float4*>(mask + ((int64_t)mask_index(g, b0 + gi) * 64 + row) * 64 + k4))
                                      : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
@@ -234,7 +281,7 @@ __device__ __forceinline__ void stage_add(float* sAdd, const float* __restrict__
         float v = 0.f;
         if (b0 + gi < g.B) {
             if (bias) v += __ldg(bias + ((int64_t)h * S + row) * S + k);
-            if (mask && g.nW > 0) v += __ldg(mask + ((int64_t)((b0 + gi) % g.nW) * S + row) * S + k);
+            if (mask && g.nW > 0) v += __ldg(mask + ((int64_t)mask_index(g, b0 + gi) * S + row) * S + k);
         }
         sAdd[gi * 4096 + row * 64 + (k ^ (row & 31))] = v;
     }
@@ -361,7 +408,7 @@ __global__ void __launch_bounds__(256, 2) attn_fwd_kernel(const __grid_constant_
     const RowId me = row_id(g, b0, qt, r);
     const int klo = g.G == 1 ? 0 : me.gi * g.spad;                // warp-uniform: a warp's 32 rows belong to one problem
     const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
-    const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+    const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)mask_index(g, me.ok ? me.b : 0) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
     const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     const int nch = (g.nk + 31) >> 5;
     const int ch_lo = klo >> 5, ch_hi = min(nch, (klo + g.S + 31) >> 5);          // chunks holding this problem's keys
@@ -667,7 +714,7 @@ __global__ void __launch_bounds__(256, 1) attn_bwd_kernel(const __grid_constant_
                     const int koff = g.G == 1 ? -j * kTile : me.gi * g.spad;
                     const int ch_lo = g.G == 1 ? 0 : (koff >> 5), ch_hi = g.G == 1 ? 4 : min(4, (koff + g.S + 31) >> 5);
                     const float* brow = bias ? bias + ((int64_t)h * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
-                    const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)((me.ok ? me.b : 0) % g.nW) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
+                    const float* mrow = (mask && g.nW > 0) ? mask + ((int64_t)mask_index(g, me.ok ? me.b : 0) * g.S + (me.ok ? me.s : 0)) * g.S : nullptr;
                     float* dbrow = (dbias && me.ok) ? sDB + (me.gi * 64 + me.s) * kDbStride : nullptr;     // rows are thread-private
                     // rows that stand for no token get lse = +inf: their probabilities come out as exact zeros
                     const float lsel = me.ok ? row_lse[i] * kLog2e : INFINITY, sl = g.scale * kLog2e, dl = delta[i];
@@ -822,8 +869,12 @@ static int make_geom(Geom* g, int B, int H, int S, int d, float scale, int nW, c
     g->manual = !(d == 64 && g->G == 1 && ((uintptr_t)p0 & 15) == 0 && ((uintptr_t)p1 & 15) == 0);
     g->qp = 3 * H * d; g->op = H * d; g->dop = H * d;
     g->win = 0; g->ws = g->nWx = g->wpi = g->Hi = g->Wi = g->shift = 0;
+    g->sp_sh = g->G == 2 ? 6 : 7;
+    g->p2 = 0; g->ws_sh = g->nwx_sh = g->wpi_sh = 0;
+    g->nw_mask = (nW > 0 && (nW & (nW - 1)) == 0) ? nW - 1 : -1;
     return 0;
 }
+static inline int ilog2(int v) { int r = 0; while ((1 << r) < v) ++r; return r; }
 
 // Window mode on top of make_geom: images of Hi x Wi tokens cut into ws x ws windows after a cyclic shift; pitches in elements.
 static int set_windows(Geom* g, int Hi, int Wi, int ws, int shift, int qp, int op, int dop) {
@@ -836,6 +887,9 @@ static int set_windows(Geom* g, int Hi, int Wi, int ws, int shift, int qp, int o
     g->win = 1; g->ws = ws; g->nWx = Wi / ws; g->wpi = wpi; g->Hi = Hi; g->Wi = Wi; g->shift = shift;
     g->qp = qp; g->op = op; g->dop = dop;
     g->manual = 1;
+    const int nwx = Wi / ws;
+    g->p2 = (ws & (ws - 1)) == 0 && (nwx & (nwx - 1)) == 0 && (wpi & (wpi - 1)) == 0;
+    g->ws_sh = ilog2(ws); g->nwx_sh = ilog2(nwx); g->wpi_sh = ilog2(wpi);
     return 0;
 }
 
