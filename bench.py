@@ -482,8 +482,9 @@ def main() -> None:
     if stoke is not None:
         stoke.reset_graphs()
     sync()
-    if world > 1 and dist.is_initialized():
-        dist.barrier(device_ids=[device.index]) if is_cuda else dist.barrier()
+    if dist.is_initialized():            # also the one-rank group the ZeRO / FSDP configs create on a single GPU
+        if world > 1:
+            dist.barrier(device_ids=[device.index]) if is_cuda else dist.barrier()
         dist.destroy_process_group()
     guard.cancel()
 
