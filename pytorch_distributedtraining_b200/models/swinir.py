@@ -81,7 +81,8 @@ class _RelBias(torch.autograd.Function):
         (index,) = ctx.saved_tensors
         gt = g.permute(1, 2, 0).reshape(index.numel(), -1)
         out = torch.zeros((ctx.rows, gt.shape[1]), dtype=gt.dtype, device=gt.device)
-        if torch.are_deterministic_algorithms_enabled():
+        from ..ops import dispatch
+        if dispatch.deterministic():
             out.index_put_((index,), gt, accumulate=True)
         else:
             out.index_add_(0, index, gt)
@@ -137,10 +138,11 @@ class WindowAttention(nn.Module):
         qkv = self.qkv(h).view(B, H, W, -1)
         p_drop = self.attn_drop.p if self.training else 0.0
         out_pitch = self.proj.phys_in or self.dim
-        if p_drop == 0.0 and window_attention_supported(qkv, heads, d, ws):
-            o = window_attention(qkv, heads, d, ws, shift, self.scale, self.rel_bias(), mask, out_pitch)
+        bias = self.rel_bias()
+        if p_drop == 0.0 and window_attention_supported(qkv, heads, d, ws, bias):
+            o = window_attention(qkv, heads, d, ws, shift, self.scale, bias, mask, out_pitch)
         else:
-            o = window_attention_reference(qkv, heads, d, ws, shift, self.scale, self.rel_bias(), mask, out_pitch, p_drop)
+            o = window_attention_reference(qkv, heads, d, ws, shift, self.scale, bias, mask, out_pitch, p_drop)
         o = o.reshape(B, L, -1)
         if self.proj_drop.p == 0.0 or not self.training:
             return self.proj(o, residual=residual)

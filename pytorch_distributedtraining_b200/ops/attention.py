@@ -119,8 +119,8 @@ def attention_supported(qkv: torch.Tensor, heads: int, bias: Optional[torch.Tens
     d = D3 // (3 * heads)
     if not (0 < S <= 256 and 2 <= d <= 64 and d % 2 == 0):
         return False
-    if bias is not None and bias.requires_grad and S > 64:
-        return False
+    if bias is not None and bias.requires_grad and (S > 64 or dispatch.deterministic()):
+        return False            # the bias gradient is accumulated with float atomics
     return True
 
 
@@ -179,10 +179,13 @@ def attention(qkv: torch.Tensor, heads: int, scale: Optional[float] = None, bias
     return _AttentionFn.apply(qkv, heads, float(scale if scale is not None else d ** -0.5), bias, mask)
 
 
-def window_attention_supported(qkv: torch.Tensor, heads: int, d: int, ws: int) -> bool:
+def window_attention_supported(qkv: torch.Tensor, heads: int, d: int, ws: int, bias: Optional[torch.Tensor] = None) -> bool:
     """``window_attention`` on the tcgen05 kernels: CUDA fp16 / bf16 ``[B, Hi, Wi, P]`` projection (P >= 3 * heads * d,
-    even), windows of at most 64 tokens that tile the token grid, even head dimension <= 64."""
+    even), windows of at most 64 tokens that tile the token grid, even head dimension <= 64.  A bias that needs a gradient
+    is served unless run-to-run determinism was asked for (its gradient is accumulated with float atomics)."""
     if not (qkv.is_cuda and qkv.dtype in _HALF and qkv.dim() == 4 and dispatch.enabled("attn") and dispatch._lib_ok()):
+        return False
+    if bias is not None and bias.requires_grad and dispatch.deterministic():
         return False
     _, Hi, Wi, P = qkv.shape
     return (qkv.is_contiguous() and P >= 3 * heads * d and P % 2 == 0 and 0 < ws * ws <= 64 and Hi % ws == 0

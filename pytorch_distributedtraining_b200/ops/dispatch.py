@@ -13,11 +13,19 @@ from typing import Any
 import torch
 
 _DISABLED = {s.strip() for s in os.environ.get("B200DP_DISABLE", "").split(",") if s.strip()}
-if os.environ.get("B200DP_DETERMINISTIC", "0") not in ("", "0"):
-    # run-to-run reproducible kernels only: the conv -> BatchNorm statistics epilogue accumulates with float
-    # atomics, so BatchNorm goes back to its own two-stage (fixed-order) reduction
+_DETERMINISTIC = os.environ.get("B200DP_DETERMINISTIC", "0") not in ("", "0")
+if _DETERMINISTIC:
+    # run-to-run reproducible kernels only.  Three places accumulate with float atomics: the conv -> BatchNorm statistics
+    # epilogue (BatchNorm goes back to its own two-stage, fixed-order reduction), the first-layer weight gradient (the layer
+    # goes back to the library) and the bias gradient of window attention (see ``deterministic()`` in ops.attention)
     _DISABLED.add("convstats")
+    _DISABLED.add("conv_first")
 _HALF = (torch.float16, torch.bfloat16)
+
+
+def deterministic() -> bool:
+    """``B200DP_DETERMINISTIC=1`` or ``torch.use_deterministic_algorithms(True)``."""
+    return _DETERMINISTIC or torch.are_deterministic_algorithms_enabled()
 
 
 def enabled(feature: str) -> bool:
