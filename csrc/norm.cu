@@ -167,9 +167,11 @@ __global__ void __launch_bounds__(kBNThreads, 3) bn_apply_kernel(
     int rpb, const float* __restrict__ sums, float count, const float* __restrict__ gamma,
     const float* __restrict__ beta, float eps, float momentum, float* __restrict__ running_mean,
     float* __restrict__ running_var, float* __restrict__ mean_out, float* __restrict__ invstd_out, int relu,
-    uint8_t* __restrict__ mask_out) {
+    uint8_t* __restrict__ mask_out, long long* __restrict__ num_batches_tracked = nullptr) {
     const int rl = threadIdx.x / cgb, cgl = threadIdx.x % cgb;
     const int cg = blockIdx.x * cgb + cgl;
+    // nn.BatchNorm's step counter rides along (one thread of the grid) instead of costing a launch per layer and step
+    if (kTrain && num_batches_tracked != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *num_batches_tracked += 1;
     if (!(rl < rpb && cg < tpr)) return;
     float sc[8], sh[8];
     const int c0 = cg * 8;
@@ -907,19 +909,29 @@ int b200dp_bn_reduce(const void* x, int64_t rows, int C, b200dp_dtype dtype, flo
     return 0;
 }
 
-int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
-                    const float* sums, float count, const float* gamma, const float* beta, float eps,
-                    float momentum, float* running_mean, float* running_var, float* mean_out,
-                    float* invstd_out, int relu, unsigned char* relu_mask, void* stream) {
+int b200dp_bn_apply_tracked(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                            const float* sums, float count, const float* gamma, const float* beta, float eps,
+                            float momentum, float* running_mean, float* running_var, float* mean_out,
+                            float* invstd_out, int relu, unsigned char* relu_mask, long long* num_batches_tracked,
+                            void* stream) {
     B200DP_REQUIRE(x && y && sums && gamma && beta && mean_out && invstd_out, "bn_apply: null argument");
     BN_COMMON_CHECKS("bn_apply")
     B200DP_DISPATCH_HALF(dtype, T, {
         bn_apply_kernel<T, true><<<dim3(bn_geom(rows, C, 3).gx, bn_geom(rows, C, 3).gy), kBNThreads, 0, s>>>((const T*)x, (const T*)residual, (T*)y, rows, C, g.tpr,
                                                              g.cgb, g.rpb, sums, count, gamma, beta, eps, momentum,
-                                                             running_mean, running_var, mean_out, invstd_out, relu, relu_mask);
+                                                             running_mean, running_var, mean_out, invstd_out, relu, relu_mask,
+                                                             num_batches_tracked);
     });
     B200DP_CHECK_LAUNCH();
     return 0;
+}
+
+int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                    const float* sums, float count, const float* gamma, const float* beta, float eps,
+                    float momentum, float* running_mean, float* running_var, float* mean_out,
+                    float* invstd_out, int relu, unsigned char* relu_mask, void* stream) {
+    return b200dp_bn_apply_tracked(x, residual, y, rows, C, dtype, sums, count, gamma, beta, eps, momentum, running_mean,
+                                   running_var, mean_out, invstd_out, relu, relu_mask, nullptr, stream);
 }
 
 int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,

@@ -173,6 +173,13 @@ int b200dp_bn_apply(const void* x, const void* residual, void* y, int64_t rows, 
                     const float* sums, float count, const float* gamma, const float* beta, float eps,
                     float momentum, float* running_mean, float* running_var, float* mean_out,
                     float* invstd_out, int relu, unsigned char* relu_mask, void* stream);
+/* Same, and *num_batches_tracked (int64, may be NULL) += 1 from inside the kernel: nn.BatchNorm's step counter without a
+ * launch of its own per layer and step. */
+int b200dp_bn_apply_tracked(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
+                            const float* sums, float count, const float* gamma, const float* beta, float eps,
+                            float momentum, float* running_mean, float* running_var, float* mean_out,
+                            float* invstd_out, int relu, unsigned char* relu_mask, long long* num_batches_tracked,
+                            void* stream);
 /* inference: y = act(gamma*(x-running_mean)*rsqrt(running_var+eps) + beta + residual) */
 int b200dp_bn_infer(const void* x, const void* residual, void* y, int64_t rows, int C, b200dp_dtype dtype,
                     const float* gamma, const float* beta, const float* running_mean,

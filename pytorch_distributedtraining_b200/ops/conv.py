@@ -237,6 +237,47 @@ def _accumulable(d_carry, x) -> bool:
 BN_STATS_ATTR = "_b200dp_bn_sums"
 
 
+class _StatsArena:
+    """Zeroed fp32 scratch for the conv -> BatchNorm statistics, handed out in slices.
+
+    Every statistics vector has to start at zero (the epilogues accumulate into it), which used to be one fill launch
+    per convolution and step — 53 for ResNet-50.  Here the vectors of a whole optimizer step are slices of one block that
+    is zeroed ONCE, at the first request after the parameters changed (``ops.fused.PARAM_EPOCH``: bumped by the fused
+    optimizers, the ZeRO engine and every graph replay that contains an optimizer step).  Without such a signal (a
+    plain torch optimizer, forward-only loops) the block is simply used up and a fresh zeroed one is allocated: one
+    memset per ~quarter million floats instead of one per layer.  Under CUDA-graph capture the same logic is recorded:
+    the graph of the first micro-batch contains the block's memset, later micro-batches of the step take the slices
+    behind it."""
+
+    BLOCK = 1 << 18          # floats
+
+    def __init__(self, device: torch.device):
+        self.device, self.buf, self.cursor, self.epoch = device, None, 0, -1
+
+    def take(self, n: int) -> torch.Tensor:
+        from . import fused
+        n_al = (n + 63) // 64 * 64
+        if self.buf is None or self.cursor + n_al > self.buf.numel():
+            self.buf = torch.zeros(max(self.BLOCK, n_al), dtype=torch.float32, device=self.device)
+            self.cursor, self.epoch = 0, fused.PARAM_EPOCH
+        elif self.epoch != fused.PARAM_EPOCH:
+            self.buf.zero_()
+            self.cursor, self.epoch = 0, fused.PARAM_EPOCH
+        out = self.buf[self.cursor: self.cursor + n]
+        self.cursor += n_al
+        return out
+
+
+_STATS_ARENAS: dict = {}
+
+
+def _stats_vector(n: int, device: torch.device) -> torch.Tensor:
+    arena = _STATS_ARENAS.get(device)
+    if arena is None:
+        arena = _STATS_ARENAS[device] = _StatsArena(device)
+    return arena.take(n)
+
+
 def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], stride, padding, dilation, groups,
            emit_bn_stats: bool = False, carry: bool = False):
     """``emit_bn_stats``: the convolution's epilogue also produces [sum(y), sum(y^2), (count slot)] per
@@ -247,7 +288,7 @@ def conv2d(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor], 
     with torch.autocast("cuda", enabled=False):
         sums = None
         if emit_bn_stats and (bias is None or tuple(weight.shape[2:]) != (1, 1) or int(stride[0]) != 1):
-            sums = torch.zeros(2 * weight.shape[0] + 1, dtype=torch.float32, device=x.device)
+            sums = _stats_vector(2 * weight.shape[0] + 1, x.device)
         out = _ConvFn.apply(x, weight, bias, dtype, int(stride[0]), int(padding[0]), sums, carry)
         y = out[0] if carry else out
         if sums is not None:

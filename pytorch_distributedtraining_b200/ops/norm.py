@@ -48,7 +48,7 @@ def column_sums(x2: torch.Tensor) -> torch.Tensor:
 class _BatchNormActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, weight, bias, running_mean, running_var, eps, momentum, relu, group, world,
-                pre_sums=None):  # type: ignore[override]
+                pre_sums=None, tracked=None):  # type: ignore[override]
         lib = require_library()
         rows, C = _rows_view(x)
         dt = ctypes.c_int(DT[x.dtype])
@@ -73,10 +73,11 @@ class _BatchNormActFn(torch.autograd.Function):
         mean = torch.empty(C, dtype=torch.float32, device=dev)
         invstd = torch.empty(C, dtype=torch.float32, device=dev)
         mask = torch.empty(rows * (C // 8), dtype=torch.uint8, device=dev) if relu else None   # 1 bit / element
-        check(lib.b200dp_bn_apply(ptr(x), ptr(residual), ptr(y), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(sums),
-                                  ctypes.c_float(count), ptr(weight), ptr(bias), ctypes.c_float(eps),
-                                  ctypes.c_float(momentum), ptr(running_mean), ptr(running_var), ptr(mean),
-                                  ptr(invstd), ctypes.c_int(int(relu)), ptr(mask), st), "bn_apply")
+        # `tracked`: the module's int64 num_batches_tracked, incremented by one thread of the kernel
+        check(lib.b200dp_bn_apply_tracked(ptr(x), ptr(residual), ptr(y), ctypes.c_int64(rows), ctypes.c_int(C), dt, ptr(sums),
+                                          ctypes.c_float(count), ptr(weight), ptr(bias), ctypes.c_float(eps),
+                                          ctypes.c_float(momentum), ptr(running_mean), ptr(running_var), ptr(mean),
+                                          ptr(invstd), ctypes.c_int(int(relu)), ptr(mask), ptr(tracked), st), "bn_apply")
         ctx.save_for_backward(x, mask, weight, mean, invstd)
         ctx.relu, ctx.group, ctx.world, ctx.count = relu, group, world, count
         ctx.total = sums[2 * C: 2 * C + 1] if world > 1 else None      # device scalar: cross-rank element count
@@ -112,7 +113,7 @@ class _BatchNormActFn(torch.autograd.Function):
         check(lib.b200dp_bn_bwd_apply(ptr(dy), None, ptr(x), ptr(dx), ptr(dres), ctypes.c_int64(rows), ctypes.c_int(C),
                                       dt, ptr(mean), ptr(invstd), ptr(weight), ptr(dsums), ctypes.c_float(ctx.count),
                                       relu, ptr(mask), st), "bn_bwd_apply")
-        return dx, dres, dweight.to(weight.dtype), dbias.to(weight.dtype), None, None, None, None, None, None, None, None
+        return dx, dres, dweight.to(weight.dtype), dbias.to(weight.dtype), None, None, None, None, None, None, None, None, None
 
 
 def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) -> torch.Tensor:
@@ -132,8 +133,10 @@ def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) 
                                   stream_ptr(x.device)), "bn_infer")
         return y
     momentum = 0.1 if mod.momentum is None else mod.momentum
-    if mod.num_batches_tracked is not None:
-        mod.num_batches_tracked.add_(1)
+    nbt = mod.num_batches_tracked
+    if nbt is not None and not (nbt.is_cuda and nbt.dtype == torch.int64 and nbt.device == x.device):
+        nbt.add_(1)                 # not where the kernel can reach it
+        nbt = None
     world, group = 1, None
     if mod.sync and dist.is_available() and dist.is_initialized():
         group = mod.process_group if mod.process_group is not None else dist.group.WORLD
@@ -142,7 +145,7 @@ def batch_norm_act(mod: Any, x: torch.Tensor, residual: Optional[torch.Tensor]) 
     if pre is not None and (pre.numel() != 2 * x.shape[1] + 1 or pre.device != x.device):
         pre = None
     return _BatchNormActFn.apply(x, residual, mod.weight, mod.bias, mod.running_mean, mod.running_var, mod.eps,
-                                 momentum, relu, group, world, pre)
+                                 momentum, relu, group, world, pre, nbt)
 
 
 class _LayerNormFn(torch.autograd.Function):

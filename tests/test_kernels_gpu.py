@@ -296,6 +296,40 @@ def test_resnet18_fused_path_matches_stock_ops():
     assert e_fused < max(1.5 * e_stock, 2e-2), (e_fused, e_stock)
 
 
+def test_bn_statistics_arena_and_step_counter_over_several_steps():
+    """The conv -> BatchNorm statistics vectors are slices of one block zeroed once per optimizer step, and
+    ``num_batches_tracked`` is incremented inside the apply kernel: several steps (with and without the parameter-epoch
+    signal between them, and past the end of a block) must keep matching fp32 BatchNorm statistics."""
+    from pytorch_distributedtraining_b200.models import resnet18
+    from pytorch_distributedtraining_b200.ops import conv as _conv, dispatch, fused
+    torch.manual_seed(0)
+    m = resnet18(num_classes=10, small_input=True).to(cuda).to(memory_format=torch.channels_last)
+    exact = copy.deepcopy(m)
+    arena = _conv._STATS_ARENAS.get(torch.device("cuda", torch.cuda.current_device()))
+    for step in range(5):
+        x = torch.randn(16, 3, 32, 32, device=cuda).contiguous(memory_format=torch.channels_last)
+        with torch.autocast("cuda", dtype=torch.float16):
+            m(x).float().square().mean().backward()
+        for f in ("bn", "ce", "gemm", "conv", "ln"):
+            dispatch.disable(f)
+        try:
+            exact(x).square().mean().backward()
+        finally:
+            for f in ("bn", "ce", "gemm", "conv", "ln"):
+                dispatch.enable(f)
+        if step in (0, 2):
+            fused.bump_param_epoch()                     # "an optimizer step happened": the block is re-zeroed and reused
+        if step == 3:
+            arena = _conv._STATS_ARENAS[x.device]
+            arena.cursor = arena.buf.numel() - 64        # the next request does not fit: a fresh zeroed block
+    bns = [(a, b) for a, b in zip(m.modules(), exact.modules()) if isinstance(a, torch.nn.BatchNorm2d)]
+    assert len(bns) >= 10
+    for a, b in bns:
+        assert int(a.num_batches_tracked) == 5 == int(b.num_batches_tracked)
+        torch.testing.assert_close(a.running_mean, b.running_mean, rtol=2e-2, atol=2e-2)
+        torch.testing.assert_close(a.running_var, b.running_var, rtol=3e-2, atol=3e-2)
+
+
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("shape,k,st,pd", [((4, 64, 112, 112), 3, 2, 1), ((2, 16, 9, 11), 3, 2, 1), ((3, 8, 8, 8), 2, 2, 0),
                                             ((2, 24, 13, 7), 3, 1, 1)])
