@@ -273,3 +273,51 @@ def test_swinir_grid_attention_and_physical_widths_match_the_roll_partition_bloc
     m.phys_mode = False
     torch.testing.assert_close(m(x), legacy(x), rtol=1e-10, atol=1e-12)
     assert m.conv_first.phys_out is None and m.layers[0].residual_group.blocks[0].attn.qkv.phys_out is None
+
+
+def test_padded_param_cache_semantics():
+    """``ops.fused.padded_param``: one persistent zero-padded buffer per parameter, refreshed when the parameter's
+    version or the global parameter epoch changed, sliced gradient, no cache for non-Parameter tensors."""
+    from pytorch_distributedtraining_b200.ops import fused
+    w = torch.nn.Parameter(torch.arange(6.0).view(2, 3))
+    holder: dict = {}
+    a = fused.padded_param(w, (4, 8), holder)
+    assert a.shape == (4, 8) and torch.equal(a[:2, :3], w.detach()) and a[2:].abs().sum() == 0 and a[:, 3:].abs().sum() == 0
+    buf = holder["buf"]
+    b = fused.padded_param(w, (4, 8), holder)
+    assert holder["buf"] is buf and b.data_ptr() == a.data_ptr()          # cache hit: same storage, nothing recomputed
+    (a * torch.arange(32.0).view(4, 8)).sum().backward()
+    torch.testing.assert_close(w.grad, torch.arange(32.0).view(4, 8)[:2, :3])
+    with torch.no_grad():
+        w.mul_(2.0)                                                       # version bump
+    c = fused.padded_param(w, (4, 8), holder)
+    assert torch.equal(c[:2, :3], w.detach())
+    w.data[0, 0] = 100.0                                                  # no version bump: stale until the epoch moves
+    assert fused.padded_param(w, (4, 8), holder)[0, 0] != 100.0
+    fused.bump_param_epoch()
+    assert fused.padded_param(w, (4, 8), holder)[0, 0] == 100.0
+    assert fused.padded_param(w, (2, 3), holder) is w                     # nothing to pad
+    t = w.detach() * 1.0                                                  # not a Parameter (e.g. an FSDP view): plain pad
+    p = fused.padded_param(t, (4, 8), {})
+    assert p.shape == (4, 8) and torch.equal(p[:2, :3], t)
+
+
+def test_relative_position_bias_gather_gradient():
+    """``_RelBias``: table[index] -> [heads, N, N]; its scatter-sum backward (index_add_ / sorted index_put_ in
+    deterministic mode) against autograd's own gather backward."""
+    from pytorch_distributedtraining_b200.models.swinir import _RelBias
+    torch.manual_seed(0)
+    table = torch.randn(225, 6, dtype=torch.double, requires_grad=True)
+    index = torch.randint(0, 225, (64 * 64,))
+    g = torch.randn(6, 64, 64, dtype=torch.double)
+    ref = table[index].view(64, 64, -1).permute(2, 0, 1)
+    (want,) = torch.autograd.grad(ref, table, g)
+    for det in (False, True):
+        torch.use_deterministic_algorithms(det)
+        try:
+            out = _RelBias.apply(table, index, 64)
+            (got,) = torch.autograd.grad(out, table, g)
+        finally:
+            torch.use_deterministic_algorithms(False)
+        assert torch.equal(out, ref)
+        torch.testing.assert_close(got, want, rtol=1e-12, atol=1e-12)
