@@ -378,6 +378,8 @@ class Stoke:
         opt = self._optimizer
         norm_clip = isinstance(gc, ClipGradNormConfig) and float(gc.norm_type) == 2.0
         fused = hasattr(opt, "fused_unscale_clip") and not isinstance(gc, ClipGradConfig) and (gc is None or norm_clip)
+        if fused and isinstance(opt, OSS) and not opt._fused_clip_usable():
+            fused = False
         zero_eng = getattr(opt, "_flat_engine", None) if isinstance(opt, OSS) else None
         ddp_eng = self._peer.get("ddp") if getattr(self, "_peer", None) else None
         if zero_eng is not None and (gc is None or norm_clip):

@@ -114,6 +114,10 @@ class OSS(Optimizer):
             local_groups = [dict(local_groups[0] if local_groups else {}, params=[self._dummy])]
         self.optim = optim(local_groups, **default)
         self._default_device = self._any_device()
+        if hasattr(self.optim, "fused_unscale_clip"):
+            # the fused optimizers compute norm + inf flag in ONE read of the (owned) gradients and apply unscale / clip
+            # inside the update kernel; exposing the entry point here lets the GradScaler / facade reach it through OSS
+            self.fused_unscale_clip = self._fused_unscale_clip
 
     # ------------------------------------------------------------------ partition
     def _any_device(self) -> torch.device:
@@ -296,6 +300,8 @@ class OSS(Optimizer):
             return self._flat_engine.clip_grad_norm(max_norm, norm_type)
         max_norm = float(max_norm)
         norm_type = float(norm_type)
+        if norm_type == 2.0 and filter_params_fn is None and self._fused_clip_usable():
+            return self._fused_unscale_clip(None, max_norm, None)
         local = [p for p in self.local_params() if p.grad is not None]
         if filter_params_fn is not None:
             local = list(filter_params_fn(local))
@@ -319,6 +325,26 @@ class OSS(Optimizer):
                 if p.grad is not None:
                     p.grad.detach().mul_(clip_coef.to(p.grad.device, p.grad.dtype))
         return total
+
+    def _fused_clip_usable(self) -> bool:
+        from ..ops import dispatch
+        if "fused_unscale_clip" not in self.__dict__ or not dispatch.enabled("oss_fused_clip"):
+            return False
+        grads = [p.grad for p in self.local_params() if p.grad is not None]
+        return bool(grads) and all(g.is_cuda for g in grads)
+
+    def _fused_unscale_clip(self, inv_scale: Optional[torch.Tensor], max_norm: Optional[float],
+                            found_inf: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        """Shard-aware norm / inf check with ONE read of the gradients this rank owns (two launches instead of four per
+        parameter): the partial sum of squares and the flag are summed across ranks, the resulting multiplier (1/scale
+        and the clip coefficient) is applied inside the inner optimizer's update kernel — gradients are not rewritten.
+        Returns the global gradient norm (device scalar) when clipping."""
+        reduce = None
+        if self.world_size > 1:
+            def reduce(buf: torch.Tensor) -> None:      # [sum g^2, non-finite flag]
+                dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group)
+                buf[1:2].clamp_(max=1.0)
+        return self.optim.fused_unscale_clip(inv_scale, max_norm, found_inf, extra_sumsq_reduce=reduce)
 
     # ------------------------------------------------------------------ state dict
     @property

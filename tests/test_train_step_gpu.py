@@ -82,3 +82,70 @@ def test_optimizer_keeps_16bit_weight_shadows_the_layers_read():
     assert fused.lp_weight(mats[0], torch.float16) is not getattr(mats[0], fused.LP_ATTR)
     loss = s.loss(s.model(x), y); s.backward(loss); s.step()
     assert fused.lp_weight(mats[0], torch.float16) is getattr(mats[0], fused.LP_ATTR)
+
+
+@pytest.mark.parametrize("fp16", ["amp", "bf16"])
+def test_oss_clip_through_the_fused_norm_matches_the_per_parameter_loop(fp16):
+    """A bare OSS (one GPU, or NCCL without the peer engine) reaches the fused optimizers' one-read norm / inf check
+    (``OSS.fused_unscale_clip``).  (1) On the SAME gradients its norm and multiplier equal the fp32 torch computation;
+    (2) the training trajectory matches the per-parameter clip loop it replaces (``B200DP_DISABLE=oss_fused_clip``) with
+    gradient accumulation and clipping that really clips, fp16 (GradScaler) and bf16.  Adam turns rounding-level
+    gradient differences into sign flips of near-zero elements, so (2) is a loss-trajectory check with a loose bound on
+    the parameters; (1) is the exact one."""
+    import argparse
+    import os, sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from pytorch_distributedtraining_b200.ops import dispatch
+    from pytorch_distributedtraining_b200.parallel.oss import OSS
+
+    def build():
+        torch.manual_seed(0)
+        cfg = dict(model="resnet18", batch=32, shape=(3, 32, 32), classes=10, fp16=fp16, oss=True, sddp=True, fsdp=False,
+                   accum=2, clip=0.05)
+        args = argparse.Namespace(cpu=False, batch_size=0, impl="ours", no_graph=True, sync_bn=False)
+        return bench.build_ours(cfg, args, 1)
+
+    def batch(g, device):
+        x = torch.randn(32, 3, 32, 32, generator=g).to(device).contiguous(memory_format=torch.channels_last)
+        return x, torch.randint(0, 10, (32,), generator=g).to(device)
+
+    def run(fused: bool):
+        (dispatch.enable if fused else dispatch.disable)("oss_fused_clip")
+        try:
+            stoke, step, device = build()
+            assert isinstance(stoke.optimizer, OSS) and ("fused_unscale_clip" in stoke.optimizer.__dict__)
+            g = torch.Generator(device="cpu").manual_seed(1)
+            losses = [float(step(*batch(g, device))) for _ in range(8)]
+            params = [p.detach().float().clone() for p in stoke.model_access.parameters()]
+        finally:
+            dispatch.enable("oss_fused_clip")
+        return losses, params
+
+    # (1) the norm itself, on gradients left in place by two accumulated micro-batches (bf16: no loss scale involved)
+    if fp16 == "bf16":
+        stoke, _step, device = build()
+        g = torch.Generator(device="cpu").manual_seed(2)
+        for _ in range(2):
+            x, y = batch(g, device)
+            stoke.backward(stoke.loss(stoke.model(x), y))
+        grads = [p.grad for p in stoke.model_access.parameters() if p.grad is not None]
+        want = torch.sqrt(sum((gr.float() ** 2).sum() for gr in grads))
+        before = [gr.clone() for gr in grads]
+        total = stoke.optimizer.clip_grad_norm(0.05, 2.0)
+        torch.testing.assert_close(total.float().reshape(()), want.reshape(()), rtol=1e-3, atol=1e-6)
+        inner = stoke.optimizer.optim
+        torch.testing.assert_close(inner._grad_mult.reshape(()), (0.05 / (want + 1e-6)).clamp(max=1.0).reshape(()),
+                                   rtol=1e-3, atol=1e-7)
+        assert all(torch.equal(a, b) for a, b in zip(before, grads))      # gradients are not rewritten
+        stoke.optimizer.step()                                            # consumes the multiplier without error
+        assert all(torch.isfinite(p).all() for p in stoke.model_access.parameters())
+
+    # (2) trajectories
+    l_new, p_new = run(True)
+    l_old, p_old = run(False)
+    assert all(l == l for l in l_new)
+    torch.testing.assert_close(torch.tensor(l_new), torch.tensor(l_old), rtol=3e-2, atol=3e-2)
+    num = sum(((a - b) ** 2).sum() for a, b in zip(p_new, p_old))
+    den = sum((b ** 2).sum() for b in p_old)
+    assert float((num / den).sqrt()) < 8e-2
