@@ -20,6 +20,10 @@ if _DETERMINISTIC:
     # goes back to the library) and the bias gradient of window attention (see ``deterministic()`` in ops.attention)
     _DISABLED.add("convstats")
     _DISABLED.add("conv_first")
+# measured on one GPU only so far (multi-rank NCCL runs without the peer engine keep the per-parameter clip loop unless
+# B200DP_ENABLE=oss_fused_clip_multirank asks for the fused norm + one all-reduce)
+if "oss_fused_clip_multirank" not in {s.strip() for s in os.environ.get("B200DP_ENABLE", "").split(",")}:
+    _DISABLED.add("oss_fused_clip_multirank")
 _HALF = (torch.float16, torch.bfloat16)
 
 

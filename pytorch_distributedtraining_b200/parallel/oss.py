@@ -330,6 +330,8 @@ class OSS(Optimizer):
         from ..ops import dispatch
         if "fused_unscale_clip" not in self.__dict__ or not dispatch.enabled("oss_fused_clip"):
             return False
+        if self.world_size > 1 and not dispatch.enabled("oss_fused_clip_multirank"):
+            return False
         grads = [p.grad for p in self.local_params() if p.grad is not None]
         return bool(grads) and all(g.is_cuda for g in grads)
 
